@@ -1,0 +1,234 @@
+// Forward geometry kernels: field-network input, per-node heading frames, per-edge local-frame
+// features, globalize + Euler update, and the caller-side step preparation.
+// Compiled with -fmad=false (see geom.cuh).
+#include "geom.cuh"
+
+namespace aether {
+
+namespace {
+
+// fin[n] = [x, vel, emb[(q+1) truncated]]   nn/state2state/aether.py:123-133
+template <int D>
+__global__ void field_input_kernel(int64_t Nn, const float* __restrict__ x, const float* __restrict__ vel,
+                                   const float* __restrict__ charges, const float* __restrict__ emb,
+                                   float* __restrict__ fin) {
+  constexpr int W = 2 * D + 16;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nn * W) return;
+  const int64_t n = i / W;
+  const int c = (int)(i % W);
+  float v;
+  if (c < D) v = x[n * D + c];
+  else if (c < 2 * D) v = vel[n * D + c - D];
+  else {
+    long long idx = (long long)(charges[n] + 1.0f);   // .long() truncates toward zero
+    idx = idx < 0 ? 0 : (idx > 2 ? 2 : idx);
+    v = emb[idx * 16 + (c - 2 * D)];
+  }
+  fin[i] = v;
+}
+
+// R[n], x0[n] = [0_D, R^T v, R^T f]   nn/state2state/aether.py:33-50
+template <int D>
+__host__ __device__ inline void node_frame_body(int64_t n, const float* vel, const float* f,
+                                  float* R, float* x0) {
+  float v[D], ff[D], Rn[D * D], a[D], b[D];
+#pragma unroll
+  for (int k = 0; k < D; ++k) { v[k] = vel[n * D + k]; ff[k] = f[n * D + k]; }
+  heading_frame<D>(v, Rn, nullptr, nullptr);
+  rot_t<D>(Rn, v, a);
+  rot_t<D>(Rn, ff, b);
+#pragma unroll
+  for (int k = 0; k < D * D; ++k) R[n * D * D + k] = Rn[k];
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    x0[n * 3 * D + k] = 0.0f;
+    x0[n * 3 * D + D + k] = a[k];
+    x0[n * 3 * D + 2 * D + k] = b[k];
+  }
+}
+
+// One thread per receiver-sorted edge.  Column order (aether.py:81-99,177):
+// [R_i^T(p_j-p_i) D | euler(R_i^T R_j)/pi O | |p_j-p_i| 1 | theta(,phi) D-1 | R_i^T v_j D | R_i^T f_j D |
+//  rel_feat[i] 3D | edge_attr_orig 2 | zero pad]
+template <int D>
+__host__ __device__ inline void edge_features_body(int64_t e, const int32_t* send, const int32_t* recv,
+                                     const int32_t* perm, const float* x,
+                                     const float* vel, const float* f,
+                                     const float* R, const float* x0,
+                                     const float* orig, float* feat, int ldf) {
+  constexpr int O = D * (D - 1) / 2;
+  constexpr int FE = 7 * D + O + 2;
+  constexpr int LD = (FE + 3) / 4 * 4;
+  const int64_t j = send[e], i = recv[e];
+  float Ri[D * D], Rj[D * D], d[D], vj[D], fj[D], out[LD];
+#pragma unroll
+  for (int k = 0; k < D * D; ++k) { Ri[k] = R[i * D * D + k]; Rj[k] = R[j * D * D + k]; }
+#pragma unroll
+  for (int k = 0; k < D; ++k) {
+    d[k] = x[j * D + k] - x[i * D + k];
+    vj[k] = vel[j * D + k];
+    fj[k] = f[j * D + k];
+  }
+  int c = 0;
+  float dl[D];
+  rot_t<D>(Ri, d, dl);
+#pragma unroll
+  for (int k = 0; k < D; ++k) out[c++] = dl[k];
+  // M = R_i^T R_j ; euler (geometry.py:76-101)
+  if (D == 2) {
+    const float m00 = Ri[0] * Rj[0] + Ri[2] * Rj[2];
+    const float m10 = Ri[1] * Rj[0] + Ri[3] * Rj[2];
+    out[c++] = atan2f(m10, m00) / AE_PI_F;
+  } else {
+    auto Mab = [&](int a, int b) { return Ri[0 * D + a] * Rj[0 * D + b] + Ri[1 * D + a] * Rj[1 * D + b] +
+                                          Ri[2 * D + a] * Rj[2 * D + b]; };
+    const float m00 = Mab(0, 0), m10 = Mab(1, 0), m20 = Mab(2, 0), m21 = Mab(2, 1), m22 = Mab(2, 2);
+    out[c++] = atan2f(m10, m00) / AE_PI_F;
+    out[c++] = asinf(-m20) / AE_PI_F;
+    out[c++] = atan2f(m21, m22) / AE_PI_F;
+  }
+  out[c++] = norm2<D>(d);
+  out[c++] = atan2f(dl[1], dl[0]);                       // symmetric theta (aether.py:73)
+  if (D == 3) {
+    const float rho = norm2<D>(dl);
+    out[c++] = acosf(clamp1(dl[2] / (rho + AE_EPS_PHI)));
+  }
+  float t[D];
+  rot_t<D>(Ri, vj, t);
+#pragma unroll
+  for (int k = 0; k < D; ++k) out[c++] = t[k];
+  rot_t<D>(Ri, fj, t);
+#pragma unroll
+  for (int k = 0; k < D; ++k) out[c++] = t[k];
+#pragma unroll
+  for (int k = 0; k < 3 * D; ++k) out[c++] = x0[i * 3 * D + k];
+  const int64_t pe = perm[e];
+  out[c++] = orig[pe * 2 + 0];
+  out[c++] = orig[pe * 2 + 1];
+#pragma unroll
+  for (int k = FE; k < LD; ++k) out[k] = 0.0f;
+  float4* dst = reinterpret_cast<float4*>(feat + (size_t)e * ldf);
+#pragma unroll
+  for (int k = 0; k < LD / 4; ++k) dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+}
+
+// out = x + R pred   (local_to_global.py:12-13, aether.py:185)
+template <int D>
+__host__ __device__ inline void globalize_body(int64_t n, const float* x, const float* R,
+                                 const float* pred, float* out) {
+  float Rn[D * D], p[D], g[D];
+#pragma unroll
+  for (int k = 0; k < D * D; ++k) Rn[k] = R[n * D * D + k];
+#pragma unroll
+  for (int k = 0; k < D; ++k) p[k] = pred[n * D + k];
+  rot<D>(Rn, p, g);
+#pragma unroll
+  for (int k = 0; k < D; ++k) out[n * D + k] = x[n * D + k] + g[k];
+}
+
+// experiments/lorentz/main.py:243-246: h = |v| ; edge_attr = [q_i q_j, |x_i - x_j|]
+template <int D>
+__global__ void caller_prep_kernel(int64_t E, int64_t Nn, const float* __restrict__ x, const float* __restrict__ vel,
+                                   const float* __restrict__ q, const int64_t* __restrict__ send,
+                                   const int64_t* __restrict__ recv, float* __restrict__ h, float* __restrict__ ea) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < E) {
+    const int64_t a = send[t], b = recv[t];
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+      const float dd = x[a * D + k] - x[b * D + k];
+      s = s + dd * dd;
+    }
+    ea[t * 2 + 0] = q[a] * q[b];
+    ea[t * 2 + 1] = sqrtf(s);
+  }
+  if (h && t < Nn) {
+    float s = 0.0f;
+#pragma unroll
+    for (int k = 0; k < D; ++k) s = s + vel[t * D + k] * vel[t * D + k];
+    h[t] = sqrtf(s);
+  }
+}
+
+template <int D>
+__global__ void node_frame_kernel(int64_t Nn, const float* __restrict__ vel, const float* __restrict__ f,
+                                  float* __restrict__ R, float* __restrict__ x0) {
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= Nn) return;
+  node_frame_body<D>(n, vel, f, R, x0);
+}
+
+template <int D>
+__global__ void edge_features_kernel(int64_t E, const int32_t* __restrict__ send, const int32_t* __restrict__ recv,
+                                     const int32_t* __restrict__ perm, const float* __restrict__ x,
+                                     const float* __restrict__ vel, const float* __restrict__ f,
+                                     const float* __restrict__ R, const float* __restrict__ x0,
+                                     const float* __restrict__ orig, float* __restrict__ feat, int ldf) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  edge_features_body<D>(e, send, recv, perm, x, vel, f, R, x0, orig, feat, ldf);
+}
+
+template <int D>
+__global__ void globalize_kernel(int64_t Nn, const float* __restrict__ x, const float* __restrict__ R,
+                                 const float* __restrict__ pred, float* __restrict__ out) {
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= Nn) return;
+  globalize_body<D>(n, x, R, pred, out);
+}
+
+inline unsigned nblk_g(int64_t n, int b) { return (unsigned)((n + b - 1) / b); }
+
+}  // namespace
+
+int launch_field_input(int D, int64_t Nn, const float* x, const float* vel, const float* charges, const float* emb,
+                       float* fin, cudaStream_t st) {
+  if (Nn <= 0) return 0;
+  const int64_t tot = Nn * (2 * D + 16);
+  if (D == 2) field_input_kernel<2><<<nblk_g(tot, 256), 256, 0, st>>>(Nn, x, vel, charges, emb, fin);
+  else field_input_kernel<3><<<nblk_g(tot, 256), 256, 0, st>>>(Nn, x, vel, charges, emb, fin);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_node_frame(int D, int64_t Nn, const float* vel, const float* f, float* R, float* x0, cudaStream_t st) {
+  if (Nn <= 0) return 0;
+  if (D == 2) node_frame_kernel<2><<<nblk_g(Nn, 128), 128, 0, st>>>(Nn, vel, f, R, x0);
+  else node_frame_kernel<3><<<nblk_g(Nn, 128), 128, 0, st>>>(Nn, vel, f, R, x0);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_edge_features(int D, int64_t E, const int32_t* send, const int32_t* recv, const int32_t* perm,
+                         const float* x, const float* vel, const float* f, const float* R, const float* x0,
+                         const float* orig, float* feat, int ldf, cudaStream_t st) {
+  if (E <= 0) return 0;
+  if (ldf != edge_feat_ld(D)) return AETHER_E_BADARG;
+  if (D == 2) edge_features_kernel<2><<<nblk_g(E, 128), 128, 0, st>>>(E, send, recv, perm, x, vel, f, R, x0, orig, feat, ldf);
+  else edge_features_kernel<3><<<nblk_g(E, 128), 128, 0, st>>>(E, send, recv, perm, x, vel, f, R, x0, orig, feat, ldf);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_globalize(int D, int64_t Nn, const float* x, const float* R, const float* pred, float* out,
+                     cudaStream_t st) {
+  if (Nn <= 0) return 0;
+  if (D == 2) globalize_kernel<2><<<nblk_g(Nn, 128), 128, 0, st>>>(Nn, x, R, pred, out);
+  else globalize_kernel<3><<<nblk_g(Nn, 128), 128, 0, st>>>(Nn, x, R, pred, out);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_caller_prep(int D, const float* x, const float* vel, const float* q, const int64_t* send,
+                       const int64_t* recv, int64_t E, int64_t Nn, float* h, float* ea, cudaStream_t st) {
+  const int64_t tot = E > Nn ? E : Nn;
+  if (tot <= 0) return 0;
+  if (D == 2) caller_prep_kernel<2><<<nblk_g(tot, 256), 256, 0, st>>>(E, Nn, x, vel, q, send, recv, h, ea);
+  else caller_prep_kernel<3><<<nblk_g(tot, 256), 256, 0, st>>>(E, Nn, x, vel, q, send, recv, h, ea);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace aether

@@ -1,0 +1,210 @@
+// Host-side orchestration of the Aether state-to-state step and its C ABI.
+//   forward : nn/state2state/aether.py:169-186
+//   backward: autograd of the same (experiments/lorentz/main.py:291)
+// Every launch goes to the caller's stream; nothing synchronises.
+#include <string.h>
+
+#include "common.cuh"
+#include "edge_mlp_tc.cuh"
+
+namespace aether {
+
+namespace {
+
+// parameter slots (state_dict order, see include/aether_b200.h)
+enum {
+  P_OUT0_W = 0, P_OUT0_B, P_OUT3_W, P_OUT3_B, P_OUT6_W, P_OUT6_B,
+  P_L1_M0_W = 6, P_L1_M0_B, P_L1_M2_W, P_L1_M2_B, P_L1_RES_W, P_L1_RES_B, P_L1_U0_W, P_L1_U0_B, P_L1_U2_W, P_L1_U2_B,
+  P_L2_BASE = 16,
+  P_F0_W = 40, P_F0_B, P_F2_W, P_F2_B, P_F4_W, P_F4_B, P_EMB = 46
+};
+struct LayerSlots { int m0w, m0b, m2w, m2b, u0w, u0b, u2w, u2b; };
+inline LayerSlots layer_slots(int l) {
+  if (l == 1) return {P_L1_M0_W, P_L1_M0_B, P_L1_M2_W, P_L1_M2_B, P_L1_U0_W, P_L1_U0_B, P_L1_U2_W, P_L1_U2_B};
+  const int b = P_L2_BASE + 8 * (l - 2);
+  return {b, b + 1, b + 2, b + 3, b + 4, b + 5, b + 6, b + 7};
+}
+
+struct Carver {
+  char* base; size_t off = 0;
+  explicit Carver(void* p) : base((char*)p) {}
+  float* f(size_t n) { float* r = (float*)(base + off); off += align_up(n * sizeof(float), 256); return r; }
+};
+
+// Everything the forward pass produces.  With AETHER_F_SAVE_FOR_BACKWARD each layer keeps its own
+// edge pre-activations; otherwise pre1 is shared and pre2 ping-pongs between two buffers.
+struct Workspace {
+  float *fin, *fz1, *fz2, *f, *R, *x0, *feat;
+  float *pre1[5], *pre2[5];
+  float *pspr, *y[5], *pre3[5], *xl[5];
+  float *o1, *o2, *pred;
+  size_t bytes;
+};
+
+Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
+  Workspace w;
+  Carver c(base);
+  const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
+  const bool save = flags & AETHER_F_SAVE_FOR_BACKWARD;
+  w.fin = c.f(Nn * (2 * D + 16));
+  w.fz1 = c.f(Nn * 32);
+  w.fz2 = c.f(Nn * 32);
+  w.f = c.f(Nn * D);
+  w.R = c.f(Nn * D * D);
+  w.x0 = c.f(Nn * 3 * D);
+  w.feat = c.f(E * edge_feat_ld(d.num_dims));
+  w.pre1[0] = w.pre2[0] = nullptr;
+  if (save) {
+    for (int l = 1; l <= 4; ++l) { w.pre1[l] = c.f(E * H); w.pre2[l] = c.f(E * H); }
+  } else {
+    float* p1 = c.f(E * H);
+    float* a = c.f(E * H);
+    float* b = c.f(E * H);
+    for (int l = 1; l <= 4; ++l) { w.pre1[l] = p1; w.pre2[l] = (l & 1) ? a : b; }
+  }
+  w.pspr = c.f(Nn * 2 * H);
+  w.y[0] = w.pre3[0] = nullptr;
+  w.xl[0] = w.x0;
+  for (int l = 1; l <= 4; ++l) { w.y[l] = c.f(Nn * H); w.pre3[l] = c.f(Nn * 2 * H); w.xl[l] = c.f(Nn * H); }
+  w.o1 = c.f(Nn * H);
+  w.o2 = c.f(Nn * H);
+  w.pred = c.f(Nn * D);
+  w.bytes = c.off;
+  return w;
+}
+
+struct Scratch {
+  float *gA, *gB, *gfeat, *gsend, *grecv;
+  float *gx, *gx2, *gy, *gpre3, *gpspr, *gx0, *go1, *go2, *gpred, *gRglob, *ssend, *srecv;
+  float *gf, *gfz1, *gfz2, *gfin, *gxin, *gvin;
+  float* partial; size_t partial_floats;
+  size_t bytes;
+};
+
+size_t partial_need(const AetherDims& d) {
+  const int64_t Nn = d.n_nodes, E = d.n_edges;
+  const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D);
+  size_t m = 0;
+  auto up = [&](size_t v) { if (v > m) m = v; };
+  up(gemm_tn_partial_floats(H, H, E));
+  up(gemm_tn_partial_floats(H, Fe, E));
+  up(gemm_tn_partial_floats(2 * H, H, Nn));
+  up(gemm_tn_partial_floats(H, 2 * H, Nn));
+  up(gemm_tn_partial_floats(H, H, Nn));
+  up(gemm_tn_partial_floats(H, 3 * D, Nn));
+  up(gemm_tn_partial_floats(D, H, Nn));
+  up(gemm_tn_partial_floats(32, 2 * D + 16, Nn));
+  up(gemm_tn_partial_floats(32, 32, Nn));
+  up(gemm_tn_partial_floats(D, 32, Nn));
+  up(colsum_partial_floats(E, H));
+  up(colsum_partial_floats(Nn, 2 * H));
+  return m + 64;
+}
+
+Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
+  Scratch s;
+  Carver c(base);
+  const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
+  s.gA = c.f(E * H);
+  s.gB = c.f(E * H);
+  s.gfeat = c.f(E * edge_feat_ld(d.num_dims));
+  s.gsend = c.f(E * geom_gs(d.num_dims));
+  s.grecv = c.f(E * geom_gr(d.num_dims));
+  s.gx = c.f(Nn * H); s.gx2 = c.f(Nn * H); s.gy = c.f(Nn * H);
+  s.gpre3 = c.f(Nn * 2 * H); s.gpspr = c.f(Nn * 2 * H);
+  s.gx0 = c.f(Nn * 3 * D); s.go1 = c.f(Nn * H); s.go2 = c.f(Nn * H);
+  s.gpred = c.f(Nn * D); s.gRglob = c.f(Nn * D * D);
+  s.ssend = c.f(Nn * geom_gs(d.num_dims)); s.srecv = c.f(Nn * geom_gr(d.num_dims));
+  s.gf = c.f(Nn * D); s.gfz1 = c.f(Nn * 32); s.gfz2 = c.f(Nn * 32); s.gfin = c.f(Nn * (2 * D + 16));
+  s.gxin = c.f(Nn * D); s.gvin = c.f(Nn * D);
+  s.partial_floats = partial_need(d);
+  s.partial = c.f(s.partial_floats);
+  s.bytes = c.off;
+  (void)flags;
+  return s;
+}
+
+bool dims_ok(const AetherDims* d) {
+  return d && (d->num_dims == 2 || d->num_dims == 3) && d->hidden >= 4 && d->hidden % 4 == 0 && d->n_nodes >= 0 &&
+         d->n_edges >= 0 && d->n_nodes < ((int64_t)1 << 31) && d->n_edges < ((int64_t)1 << 31);
+}
+
+// y = epi(tf(A) W^T + b)
+int linear(const float* A, int64_t lda, int64_t M, int K, const float* W, int64_t ldw, const float* b, int N, float* C,
+           int64_t ldc, int tf, const float* mask, const float* res, int64_t ldr, cudaStream_t st) {
+  GemmArgs g;
+  g.A = A; g.lda = lda; g.B = W; g.ldb = ldw; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
+  g.tf = tf; g.tf_mask = mask; g.bias = b; g.res = res; g.ldr = ldr;
+  return gemm_f32(GEMM_NT, g, st);
+}
+
+int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, const float* x, const float* vel,
+            const float* q, const float* orig, const float* dmask, float* out, const Workspace& w, uint32_t flags,
+            cudaStream_t st) {
+  const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D), ldf = edge_feat_ld(D);
+  const int64_t Nn = d.n_nodes, E = d.n_edges;
+  const bool bf16 = flags & AETHER_F_BF16_EDGE_MLP;
+  // neural field at the particles (aether.py:127-134)
+  AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
+  AE_CHECK(linear(w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
+                  nullptr, 0, st));
+  AE_CHECK(linear(w.fz1, 32, Nn, 32, P[P_F2_W], 32, P[P_F2_B], 32, w.fz2, 32, TF_SILU, nullptr, nullptr, 0, st));
+  AE_CHECK(linear(w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
+  // local frames and features (aether.py:33-100,177)
+  AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
+  AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
+  // four message-passing layers (locs.py:187-190, 227-243)
+  for (int l = 1; l <= 4; ++l) {
+    const LayerSlots s = layer_slots(l);
+    const float* xin = w.xl[l - 1];
+    if (l > 1) {
+      // node-factorised first Linear: [x_s | x_r | e] W^T = x_s Ws^T + x_r Wr^T + e We^T
+      AE_CHECK(linear(xin, H, Nn, H, P[s.m0w], 3 * H, nullptr, H, w.pspr, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+      AE_CHECK(linear(xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+    }
+    bool done = false;
+    if (bf16) {
+      int rc = edge_mlp_tc_forward(d, l, l == 1 ? w.feat : w.pre2[l - 1], l == 1 ? ldf : H, P[s.m0w], P[s.m0b],
+                                   P[s.m2w], P[s.m2b], w.pspr, G.send, G.recv, w.pre1[l], w.pre2[l], st);
+      if (rc == 0) done = true;
+      else if (rc != AETHER_E_UNSUPPORTED) return rc;
+    }
+    if (!done) {
+      GemmArgs g;
+      if (l == 1) {
+        g.A = w.feat; g.lda = ldf; g.K = Fe; g.B = P[s.m0w]; g.ldb = Fe; g.tf = TF_NONE;
+      } else {
+        g.A = w.pre2[l - 1]; g.lda = H; g.K = H; g.B = P[s.m0w] + 2 * H; g.ldb = 3 * H; g.tf = TF_SILU;
+        g.gat = w.pspr; g.ldg = 2 * H; g.idx_a = G.send; g.idx_b = G.recv; g.goff_b = H;
+      }
+      g.C = w.pre1[l]; g.ldc = H; g.M = E; g.N = H; g.bias = P[s.m0b];
+      AE_CHECK(gemm_f32(GEMM_NT, g, st));
+      AE_CHECK(linear(w.pre1[l], H, E, H, P[s.m2w], H, P[s.m2b], H, w.pre2[l], H, TF_SILU, nullptr, nullptr, 0, st));
+    }
+    // y = res(x) + mean_recv(silu(pre2))   (locs.py:236-240)
+    const float* base = xin;
+    if (l == 1) {
+      AE_CHECK(linear(w.x0, 3 * D, Nn, 3 * D, P[P_L1_RES_W], 3 * D, P[P_L1_RES_B], H, w.y[1], H, TF_NONE, nullptr,
+                      nullptr, 0, st));
+      base = w.y[1];
+    }
+    AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
+    // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
+    AE_CHECK(linear(w.y[l], H, Nn, H, P[s.u0w], H, P[s.u0b], 2 * H, w.pre3[l], 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+    AE_CHECK(linear(w.pre3[l], 2 * H, Nn, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, w.xl[l], H, TF_SILU, nullptr, w.y[l], H, st));
+  }
+  // out MLP (locs.py:160-168,193), globalize and Euler update (local_to_global.py:12-13, aether.py:185)
+  const float* m1 = dmask;
+  const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
+  AE_CHECK(linear(w.xl[4], H, Nn, H, P[P_OUT0_W], H, P[P_OUT0_B], H, w.o1, H, TF_NONE, nullptr, nullptr, 0, st));
+  AE_CHECK(linear(w.o1, H, Nn, H, P[P_OUT3_W], H, P[P_OUT3_B], H, w.o2, H, m1 ? TF_SILU_MASK : TF_SILU, m1, nullptr, 0, st));
+  AE_CHECK(linear(w.o2, H, Nn, H, P[P_OUT6_W], H, P[P_OUT6_B], D, w.pred, D, m2 ? TF_SILU_MASK : TF_SILU, m2, nullptr, 0, st));
+  AE_CHECK(launch_globalize(D, Nn, x, w.R, w.pred, out, st));
+  return 0;
+}
+
+}  // namespace
+}  // namespace aether
+
+#include "step_backward.inl"
+#include "step_abi.inl"

@@ -1,0 +1,107 @@
+// extern "C" surface of the step (included by step.cu).  See include/aether_b200.h.
+using namespace aether;
+
+extern "C" int aether_abi_version(void) { return AETHER_B200_ABI_VERSION; }
+
+extern "C" const char* aether_error_string(int code) {
+  switch (code) {
+    case 0: return "success";
+    case AETHER_E_BADARG: return "aether_b200: bad argument";
+    case AETHER_E_WORKSPACE: return "aether_b200: workspace or scratch buffer too small";
+    case AETHER_E_UNSUPPORTED: return "aether_b200: configuration not supported by this kernel";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "aether_b200: unknown error";
+  }
+}
+
+extern "C" size_t aether_workspace_bytes(const AetherDims* dims, uint32_t flags) {
+  if (!dims_ok(dims)) return 0;
+  return carve(*dims, flags, nullptr).bytes + 256;
+}
+
+extern "C" size_t aether_backward_scratch_bytes(const AetherDims* dims, uint32_t flags) {
+  if (!dims_ok(dims)) return 0;
+  return carve_scratch(*dims, flags, nullptr).bytes + 256;
+}
+
+extern "C" int aether_caller_prep(const float* x, const float* vel, const float* charges, int32_t num_dims,
+                                  const int64_t* send, const int64_t* recv, int64_t n_edges, int64_t n_nodes, float* h,
+                                  float* edge_attr_orig, void* stream) {
+  if (num_dims != 2 && num_dims != 3) return AETHER_E_BADARG;
+  return launch_caller_prep(num_dims, x, vel, charges, send, recv, n_edges, n_nodes, h, edge_attr_orig,
+                            (cudaStream_t)stream);
+}
+
+extern "C" int aether_step_forward(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                                   const float* x, const float* vel, const float* charges, const float* edge_attr_orig,
+                                   const float* dropout_mask, float* out, void* workspace, size_t workspace_bytes,
+                                   uint32_t flags, void* stream) {
+  if (!dims_ok(dims) || !params || !graph || !out) return AETHER_E_BADARG;
+  if (!workspace || ((uintptr_t)workspace & 255) || workspace_bytes < carve(*dims, flags, nullptr).bytes)
+    return AETHER_E_WORKSPACE;
+  const Workspace w = carve(*dims, flags, workspace);
+  return forward(*dims, params, *graph, x, vel, charges, edge_attr_orig, dropout_mask, out, w, flags,
+                 (cudaStream_t)stream);
+}
+
+extern "C" int aether_step_backward(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                                    const float* x, const float* vel, const float* charges,
+                                    const float* edge_attr_orig, const float* dropout_mask, const float* grad_out,
+                                    float* const* param_grads, float* grad_x, float* grad_vel, void* workspace,
+                                    size_t workspace_bytes, void* scratch, size_t scratch_bytes, uint32_t flags,
+                                    void* stream) {
+  (void)edge_attr_orig;
+  if (!dims_ok(dims) || !params || !graph || !grad_out || !param_grads) return AETHER_E_BADARG;
+  if (!(flags & AETHER_F_SAVE_FOR_BACKWARD)) return AETHER_E_BADARG;
+  if (!workspace || ((uintptr_t)workspace & 255) || workspace_bytes < carve(*dims, flags, nullptr).bytes)
+    return AETHER_E_WORKSPACE;
+  if (!scratch || ((uintptr_t)scratch & 255) || scratch_bytes < carve_scratch(*dims, flags, nullptr).bytes)
+    return AETHER_E_WORKSPACE;
+  const Workspace w = carve(*dims, flags, workspace);
+  const Scratch s = carve_scratch(*dims, flags, scratch);
+  return backward(*dims, params, *graph, x, vel, charges, dropout_mask, grad_out, param_grads, grad_x, grad_vel, w, s,
+                  flags, (cudaStream_t)stream);
+}
+
+namespace aether {
+namespace {
+__global__ void silu_copy_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n, int apply) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = apply ? silu_f(src[i]) : src[i];
+}
+__global__ void strided_copy_kernel(const float* __restrict__ src, int64_t lds, float* __restrict__ dst, int64_t rows,
+                                    int cols) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (size_t)rows * cols) dst[i] = src[(i / cols) * lds + i % cols];
+}
+}  // namespace
+}  // namespace aether
+
+extern "C" int64_t aether_debug_stage(const AetherDims* dims, const void* workspace, uint32_t flags,
+                                      const char* stage, float* dst, int64_t dst_floats, void* stream) {
+  if (!dims_ok(dims) || !workspace || !stage || !dst) return AETHER_E_BADARG;
+  const Workspace w = carve(*dims, flags, const_cast<void*>(workspace));
+  const int64_t Nn = dims->n_nodes, E = dims->n_edges;
+  const int D = dims->num_dims, H = dims->hidden;
+  cudaStream_t st = (cudaStream_t)stream;
+  const float* src = nullptr;
+  int64_t n = 0;
+  int silu = 0;
+  if (!strcmp(stage, "field")) { src = w.f; n = Nn * D; }
+  else if (!strcmp(stage, "rel_feat")) { src = w.x0; n = Nn * 3 * D; }
+  else if (!strcmp(stage, "R")) { src = w.R; n = Nn * D * D; }
+  else if (!strcmp(stage, "pred")) { src = w.pred; n = Nn * D; }
+  else if (!strcmp(stage, "edge_attr")) {
+    const int Fe = num_edge_feat(D);
+    n = E * Fe;
+    if (dst_floats < n) return AETHER_E_WORKSPACE;
+    if (n) strided_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w.feat, edge_feat_ld(D), dst, E, Fe);
+    return cudaPeekAtLastError() == cudaSuccess ? n : AETHER_E_BADARG;
+  } else if ((stage[0] == 'e' || stage[0] == 'x') && stage[1] >= '1' && stage[1] <= '4' && !stage[2]) {
+    const int l = stage[1] - '0';
+    if (stage[0] == 'e') { src = w.pre2[l]; n = E * H; silu = 1; }
+    else { src = w.xl[l]; n = Nn * H; }
+  } else return AETHER_E_BADARG;
+  if (dst_floats < n) return AETHER_E_WORKSPACE;
+  if (n) silu_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, dst, (size_t)n, silu);
+  return cudaPeekAtLastError() == cudaSuccess ? n : AETHER_E_BADARG;
+}

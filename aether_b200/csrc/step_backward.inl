@@ -1,0 +1,119 @@
+// Backward of the step (included by step.cu).  Reverse of forward(): every Linear contributes a
+// data gradient (GEMM_NN, fused silu' / mask epilogue), a weight gradient (GEMM_TN, deterministic
+// split-K) and a bias gradient (column sums); the receiver mean becomes a broadcast over the CSR
+// segment; the two gathers of the node-factorised first Linear become segment sums over the
+// receiver- and sender-grouped views -- no atomics anywhere.
+namespace aether {
+namespace {
+
+struct Bwd {
+  const AetherDims& d; const float* const* P; float* const* G; const Scratch& s; cudaStream_t st;
+
+  // dW[N_out, K_in] = gy^T act(a)   ;   db = colsum(gy)
+  int wgrad(const float* gy, int64_t ldgy, int64_t rows, int n_out, const float* a, int64_t lda, int k_in, int tf,
+            const float* mask, float* dW, int64_t lddw, float* db) const {
+    GemmArgs g;
+    g.A = gy; g.lda = ldgy; g.B = a; g.ldb = lda; g.C = dW; g.ldc = lddw; g.M = n_out; g.N = k_in; g.K = rows;
+    g.tf = tf; g.tf_mask = mask; g.partial = s.partial; g.partial_floats = s.partial_floats;
+    AE_CHECK(gemm_f32(GEMM_TN, g, st));
+    if (db) AE_CHECK(colsum_f32(gy, ldgy, rows, n_out, db, s.partial, s.partial_floats, st));
+    return 0;
+  }
+  // gx[rows, K_in] = epi(gy W)    W is [N_out, K_in] with leading dimension ldw
+  int dgrad(const float* gy, int64_t ldgy, int64_t rows, int n_out, const float* W, int64_t ldw, int k_in, float* gx,
+            int64_t ldgx, const float* dsilu_src, const float* mask, const float* res, int accumulate) const {
+    GemmArgs g;
+    g.A = gy; g.lda = ldgy; g.B = W; g.ldb = ldw; g.C = gx; g.ldc = ldgx; g.M = rows; g.N = k_in; g.K = n_out;
+    g.dsilu = dsilu_src; g.ldd = ldgx; g.emask = mask; g.ldm = ldgx; g.res = res; g.ldr = ldgx;
+    g.accumulate = accumulate;
+    return gemm_f32(GEMM_NN, g, st);
+  }
+};
+
+int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, const float* x, const float* vel,
+             const float* q, const float* dmask, const float* gout, float* const* G, float* gx_out, float* gvel_out,
+             const Workspace& w, const Scratch& s, uint32_t flags, cudaStream_t st) {
+  const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D), ldf = edge_feat_ld(D);
+  const int64_t Nn = d.n_nodes, E = d.n_edges;
+  const Bwd b{d, P, G, s, st};
+  const float* m1 = dmask;
+  const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
+  (void)flags;
+
+  // out = x + R pred
+  AE_CHECK(launch_globalize_bwd(D, Nn, w.R, w.pred, gout, s.gpred, s.gRglob, st));
+  // out MLP
+  AE_CHECK(b.wgrad(s.gpred, D, Nn, D, w.o2, H, H, m2 ? TF_SILU_MASK : TF_SILU, m2, G[P_OUT6_W], H, G[P_OUT6_B]));
+  AE_CHECK(b.dgrad(s.gpred, D, Nn, D, P[P_OUT6_W], H, H, s.go2, H, w.o2, m2, nullptr, 0));
+  AE_CHECK(b.wgrad(s.go2, H, Nn, H, w.o1, H, H, m1 ? TF_SILU_MASK : TF_SILU, m1, G[P_OUT3_W], H, G[P_OUT3_B]));
+  AE_CHECK(b.dgrad(s.go2, H, Nn, H, P[P_OUT3_W], H, H, s.go1, H, w.o1, m1, nullptr, 0));
+  AE_CHECK(b.wgrad(s.go1, H, Nn, H, w.xl[4], H, H, TF_NONE, nullptr, G[P_OUT0_W], H, G[P_OUT0_B]));
+  float* gx = s.gx;      // gradient w.r.t. the current layer's output node state
+  float* gxn = s.gx2;    // ... and the next one down
+  AE_CHECK(b.dgrad(s.go1, H, Nn, H, P[P_OUT0_W], H, H, gx, H, nullptr, nullptr, nullptr, 0));
+  const float* ge = nullptr;   // gradient w.r.t. e_l from layer l+1 (none for the last layer)
+
+  for (int l = 4; l >= 1; --l) {
+    const LayerSlots sl = layer_slots(l);
+    // x_l = y + W4 silu(pre3) + b4 ; pre3 = W3 y + b3
+    AE_CHECK(b.wgrad(gx, H, Nn, H, w.pre3[l], 2 * H, 2 * H, TF_SILU, nullptr, G[sl.u2w], 2 * H, G[sl.u2b]));
+    AE_CHECK(b.dgrad(gx, H, Nn, H, P[sl.u2w], 2 * H, 2 * H, s.gpre3, 2 * H, w.pre3[l], nullptr, nullptr, 0));
+    AE_CHECK(b.wgrad(s.gpre3, 2 * H, Nn, 2 * H, w.y[l], H, H, TF_NONE, nullptr, G[sl.u0w], H, G[sl.u0b]));
+    AE_CHECK(b.dgrad(s.gpre3, 2 * H, Nn, 2 * H, P[sl.u0w], H, H, s.gy, H, nullptr, nullptr, gx, 0));
+    // y = base + mean_recv(silu(pre2)) : broadcast gy / deg over the segment, add grad from layer l+1
+    float* g2 = s.gA;
+    AE_CHECK(launch_edge_dpre2(E, H, Gr.recv, Gr.rowptr, ge, s.gy, w.pre2[l], g2, st));
+    // pre2 = W2 silu(pre1) + b2
+    AE_CHECK(b.wgrad(g2, H, E, H, w.pre1[l], H, H, TF_SILU, nullptr, G[sl.m2w], H, G[sl.m2b]));
+    float* g1 = s.gB;
+    AE_CHECK(b.dgrad(g2, H, E, H, P[sl.m2w], H, H, g1, H, w.pre1[l], nullptr, nullptr, 0));
+    AE_CHECK(colsum_f32(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
+    if (l > 1) {
+      // pre1 = Ps[send] + Pr[recv] + We silu(pre2_{l-1}) + b1
+      AE_CHECK(b.wgrad(g1, H, E, H, w.pre2[l - 1], H, H, TF_SILU, nullptr, G[sl.m0w] + 2 * H, 3 * H, nullptr));
+      AE_CHECK(b.dgrad(g1, H, E, H, P[sl.m0w] + 2 * H, 3 * H, H, s.gA, H, nullptr, nullptr, nullptr, 0));
+      ge = s.gA;
+      AE_CHECK(launch_segsum(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, 0, st));
+      AE_CHECK(launch_segsum(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, 0, st));
+      const float* xin = w.xl[l - 1];
+      AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
+      AE_CHECK(b.wgrad(s.gpspr + H, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w] + H, 3 * H, nullptr));
+      AE_CHECK(b.dgrad(s.gpspr, 2 * H, Nn, H, P[sl.m0w], 3 * H, H, gxn, H, nullptr, nullptr, s.gy, 0));
+      AE_CHECK(b.dgrad(s.gpspr + H, 2 * H, Nn, H, P[sl.m0w] + H, 3 * H, H, gxn, H, nullptr, nullptr, nullptr, 1));
+      float* t = gx; gx = gxn; gxn = t;
+    } else {
+      // pre1 = W1 feat + b1 ; y1 = Wres x0 + bres + agg
+      AE_CHECK(b.wgrad(g1, H, E, H, w.feat, ldf, Fe, TF_NONE, nullptr, G[sl.m0w], Fe, nullptr));
+      {
+        GemmArgs g;
+        g.A = g1; g.lda = H; g.B = P[sl.m0w]; g.ldb = Fe; g.C = s.gfeat; g.ldc = ldf; g.M = E; g.N = Fe; g.K = H;
+        AE_CHECK(gemm_f32(GEMM_NN, g, st));
+      }
+      AE_CHECK(b.wgrad(s.gy, H, Nn, H, w.x0, 3 * D, 3 * D, TF_NONE, nullptr, G[P_L1_RES_W], 3 * D, G[P_L1_RES_B]));
+      AE_CHECK(b.dgrad(s.gy, H, Nn, H, P[P_L1_RES_W], 3 * D, 3 * D, s.gx0, 3 * D, nullptr, nullptr, nullptr, 0));
+    }
+  }
+
+  // localizer: per-edge partials, then segment sums by receiver (contiguous) and by sender (sperm)
+  const int GS = geom_gs(D), GR = geom_gr(D);
+  AE_CHECK(launch_edge_features_bwd(D, E, Gr.send, Gr.recv, x, vel, w.f, w.R, s.gfeat, ldf, s.gsend, s.grecv, st));
+  AE_CHECK(launch_segsum(Nn, GS, Gr.colptr, Gr.sperm, s.gsend, GS, s.ssend, GS, 0, st));
+  AE_CHECK(launch_segsum(Nn, GR, Gr.rowptr, nullptr, s.grecv, GR, s.srecv, GR, 0, st));
+  float* gxin = gx_out ? gx_out : s.gxin;
+  float* gvin = gvel_out ? gvel_out : s.gvin;
+  AE_CHECK(launch_node_frame_bwd(D, Nn, vel, w.f, w.R, s.gx0, s.ssend, s.srecv, s.gRglob, gout, s.gf, gxin, gvin, st));
+  // field network (aether.py:113-119,127-134)
+  AE_CHECK(b.wgrad(s.gf, D, Nn, D, w.fz2, 32, 32, TF_SILU, nullptr, G[P_F4_W], 32, G[P_F4_B]));
+  AE_CHECK(b.dgrad(s.gf, D, Nn, D, P[P_F4_W], 32, 32, s.gfz2, 32, w.fz2, nullptr, nullptr, 0));
+  AE_CHECK(b.wgrad(s.gfz2, 32, Nn, 32, w.fz1, 32, 32, TF_SILU, nullptr, G[P_F2_W], 32, G[P_F2_B]));
+  AE_CHECK(b.dgrad(s.gfz2, 32, Nn, 32, P[P_F2_W], 32, 32, s.gfz1, 32, w.fz1, nullptr, nullptr, 0));
+  const int FI = 2 * D + 16;
+  AE_CHECK(b.wgrad(s.gfz1, 32, Nn, 32, w.fin, FI, FI, TF_NONE, nullptr, G[P_F0_W], FI, G[P_F0_B]));
+  AE_CHECK(b.dgrad(s.gfz1, 32, Nn, 32, P[P_F0_W], FI, FI, s.gfin, FI, nullptr, nullptr, nullptr, 0));
+  AE_CHECK(launch_embedding_bwd(D, Nn, q, s.gfin, G[P_EMB], st));
+  if (gx_out || gvel_out) AE_CHECK(launch_add_field_input_grads(D, Nn, s.gfin, gx_out, gvel_out, st));
+  return 0;
+}
+
+}  // namespace
+}  // namespace aether

@@ -1,0 +1,143 @@
+/*
+ * aether_b200 -- C ABI of the B200 (sm_100a) implementation of Aether's
+ * state-to-state step.
+ *
+ * The reference is pure Python/PyTorch and has no FFI of its own; the entry
+ * points below are what a binding for the hot path would bind, one per stage
+ * the reference runs from Python.  Paths are relative to the reference repo
+ * (mkofinas/aether):
+ *
+ *   aether_graph_prepare      replaces the per-batch edge handling of
+ *                             experiments/lorentz/main.py:211-212 plus the index
+ *                             work inside torch_scatter.scatter at
+ *                             nn/state2state/locs/locs.py:236-238 (the reference
+ *                             scatters unsorted; this library sorts by receiver
+ *                             once and reuses the CSR in every layer).
+ *   aether_fc_edges           experiments/lorentz/dataset4newton.py:54-61,84-94
+ *   aether_knn_edges          experiments/ind/single_ind_data.py:186-217
+ *   aether_caller_prep        experiments/lorentz/main.py:243-246
+ *   aether_step_forward       Aether.forward, nn/state2state/aether.py:169-186
+ *                             (FieldNetwork :127-134, AetherLocalizer :33-100,
+ *                             GNN locs.py:183-194, GNNLayer locs.py:227-243,
+ *                             Globalizer nn/utils/local_to_global.py:12-13)
+ *   aether_step_backward      loss.backward() through that forward,
+ *                             experiments/lorentz/main.py:291
+ *   aether_rollout_step       one harness-level rollout step:
+ *                             caller prep + forward + v' = x' - x
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - the caller owns all memory, including the workspace; sizes come from
+ *     aether_workspace_bytes / aether_graph_scratch_bytes;
+ *   - all work is enqueued on the stream passed in (a cudaStream_t cast to
+ *     void*); no call synchronises, reads device data on the host, or keeps
+ *     global state, so every call can be captured in a CUDA graph;
+ *   - return value: 0 on success, otherwise a cudaError_t value or one of the
+ *     negative AETHER_E_* codes; nothing throws or aborts.
+ *   - floating point is fp32 at this boundary; indices are int64 on input (as
+ *     the reference passes them) and int32 inside the prepared graph.
+ */
+#ifndef AETHER_B200_H_
+#define AETHER_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AETHER_B200_ABI_VERSION 1
+
+/* error codes (negative; positive values are cudaError_t) */
+#define AETHER_E_BADARG   (-1)
+#define AETHER_E_WORKSPACE (-2)
+#define AETHER_E_UNSUPPORTED (-3)
+
+/* flags for aether_step_forward / aether_workspace_bytes */
+#define AETHER_F_SAVE_FOR_BACKWARD 1u   /* keep activations for aether_step_backward  */
+#define AETHER_F_BF16_EDGE_MLP     2u   /* edge-MLP GEMMs on tcgen05 in bf16 (fp32 accumulate) */
+#define AETHER_F_INPUT_GRADS       4u   /* backward also returns d/dx and d/dvel      */
+
+/* Number of parameter tensors of Aether, in state_dict order
+ * (nn/state2state/aether.py:143-159, locs.py:160-181):
+ *   0..5    gnn.out_mlp.{0,3,6}.{weight,bias}
+ *   6..15   gnn.layer_1.{message_fn.0, message_fn.2, res, update_fn.0, update_fn.2}.{weight,bias}
+ *   16..23  gnn.layer_2.{message_fn.0, message_fn.2, update_fn.0, update_fn.2}.{weight,bias}
+ *   24..31  gnn.layer_3.(same)        32..39  gnn.layer_4.(same)
+ *   40..45  field_net.net.{0,2,4}.{weight,bias}
+ *   46      field_net.class_embedding.weight
+ */
+#define AETHER_NUM_PARAMS 47
+
+typedef struct AetherDims {
+  int32_t num_dims;     /* D: 2 or 3                                   */
+  int32_t hidden;       /* H: multiple of 4                            */
+  int64_t n_nodes;      /* Nn: nodes flattened over the batch          */
+  int64_t n_edges;      /* E                                           */
+} AetherDims;
+
+/* Receiver-sorted view of an edge list, all arrays caller-allocated:
+ *   perm[E]      sorted position -> original edge id (stable by receiver)
+ *   rowptr[Nn+1] segment offsets of receivers in the sorted order
+ *   send[E], recv[E]   endpoints in sorted order
+ *   sperm[E]     positions of the sorted list grouped by sender (stable)
+ *   colptr[Nn+1] segment offsets of senders in sperm
+ */
+typedef struct AetherGraph {
+  int32_t* perm;
+  int32_t* rowptr;
+  int32_t* send;
+  int32_t* recv;
+  int32_t* sperm;
+  int32_t* colptr;
+} AetherGraph;
+
+int aether_abi_version(void);
+const char* aether_error_string(int code);
+
+/* ---- integer path -------------------------------------------------------- */
+size_t aether_graph_scratch_bytes(int64_t n_nodes, int64_t n_edges);
+int aether_graph_prepare(const int64_t* send, const int64_t* recv, int64_t n_edges, int64_t n_nodes,
+                         AetherGraph* graph, int32_t* status /* device, 1 word: !=0 on out-of-range index */,
+                         void* scratch, size_t scratch_bytes, void* stream);
+int aether_fc_edges(int64_t nodes_per_graph, int64_t n_graphs, int64_t* send, int64_t* recv, void* stream);
+/* Ragged batch of scenes; scene s owns nodes [node_off[s], node_off[s+1]).  Writes
+ * edge_off[s] + i*kk + j for query agent i of scene s (kk = min(k, n_s - 1)).  edge_off is
+ * computed by the caller (it depends only on the scene sizes). */
+int aether_knn_edges(const float* pos, int32_t pos_stride, const int32_t* node_off, const int64_t* edge_off,
+                     int32_t n_scenes, int32_t k, int64_t* send, int64_t* recv, void* stream);
+int aether_caller_prep(const float* x, const float* vel, const float* charges, int32_t num_dims,
+                       const int64_t* send, const int64_t* recv, int64_t n_edges, int64_t n_nodes,
+                       float* h /* [Nn] or NULL */, float* edge_attr_orig /* [E,2] */, void* stream);
+
+/* ---- the step ------------------------------------------------------------ */
+size_t aether_workspace_bytes(const AetherDims* dims, uint32_t flags);
+size_t aether_backward_scratch_bytes(const AetherDims* dims, uint32_t flags);
+
+int aether_step_forward(const AetherDims* dims, const float* const* params /* [47] device ptrs, host array */,
+                        const AetherGraph* graph, const float* x, const float* vel, const float* charges,
+                        const float* edge_attr_orig /* [E,2], ORIGINAL edge order */,
+                        const float* dropout_mask /* [2,Nn,H] scale-or-zero, or NULL */,
+                        float* out /* [Nn,D] */, void* workspace, size_t workspace_bytes, uint32_t flags,
+                        void* stream);
+
+int aether_step_backward(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                         const float* x, const float* vel, const float* charges, const float* edge_attr_orig,
+                         const float* dropout_mask, const float* grad_out /* [Nn,D] */,
+                         float* const* param_grads /* [47] device ptrs, overwritten */,
+                         float* grad_x /* [Nn,D] or NULL */, float* grad_vel /* [Nn,D] or NULL */,
+                         void* workspace /* the one forward filled */, size_t workspace_bytes,
+                         void* scratch, size_t scratch_bytes, uint32_t flags, void* stream);
+
+/* Debug/test hook: copy a named stage out of a forward workspace (fp32, device to device).
+ * Stages: "field" [Nn,D], "rel_feat" [Nn,3D], "R" [Nn,D,D], "edge_attr" [E,Fe] (sorted order),
+ * "e1".."e4" [E,H] (sorted order), "x1".."x4" [Nn,H], "pred" [Nn,D].  Returns the number of
+ * floats written, or a negative error. */
+int64_t aether_debug_stage(const AetherDims* dims, const void* workspace, uint32_t flags, const char* stage,
+                           float* dst, int64_t dst_floats, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AETHER_B200_H_ */
