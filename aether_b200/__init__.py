@@ -1,0 +1,14 @@
+"""aether_b200 -- B200 (sm_100a) implementation of Aether's state-to-state step.
+
+Public surface (mirrors the reference's nn/state2state/aether.py):
+    Aether              drop-in nn.Module (same constructor / forward signature / state_dict)
+    PreparedGraph       receiver-sorted CSR of an edge list (device)
+    fc_edges, knn_edges, KnnPlan, caller_prep   the reference's edge builders / caller prep on device
+    Rollout, rollout    multi-step rollouts (optionally CUDA-graph captured)
+Everything computes through aether_b200/lib/libaether_b200.so; there is no CPU or ATen fallback.
+"""
+from .aether import Aether, AetherLocalizer, FieldNetwork, Globalizer, GNN, GNNLayer  # noqa: F401
+from .graph import KnnPlan, PreparedGraph, caller_prep, fc_edges, knn_edges  # noqa: F401
+from .rollout import Rollout, rollout  # noqa: F401
+
+__all__ = ["Aether", "PreparedGraph", "KnnPlan", "fc_edges", "knn_edges", "caller_prep", "Rollout", "rollout"]

@@ -32,6 +32,7 @@ SOURCES = [
     ("graph.cu", []),
     ("step.cu", []),
     ("edge_mlp_tc.cu", []),
+    ("prof.cu", []),
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),
 ]

@@ -14,11 +14,23 @@
 
 #define AE_LAUNCH_CHECK()                           \
   do {                                              \
+    ++::aether::g_launch_count;                     \
     cudaError_t _e = cudaPeekAtLastError();         \
     if (_e != cudaSuccess) return (int)_e;          \
   } while (0)
 
 namespace aether {
+
+// prof.cu: number of kernels launched by this library (every launch site runs AE_LAUNCH_CHECK)
+extern unsigned long long g_launch_count;
+// Optional CUDA-event timing of a group of launches; a no-op unless aether_profile_enable(1).
+enum ProfCat { PROF_EDGE_MLP_FWD = 0, PROF_EDGE_BWD_DATA = 1, PROF_EDGE_WGRAD = 2, PROF_SEGMENT = 3,
+               PROF_EDGE_FEAT = 4, PROF_NODE = 5, PROF_NUM = 6 };
+struct ProfScope {
+  ProfScope(int cat, cudaStream_t st);
+  ~ProfScope();
+  cudaStream_t st_; long idx_;
+};
 
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

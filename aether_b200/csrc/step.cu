@@ -152,7 +152,10 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   AE_CHECK(linear(w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
   // local frames and features (aether.py:33-100,177)
   AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
-  AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
+  {
+    ProfScope ps(PROF_EDGE_FEAT, st);
+    AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
+  }
   // four message-passing layers (locs.py:187-190, 227-243)
   for (int l = 1; l <= 4; ++l) {
     const LayerSlots s = layer_slots(l);
@@ -163,6 +166,8 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       AE_CHECK(linear(xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
     }
     bool done = false;
+    {
+    ProfScope ps(PROF_EDGE_MLP_FWD, st);
     if (bf16) {
       int rc = edge_mlp_tc_forward(d, l, l == 1 ? w.feat : w.pre2[l - 1], l == 1 ? ldf : H, P[s.m0w], P[s.m0b],
                                    P[s.m2w], P[s.m2b], w.pspr, G.send, G.recv, w.pre1[l], w.pre2[l], st);
@@ -181,6 +186,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       AE_CHECK(gemm_f32(GEMM_NT, g, st));
       AE_CHECK(linear(w.pre1[l], H, E, H, P[s.m2w], H, P[s.m2b], H, w.pre2[l], H, TF_SILU, nullptr, nullptr, 0, st));
     }
+    }
     // y = res(x) + mean_recv(silu(pre2))   (locs.py:236-240)
     const float* base = xin;
     if (l == 1) {
@@ -188,7 +194,10 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
                       nullptr, 0, st));
       base = w.y[1];
     }
-    AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
+    {
+      ProfScope ps(PROF_SEGMENT, st);
+      AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
+    }
     // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
     AE_CHECK(linear(w.y[l], H, Nn, H, P[s.u0w], H, P[s.u0b], 2 * H, w.pre3[l], 2 * H, TF_NONE, nullptr, nullptr, 0, st));
     AE_CHECK(linear(w.pre3[l], 2 * H, Nn, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, w.xl[l], H, TF_SILU, nullptr, w.y[l], H, st));

@@ -73,8 +73,29 @@ __global__ void strided_copy_kernel(const float* __restrict__ src, int64_t lds, 
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < (size_t)rows * cols) dst[i] = src[(i / cols) * lds + i % cols];
 }
+__global__ void sub_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ c, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) c[i] = a[i] - b[i];
+}
 }  // namespace
 }  // namespace aether
+
+extern "C" int aether_rollout_step(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                                   const int64_t* send64, const int64_t* recv64, const float* x, const float* vel,
+                                   const float* charges, float* x_next, float* vel_next, float* edge_attr_scratch,
+                                   void* workspace, size_t workspace_bytes, uint32_t flags, void* stream) {
+  if (!dims_ok(dims) || !x_next || !vel_next || x_next == x || vel_next == vel) return AETHER_E_BADARG;
+  if (dims->n_edges > 0 && (!send64 || !recv64 || !edge_attr_scratch)) return AETHER_E_BADARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  AE_CHECK(launch_caller_prep(dims->num_dims, x, vel, charges, send64, recv64, dims->n_edges, dims->n_nodes, nullptr,
+                              edge_attr_scratch, st));
+  AE_CHECK(aether_step_forward(dims, params, graph, x, vel, charges, edge_attr_scratch, nullptr, x_next, workspace,
+                               workspace_bytes, flags & ~AETHER_F_SAVE_FOR_BACKWARD, stream));
+  const size_t n = (size_t)dims->n_nodes * dims->num_dims;
+  if (n) sub_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x_next, x, vel_next, n);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int64_t aether_debug_stage(const AetherDims* dims, const void* workspace, uint32_t flags,
                                       const char* stage, float* dst, int64_t dst_floats, void* stream) {

@@ -62,19 +62,34 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
     AE_CHECK(b.dgrad(s.gpre3, 2 * H, Nn, 2 * H, P[sl.u0w], H, H, s.gy, H, nullptr, nullptr, gx, 0));
     // y = base + mean_recv(silu(pre2)) : broadcast gy / deg over the segment, add grad from layer l+1
     float* g2 = s.gA;
-    AE_CHECK(launch_edge_dpre2(E, H, Gr.recv, Gr.rowptr, ge, s.gy, w.pre2[l], g2, st));
-    // pre2 = W2 silu(pre1) + b2
-    AE_CHECK(b.wgrad(g2, H, E, H, w.pre1[l], H, H, TF_SILU, nullptr, G[sl.m2w], H, G[sl.m2b]));
     float* g1 = s.gB;
-    AE_CHECK(b.dgrad(g2, H, E, H, P[sl.m2w], H, H, g1, H, w.pre1[l], nullptr, nullptr, 0));
-    AE_CHECK(colsum_f32(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
+    {
+      ProfScope ps(PROF_EDGE_BWD_DATA, st);
+      AE_CHECK(launch_edge_dpre2(E, H, Gr.recv, Gr.rowptr, ge, s.gy, w.pre2[l], g2, st));
+      // pre2 = W2 silu(pre1) + b2
+      AE_CHECK(b.dgrad(g2, H, E, H, P[sl.m2w], H, H, g1, H, w.pre1[l], nullptr, nullptr, 0));
+    }
+    {
+      ProfScope ps(PROF_EDGE_WGRAD, st);
+      AE_CHECK(b.wgrad(g2, H, E, H, w.pre1[l], H, H, TF_SILU, nullptr, G[sl.m2w], H, G[sl.m2b]));
+      AE_CHECK(colsum_f32(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
+    }
     if (l > 1) {
       // pre1 = Ps[send] + Pr[recv] + We silu(pre2_{l-1}) + b1
-      AE_CHECK(b.wgrad(g1, H, E, H, w.pre2[l - 1], H, H, TF_SILU, nullptr, G[sl.m0w] + 2 * H, 3 * H, nullptr));
-      AE_CHECK(b.dgrad(g1, H, E, H, P[sl.m0w] + 2 * H, 3 * H, H, s.gA, H, nullptr, nullptr, nullptr, 0));
+      {
+        ProfScope ps(PROF_EDGE_WGRAD, st);
+        AE_CHECK(b.wgrad(g1, H, E, H, w.pre2[l - 1], H, H, TF_SILU, nullptr, G[sl.m0w] + 2 * H, 3 * H, nullptr));
+      }
+      {
+        ProfScope ps(PROF_EDGE_BWD_DATA, st);
+        AE_CHECK(b.dgrad(g1, H, E, H, P[sl.m0w] + 2 * H, 3 * H, H, s.gA, H, nullptr, nullptr, nullptr, 0));
+      }
       ge = s.gA;
-      AE_CHECK(launch_segsum(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, 0, st));
-      AE_CHECK(launch_segsum(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, 0, st));
+      {
+        ProfScope ps(PROF_SEGMENT, st);
+        AE_CHECK(launch_segsum(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, 0, st));
+        AE_CHECK(launch_segsum(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, 0, st));
+      }
       const float* xin = w.xl[l - 1];
       AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
       AE_CHECK(b.wgrad(s.gpspr + H, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w] + H, 3 * H, nullptr));

@@ -1,0 +1,114 @@
+"""The step as a differentiable op: thin autograd wrapper over the C ABI.
+
+forward  -> aether_step_forward   (Aether.forward, nn/state2state/aether.py:169-186)
+backward -> aether_step_backward  (loss.backward(), experiments/lorentz/main.py:291)
+
+All buffers (workspace, scratch, gradients) are torch allocations handed to the library as raw
+pointers; launches go to torch's current stream, so the calls can be captured in a CUDA graph.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from .graph import PreparedGraph
+
+
+def _stream() -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _dims(D: int, H: int, graph: PreparedGraph) -> "_lib.AetherDims":
+    return _lib.AetherDims(D, H, graph.n_nodes, graph.n_edges)
+
+
+def step_forward_raw(params: Sequence[torch.Tensor], graph: PreparedGraph, x, vel, charges, edge_attr_orig, D: int,
+                     H: int, flags: int, dropout_mask: Optional[torch.Tensor] = None,
+                     workspace: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
+    """One forward step on raw tensors.  Returns (out, workspace)."""
+    lib = _lib.load()
+    if x.device.type != "cuda":
+        raise RuntimeError("aether_b200 runs on CUDA devices only (no CPU fallback)")
+    if len(params) != _lib.NUM_PARAMS:
+        raise ValueError("expected %d parameter tensors" % _lib.NUM_PARAMS)
+    dims = _dims(D, H, graph)
+    if x.shape[0] != graph.n_nodes or edge_attr_orig.shape[0] != graph.n_edges:
+        raise ValueError("node/edge counts do not match the prepared graph")
+    nbytes = lib.aether_workspace_bytes(ctypes.byref(dims), flags)
+    if workspace is None or workspace.numel() < nbytes:
+        workspace = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    if out is None:
+        out = torch.empty(graph.n_nodes, D, dtype=torch.float32, device=x.device)
+    parr = _lib.ptr_array(params)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.aether_step_forward(ctypes.byref(dims), parr, ctypes.byref(graph.c_struct()), _lib.ptr(x),
+                                           _lib.ptr(vel), _lib.ptr(charges), _lib.ptr(edge_attr_orig),
+                                           _lib.ptr(dropout_mask), _lib.ptr(out), _lib.ptr(workspace),
+                                           workspace.numel(), flags, _stream()), "aether_step_forward")
+    return out, workspace
+
+
+class AetherStepFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, vel, charges, edge_attr_orig, graph, D, H, flags, dropout_mask, *params):
+        x, vel, charges, edge_attr_orig = _f32c(x), _f32c(vel), _f32c(charges), _f32c(edge_attr_orig)
+        params = [_f32c(p) for p in params]
+        need = any(ctx.needs_input_grad)
+        f = int(flags) | (_lib.F_SAVE if need else 0)
+        out, ws = step_forward_raw(params, graph, x, vel, charges, edge_attr_orig, D, H, f, dropout_mask)
+        if need:
+            ctx.save_for_backward(x, vel, charges, edge_attr_orig, *params)
+            ctx.ws, ctx.graph, ctx.dims, ctx.flags, ctx.dmask = ws, graph, (D, H), f, dropout_mask
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        lib = _lib.load()
+        x, vel, charges, ea, *params = ctx.saved_tensors
+        D, H = ctx.dims
+        graph = ctx.graph
+        dims = _dims(D, H, graph)
+        grad_out = _f32c(grad_out)
+        grads = [torch.empty_like(p) for p in params]
+        gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        gv = torch.empty_like(vel) if ctx.needs_input_grad[1] else None
+        nbytes = lib.aether_backward_scratch_bytes(ctypes.byref(dims), ctx.flags)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(lib.aether_step_backward(ctypes.byref(dims), _lib.ptr_array(params),
+                                                ctypes.byref(graph.c_struct()), _lib.ptr(x), _lib.ptr(vel),
+                                                _lib.ptr(charges), _lib.ptr(ea), _lib.ptr(ctx.dmask),
+                                                _lib.ptr(grad_out), _lib.ptr_array(grads), _lib.ptr(gx), _lib.ptr(gv),
+                                                _lib.ptr(ctx.ws), ctx.ws.numel(), _lib.ptr(scratch), nbytes,
+                                                ctx.flags, _stream()), "aether_step_backward")
+        ctx.ws = None
+        return (gx, gv, None, None, None, None, None, None, None, *grads)
+
+
+def debug_stage(ws: torch.Tensor, graph: PreparedGraph, D: int, H: int, flags: int, stage: str) -> torch.Tensor:
+    """Copy a named intermediate out of a forward workspace (tests only)."""
+    lib = _lib.load()
+    dims = _dims(D, H, graph)
+    Nn, E = graph.n_nodes, graph.n_edges
+    O = D * (D - 1) // 2
+    shapes = {"field": (Nn, D), "rel_feat": (Nn, 3 * D), "R": (Nn, D, D), "pred": (Nn, D),
+              "edge_attr": (E, 7 * D + O + 2)}
+    for l in "1234":
+        shapes["e" + l] = (E, H)
+        shapes["x" + l] = (Nn, H)
+    out = torch.empty(shapes[stage], dtype=torch.float32, device=ws.device)
+    with torch.cuda.device(ws.device):
+        n = lib.aether_debug_stage(ctypes.byref(dims), _lib.ptr(ws), flags, stage.encode(), _lib.ptr(out), out.numel(),
+                                   _stream())
+    if n < 0:
+        _lib.check(int(n), "aether_debug_stage")
+    return out

@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""Benchmark of the Aether state-to-state step (BASELINE.json metric: edge-messages/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2b|c2|c1] [--hidden H]
+                    [--precision fp32|bf16] [--impl ours|reference]
+
+Prints ONE JSON line (rank 0).  A step is one pass of the hot path over one batch of synthetic
+particles: training workloads run caller prep + forward + MSE + backward + AdamW
+(experiments/lorentz/main.py:243-247,289-292); rollout workloads run T rollout steps.
+  value : whole-job edge-messages/s (4 per edge per step) with inputs resident in HBM
+  e2e   : the same through the public module API with pinned HOST inputs copied every step,
+          the edge list rebuilt on the device every step and the loss read back
+  roofline : edge-MLP kernels, algorithmic FLOPs / CUDA-event time of those launches
+  cpu_baseline : the CPU oracle (torch CPU restatement of the reference) on a bounded sample
+`--impl reference` times that CPU path alone.  Nothing here reads /root/reference.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (D, N, graphs per GPU, H default, mode, rollout steps)
+    "c4": dict(D=2, N=100, B=1024, H=256, mode="train", T=1,
+               name="config4: synthetic 2D charged, 100 particles fully connected (9900 edges/graph), batch 1024 per GPU, train step"),
+    "c2b": dict(D=3, N=20, B=128, H=64, mode="train", T=1, name="lorentz dynamic_20body shape, batch 128, train step"),
+    "c2": dict(D=3, N=5, B=128, H=64, mode="train", T=1, name="config2: gravitational 3D, 5 particles, batch 128, train step"),
+    "c1": dict(D=2, N=5, B=16, H=64, mode="rollout", T=20, name="config1: electrostatic 2D, 5 particles, batch 16, 20-step rollout"),
+}
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def algorithmic_flops_edge_mlp(D, H, E):
+    """Forward FLOPs of the four message_fn MLPs in the reference's formulation."""
+    fe = 7 * D + D * (D - 1) // 2 + 2
+    return 2.0 * E * (fe * H + 13 * H * H)
+
+
+def executed_flops_edge_mlp(D, H, E):
+    fe = 7 * D + D * (D - 1) // 2 + 2
+    return 2.0 * E * (fe * H + H * H + 3 * 2 * H * H)     # node-factorised: 2 H^2 per edge in layers 2-4
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_step_sample(cfg, H, graphs, seed=1):
+    """Returns (step_fn, edges_per_step): one CPU-oracle pass of the workload on `graphs` graphs."""
+    from oracle import aether_oracle as O
+    D, N = cfg["D"], cfg["N"]
+    p = {k: v.requires_grad_(True) for k, v in O.init_params(D, H, seed).items()}
+    x, v, q = O.synth_state(graphs, N, D, seed=seed)
+    send, recv = O.fc_edges(N, graphs)
+    E = send.numel()
+    if cfg["mode"] == "train":
+        opt = torch.optim.AdamW(list(p.values()), lr=5e-4, weight_decay=1e-12)
+        target = x + 0.05
+
+        def step():
+            opt.zero_grad()
+            _, ea = O.caller_prep(x, v, q, send, recv)
+            out = O.aether_step(p, x, (send, recv), v, ea, q)
+            loss = torch.nn.functional.mse_loss(out, target)
+            loss.backward()
+            opt.step()
+            return float(loss.detach())
+        return step, E
+    T = cfg["T"]
+
+    def step():
+        with torch.no_grad():
+            O.rollout(p, x, v, q, lambda xx: (send, recv), T)
+    return step, E * T
+
+
+def cpu_sample_graphs(cfg, H):
+    E = cfg["N"] * (cfg["N"] - 1)
+    budget = 4.0e5 * (64.0 / H) ** 2 if cfg["mode"] == "train" else 2.0e6   # edges per sample step
+    return int(max(1, min(cfg["B"], budget // max(E, 1))))
+
+
+def run_reference(args, cfg, H):
+    """--impl reference: the CPU oracle port on the host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    graphs = cpu_sample_graphs(cfg, H)
+    step, e_step = cpu_step_sample(cfg, H, graphs)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    val = 4.0 * e_step * args.steps / dt
+    sample = "%d of %d graphs per step (%d edges), all %d host threads" % (graphs, cfg["B"], e_step, cores)
+    line = {"impl": "reference", "metric": "edge_messages_per_sec", "value": val, "unit": "edge-messages/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": cfg["name"], "hidden": H, "mode": cfg["mode"], "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "edge-messages/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "edge-messages/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--hidden", type=int, default=0)
+    ap.add_argument("--batch", type=int, default=0, help="graphs per GPU (default: the workload's)")
+    ap.add_argument("--precision", default=os.environ.get("AETHER_B200_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    cfg = dict(WORKLOADS[args.workload])
+    H = args.hidden or cfg["H"]
+    if args.batch:
+        cfg["B"] = args.batch
+    if args.impl == "reference":
+        return run_reference(args, cfg, H)
+
+    import aether_b200 as ab
+    from aether_b200 import _lib
+    from oracle import aether_oracle as O   # synthetic inputs + the cpu_baseline leg only
+    lib = _lib.load(build_if_missing=False)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    D, N, B, T = cfg["D"], cfg["N"], cfg["B"], cfg["T"]
+    torch.manual_seed(1)
+    model = ab.Aether(2 * D, H, 0.0, D, device=dev, precision=args.precision)
+    x, v, q = O.synth_state(B, N, D, seed=1 + rank)
+    target = x + 0.05 * torch.randn(x.shape, generator=torch.Generator().manual_seed(7 + rank))
+    Nn = x.shape[0]
+    host = [t.pin_memory() for t in (x, v, q, target)]
+    xd, vd, qd, td = [t.to(dev) for t in host]
+    qd1 = qd.reshape(-1)
+    send, recv = ab.fc_edges(N, B, dev)
+    E = int(send.numel())
+    graph = ab.PreparedGraph(send, recv, Nn)
+    train = cfg["mode"] == "train"
+    params = model.param_list()
+    flat_n = sum(p.numel() for p in params)
+    if train:
+        opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=1e-12, fused=True)
+        model.train()
+    else:
+        model.eval()
+        roll = ab.Rollout(model, Nn, T, edges=(send, recv), cuda_graph=True)
+
+    def allreduce_grads():
+        if world == 1:
+            return
+        flat = torch.cat([p.grad.reshape(-1) for p in params])
+        dist.all_reduce(flat)
+        flat.div_(world)
+        off = 0
+        for p in params:
+            p.grad.copy_(flat[off:off + p.numel()].view_as(p.grad))
+            off += p.numel()
+
+    def step_resident():
+        if not train:
+            roll.run(xd, vd, qd1)
+            return None
+        opt.zero_grad(set_to_none=True)
+        h, ea = ab.caller_prep(xd, vd, qd1, send, recv)
+        out = model(h, xd, graph, vd, ea, qd)
+        loss = torch.nn.functional.mse_loss(out, td)
+        loss.backward()
+        allreduce_grads()
+        opt.step()
+        return loss
+
+    def step_e2e():
+        xs, vs, qs, ts = [t.to(dev, non_blocking=True) for t in host]
+        if not train:
+            traj = roll.run(xs, vs, qs.reshape(-1))
+            return float(traj[-1].abs().mean().item())
+        s, r = ab.fc_edges(N, B, dev)                       # the reference rebuilds the edge list per batch
+        opt.zero_grad(set_to_none=True)
+        h, ea = ab.caller_prep(xs, vs, qs.reshape(-1), s, r)
+        out = model(h, xs, [s, r], vs, ea, qs)
+        loss = torch.nn.functional.mse_loss(out, ts)
+        loss.backward()
+        allreduce_grads()
+        opt.step()
+        return float(loss.item())
+
+    small = E * H * 4 * 2 < 256e6            # working set may sit in the 126 MB L2: flush between steps
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev) if small else None
+
+    def timed(fn, steps, warmup, profile=False):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if profile:
+            lib.aether_profile_enable(1)
+        n0 = lib.aether_launch_count()
+        total = 0.0
+        evs = []
+        for _ in range(steps):
+            if flush is not None:
+                flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        launches = lib.aether_launch_count() - n0
+        total = sum(a.elapsed_time(b) for a, b in evs) * 1e-3
+        prof = None
+        if profile:
+            lib.aether_profile_enable(0)
+            import ctypes
+            ms = (ctypes.c_double * 6)()
+            cnt = (ctypes.c_int64 * 6)()
+            lib.aether_profile_collect(ms, cnt, 6)
+            prof = {"ms": list(ms), "spans": list(cnt)}
+        if dist is not None:
+            t = torch.tensor([total], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total = float(t.item())
+        return total, launches, prof
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e = None
+    if not args.no_e2e:
+        e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
+        e2e = 4.0 * E * T * world * args.steps / e2e_total
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    pk, pk_src = peaks()
+    value = 4.0 * E * T * world * args.steps / total
+    # roofline of the dominant kernels: the edge-MLP launches of the forward pass (category 0)
+    spans = max(prof["spans"][0], 1)
+    ms_per_layer = prof["ms"][0] / spans
+    alg = algorithmic_flops_edge_mlp(D, H, E) / 4.0          # per span = one layer, averaged over the four
+    achieved = alg / (ms_per_layer * 1e-3) / 1e12 if ms_per_layer > 0 else 0.0
+    peak = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload + "_" + args.precision)
+    except Exception:
+        pass
+    roofline = {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer)", "achieved": achieved,
+                "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
+                "peak_source": pk_src + " bf16 sustained", "algorithmic_flops_per_launch_group": alg,
+                "executed_flops_per_launch_group": executed_flops_edge_mlp(D, H, E) / 4.0,
+                "avg_ms_per_launch_group": ms_per_layer}
+    step_ms = total / args.steps * 1e3
+    share = {k: (prof["ms"][i] / args.steps) / step_ms for i, k in
+             enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment", "edge_feat", "node"])}
+    line = {"metric": "edge_messages_per_sec", "value": value, "unit": "edge-messages/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
+            "data": "synthetic",
+            "config": {"workload": cfg["name"], "num_dims": D, "particles_per_graph": N, "graphs_per_gpu": B,
+                       "hidden": H, "mode": cfg["mode"], "rollout_steps": T, "edges_per_gpu": E, "nodes_per_gpu": Nn,
+                       "precision": args.precision, "parallelism": "dp%d" % world,
+                       "l2": "flushed between steps" if small else "working set exceeds L2"},
+            "particle_steps_per_sec": Nn * T * world * args.steps / total,
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "time_share": share}
+    if e2e is not None:
+        h2d = sum(t.numel() * t.element_size() for t in host)
+        line["e2e"] = {"value": e2e, "unit": "edge-messages/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
+    if not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        graphs = cpu_sample_graphs(cfg, H)
+        cstep, e_step = cpu_step_sample(cfg, H, graphs)
+        cstep()
+        t0, it = time.perf_counter(), 0
+        while it < 2 or (time.perf_counter() - t0 < args.cpu_seconds and it < 50):
+            cstep()
+            it += 1
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": 4.0 * e_step * it / dt, "unit": "edge-messages/s", "cores": cores, "kind": "port",
+                                "sample": "%d of %d graphs per step (%d edges), %d steps, %d host threads" %
+                                          (graphs, B, e_step, it, cores)}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -130,6 +130,21 @@ int aether_step_backward(const AetherDims* dims, const float* const* params, con
                          void* workspace /* the one forward filled */, size_t workspace_bytes,
                          void* scratch, size_t scratch_bytes, uint32_t flags, void* stream);
 
+/* One harness-level rollout step: edge_attr = [q_i q_j, |x_i - x_j|] over the ORIGINAL
+ * edge list (send64/recv64, experiments/lorentz/main.py:243-246), x_next = step(x, vel),
+ * vel_next = x_next - x.  x_next/vel_next must not alias x/vel. */
+int aether_rollout_step(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                        const int64_t* send64, const int64_t* recv64, const float* x, const float* vel,
+                        const float* charges, float* x_next, float* vel_next, float* edge_attr_scratch /* [E,2] */,
+                        void* workspace, size_t workspace_bytes, uint32_t flags, void* stream);
+
+/* Bench support: kernels launched by this library so far; optional per-category CUDA-event timing
+ * (categories: 0 edge-MLP forward, 1 edge backward data grads, 2 edge weight grads, 3 segment
+ * reductions, 4 edge features, 5 node-level work).  collect() synchronises the device. */
+uint64_t aether_launch_count(void);
+int aether_profile_enable(int on);
+int aether_profile_collect(double* ms_by_cat, int64_t* spans_by_cat, int32_t n_cat);
+
 /* Debug/test hook: copy a named stage out of a forward workspace (fp32, device to device).
  * Stages: "field" [Nn,D], "rel_feat" [Nn,3D], "R" [Nn,D,D], "edge_attr" [E,Fe] (sorted order),
  * "e1".."e4" [E,H] (sorted order), "x1".."x4" [Nn,H], "pred" [Nn,D].  Returns the number of

@@ -1,0 +1,77 @@
+"""The C-ABI library builds, loads and exports every symbol include/aether_b200.h declares.
+No compute calls here (no GPU): only size queries and argument validation."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from aether_b200 import _lib
+    return _lib.load()
+
+
+def header_functions():
+    src = open(os.path.join(ROOT, "include", "aether_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(aether_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported(lib):
+    from aether_b200 import _lib
+    names = header_functions()
+    assert len(names) >= 12
+    for n in names:
+        assert hasattr(lib, n), n
+    assert sorted(_lib.SIGNATURES) == names          # the ctypes table covers the header one to one
+
+
+def test_version_and_errors(lib):
+    assert lib.aether_abi_version() == 1
+    assert lib.aether_error_string(0) == b"success"
+    assert b"workspace" in lib.aether_error_string(-2)
+
+
+def test_size_queries(lib):
+    from aether_b200 import _lib
+    d = _lib.AetherDims(3, 64, 640, 2560)
+    inf = lib.aether_workspace_bytes(ctypes.byref(d), 0)
+    sav = lib.aether_workspace_bytes(ctypes.byref(d), _lib.F_SAVE)
+    assert 0 < inf < sav
+    assert sav >= 8 * 2560 * 64 * 4                  # four layers keep two [E,H] fp32 pre-activations
+    assert lib.aether_backward_scratch_bytes(ctypes.byref(d), _lib.F_SAVE) > 2 * 2560 * 64 * 4
+    assert lib.aether_graph_scratch_bytes(640, 2560) >= 2560 * 4
+    bad = _lib.AetherDims(4, 64, 10, 10)
+    assert lib.aether_workspace_bytes(ctypes.byref(bad), 0) == 0
+
+
+def test_bad_arguments_return_codes(lib):
+    from aether_b200 import _lib
+    bad = _lib.AetherDims(4, 64, 10, 10)
+    rc = lib.aether_step_forward(ctypes.byref(bad), None, None, None, None, None, None, None, None, None, 0, 0, None)
+    assert rc == -1
+    d = _lib.AetherDims(2, 64, 10, 10)
+    g = _lib.AetherGraphC()
+    arr = (ctypes.c_void_p * 47)()
+    rc = lib.aether_step_forward(ctypes.byref(d), arr, ctypes.byref(g), None, None, None, None, None,
+                                 ctypes.c_void_p(256), None, 0, 0, None)
+    assert rc == -2                                  # workspace missing
+
+
+def test_module_state_dict_matches_reference_layout():
+    import torch
+    import aether_b200
+    from oracle import aether_oracle as O
+    for D, H in [(2, 32), (3, 64)]:
+        torch.manual_seed(1)
+        m = aether_b200.Aether(2 * D, H, 0.0, D, device="cpu")
+        assert [k for k, _ in O.param_shapes(D, H)] == list(m.state_dict().keys())
+        p = O.init_params(D, H, seed=1)
+        assert all(torch.equal(p[k], v) for k, v in m.state_dict().items())
+    with pytest.raises(RuntimeError):
+        m(None, torch.zeros(4, 3), [torch.zeros(0, dtype=torch.long)] * 2, torch.zeros(4, 3), torch.zeros(0, 2),
+          torch.zeros(4, 1))
