@@ -32,6 +32,9 @@ SOURCES = [
     ("graph.cu", []),
     ("step.cu", []),
     ("edge_mlp_tc.cu", []),
+    ("tc_gemm.cu", []),
+    ("tc_wgrad.cu", []),
+    ("tc_abi.cu", []),
     ("prof.cu", []),
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),

@@ -1,0 +1,346 @@
+// Persistent tcgen05 GEMM over edge (or node) rows:
+//
+//     out[M, N] = epi( tf(A[M, K]) * B^T )          A bf16 row-major in HBM, B = packed bf16 weights
+//
+// This is every Linear of GNNLayer.message_fn (nn/state2state/locs/locs.py:206-212,235) in the bf16
+// path and the data-gradient GEMMs of its backward.  One CTA per SM, warp-specialised:
+//
+//   warp 4      TMA producer : the weight image once (cp.async.bulk), then one 128x64 bf16 box of A
+//               per pipeline slot (cp.async.bulk.tensor, 128-byte swizzle = the UMMA K-major layout)
+//   warps 6-9   transform    : optional in-place SiLU on the landed box (the consumer of a stored
+//               pre-activation applies the activation, so activations are never written to HBM)
+//   warp 5      MMA issuer   : one thread, tcgen05.mma 128 x N x 16 per instruction, fp32
+//               accumulators in TMEM, two accumulators ping-pong between MMA and epilogue
+//   warps 0-3   epilogue     : tcgen05.ld (one output row per thread), + bias, + gathered node terms
+//               P_s[send] + P_r[recv] (node-factorised first Linear), x silu'(saved pre-activation)
+//               for the backward chain, bf16 or fp32 store
+//
+// Shared memory: weights N*K*2 bytes resident for the whole kernel (128 KB at N=K=256), the rest is
+// the A ring (16 KB per slot, 6 slots at N=K=256).  HBM traffic per row: 2K bytes in, 2N bytes out.
+#include "tc_gemm.cuh"
+
+namespace aether {
+
+namespace {
+
+using namespace tc;
+
+constexpr int kThreads = 320;
+constexpr int kTileM = 128;
+constexpr int kSlotBytes = kTileM * 128;          // 128 rows x 64 bf16
+constexpr int kSmemMax = 232448;                  // 227 KB
+constexpr int kMiscBytes = 2048;                  // barriers + tmem pointer + bias
+
+__host__ __device__ constexpr int weight_bytes(int K, int N) { return K * N * 2; }
+__host__ __device__ constexpr int num_slots(int K, int N) {
+  int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N)) / kSlotBytes;
+  return s > 8 ? 8 : s;
+}
+__host__ __device__ constexpr int smem_bytes(int K, int N) {
+  return 1024 + weight_bytes(K, N) + num_slots(K, N) * kSlotBytes + kMiscBytes;
+}
+__host__ __device__ constexpr int tmem_cols(int N) { return 2 * N < 32 ? 32 : 2 * N; }
+
+template <int K, int N, int TF>
+__global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, TcGemmArgs g) {
+  static_assert(K % 64 == 0 && N % 32 == 0 && N <= 256 && (N & (N - 1)) == 0, "unsupported shape");
+  constexpr int KC = K / 64;                      // 64-wide K chunks = pipeline slots per tile
+  constexpr int S = num_slots(K, N);
+  constexpr uint32_t IDESC = make_idesc(128, N, MAJOR_K, MAJOR_K);
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sW = base;
+  const uint32_t sA = base + weight_bytes(K, N);
+  const uint32_t sMisc = sA + S * kSlotBytes;
+  // barriers (8 bytes each)
+  const uint32_t bar_raw = sMisc;                 // [S] TMA landed
+  const uint32_t bar_rdy = sMisc + 64;            // [S] transform done
+  const uint32_t bar_free = sMisc + 128;          // [S] MMA consumed
+  const uint32_t bar_accf = sMisc + 192;          // [2] accumulator full
+  const uint32_t bar_acce = sMisc + 208;          // [2] accumulator drained
+  const uint32_t bar_w = sMisc + 224;             // weights landed
+  const uint32_t tmem_slot = sMisc + 240;
+  uint8_t* misc_ptr = smem_raw + (sMisc - smem_u32(smem_raw));
+  float* sbias = reinterpret_cast<float*>(misc_ptr + 1024);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t n_tiles = (g.M + kTileM - 1) / kTileM;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(bar_raw + 8 * s, 1);
+      mbar_init(bar_rdy + 8 * s, 128);
+      mbar_init(bar_free + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bar_accf + 8 * a, 1);
+      mbar_init(bar_acce + 8 * a, 4);
+    }
+    mbar_init(bar_w, 1);
+    fence_mbar_init();
+  }
+  if (threadIdx.x < N) sbias[threadIdx.x] = g.bias ? g.bias[threadIdx.x] : 0.0f;
+  if (warp == 5) tmem_alloc(tmem_slot, tmem_cols(N));
+  if (warp == 4 && lane == 0) tma_prefetch_desc(&tmA);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 4) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar_w, weight_bytes(K, N));
+      for (int c = 0; c < KC; ++c)
+        bulk_load(sW + c * (N * 128), (const uint8_t*)g.wpack + (size_t)c * (N * 128), N * 128, bar_w);
+      uint32_t it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int c = 0; c < KC; ++c, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait(bar_free + 8 * s, ph ^ 1);
+          mbar_arrive_expect_tx(bar_raw + 8 * s, kSlotBytes);
+          tma_load_2d(sA + s * kSlotBytes, &tmA, c * 64, (int)(t * kTileM), bar_raw + 8 * s);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      mbar_wait(bar_w, 0);
+      uint32_t it = 0, lt = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+        const uint32_t acc = lt & 1;
+        mbar_wait(bar_acce + 8 * acc, ((lt >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + acc * N;
+        for (int c = 0; c < KC; ++c, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait((TF != TC_TF_NONE ? bar_rdy : bar_raw) + 8 * s, ph);
+          tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t ad = make_sdesc(sA + s * kSlotBytes + k * 32, 16, 1024);
+            const uint64_t bd = make_sdesc(sW + c * (N * 128) + k * 32, 16, 1024);
+            umma_bf16(d, ad, bd, IDESC, (c | k) != 0);
+          }
+          umma_commit(bar_free + 8 * s);
+        }
+        umma_commit(bar_accf + 8 * acc);
+      }
+    }
+  } else if (warp >= 6) {
+    // ===== transform: in-place SiLU on the landed A box =====
+    if (TF != TC_TF_NONE) {
+      const int tt = threadIdx.x - 192;           // 0..127
+      uint32_t it = 0;
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int c = 0; c < KC; ++c, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait(bar_raw + 8 * s, ph);
+          const uint32_t a0 = sA + s * kSlotBytes + tt * 16;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            uint32_t u[4];
+            const uint32_t addr = a0 + i * 2048;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "r"(addr));
+#pragma unroll
+            for (int q = 0; q < 4; ++q) u[q] = pack_bf16(silu_fast(bf16_lo(u[q])), silu_fast(bf16_hi(u[q])));
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]) : "memory");
+          }
+          fence_proxy_async_smem();
+          mbar_arrive(bar_rdy + 8 * s);
+        }
+      }
+    }
+  } else {
+    // ===== epilogue: warps 0..3, one output row per thread =====
+    uint32_t lt = 0;
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+      const uint32_t acc = lt & 1;
+      mbar_wait(bar_accf + 8 * acc, (lt >> 1) & 1);
+      tc_fence_after();
+      const int64_t row = t * kTileM + warp * 32 + lane;
+      const bool live = row < g.M;
+      int ia = 0, ib = 0;
+      if (g.gat && live) { ia = g.idx_a[row]; ib = g.idx_b[row]; }
+#pragma unroll 1
+      for (int j = 0; j < N / 32; ++j) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + acc * N + j * 32, r);
+        tmem_ld_wait();
+        if (!live) continue;
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + sbias[j * 32 + i];
+        if (g.gat) {
+          const float4* pa = reinterpret_cast<const float4*>(g.gat + (size_t)ia * g.ldg + j * 32);
+          const float4* pb = reinterpret_cast<const float4*>(g.gat + (size_t)ib * g.ldg + g.goff_b + j * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 a = __ldg(pa + q), b = __ldg(pb + q);
+            v[4 * q] += a.x + b.x; v[4 * q + 1] += a.y + b.y; v[4 * q + 2] += a.z + b.z; v[4 * q + 3] += a.w + b.w;
+          }
+        }
+        if (g.dsilu) {
+          const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)row * g.ldd + j * 32);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint4 z = __ldg(pd + q);
+            const uint32_t zz[4] = {z.x, z.y, z.z, z.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              v[8 * q + 2 * e] *= dsilu_fast(bf16_lo(zz[e]));
+              v[8 * q + 2 * e + 1] *= dsilu_fast(bf16_hi(zz[e]));
+            }
+          }
+        }
+        if (g.out_bf16) {
+          uint4* po = reinterpret_cast<uint4*>(g.out_bf16 + (size_t)row * g.ldo + j * 32);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 o;
+            o.x = pack_bf16(v[8 * q], v[8 * q + 1]); o.y = pack_bf16(v[8 * q + 2], v[8 * q + 3]);
+            o.z = pack_bf16(v[8 * q + 4], v[8 * q + 5]); o.w = pack_bf16(v[8 * q + 6], v[8 * q + 7]);
+            po[q] = o;
+          }
+        }
+        if (g.out_f32) {
+          float* po = g.out_f32 + (size_t)row * g.ldo32 + j * 32;
+          if (j * 32 + 32 <= g.n_valid && (g.ldo32 & 3) == 0) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              reinterpret_cast<float4*>(po)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (j * 32 + i < g.n_valid) po[i] = v[i];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_acce + 8 * acc);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols(N));
+  }
+}
+
+// fp32 weights -> bf16 shared-memory image of the B operand (K-major, 128-byte swizzle):
+// logical B[n][k] = transpose ? W[k*ldw + n] : W[n*ldw + (kmod ? k % kmod : k)], zero outside
+// [n_valid, k_valid].
+__global__ void pack_weight_kernel(const float* __restrict__ W, int64_t ldw, int N, int K, int n_valid, int k_valid,
+                                   int transpose, int kmod, uint8_t* __restrict__ out) {
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;   // one 16-byte unit = 8 consecutive k
+  if (u >= N * K / 8) return;
+  const int n = u % N, kb = u / N;                       // kb: 8-element block index along K
+  uint32_t w[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    float f[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = kb * 8 + 2 * e + h;
+      const int ks = kmod ? k % kmod : k;
+      float x = 0.0f;
+      if (n < n_valid && ks < k_valid) x = transpose ? W[(size_t)ks * ldw + n] : W[(size_t)n * ldw + ks];
+      f[h] = x;
+    }
+    w[e] = tc::pack_bf16(f[0], f[1]);
+  }
+  const int c = kb / 8, j = kb % 8;
+  const size_t off = (size_t)c * N * 128 + (size_t)n * 128 + (size_t)((j ^ (n & 7)) * 16);
+  *reinterpret_cast<uint4*>(out + off) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+template <int K, int N>
+int launch_kn(const TcGemmArgs& g, const CUtensorMap& tm, int tf, cudaStream_t st) {
+  const int64_t tiles = (g.M + kTileM - 1) / kTileM;
+  int sms = tc_sm_count();
+  const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+  const int smem = smem_bytes(K, N);
+  cudaError_t e;
+  if (tf == TC_TF_SILU) {
+    e = cudaFuncSetAttribute(tc_gemm_kernel<K, N, TC_TF_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    tc_gemm_kernel<K, N, TC_TF_SILU><<<grid, kThreads, smem, st>>>(tm, g);
+  } else {
+    e = cudaFuncSetAttribute(tc_gemm_kernel<K, N, TC_TF_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    tc_gemm_kernel<K, N, TC_TF_NONE><<<grid, kThreads, smem, st>>>(tm, g);
+  }
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+
+int tc_sm_count() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    sms = n;
+  }
+  return sms;
+}
+
+int tc_make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
+    if (e != cudaSuccess) return (int)e;
+    if (!p || q != cudaDriverEntryPointSuccess) return AETHER_E_UNSUPPORTED;
+    fn = (EncodeFn)p;
+  }
+  if (rows <= 0 || cols < 64 || (ld * 2) % 16 || ((uintptr_t)base & 15)) return AETHER_E_BADARG;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : AETHER_E_BADARG;
+}
+
+size_t tc_weight_pack_bytes(int K, int N) { return (size_t)K * N * 2; }
+
+int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k_valid, int transpose, int kmod,
+                   void* out, cudaStream_t st) {
+  if (K % 64 || N % 8 || ((uintptr_t)out & 15)) return AETHER_E_BADARG;
+  const int units = N * K / 8;
+  pack_weight_kernel<<<(units + 255) / 256, 256, 0, st>>>(W, ldw, N, K, n_valid, k_valid, transpose, kmod, (uint8_t*)out);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+bool tc_gemm_supported(int K, int N) {
+  return (K == 64 || K == 128 || K == 256) && (N == 32 || N == 64 || N == 128 || N == 256);
+}
+
+int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int tf, cudaStream_t st) {
+  if (g.M <= 0) return 0;
+  if (!tc_gemm_supported(K, N)) return AETHER_E_UNSUPPORTED;
+  CUtensorMap tm;
+  AE_CHECK(tc_make_tmap_bf16(&tm, A, g.M, K, lda, kTileM));
+#define AE_TC_CASE(KK, NN) if (K == KK && N == NN) return launch_kn<KK, NN>(g, tm, tf, st);
+  AE_TC_CASE(256, 256) AE_TC_CASE(256, 32) AE_TC_CASE(64, 256)
+  AE_TC_CASE(128, 128) AE_TC_CASE(128, 32) AE_TC_CASE(64, 128)
+  AE_TC_CASE(64, 64) AE_TC_CASE(64, 32)
+#undef AE_TC_CASE
+  return AETHER_E_UNSUPPORTED;
+}
+
+}  // namespace aether

@@ -1,0 +1,40 @@
+// Host interface of the tcgen05 kernels (tc_gemm.cu, tc_wgrad.cu).
+#pragma once
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace aether {
+
+enum { TC_TF_NONE = 0, TC_TF_SILU = 1 };
+
+struct TcGemmArgs {
+  int64_t M = 0;                       // rows of A / out
+  const void* wpack = nullptr;         // packed weight image from tc_pack_weight (N*K*2 bytes)
+  const float* bias = nullptr;         // [N] or null
+  // + gat[idx_a[m]*ldg + n] + gat[idx_b[m]*ldg + goff_b + n]
+  const float* gat = nullptr; int64_t ldg = 0;
+  const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int goff_b = 0;
+  // * silu'(dsilu[m*ldd + n])
+  const __nv_bfloat16* dsilu = nullptr; int64_t ldd = 0;
+  __nv_bfloat16* out_bf16 = nullptr; int64_t ldo = 0;
+  float* out_f32 = nullptr; int64_t ldo32 = 0; int n_valid = 0;   // fp32 output writes columns < n_valid
+};
+
+int tc_sm_count();
+bool tc_gemm_supported(int K, int N);
+size_t tc_weight_pack_bytes(int K, int N);
+// B[n][k] = transpose ? W[k*ldw+n] : W[n*ldw + (kmod ? k%kmod : k)], zero outside [n_valid,k_valid]
+int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k_valid, int transpose, int kmod,
+                   void* out, cudaStream_t st);
+// out = epi(tf(A) B^T); A is bf16 [M, K] with leading dimension lda (elements)
+int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int tf, cudaStream_t st);
+
+// dW[MG, NA] = sum_e G[e, :]^T tf(ACT[e, :]) over E rows; both operands bf16 row-major.
+// partial: tc_wgrad_partial_floats(MG, NA) floats of scratch.  fold32: dW[m][j] = P[m][j] + P[m][32+j]
+// for j < n_valid (layer-1 hi/lo operand), otherwise columns < n_valid are written.
+bool tc_wgrad_supported(int MG, int NA);
+size_t tc_wgrad_partial_floats(int MG, int NA);
+int tc_wgrad(const void* G, int64_t ldg, int MG, const void* ACT, int64_t lda, int NA, int tf, int64_t E, float* dW,
+             int64_t lddw, int n_valid, int fold32, float* partial, size_t partial_floats, cudaStream_t st);
+
+}  // namespace aether
