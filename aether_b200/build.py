@@ -31,10 +31,10 @@ SOURCES = [
     ("segment.cu", []),
     ("graph.cu", []),
     ("step.cu", []),
-    ("edge_mlp_tc.cu", []),
     ("tc_gemm.cu", []),
     ("tc_wgrad.cu", []),
     ("tc_abi.cu", []),
+    ("edge_bf16.cu", []),
     ("prof.cu", []),
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),

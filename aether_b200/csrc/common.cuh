@@ -97,6 +97,10 @@ int launch_node_frame(int D, int64_t Nn, const float* vel, const float* f, float
 int launch_edge_features(int D, int64_t E, const int32_t* send, const int32_t* recv, const int32_t* perm,
                          const float* x, const float* vel, const float* f, const float* R, const float* x0,
                          const float* edge_attr_orig, float* feat, int ldf, cudaStream_t st);
+// bf16 path: features as [E, 64] bf16 = [hi(32) | lo(32)] (A operand of the layer-1 tcgen05 GEMM)
+int launch_edge_features_hilo(int D, int64_t E, const int32_t* send, const int32_t* recv, const int32_t* perm,
+                              const float* x, const float* vel, const float* f, const float* R, const float* x0,
+                              const float* edge_attr_orig, void* feat16, cudaStream_t st);
 int launch_globalize(int D, int64_t Nn, const float* x, const float* R, const float* pred, float* out, cudaStream_t st);
 int launch_caller_prep(int D, const float* x, const float* vel, const float* q, const int64_t* send,
                        const int64_t* recv, int64_t E, int64_t Nn, float* h, float* ea, cudaStream_t st);
@@ -127,6 +131,17 @@ int launch_edge_dpre2(int64_t E, int H, const int32_t* recv, const int32_t* rowp
 // embedding gradient: gemb[r, :] = sum_{n: idx(n)==r} gfin[n, 2D:2D+16]
 int launch_embedding_bwd(int D, int64_t Nn, const float* charges, const float* gfin, float* gemb, cudaStream_t st);
 int launch_fill(float* p, size_t n, float v, cudaStream_t st);
+
+// ---- bf16 edge kernels (edge_bf16.cu): [E, W] tensors stored as bf16, W in {64, 128, 256} ----------
+int launch_segmean_silu_bf16(int64_t Nn, int H, const int32_t* rowptr, const void* src, int64_t lds, const float* base,
+                             int64_t ldb, float* y, int64_t ldy, cudaStream_t st);
+int launch_segsum_bf16(int64_t Nn, int W, const int32_t* ptr, const int32_t* list, const void* src, int64_t lds,
+                       float* out, int64_t ldo, cudaStream_t st);
+int launch_edge_dpre2_bf16(int64_t E, int H, const int32_t* recv, const int32_t* rowptr, const void* ge, const float* gy,
+                           const void* pre2, void* g, cudaStream_t st);
+int colsum_bf16(const void* A, int64_t lda, int64_t M, int N, float* out, float* partial, size_t partial_floats,
+                cudaStream_t st);
+size_t colsum_bf16_partial_floats(int64_t M, int N);
 
 // ---- graph kernels (graph.cu) --------------------------------------------------
 }  // namespace aether

@@ -1,6 +1,8 @@
 // Forward geometry kernels: field-network input, per-node heading frames, per-edge local-frame
 // features, globalize + Euler update, and the caller-side step preparation.
 // Compiled with -fmad=false (see geom.cuh).
+#include <cuda_bf16.h>
+
 #include "geom.cuh"
 
 namespace aether {
@@ -52,16 +54,16 @@ __host__ __device__ inline void node_frame_body(int64_t n, const float* vel, con
 // [R_i^T(p_j-p_i) D | euler(R_i^T R_j)/pi O | |p_j-p_i| 1 | theta(,phi) D-1 | R_i^T v_j D | R_i^T f_j D |
 //  rel_feat[i] 3D | edge_attr_orig 2 | zero pad]
 template <int D>
-__host__ __device__ inline void edge_features_body(int64_t e, const int32_t* send, const int32_t* recv,
+__host__ __device__ inline void edge_features_values(int64_t e, const int32_t* send, const int32_t* recv,
                                      const int32_t* perm, const float* x,
                                      const float* vel, const float* f,
                                      const float* R, const float* x0,
-                                     const float* orig, float* feat, int ldf) {
+                                     const float* orig, float* out /* [(FE+3)/4*4], tail zeroed */) {
   constexpr int O = D * (D - 1) / 2;
   constexpr int FE = 7 * D + O + 2;
   constexpr int LD = (FE + 3) / 4 * 4;
   const int64_t j = send[e], i = recv[e];
-  float Ri[D * D], Rj[D * D], d[D], vj[D], fj[D], out[LD];
+  float Ri[D * D], Rj[D * D], d[D], vj[D], fj[D];
 #pragma unroll
   for (int k = 0; k < D * D; ++k) { Ri[k] = R[i * D * D + k]; Rj[k] = R[j * D * D + k]; }
 #pragma unroll
@@ -108,6 +110,17 @@ __host__ __device__ inline void edge_features_body(int64_t e, const int32_t* sen
   out[c++] = orig[pe * 2 + 1];
 #pragma unroll
   for (int k = FE; k < LD; ++k) out[k] = 0.0f;
+}
+
+template <int D>
+__host__ __device__ inline void edge_features_body(int64_t e, const int32_t* send, const int32_t* recv,
+                                     const int32_t* perm, const float* x,
+                                     const float* vel, const float* f,
+                                     const float* R, const float* x0,
+                                     const float* orig, float* feat, int ldf) {
+  constexpr int LD = (7 * D + D * (D - 1) / 2 + 2 + 3) / 4 * 4;
+  float out[LD];
+  edge_features_values<D>(e, send, recv, perm, x, vel, f, R, x0, orig, out);
   float4* dst = reinterpret_cast<float4*>(feat + (size_t)e * ldf);
 #pragma unroll
   for (int k = 0; k < LD / 4; ++k) dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
@@ -171,6 +184,40 @@ __global__ void edge_features_kernel(int64_t E, const int32_t* __restrict__ send
   edge_features_body<D>(e, send, recv, perm, x, vel, f, R, x0, orig, feat, ldf);
 }
 
+// bf16 path: the features as the A operand of the layer-1 tcgen05 GEMM, K = 64 = [hi(32) | lo(32)] with
+// hi = bf16(v), lo = bf16(v - hi): the product against bf16 weights keeps ~16 bits of the feature.
+#ifdef __CUDACC__
+template <int D>
+__global__ void edge_features_hilo_kernel(int64_t E, const int32_t* __restrict__ send, const int32_t* __restrict__ recv,
+                                          const int32_t* __restrict__ perm, const float* __restrict__ x,
+                                          const float* __restrict__ vel, const float* __restrict__ f,
+                                          const float* __restrict__ R, const float* __restrict__ x0,
+                                          const float* __restrict__ orig, uint4* __restrict__ feat16) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  constexpr int FE = 7 * D + D * (D - 1) / 2 + 2;
+  constexpr int LD = (FE + 3) / 4 * 4;
+  float out[32];
+  edge_features_values<D>(e, send, recv, perm, x, vel, f, R, x0, orig, out);
+#pragma unroll
+  for (int k = LD; k < 32; ++k) out[k] = 0.0f;
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(out[2 * k]), h1 = __float2bfloat16_rn(out[2 * k + 1]);
+    const __nv_bfloat16 l0 = __float2bfloat16_rn(out[2 * k] - __bfloat162float(h0));
+    const __nv_bfloat16 l1 = __float2bfloat16_rn(out[2 * k + 1] - __bfloat162float(h1));
+    hi[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+    lo[k] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+  }
+  uint4* dst = feat16 + (size_t)e * 8;   // 128 bytes per edge
+#pragma unroll
+  for (int k = 0; k < 4; ++k) dst[k] = make_uint4(hi[4 * k], hi[4 * k + 1], hi[4 * k + 2], hi[4 * k + 3]);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) dst[4 + k] = make_uint4(lo[4 * k], lo[4 * k + 1], lo[4 * k + 2], lo[4 * k + 3]);
+}
+#endif
+
 template <int D>
 __global__ void globalize_kernel(int64_t Nn, const float* __restrict__ x, const float* __restrict__ R,
                                  const float* __restrict__ pred, float* __restrict__ out) {
@@ -208,6 +255,16 @@ int launch_edge_features(int D, int64_t E, const int32_t* send, const int32_t* r
   if (ldf != edge_feat_ld(D)) return AETHER_E_BADARG;
   if (D == 2) edge_features_kernel<2><<<nblk_g(E, 128), 128, 0, st>>>(E, send, recv, perm, x, vel, f, R, x0, orig, feat, ldf);
   else edge_features_kernel<3><<<nblk_g(E, 128), 128, 0, st>>>(E, send, recv, perm, x, vel, f, R, x0, orig, feat, ldf);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_edge_features_hilo(int D, int64_t E, const int32_t* send, const int32_t* recv, const int32_t* perm,
+                              const float* x, const float* vel, const float* f, const float* R, const float* x0,
+                              const float* orig, void* feat16, cudaStream_t st) {
+  if (E <= 0) return 0;
+  if (D == 2) edge_features_hilo_kernel<2><<<nblk_g(E, 128), 128, 0, st>>>(E, send, recv, perm, x, vel, f, R, x0, orig, (uint4*)feat16);
+  else edge_features_hilo_kernel<3><<<nblk_g(E, 128), 128, 0, st>>>(E, send, recv, perm, x, vel, f, R, x0, orig, (uint4*)feat16);
   AE_LAUNCH_CHECK();
   return 0;
 }

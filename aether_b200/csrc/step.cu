@@ -5,7 +5,7 @@
 #include <string.h>
 
 #include "common.cuh"
-#include "edge_mlp_tc.cuh"
+#include "tc_gemm.cuh"
 
 namespace aether {
 
@@ -29,7 +29,13 @@ struct Carver {
   char* base; size_t off = 0;
   explicit Carver(void* p) : base((char*)p) {}
   float* f(size_t n) { float* r = (float*)(base + off); off += align_up(n * sizeof(float), 256); return r; }
+  void* b(size_t bytes) { void* r = base + off; off += align_up(bytes, 1024); return r; }
 };
+
+// bf16 tensor-core path for the edge MLPs: requested by the flag and available for this hidden size
+inline bool use_tc(const AetherDims& d, uint32_t flags) {
+  return (flags & AETHER_F_BF16_EDGE_MLP) && (d.hidden == 64 || d.hidden == 128 || d.hidden == 256);
+}
 
 // Everything the forward pass produces.  With AETHER_F_SAVE_FOR_BACKWARD each layer keeps its own
 // edge pre-activations; otherwise pre1 is shared and pre2 ping-pongs between two buffers.
@@ -38,6 +44,8 @@ struct Workspace {
   float *pre1[5], *pre2[5];
   float *pspr, *y[5], *pre3[5], *xl[5];
   float *o1, *o2, *pred;
+  // bf16 path: features [E,64] (hi|lo), pre-activations [E,H] bf16, packed weight images per layer
+  void* feat16; void *bpre1[5], *bpre2[5]; void *wpA[5], *wpB[5];
   size_t bytes;
 };
 
@@ -52,8 +60,22 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
   w.f = c.f(Nn * D);
   w.R = c.f(Nn * D * D);
   w.x0 = c.f(Nn * 3 * D);
-  w.feat = c.f(E * edge_feat_ld(d.num_dims));
   w.pre1[0] = w.pre2[0] = nullptr;
+  w.feat = nullptr; w.feat16 = nullptr;
+  for (int l = 0; l <= 4; ++l) { w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr; }
+  if (use_tc(d, flags)) {
+    w.feat16 = c.b(E * 64 * 2);
+    if (save) {
+      for (int l = 1; l <= 4; ++l) { w.bpre1[l] = c.b(E * H * 2); w.bpre2[l] = c.b(E * H * 2); }
+    } else {
+      void* p1 = c.b(E * H * 2);
+      void* a = c.b(E * H * 2);
+      void* b = c.b(E * H * 2);
+      for (int l = 1; l <= 4; ++l) { w.bpre1[l] = p1; w.bpre2[l] = (l & 1) ? a : b; }
+    }
+    for (int l = 1; l <= 4; ++l) { w.wpA[l] = c.b(tc_weight_pack_bytes(l == 1 ? 64 : H, H)); w.wpB[l] = c.b(tc_weight_pack_bytes(H, H)); }
+  } else {
+  w.feat = c.f(E * edge_feat_ld(d.num_dims));
   if (save) {
     for (int l = 1; l <= 4; ++l) { w.pre1[l] = c.f(E * H); w.pre2[l] = c.f(E * H); }
   } else {
@@ -61,6 +83,7 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
     float* a = c.f(E * H);
     float* b = c.f(E * H);
     for (int l = 1; l <= 4; ++l) { w.pre1[l] = p1; w.pre2[l] = (l & 1) ? a : b; }
+  }
   }
   w.pspr = c.f(Nn * 2 * H);
   w.y[0] = w.pre3[0] = nullptr;
@@ -78,16 +101,25 @@ struct Scratch {
   float *gx, *gx2, *gy, *gpre3, *gpspr, *gx0, *go1, *go2, *gpred, *gRglob, *ssend, *srecv;
   float *gf, *gfz1, *gfz2, *gfin, *gxin, *gvin;
   float* partial; size_t partial_floats;
+  // bf16 path: edge gradients [E,H] bf16 (ge, g2, g1), transposed weight images
+  void *bge, *bg2, *bg1; void *wtA, *wtB;
   size_t bytes;
 };
 
-size_t partial_need(const AetherDims& d) {
+size_t partial_need(const AetherDims& d, uint32_t flags) {
   const int64_t Nn = d.n_nodes, E = d.n_edges;
   const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D);
   size_t m = 0;
   auto up = [&](size_t v) { if (v > m) m = v; };
+  if (use_tc(d, flags)) {
+    up(tc_wgrad_partial_floats(H, H));
+    up(tc_wgrad_partial_floats(H, 64));
+    up(colsum_bf16_partial_floats(E, H));
+  } else {
   up(gemm_tn_partial_floats(H, H, E));
   up(gemm_tn_partial_floats(H, Fe, E));
+  up(colsum_partial_floats(E, H));
+  }
   up(gemm_tn_partial_floats(2 * H, H, Nn));
   up(gemm_tn_partial_floats(H, 2 * H, Nn));
   up(gemm_tn_partial_floats(H, H, Nn));
@@ -96,7 +128,6 @@ size_t partial_need(const AetherDims& d) {
   up(gemm_tn_partial_floats(32, 2 * D + 16, Nn));
   up(gemm_tn_partial_floats(32, 32, Nn));
   up(gemm_tn_partial_floats(D, 32, Nn));
-  up(colsum_partial_floats(E, H));
   up(colsum_partial_floats(Nn, 2 * H));
   return m + 64;
 }
@@ -105,9 +136,17 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   Scratch s;
   Carver c(base);
   const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
-  s.gA = c.f(E * H);
-  s.gB = c.f(E * H);
-  s.gfeat = c.f(E * edge_feat_ld(d.num_dims));
+  s.gA = s.gB = nullptr;
+  s.bge = s.bg2 = s.bg1 = s.wtA = s.wtB = nullptr;
+  if (use_tc(d, flags)) {
+    s.bge = c.b(E * H * 2); s.bg2 = c.b(E * H * 2); s.bg1 = c.b(E * H * 2);
+    s.wtA = c.b(tc_weight_pack_bytes(H, H)); s.wtB = c.b(tc_weight_pack_bytes(H, H));
+    s.gfeat = c.f(E * 32);
+  } else {
+    s.gA = c.f(E * H);
+    s.gB = c.f(E * H);
+    s.gfeat = c.f(E * edge_feat_ld(d.num_dims));
+  }
   s.gsend = c.f(E * geom_gs(d.num_dims));
   s.grecv = c.f(E * geom_gr(d.num_dims));
   s.gx = c.f(Nn * H); s.gx2 = c.f(Nn * H); s.gy = c.f(Nn * H);
@@ -117,10 +156,9 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   s.ssend = c.f(Nn * geom_gs(d.num_dims)); s.srecv = c.f(Nn * geom_gr(d.num_dims));
   s.gf = c.f(Nn * D); s.gfz1 = c.f(Nn * 32); s.gfz2 = c.f(Nn * 32); s.gfin = c.f(Nn * (2 * D + 16));
   s.gxin = c.f(Nn * D); s.gvin = c.f(Nn * D);
-  s.partial_floats = partial_need(d);
+  s.partial_floats = partial_need(d, flags);
   s.partial = c.f(s.partial_floats);
   s.bytes = c.off;
-  (void)flags;
   return s;
 }
 
@@ -143,7 +181,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
             cudaStream_t st) {
   const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D), ldf = edge_feat_ld(D);
   const int64_t Nn = d.n_nodes, E = d.n_edges;
-  const bool bf16 = flags & AETHER_F_BF16_EDGE_MLP;
+  const bool bf16 = use_tc(d, flags);
   // neural field at the particles (aether.py:127-134)
   AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
   AE_CHECK(linear(w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
@@ -154,7 +192,18 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
   {
     ProfScope ps(PROF_EDGE_FEAT, st);
-    AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
+    if (bf16) AE_CHECK(launch_edge_features_hilo(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat16, st));
+    else AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
+  }
+  if (bf16) {
+    // bf16 shared-memory images of the edge-MLP weights (first Linear: per-edge block only; layer 1: the
+    // feature columns repeated for the hi and lo halves of the operand)
+    AE_CHECK(tc_pack_weight(P[P_L1_M0_W], Fe, H, 64, H, Fe, 0, 32, w.wpA[1], st));
+    for (int l = 1; l <= 4; ++l) {
+      const LayerSlots s = layer_slots(l);
+      if (l > 1) AE_CHECK(tc_pack_weight(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 0, 0, w.wpA[l], st));
+      AE_CHECK(tc_pack_weight(P[s.m2w], H, H, H, H, H, 0, 0, w.wpB[l], st));
+    }
   }
   // four message-passing layers (locs.py:187-190, 227-243)
   for (int l = 1; l <= 4; ++l) {
@@ -165,16 +214,19 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       AE_CHECK(linear(xin, H, Nn, H, P[s.m0w], 3 * H, nullptr, H, w.pspr, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
       AE_CHECK(linear(xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
     }
-    bool done = false;
     {
     ProfScope ps(PROF_EDGE_MLP_FWD, st);
     if (bf16) {
-      int rc = edge_mlp_tc_forward(d, l, l == 1 ? w.feat : w.pre2[l - 1], l == 1 ? ldf : H, P[s.m0w], P[s.m0b],
-                                   P[s.m2w], P[s.m2b], w.pspr, G.send, G.recv, w.pre1[l], w.pre2[l], st);
-      if (rc == 0) done = true;
-      else if (rc != AETHER_E_UNSUPPORTED) return rc;
-    }
-    if (!done) {
+      // pre1 = [silu(pre2_{l-1}) | feat] We^T + b1 (+ P_s[send] + P_r[recv]) ; pre2 = silu(pre1) W2^T + b2
+      TcGemmArgs a;
+      a.M = E; a.wpack = w.wpA[l]; a.bias = P[s.m0b]; a.out_bf16 = (__nv_bfloat16*)w.bpre1[l]; a.ldo = H;
+      if (l > 1) { a.gat = w.pspr; a.ldg = 2 * H; a.idx_a = G.send; a.idx_b = G.recv; a.goff_b = H; }
+      if (l == 1) AE_CHECK(tc_gemm(a, w.feat16, 64, 64, H, TC_TF_NONE, st));
+      else AE_CHECK(tc_gemm(a, w.bpre2[l - 1], H, H, H, TC_TF_SILU, st));
+      TcGemmArgs b;
+      b.M = E; b.wpack = w.wpB[l]; b.bias = P[s.m2b]; b.out_bf16 = (__nv_bfloat16*)w.bpre2[l]; b.ldo = H;
+      AE_CHECK(tc_gemm(b, w.bpre1[l], H, H, H, TC_TF_SILU, st));
+    } else {
       GemmArgs g;
       if (l == 1) {
         g.A = w.feat; g.lda = ldf; g.K = Fe; g.B = P[s.m0w]; g.ldb = Fe; g.tf = TF_NONE;
@@ -196,7 +248,8 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     }
     {
       ProfScope ps(PROF_SEGMENT, st);
-      AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
+      if (bf16) AE_CHECK(launch_segmean_silu_bf16(Nn, H, G.rowptr, w.bpre2[l], H, base, H, w.y[l], H, st));
+      else AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
     }
     // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
     AE_CHECK(linear(w.y[l], H, Nn, H, P[s.u0w], H, P[s.u0b], 2 * H, w.pre3[l], 2 * H, TF_NONE, nullptr, nullptr, 0, st));

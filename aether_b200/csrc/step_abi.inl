@@ -73,6 +73,18 @@ __global__ void strided_copy_kernel(const float* __restrict__ src, int64_t lds, 
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < (size_t)rows * cols) dst[i] = src[(i / cols) * lds + i % cols];
 }
+__global__ void silu_copy_bf16_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n, int apply) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { const float v = __bfloat162float(src[i]); dst[i] = apply ? silu_f(v) : v; }
+}
+// feat16 [E, 64] = [hi(32) | lo(32)] -> fp32 [E, Fe]
+__global__ void hilo_copy_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int64_t rows, int cols) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (size_t)rows * cols) {
+    const size_t r = i / cols, c = i % cols;
+    dst[i] = __bfloat162float(src[r * 64 + c]) + __bfloat162float(src[r * 64 + 32 + c]);
+  }
+}
 __global__ void sub_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ c, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) c[i] = a[i] - b[i];
@@ -115,11 +127,19 @@ extern "C" int64_t aether_debug_stage(const AetherDims* dims, const void* worksp
     const int Fe = num_edge_feat(D);
     n = E * Fe;
     if (dst_floats < n) return AETHER_E_WORKSPACE;
-    if (n) strided_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w.feat, edge_feat_ld(D), dst, E, Fe);
+    if (n && w.feat16) hilo_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)w.feat16, dst, E, Fe);
+    else if (n) strided_copy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(w.feat, edge_feat_ld(D), dst, E, Fe);
     return cudaPeekAtLastError() == cudaSuccess ? n : AETHER_E_BADARG;
   } else if ((stage[0] == 'e' || stage[0] == 'x') && stage[1] >= '1' && stage[1] <= '4' && !stage[2]) {
     const int l = stage[1] - '0';
-    if (stage[0] == 'e') { src = w.pre2[l]; n = E * H; silu = 1; }
+    if (stage[0] == 'e') {
+      src = w.pre2[l]; n = E * H; silu = 1;
+      if (w.bpre2[l]) {
+        if (dst_floats < n) return AETHER_E_WORKSPACE;
+        if (n) silu_copy_bf16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const __nv_bfloat16*)w.bpre2[l], dst, (size_t)n, 1);
+        return cudaPeekAtLastError() == cudaSuccess ? n : AETHER_E_BADARG;
+      }
+    }
     else { src = w.xl[l]; n = Nn * H; }
   } else return AETHER_E_BADARG;
   if (dst_floats < n) return AETHER_E_WORKSPACE;

@@ -38,7 +38,6 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   const Bwd b{d, P, G, s, st};
   const float* m1 = dmask;
   const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
-  (void)flags;
 
   // out = x + R pred
   AE_CHECK(launch_globalize_bwd(D, Nn, w.R, w.pred, gout, s.gpred, s.gRglob, st));
@@ -52,6 +51,9 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   float* gxn = s.gx2;    // ... and the next one down
   AE_CHECK(b.dgrad(s.go1, H, Nn, H, P[P_OUT0_W], H, H, gx, H, nullptr, nullptr, nullptr, 0));
   const float* ge = nullptr;   // gradient w.r.t. e_l from layer l+1 (none for the last layer)
+  const bool tc = use_tc(d, flags);
+  bool have_ge = false;
+  const int ldgf = tc ? 32 : ldf;   // leading dimension of gfeat
 
   for (int l = 4; l >= 1; --l) {
     const LayerSlots sl = layer_slots(l);
@@ -61,35 +63,92 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
     AE_CHECK(b.wgrad(s.gpre3, 2 * H, Nn, 2 * H, w.y[l], H, H, TF_NONE, nullptr, G[sl.u0w], H, G[sl.u0b]));
     AE_CHECK(b.dgrad(s.gpre3, 2 * H, Nn, 2 * H, P[sl.u0w], H, H, s.gy, H, nullptr, nullptr, gx, 0));
     // y = base + mean_recv(silu(pre2)) : broadcast gy / deg over the segment, add grad from layer l+1
-    float* g2 = s.gA;
-    float* g1 = s.gB;
-    {
-      ProfScope ps(PROF_EDGE_BWD_DATA, st);
-      AE_CHECK(launch_edge_dpre2(E, H, Gr.recv, Gr.rowptr, ge, s.gy, w.pre2[l], g2, st));
-      // pre2 = W2 silu(pre1) + b2
-      AE_CHECK(b.dgrad(g2, H, E, H, P[sl.m2w], H, H, g1, H, w.pre1[l], nullptr, nullptr, 0));
-    }
-    {
-      ProfScope ps(PROF_EDGE_WGRAD, st);
-      AE_CHECK(b.wgrad(g2, H, E, H, w.pre1[l], H, H, TF_SILU, nullptr, G[sl.m2w], H, G[sl.m2b]));
-      AE_CHECK(colsum_f32(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
-    }
-    if (l > 1) {
-      // pre1 = Ps[send] + Pr[recv] + We silu(pre2_{l-1}) + b1
-      {
-        ProfScope ps(PROF_EDGE_WGRAD, st);
-        AE_CHECK(b.wgrad(g1, H, E, H, w.pre2[l - 1], H, H, TF_SILU, nullptr, G[sl.m0w] + 2 * H, 3 * H, nullptr));
-      }
+    if (tc) {
+      // ---- bf16 tensor-core path: edge gradients stored as bf16, GEMMs on tcgen05 ----
+      void* g2 = s.bg2;
+      void* g1 = s.bg1;
       {
         ProfScope ps(PROF_EDGE_BWD_DATA, st);
-        AE_CHECK(b.dgrad(g1, H, E, H, P[sl.m0w] + 2 * H, 3 * H, H, s.gA, H, nullptr, nullptr, nullptr, 0));
+        // g2 = (ge + gy[recv]/deg) * silu'(pre2) ; g1 = (g2 W2) * silu'(pre1)
+        AE_CHECK(launch_edge_dpre2_bf16(E, H, Gr.recv, Gr.rowptr, have_ge ? s.bge : nullptr, s.gy, w.bpre2[l], g2, st));
+        AE_CHECK(tc_pack_weight(P[sl.m2w], H, H, H, H, H, 1, 0, s.wtB, st));
+        TcGemmArgs a;
+        a.M = E; a.wpack = s.wtB; a.dsilu = (const __nv_bfloat16*)w.bpre1[l]; a.ldd = H;
+        a.out_bf16 = (__nv_bfloat16*)g1; a.ldo = H;
+        AE_CHECK(tc_gemm(a, g2, H, H, H, TC_TF_NONE, st));
       }
-      ge = s.gA;
       {
-        ProfScope ps(PROF_SEGMENT, st);
-        AE_CHECK(launch_segsum(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, 0, st));
-        AE_CHECK(launch_segsum(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, 0, st));
+        ProfScope ps(PROF_EDGE_WGRAD, st);
+        AE_CHECK(tc_wgrad(g2, H, H, w.bpre1[l], H, H, TC_TF_SILU, E, G[sl.m2w], H, H, 0, s.partial, s.partial_floats, st));
+        AE_CHECK(colsum_bf16(g2, H, E, H, G[sl.m2b], s.partial, s.partial_floats, st));
+        AE_CHECK(colsum_bf16(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
+        if (l > 1)
+          AE_CHECK(tc_wgrad(g1, H, H, w.bpre2[l - 1], H, H, TC_TF_SILU, E, G[sl.m0w] + 2 * H, 3 * H, H, 0, s.partial,
+                            s.partial_floats, st));
+        else
+          AE_CHECK(tc_wgrad(g1, H, H, w.feat16, 64, 64, TC_TF_NONE, E, G[sl.m0w], Fe, Fe, 1, s.partial, s.partial_floats, st));
       }
+      if (l > 1) {
+        {
+          ProfScope ps(PROF_EDGE_BWD_DATA, st);
+          // ge_{l-1} = g1 We
+          AE_CHECK(tc_pack_weight(P[sl.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, s.wtA, st));
+          TcGemmArgs a;
+          a.M = E; a.wpack = s.wtA; a.out_bf16 = (__nv_bfloat16*)s.bge; a.ldo = H;
+          AE_CHECK(tc_gemm(a, g1, H, H, H, TC_TF_NONE, st));
+          have_ge = true;
+        }
+        {
+          ProfScope ps(PROF_SEGMENT, st);
+          AE_CHECK(launch_segsum_bf16(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, st));
+          AE_CHECK(launch_segsum_bf16(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, st));
+        }
+      } else {
+        // gfeat[E, 32] = g1 W1 (fp32, consumed by the geometry backward)
+        AE_CHECK(tc_pack_weight(P[sl.m0w], Fe, 32, H, Fe, H, 1, 0, s.wtA, st));
+        TcGemmArgs a;
+        a.M = E; a.wpack = s.wtA; a.out_f32 = s.gfeat; a.ldo32 = 32; a.n_valid = 32;
+        AE_CHECK(tc_gemm(a, g1, H, H, 32, TC_TF_NONE, st));
+      }
+    } else {
+      float* g2 = s.gA;
+      float* g1 = s.gB;
+      {
+        ProfScope ps(PROF_EDGE_BWD_DATA, st);
+        AE_CHECK(launch_edge_dpre2(E, H, Gr.recv, Gr.rowptr, ge, s.gy, w.pre2[l], g2, st));
+        // pre2 = W2 silu(pre1) + b2
+        AE_CHECK(b.dgrad(g2, H, E, H, P[sl.m2w], H, H, g1, H, w.pre1[l], nullptr, nullptr, 0));
+      }
+      {
+        ProfScope ps(PROF_EDGE_WGRAD, st);
+        AE_CHECK(b.wgrad(g2, H, E, H, w.pre1[l], H, H, TF_SILU, nullptr, G[sl.m2w], H, G[sl.m2b]));
+        AE_CHECK(colsum_f32(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
+      }
+      if (l > 1) {
+        // pre1 = Ps[send] + Pr[recv] + We silu(pre2_{l-1}) + b1
+        {
+          ProfScope ps(PROF_EDGE_WGRAD, st);
+          AE_CHECK(b.wgrad(g1, H, E, H, w.pre2[l - 1], H, H, TF_SILU, nullptr, G[sl.m0w] + 2 * H, 3 * H, nullptr));
+        }
+        {
+          ProfScope ps(PROF_EDGE_BWD_DATA, st);
+          AE_CHECK(b.dgrad(g1, H, E, H, P[sl.m0w] + 2 * H, 3 * H, H, s.gA, H, nullptr, nullptr, nullptr, 0));
+        }
+        ge = s.gA;
+        {
+          ProfScope ps(PROF_SEGMENT, st);
+          AE_CHECK(launch_segsum(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, 0, st));
+          AE_CHECK(launch_segsum(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, 0, st));
+        }
+      } else {
+        // pre1 = W1 feat + b1
+        AE_CHECK(b.wgrad(g1, H, E, H, w.feat, ldf, Fe, TF_NONE, nullptr, G[sl.m0w], Fe, nullptr));
+        GemmArgs g;
+        g.A = g1; g.lda = H; g.B = P[sl.m0w]; g.ldb = Fe; g.C = s.gfeat; g.ldc = ldf; g.M = E; g.N = Fe; g.K = H;
+        AE_CHECK(gemm_f32(GEMM_NN, g, st));
+      }
+    }
+    if (l > 1) {
       const float* xin = w.xl[l - 1];
       AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
       AE_CHECK(b.wgrad(s.gpspr + H, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w] + H, 3 * H, nullptr));
@@ -97,13 +156,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
       AE_CHECK(b.dgrad(s.gpspr + H, 2 * H, Nn, H, P[sl.m0w] + H, 3 * H, H, gxn, H, nullptr, nullptr, nullptr, 1));
       float* t = gx; gx = gxn; gxn = t;
     } else {
-      // pre1 = W1 feat + b1 ; y1 = Wres x0 + bres + agg
-      AE_CHECK(b.wgrad(g1, H, E, H, w.feat, ldf, Fe, TF_NONE, nullptr, G[sl.m0w], Fe, nullptr));
-      {
-        GemmArgs g;
-        g.A = g1; g.lda = H; g.B = P[sl.m0w]; g.ldb = Fe; g.C = s.gfeat; g.ldc = ldf; g.M = E; g.N = Fe; g.K = H;
-        AE_CHECK(gemm_f32(GEMM_NN, g, st));
-      }
+      // y1 = Wres x0 + bres + agg
       AE_CHECK(b.wgrad(s.gy, H, Nn, H, w.x0, 3 * D, 3 * D, TF_NONE, nullptr, G[P_L1_RES_W], 3 * D, G[P_L1_RES_B]));
       AE_CHECK(b.dgrad(s.gy, H, Nn, H, P[P_L1_RES_W], 3 * D, 3 * D, s.gx0, 3 * D, nullptr, nullptr, nullptr, 0));
     }
@@ -111,7 +164,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
 
   // localizer: per-edge partials, then segment sums by receiver (contiguous) and by sender (sperm)
   const int GS = geom_gs(D), GR = geom_gr(D);
-  AE_CHECK(launch_edge_features_bwd(D, E, Gr.send, Gr.recv, x, vel, w.f, w.R, s.gfeat, ldf, s.gsend, s.grecv, st));
+  AE_CHECK(launch_edge_features_bwd(D, E, Gr.send, Gr.recv, x, vel, w.f, w.R, s.gfeat, ldgf, s.gsend, s.grecv, st));
   AE_CHECK(launch_segsum(Nn, GS, Gr.colptr, Gr.sperm, s.gsend, GS, s.ssend, GS, 0, st));
   AE_CHECK(launch_segsum(Nn, GR, Gr.rowptr, nullptr, s.grecv, GR, s.srecv, GR, 0, st));
   float* gxin = gx_out ? gx_out : s.gxin;
