@@ -44,7 +44,7 @@ __global__ void segreduce_bf16_kernel(int64_t Nn, const int32_t* __restrict__ pt
     unpack8(u0, v0);
     unpack8(u1, v1);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s[i] += SILU ? silu_f(v0[i]) + silu_f(v1[i]) : v0[i] + v1[i];
+    for (int i = 0; i < 8; ++i) s[i] += SILU ? tc::silu_fast(v0[i]) + tc::silu_fast(v1[i]) : v0[i] + v1[i];
   }
   if (k < e) {
     const int64_t r0 = list ? list[k] : k;
@@ -52,7 +52,7 @@ __global__ void segreduce_bf16_kernel(int64_t Nn, const int32_t* __restrict__ pt
     float v0[8];
     unpack8(u0, v0);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s[i] += SILU ? silu_f(v0[i]) : v0[i];
+    for (int i = 0; i < 8; ++i) s[i] += SILU ? tc::silu_fast(v0[i]) : v0[i];
   }
 #pragma unroll
   for (int off = LPR; off < 32; off <<= 1)
@@ -99,7 +99,7 @@ __global__ void edge_dpre2_bf16_kernel(int64_t E, int H, const int32_t* __restri
   float z[8];
   unpack8(__ldg(reinterpret_cast<const uint4*>(pre2 + (size_t)k * H + c)), z);
 #pragma unroll
-  for (int q = 0; q < 8; ++q) o[q] *= dsilu_f(z[q]);
+  for (int q = 0; q < 8; ++q) o[q] *= tc::dsilu_fast(z[q]);
   uint4 w;
   w.x = tc::pack_bf16(o[0], o[1]); w.y = tc::pack_bf16(o[2], o[3]);
   w.z = tc::pack_bf16(o[4], o[5]); w.w = tc::pack_bf16(o[6], o[7]);

@@ -76,29 +76,26 @@ __global__ void edge_dpre2_kernel(int64_t E, int H, const int32_t* __restrict__ 
   *reinterpret_cast<float4*>(g + (size_t)k * H + c) = o;
 }
 
-// 3 rows x 16 columns; one block, thread (r, c) walks all nodes in order: deterministic.
-// Node counts here are small next to the edge work; 48 threads x Nn reads of L2-resident data.
+// gemb[r, c] = sum over nodes with class r of gfin[n, 2D + c].  One block of 1024 threads: thread (lane, c)
+// walks nodes lane, lane+64, ... keeping one sum per class; lanes are combined in a fixed order.
 __global__ void embedding_bwd_kernel(int D, int64_t Nn, const float* __restrict__ charges,
                                      const float* __restrict__ gfin, float* __restrict__ gemb) {
-  __shared__ float part[8][48];
-  const int t = threadIdx.x % 48, slice = threadIdx.x / 48;   // 8 slices x 48
-  const int r = t / 16, c = t % 16;
+  __shared__ float part[64][49];
+  const int c = threadIdx.x & 15, ln = threadIdx.x >> 4;   // 64 node lanes x 16 columns
   const int W = 2 * D + 16;
-  const int64_t per = (Nn + 7) / 8;
-  const int64_t n0 = slice * per, n1 = n0 + per < Nn ? n0 + per : Nn;
-  float s = 0.f;
-  for (int64_t n = n0; n < n1; ++n) {
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+  for (int64_t n = ln; n < Nn; n += 64) {
     long long idx = (long long)(charges[n] + 1.0f);
     idx = idx < 0 ? 0 : (idx > 2 ? 2 : idx);
-    if (idx == r) s += gfin[(size_t)n * W + 2 * D + c];
+    const float v = gfin[(size_t)n * W + 2 * D + c];
+    if (idx == 0) s0 += v; else if (idx == 1) s1 += v; else s2 += v;
   }
-  part[slice][t] = s;
+  part[ln][c] = s0; part[ln][16 + c] = s1; part[ln][32 + c] = s2;
   __syncthreads();
-  if (slice == 0) {
+  if (threadIdx.x < 48) {
     float a = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) a += part[i][t];
-    gemb[t] = a;
+    for (int i = 0; i < 64; ++i) a += part[i][threadIdx.x];
+    gemb[threadIdx.x] = a;
   }
 }
 
@@ -138,7 +135,7 @@ int launch_edge_dpre2(int64_t E, int H, const int32_t* recv, const int32_t* rowp
 }
 
 int launch_embedding_bwd(int D, int64_t Nn, const float* charges, const float* gfin, float* gemb, cudaStream_t st) {
-  embedding_bwd_kernel<<<1, 384, 0, st>>>(D, Nn, charges, gfin, gemb);
+  embedding_bwd_kernel<<<1, 1024, 0, st>>>(D, Nn, charges, gfin, gemb);
   AE_LAUNCH_CHECK();
   return 0;
 }

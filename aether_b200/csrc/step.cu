@@ -46,6 +46,7 @@ struct Workspace {
   float *o1, *o2, *pred;
   // bf16 path: features [E,64] (hi|lo), pre-activations [E,H] bf16, packed weight images per layer
   void* feat16; void *bpre1[5], *bpre2[5]; void *wpA[5], *wpB[5];
+  void *na16, *nwp;     // node-level tensor-core scratch: bf16 operand copy [Nn,256], weight image
   size_t bytes;
 };
 
@@ -61,9 +62,11 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
   w.R = c.f(Nn * D * D);
   w.x0 = c.f(Nn * 3 * D);
   w.pre1[0] = w.pre2[0] = nullptr;
-  w.feat = nullptr; w.feat16 = nullptr;
+  w.feat = nullptr; w.feat16 = nullptr; w.na16 = w.nwp = nullptr;
   for (int l = 0; l <= 4; ++l) { w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr; }
   if (use_tc(d, flags)) {
+    w.na16 = c.b(Nn * 256 * 2);
+    w.nwp = c.b(tc_weight_pack_bytes(256, 256));
     w.feat16 = c.b(E * 64 * 2);
     if (save) {
       for (int l = 1; l <= 4; ++l) { w.bpre1[l] = c.b(E * H * 2); w.bpre2[l] = c.b(E * H * 2); }
@@ -103,6 +106,7 @@ struct Scratch {
   float* partial; size_t partial_floats;
   // bf16 path: edge gradients [E,H] bf16 (ge, g2, g1), transposed weight images
   void *bge, *bg2, *bg1; void *wtA, *wtB;
+  void *na16, *ng16, *nwp;
   size_t bytes;
 };
 
@@ -112,7 +116,8 @@ size_t partial_need(const AetherDims& d, uint32_t flags) {
   size_t m = 0;
   auto up = [&](size_t v) { if (v > m) m = v; };
   if (use_tc(d, flags)) {
-    up(tc_wgrad_partial_floats(H, H));
+    const int c2 = 2 * H > 256 ? 256 : 2 * H;
+    up(tc_wgrad_partial_floats(c2, c2));
     up(tc_wgrad_partial_floats(H, 64));
     up(colsum_bf16_partial_floats(E, H));
   } else {
@@ -138,7 +143,9 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
   s.gA = s.gB = nullptr;
   s.bge = s.bg2 = s.bg1 = s.wtA = s.wtB = nullptr;
+  s.na16 = s.ng16 = s.nwp = nullptr;
   if (use_tc(d, flags)) {
+    s.na16 = c.b(Nn * 256 * 2); s.ng16 = c.b(Nn * 256 * 2); s.nwp = c.b(tc_weight_pack_bytes(256, 256));
     s.bge = c.b(E * H * 2); s.bg2 = c.b(E * H * 2); s.bg1 = c.b(E * H * 2);
     s.wtA = c.b(tc_weight_pack_bytes(H, H)); s.wtB = c.b(tc_weight_pack_bytes(H, H));
     s.gfeat = c.f(E * 32);
@@ -167,9 +174,17 @@ bool dims_ok(const AetherDims* d) {
          d->n_edges >= 0 && d->n_nodes < ((int64_t)1 << 31) && d->n_edges < ((int64_t)1 << 31);
 }
 
+}  // namespace
+}  // namespace aether
+#include "step_node_tc.inl"
+namespace aether {
+namespace {
+
 // y = epi(tf(A) W^T + b)
-int linear(const float* A, int64_t lda, int64_t M, int K, const float* W, int64_t ldw, const float* b, int N, float* C,
-           int64_t ldc, int tf, const float* mask, const float* res, int64_t ldr, cudaStream_t st) {
+int linear(const NodeTc& nc, const float* A, int64_t lda, int64_t M, int K, const float* W, int64_t ldw, const float* b,
+           int N, float* C, int64_t ldc, int tf, const float* mask, const float* res, int64_t ldr, cudaStream_t st) {
+  const int rc = linear_tc(nc, A, lda, M, K, W, ldw, b, N, C, ldc, tf, mask, res, ldr, st);
+  if (rc != AETHER_E_UNSUPPORTED) return rc;
   GemmArgs g;
   g.A = A; g.lda = lda; g.B = W; g.ldb = ldw; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
   g.tf = tf; g.tf_mask = mask; g.bias = b; g.res = res; g.ldr = ldr;
@@ -182,12 +197,14 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D), ldf = edge_feat_ld(D);
   const int64_t Nn = d.n_nodes, E = d.n_edges;
   const bool bf16 = use_tc(d, flags);
+  NodeTc nc;
+  nc.on = bf16; nc.a16 = w.na16; nc.wp = w.nwp;
   // neural field at the particles (aether.py:127-134)
   AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
-  AE_CHECK(linear(w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
+  AE_CHECK(linear(nc, w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
                   nullptr, 0, st));
-  AE_CHECK(linear(w.fz1, 32, Nn, 32, P[P_F2_W], 32, P[P_F2_B], 32, w.fz2, 32, TF_SILU, nullptr, nullptr, 0, st));
-  AE_CHECK(linear(w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
+  AE_CHECK(linear(nc, w.fz1, 32, Nn, 32, P[P_F2_W], 32, P[P_F2_B], 32, w.fz2, 32, TF_SILU, nullptr, nullptr, 0, st));
+  AE_CHECK(linear(nc, w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
   // local frames and features (aether.py:33-100,177)
   AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
   {
@@ -211,8 +228,8 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     const float* xin = w.xl[l - 1];
     if (l > 1) {
       // node-factorised first Linear: [x_s | x_r | e] W^T = x_s Ws^T + x_r Wr^T + e We^T
-      AE_CHECK(linear(xin, H, Nn, H, P[s.m0w], 3 * H, nullptr, H, w.pspr, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
-      AE_CHECK(linear(xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+      AE_CHECK(linear(nc, xin, H, Nn, H, P[s.m0w], 3 * H, nullptr, H, w.pspr, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+      AE_CHECK(linear(nc, xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
     }
     {
     ProfScope ps(PROF_EDGE_MLP_FWD, st);
@@ -236,13 +253,13 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       }
       g.C = w.pre1[l]; g.ldc = H; g.M = E; g.N = H; g.bias = P[s.m0b];
       AE_CHECK(gemm_f32(GEMM_NT, g, st));
-      AE_CHECK(linear(w.pre1[l], H, E, H, P[s.m2w], H, P[s.m2b], H, w.pre2[l], H, TF_SILU, nullptr, nullptr, 0, st));
+      AE_CHECK(linear(nc, w.pre1[l], H, E, H, P[s.m2w], H, P[s.m2b], H, w.pre2[l], H, TF_SILU, nullptr, nullptr, 0, st));
     }
     }
     // y = res(x) + mean_recv(silu(pre2))   (locs.py:236-240)
     const float* base = xin;
     if (l == 1) {
-      AE_CHECK(linear(w.x0, 3 * D, Nn, 3 * D, P[P_L1_RES_W], 3 * D, P[P_L1_RES_B], H, w.y[1], H, TF_NONE, nullptr,
+      AE_CHECK(linear(nc, w.x0, 3 * D, Nn, 3 * D, P[P_L1_RES_W], 3 * D, P[P_L1_RES_B], H, w.y[1], H, TF_NONE, nullptr,
                       nullptr, 0, st));
       base = w.y[1];
     }
@@ -252,15 +269,15 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       else AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
     }
     // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
-    AE_CHECK(linear(w.y[l], H, Nn, H, P[s.u0w], H, P[s.u0b], 2 * H, w.pre3[l], 2 * H, TF_NONE, nullptr, nullptr, 0, st));
-    AE_CHECK(linear(w.pre3[l], 2 * H, Nn, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, w.xl[l], H, TF_SILU, nullptr, w.y[l], H, st));
+    AE_CHECK(linear(nc, w.y[l], H, Nn, H, P[s.u0w], H, P[s.u0b], 2 * H, w.pre3[l], 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+    AE_CHECK(linear(nc, w.pre3[l], 2 * H, Nn, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, w.xl[l], H, TF_SILU, nullptr, w.y[l], H, st));
   }
   // out MLP (locs.py:160-168,193), globalize and Euler update (local_to_global.py:12-13, aether.py:185)
   const float* m1 = dmask;
   const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
-  AE_CHECK(linear(w.xl[4], H, Nn, H, P[P_OUT0_W], H, P[P_OUT0_B], H, w.o1, H, TF_NONE, nullptr, nullptr, 0, st));
-  AE_CHECK(linear(w.o1, H, Nn, H, P[P_OUT3_W], H, P[P_OUT3_B], H, w.o2, H, m1 ? TF_SILU_MASK : TF_SILU, m1, nullptr, 0, st));
-  AE_CHECK(linear(w.o2, H, Nn, H, P[P_OUT6_W], H, P[P_OUT6_B], D, w.pred, D, m2 ? TF_SILU_MASK : TF_SILU, m2, nullptr, 0, st));
+  AE_CHECK(linear(nc, w.xl[4], H, Nn, H, P[P_OUT0_W], H, P[P_OUT0_B], H, w.o1, H, TF_NONE, nullptr, nullptr, 0, st));
+  AE_CHECK(linear(nc, w.o1, H, Nn, H, P[P_OUT3_W], H, P[P_OUT3_B], H, w.o2, H, m1 ? TF_SILU_MASK : TF_SILU, m1, nullptr, 0, st));
+  AE_CHECK(linear(nc, w.o2, H, Nn, H, P[P_OUT6_W], H, P[P_OUT6_B], D, w.pred, D, m2 ? TF_SILU_MASK : TF_SILU, m2, nullptr, 0, st));
   AE_CHECK(launch_globalize(D, Nn, x, w.R, w.pred, out, st));
   return 0;
 }

@@ -7,11 +7,17 @@ namespace aether {
 namespace {
 
 struct Bwd {
-  const AetherDims& d; const float* const* P; float* const* G; const Scratch& s; cudaStream_t st;
+  const AetherDims& d; const float* const* P; float* const* G; const Scratch& s; cudaStream_t st; NodeTc nc;
 
   // dW[N_out, K_in] = gy^T act(a)   ;   db = colsum(gy)
   int wgrad(const float* gy, int64_t ldgy, int64_t rows, int n_out, const float* a, int64_t lda, int k_in, int tf,
             const float* mask, float* dW, int64_t lddw, float* db) const {
+    const int rc = wgrad_tc(nc, gy, ldgy, rows, n_out, a, lda, k_in, tf, mask, dW, lddw, st);
+    if (rc != AETHER_E_UNSUPPORTED) {
+      if (rc != 0) return rc;
+      if (db) AE_CHECK(colsum_f32(gy, ldgy, rows, n_out, db, s.partial, s.partial_floats, st));
+      return 0;
+    }
     GemmArgs g;
     g.A = gy; g.lda = ldgy; g.B = a; g.ldb = lda; g.C = dW; g.ldc = lddw; g.M = n_out; g.N = k_in; g.K = rows;
     g.tf = tf; g.tf_mask = mask; g.partial = s.partial; g.partial_floats = s.partial_floats;
@@ -22,6 +28,8 @@ struct Bwd {
   // gx[rows, K_in] = epi(gy W)    W is [N_out, K_in] with leading dimension ldw
   int dgrad(const float* gy, int64_t ldgy, int64_t rows, int n_out, const float* W, int64_t ldw, int k_in, float* gx,
             int64_t ldgx, const float* dsilu_src, const float* mask, const float* res, int accumulate) const {
+    const int rc = dgrad_tc(nc, gy, ldgy, rows, n_out, W, ldw, k_in, gx, ldgx, dsilu_src, mask, res, accumulate, st);
+    if (rc != AETHER_E_UNSUPPORTED) return rc;
     GemmArgs g;
     g.A = gy; g.lda = ldgy; g.B = W; g.ldb = ldw; g.C = gx; g.ldc = ldgx; g.M = rows; g.N = k_in; g.K = n_out;
     g.dsilu = dsilu_src; g.ldd = ldgx; g.emask = mask; g.ldm = ldgx; g.res = res; g.ldr = ldgx;
@@ -35,7 +43,10 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
              const Workspace& w, const Scratch& s, uint32_t flags, cudaStream_t st) {
   const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D), ldf = edge_feat_ld(D);
   const int64_t Nn = d.n_nodes, E = d.n_edges;
-  const Bwd b{d, P, G, s, st};
+  NodeTc nc;
+  nc.on = use_tc(d, flags); nc.a16 = s.na16; nc.g16 = s.ng16; nc.wp = s.nwp; nc.partial = s.partial;
+  nc.partial_floats = s.partial_floats;
+  const Bwd b{d, P, G, s, st, nc};
   const float* m1 = dmask;
   const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
 

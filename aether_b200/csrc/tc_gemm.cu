@@ -195,6 +195,38 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
             }
           }
         }
+        if (g.res) {
+          const float4* pr = reinterpret_cast<const float4*>(g.res + (size_t)row * g.ldr + j * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 a = pr[q];
+            v[4 * q] += a.x; v[4 * q + 1] += a.y; v[4 * q + 2] += a.z; v[4 * q + 3] += a.w;
+          }
+        }
+        if (g.dsilu32) {
+          const float4* pz = reinterpret_cast<const float4*>(g.dsilu32 + (size_t)row * g.ldd32 + j * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 z = __ldg(pz + q);
+            v[4 * q] *= dsilu_f(z.x); v[4 * q + 1] *= dsilu_f(z.y); v[4 * q + 2] *= dsilu_f(z.z); v[4 * q + 3] *= dsilu_f(z.w);
+          }
+        }
+        if (g.emask) {
+          const float4* pm = reinterpret_cast<const float4*>(g.emask + (size_t)row * g.ldm + j * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 z = __ldg(pm + q);
+            v[4 * q] *= z.x; v[4 * q + 1] *= z.y; v[4 * q + 2] *= z.z; v[4 * q + 3] *= z.w;
+          }
+        }
+        if (g.accumulate) {
+          const float4* pc = reinterpret_cast<const float4*>(g.out_f32 + (size_t)row * g.ldo32 + j * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 a = pc[q];
+            v[4 * q] += a.x; v[4 * q + 1] += a.y; v[4 * q + 2] += a.z; v[4 * q + 3] += a.w;
+          }
+        }
         if (g.out_bf16) {
           uint4* po = reinterpret_cast<uint4*>(g.out_bf16 + (size_t)row * g.ldo + j * 32);
 #pragma unroll
@@ -256,6 +288,27 @@ __global__ void pack_weight_kernel(const float* __restrict__ W, int64_t ldw, int
   const int c = kb / 8, j = kb % 8;
   const size_t off = (size_t)c * N * 128 + (size_t)n * 128 + (size_t)((j ^ (n & 7)) * 16);
   *reinterpret_cast<uint4*>(out + off) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+__global__ void convert_bf16_kernel(const float* __restrict__ A, int64_t lda, int64_t M, int cols, int tf,
+                                    const float* __restrict__ mask, __nv_bfloat16* __restrict__ out, int64_t ldo) {
+  const int cq = cols / 4;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= M * cq) return;
+  const int64_t m = i / cq;
+  const int c = (int)(i % cq) * 4;
+  float4 v = *reinterpret_cast<const float4*>(A + (size_t)m * lda + c);
+  if (tf != TF_NONE) {
+    v.x = silu_f(v.x); v.y = silu_f(v.y); v.z = silu_f(v.z); v.w = silu_f(v.w);
+    if (tf == TF_SILU_MASK) {
+      const float4 k = *reinterpret_cast<const float4*>(mask + (size_t)m * lda + c);
+      v.x *= k.x; v.y *= k.y; v.z *= k.z; v.w *= k.w;
+    }
+  }
+  uint2 o;
+  o.x = pack_bf16(v.x, v.y);
+  o.y = pack_bf16(v.z, v.w);
+  *reinterpret_cast<uint2*>(out + (size_t)m * ldo + c) = o;
 }
 
 template <int K, int N>
@@ -326,6 +379,16 @@ int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k
   return 0;
 }
 
+int tc_convert_bf16(const float* A, int64_t lda, int64_t M, int cols, int tf, const float* mask, void* out, int64_t ldo,
+                    cudaStream_t st) {
+  if (M <= 0 || cols <= 0) return 0;
+  if (cols % 4 || lda % 4 || ldo % 4 || ((uintptr_t)A & 15)) return AETHER_E_BADARG;
+  const int64_t tot = M * (cols / 4);
+  convert_bf16_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(A, lda, M, cols, tf, mask, (__nv_bfloat16*)out, ldo);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
 bool tc_gemm_supported(int K, int N) {
   return (K == 64 || K == 128 || K == 256) && (N == 32 || N == 64 || N == 128 || N == 256);
 }
@@ -339,6 +402,7 @@ int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int t
   AE_TC_CASE(256, 256) AE_TC_CASE(256, 32) AE_TC_CASE(64, 256)
   AE_TC_CASE(128, 128) AE_TC_CASE(128, 32) AE_TC_CASE(64, 128)
   AE_TC_CASE(64, 64) AE_TC_CASE(64, 32)
+  AE_TC_CASE(128, 256) AE_TC_CASE(256, 128) AE_TC_CASE(128, 64) AE_TC_CASE(256, 64)
 #undef AE_TC_CASE
   return AETHER_E_UNSUPPORTED;
 }

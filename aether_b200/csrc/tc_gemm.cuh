@@ -16,6 +16,11 @@ struct TcGemmArgs {
   const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int goff_b = 0;
   // * silu'(dsilu[m*ldd + n])
   const __nv_bfloat16* dsilu = nullptr; int64_t ldd = 0;
+  // node-level (fp32) epilogue terms, applied in this order after the ones above:
+  const float* res = nullptr; int64_t ldr = 0;            // + res[m*ldr + n]
+  const float* dsilu32 = nullptr; int64_t ldd32 = 0;      // * silu'(dsilu32[m*ldd32 + n])
+  const float* emask = nullptr; int64_t ldm = 0;          // * emask[m*ldm + n]
+  int accumulate = 0;                                     // out_f32 += result
   __nv_bfloat16* out_bf16 = nullptr; int64_t ldo = 0;
   float* out_f32 = nullptr; int64_t ldo32 = 0; int n_valid = 0;   // fp32 output writes columns < n_valid
 };
@@ -28,6 +33,11 @@ int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k
                    void* out, cudaStream_t st);
 // out = epi(tf(A) B^T); A is bf16 [M, K] with leading dimension lda (elements)
 int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int tf, cudaStream_t st);
+
+// fp32 [M, cols] (leading dimension lda) -> bf16 [M, cols] (leading dimension ldo), optionally through
+// SiLU (tf = TF_SILU) and a dropout mask (TF_SILU_MASK, mask has the layout of A)
+int tc_convert_bf16(const float* A, int64_t lda, int64_t M, int cols, int tf, const float* mask, void* out, int64_t ldo,
+                    cudaStream_t st);
 
 // dW[MG, NA] = sum_e G[e, :]^T tf(ACT[e, :]) over E rows; both operands bf16 row-major.
 // partial: tc_wgrad_partial_floats(MG, NA) floats of scratch.  fold32: dW[m][j] = P[m][j] + P[m][32+j]

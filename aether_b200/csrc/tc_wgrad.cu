@@ -230,6 +230,7 @@ int tc_wgrad(const void* G, int64_t ldg, int MG, const void* ACT, int64_t lda, i
     int rc = AETHER_E_UNSUPPORTED;
 #define AE_WG_CASE(MM, NN) if (MG == MM && NA == NN) rc = launch_wg<MM, NN>(tg, ta, tf, n_stages, grid, partial, st);
     AE_WG_CASE(256, 256) AE_WG_CASE(256, 64) AE_WG_CASE(128, 128) AE_WG_CASE(128, 64) AE_WG_CASE(64, 64)
+    AE_WG_CASE(256, 128) AE_WG_CASE(128, 256) AE_WG_CASE(64, 128) AE_WG_CASE(64, 256)
 #undef AE_WG_CASE
     if (rc != 0) return rc;
   }
