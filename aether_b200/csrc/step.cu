@@ -47,6 +47,7 @@ struct Workspace {
   // bf16 path: features [E,64] (hi|lo), pre-activations [E,H] bf16, packed weight images per layer
   void* feat16; void *bpre1[5], *bpre2[5]; void *wpA[5], *wpB[5];
   void *na16, *nwp;     // node-level tensor-core scratch: bf16 operand copy [Nn,256], weight image
+  void* pspr16;         // [Nn, 2H] bf16 node terms P_s | P_r of the factorised first Linear
   size_t bytes;
 };
 
@@ -62,11 +63,12 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
   w.R = c.f(Nn * D * D);
   w.x0 = c.f(Nn * 3 * D);
   w.pre1[0] = w.pre2[0] = nullptr;
-  w.feat = nullptr; w.feat16 = nullptr; w.na16 = w.nwp = nullptr;
+  w.feat = nullptr; w.feat16 = nullptr; w.na16 = w.nwp = w.pspr16 = nullptr;
   for (int l = 0; l <= 4; ++l) { w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr; }
   if (use_tc(d, flags)) {
     w.na16 = c.b(Nn * 256 * 2);
     w.nwp = c.b(tc_weight_pack_bytes(256, 256));
+    w.pspr16 = c.b(Nn * 2 * H * 2);
     w.feat16 = c.b(E * 64 * 2);
     if (save) {
       for (int l = 1; l <= 4; ++l) { w.bpre1[l] = c.b(E * H * 2); w.bpre2[l] = c.b(E * H * 2); }
@@ -228,8 +230,13 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     const float* xin = w.xl[l - 1];
     if (l > 1) {
       // node-factorised first Linear: [x_s | x_r | e] W^T = x_s Ws^T + x_r Wr^T + e We^T
+      if (bf16) {
+        AE_CHECK(linear_tc_bf16out(nc, xin, H, Nn, H, P[s.m0w], 3 * H, H, w.pspr16, 2 * H, st));
+        AE_CHECK(linear_tc_bf16out(nc, xin, H, Nn, H, P[s.m0w] + H, 3 * H, H, (__nv_bfloat16*)w.pspr16 + H, 2 * H, st));
+      } else {
       AE_CHECK(linear(nc, xin, H, Nn, H, P[s.m0w], 3 * H, nullptr, H, w.pspr, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
       AE_CHECK(linear(nc, xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+      }
     }
     {
     ProfScope ps(PROF_EDGE_MLP_FWD, st);
@@ -237,7 +244,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       // pre1 = [silu(pre2_{l-1}) | feat] We^T + b1 (+ P_s[send] + P_r[recv]) ; pre2 = silu(pre1) W2^T + b2
       TcGemmArgs a;
       a.M = E; a.wpack = w.wpA[l]; a.bias = P[s.m0b]; a.out_bf16 = (__nv_bfloat16*)w.bpre1[l]; a.ldo = H;
-      if (l > 1) { a.gat = w.pspr; a.ldg = 2 * H; a.idx_a = G.send; a.idx_b = G.recv; a.goff_b = H; }
+      if (l > 1) { a.gat16 = (const __nv_bfloat16*)w.pspr16; a.ldg = 2 * H; a.idx_a = G.send; a.idx_b = G.recv; a.goff_b = H; }
       if (l == 1) AE_CHECK(tc_gemm(a, w.feat16, 64, 64, H, TC_TF_NONE, st));
       else AE_CHECK(tc_gemm(a, w.bpre2[l - 1], H, H, H, TC_TF_SILU, st));
       TcGemmArgs b;

@@ -41,6 +41,22 @@ int linear_tc(const NodeTc& c, const float* A, int64_t lda, int64_t M, int K, co
   return 0;
 }
 
+// C16[M,N] (bf16) = A[M,K] W^T     (node terms P_s | P_r gathered by the edge GEMM's epilogue)
+int linear_tc_bf16out(const NodeTc& c, const float* A, int64_t lda, int64_t M, int K, const float* W, int64_t ldw, int N,
+                      void* C16, int64_t ldc16, cudaStream_t st) {
+  if (!c.on || !tc_dim_ok(K) || K > 256 || !tc_dim_ok(N) || M < 1) return AETHER_E_UNSUPPORTED;
+  const int Nc = tc_chunk(N);
+  AE_CHECK(tc_convert_bf16(A, lda, M, K, TF_NONE, nullptr, c.a16, K, st));
+  for (int n0 = 0; n0 < N; n0 += Nc) {
+    AE_CHECK(tc_pack_weight(W + (size_t)n0 * ldw, ldw, Nc, K, Nc, K, 0, 0, c.wp, st));
+    TcGemmArgs g;
+    g.M = M; g.wpack = c.wp;
+    g.out_bf16 = (__nv_bfloat16*)C16 + n0; g.ldo = ldc16;
+    AE_CHECK(tc_gemm(g, c.a16, K, K, Nc, TC_TF_NONE, st));
+  }
+  return 0;
+}
+
 // gx[rows, k_in] = ((gy[rows, n_out] W + res) * silu'(dsilu_src)) * mask (+ gx)     W: [n_out, k_in], ld ldw
 int dgrad_tc(const NodeTc& c, const float* gy, int64_t ldgy, int64_t rows, int n_out, const float* W, int64_t ldw,
              int k_in, float* gx, int64_t ldgx, const float* dsilu_src, const float* mask, const float* res,

@@ -6,16 +6,16 @@ using namespace aether;
 
 extern "C" int aether_dbg_tc_gemm(const void* A_bf16, int64_t M, int32_t K, int64_t lda, const float* W, int64_t ldw,
                                   int32_t N, int32_t n_valid, int32_t k_valid, int32_t transpose, int32_t kmod,
-                                  int32_t silu_on_load, const float* bias, const float* gat, int64_t ldg,
+                                  int32_t silu_on_load, const float* bias, const void* gat_bf16, int64_t ldg,
                                   const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, const void* dsilu_bf16,
                                   void* out_bf16, float* out_f32, void* wpack_scratch, void* stream) {
-  if (!A_bf16 || !W || !wpack_scratch || (!out_bf16 && !out_f32)) return AETHER_E_BADARG;
+  if (!A_bf16 || !W || !wpack_scratch || ((out_bf16 != nullptr) == (out_f32 != nullptr))) return AETHER_E_BADARG;
   if (!tc_gemm_supported(K, N)) return AETHER_E_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   AE_CHECK(tc_pack_weight(W, ldw, N, K, n_valid, k_valid, transpose, kmod, wpack_scratch, st));
   TcGemmArgs g;
   g.M = M; g.wpack = wpack_scratch; g.bias = bias;
-  g.gat = gat; g.ldg = ldg; g.idx_a = idx_a; g.idx_b = idx_b; g.goff_b = goff_b;
+  g.gat16 = (const __nv_bfloat16*)gat_bf16; g.ldg = ldg; g.idx_a = idx_a; g.idx_b = idx_b; g.goff_b = goff_b;
   g.dsilu = (const __nv_bfloat16*)dsilu_bf16; g.ldd = N;
   g.out_bf16 = (__nv_bfloat16*)out_bf16; g.ldo = N;
   g.out_f32 = out_f32; g.ldo32 = N; g.n_valid = n_valid;

@@ -17,6 +17,8 @@
 //
 // Shared memory: weights N*K*2 bytes resident for the whole kernel (128 KB at N=K=256), the rest is
 // the A ring (16 KB per slot, 6 slots at N=K=256).  HBM traffic per row: 2K bytes in, 2N bytes out.
+#include <string.h>
+
 #include "tc_gemm.cuh"
 
 namespace aether {
@@ -32,26 +34,30 @@ constexpr int kSmemMax = 232448;                  // 227 KB
 constexpr int kMiscBytes = 2048;                  // barriers + tmem pointer + bias
 
 __host__ __device__ constexpr int weight_bytes(int K, int N) { return K * N * 2; }
-__host__ __device__ constexpr int num_slots(int K, int N) {
-  int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N)) / kSlotBytes;
+constexpr int kStageBytes = 4 * 2 * 4096;         // bf16 epilogue: per warp two 32-row x 64-column boxes
+__host__ __device__ constexpr int num_slots(int K, int N, bool staged) {
+  int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N) - (staged ? kStageBytes : 0)) / kSlotBytes;
   return s > 8 ? 8 : s;
 }
-__host__ __device__ constexpr int smem_bytes(int K, int N) {
-  return 1024 + weight_bytes(K, N) + num_slots(K, N) * kSlotBytes + kMiscBytes;
+__host__ __device__ constexpr int smem_bytes(int K, int N, bool staged) {
+  return 1024 + weight_bytes(K, N) + num_slots(K, N, staged) * kSlotBytes + (staged ? kStageBytes : 0) + kMiscBytes;
 }
 __host__ __device__ constexpr int tmem_cols(int N) { return 2 * N < 32 ? 32 : 2 * N; }
 
-template <int K, int N, int TF>
-__global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, TcGemmArgs g) {
+template <int K, int N, int TF, bool STAGED>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmO, TcGemmArgs g) {
   static_assert(K % 64 == 0 && N % 32 == 0 && N <= 256 && (N & (N - 1)) == 0, "unsupported shape");
+  static_assert(!STAGED || N % 64 == 0, "staged epilogue works on 64-column boxes");
   constexpr int KC = K / 64;                      // 64-wide K chunks = pipeline slots per tile
-  constexpr int S = num_slots(K, N);
+  constexpr int S = num_slots(K, N, STAGED);
   constexpr uint32_t IDESC = make_idesc(128, N, MAJOR_K, MAJOR_K);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sW = base;
   const uint32_t sA = base + weight_bytes(K, N);
-  const uint32_t sMisc = sA + S * kSlotBytes;
+  const uint32_t sStage = sA + S * kSlotBytes;
+  const uint32_t sMisc = sStage + (STAGED ? kStageBytes : 0);
   // barriers (8 bytes each)
   const uint32_t bar_raw = sMisc;                 // [S] TMA landed
   const uint32_t bar_rdy = sMisc + 64;            // [S] transform done
@@ -81,7 +87,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
   }
   if (threadIdx.x < N) sbias[threadIdx.x] = g.bias ? g.bias[threadIdx.x] : 0.0f;
   if (warp == 5) tmem_alloc(tmem_slot, tmem_cols(N));
-  if (warp == 4 && lane == 0) tma_prefetch_desc(&tmA);
+  if (warp == 4 && lane == 0) { tma_prefetch_desc(&tmA); if (STAGED) tma_prefetch_desc(&tmO); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -153,8 +159,96 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
         }
       }
     }
+  } else if (STAGED) {
+    // ===== epilogue, bf16 output: TMEM -> registers (one row per thread) -> swizzled shared staging
+    //       -> TMA store; gathered node terms and the silu' factor are applied in registers =====
+    // Each warp owns two 32-row x 64-column staging boxes (4 KB each), so only __syncwarp is needed.
+    const uint32_t sbuf = sStage + warp * 8192;
+    uint32_t lt = 0, nbox = 0;
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+      const uint32_t acc = lt & 1;
+      mbar_wait(bar_accf + 8 * acc, (lt >> 1) & 1);
+      tc_fence_after();
+      const int64_t row0 = t * kTileM + warp * 32;
+      const int64_t row = row0 + lane;
+      int ia = 0, ib = 0;
+      if (g.gat16 && row < g.M) { ia = g.idx_a[row]; ib = g.idx_b[row]; }
+      const int64_t zrow = row < g.M ? row : g.M - 1;     // rows past the end read valid memory, TMA clips them
+#pragma unroll 1
+      for (int jj = 0; jj < N / 64; ++jj, ++nbox) {
+        const uint32_t buf = sbuf + (nbox & 1) * 4096;
+        // the TMA store that read this buffer two boxes ago must have finished reading it
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + acc * N + jj * 64 + h * 32, r);
+          tmem_ld_wait();
+          const float* bs = sbias + jj * 64 + h * 32;
+          const int c0 = jj * 64 + h * 32;
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
+          if (g.gat16) {
+            // node terms of the factorised first Linear: 64 contiguous bytes per row and source
+            const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia * g.ldg + c0);
+            const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ib * g.ldg + g.goff_b + c0);
+            uint4 a4[4], b4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { a4[q] = __ldg(pa + q); b4[q] = __ldg(pb + q); }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w}, bb[4] = {b4[q].x, b4[q].y, b4[q].z, b4[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                v[8 * q + 2 * e] += bf16_lo(aa[e]) + bf16_lo(bb[e]);
+                v[8 * q + 2 * e + 1] += bf16_hi(aa[e]) + bf16_hi(bb[e]);
+              }
+            }
+          }
+          if (g.dsilu) {
+            const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow * g.ldd + c0);
+            uint4 z4[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) z4[q] = __ldg(pd + q);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t zz[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                v[8 * q + 2 * e] *= dsilu_fast(bf16_lo(zz[e]));
+                v[8 * q + 2 * e + 1] *= dsilu_fast(bf16_hi(zz[e]));
+              }
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint32_t o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o[e] = pack_bf16(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
+            const uint32_t addr = buf + lane * 128 + (((h * 4 + q) ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+          }
+        }
+        if (jj == N / 64 - 1) {
+          // accumulator fully read: hand it back to the MMA warp before the slow part
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_acce + 8 * acc);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0 && row0 < g.M) {
+          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                       :: "l"((uint64_t)&tmO), "r"(jj * 64), "r"((int)row0), "r"(buf) : "memory");
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else {
-    // ===== epilogue: warps 0..3, one output row per thread =====
+    // ===== epilogue, fp32 output (node-level Linears, layer-1 feature gradients): direct stores =====
     uint32_t lt = 0;
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
       const uint32_t acc = lt & 1;
@@ -162,8 +256,6 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
       tc_fence_after();
       const int64_t row = t * kTileM + warp * 32 + lane;
       const bool live = row < g.M;
-      int ia = 0, ib = 0;
-      if (g.gat && live) { ia = g.idx_a[row]; ib = g.idx_b[row]; }
 #pragma unroll 1
       for (int j = 0; j < N / 32; ++j) {
         uint32_t r[32];
@@ -173,28 +265,6 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + sbias[j * 32 + i];
-        if (g.gat) {
-          const float4* pa = reinterpret_cast<const float4*>(g.gat + (size_t)ia * g.ldg + j * 32);
-          const float4* pb = reinterpret_cast<const float4*>(g.gat + (size_t)ib * g.ldg + g.goff_b + j * 32);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 a = __ldg(pa + q), b = __ldg(pb + q);
-            v[4 * q] += a.x + b.x; v[4 * q + 1] += a.y + b.y; v[4 * q + 2] += a.z + b.z; v[4 * q + 3] += a.w + b.w;
-          }
-        }
-        if (g.dsilu) {
-          const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)row * g.ldd + j * 32);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint4 z = __ldg(pd + q);
-            const uint32_t zz[4] = {z.x, z.y, z.z, z.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              v[8 * q + 2 * e] *= dsilu_fast(bf16_lo(zz[e]));
-              v[8 * q + 2 * e + 1] *= dsilu_fast(bf16_hi(zz[e]));
-            }
-          }
-        }
         if (g.res) {
           const float4* pr = reinterpret_cast<const float4*>(g.res + (size_t)row * g.ldr + j * 32);
 #pragma unroll
@@ -227,27 +297,15 @@ __global__ void __launch_bounds__(kThreads, 1) tc_gemm_kernel(const __grid_const
             v[4 * q] += a.x; v[4 * q + 1] += a.y; v[4 * q + 2] += a.z; v[4 * q + 3] += a.w;
           }
         }
-        if (g.out_bf16) {
-          uint4* po = reinterpret_cast<uint4*>(g.out_bf16 + (size_t)row * g.ldo + j * 32);
+        float* po = g.out_f32 + (size_t)row * g.ldo32 + j * 32;
+        if (j * 32 + 32 <= g.n_valid && (g.ldo32 & 3) == 0) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint4 o;
-            o.x = pack_bf16(v[8 * q], v[8 * q + 1]); o.y = pack_bf16(v[8 * q + 2], v[8 * q + 3]);
-            o.z = pack_bf16(v[8 * q + 4], v[8 * q + 5]); o.w = pack_bf16(v[8 * q + 6], v[8 * q + 7]);
-            po[q] = o;
-          }
-        }
-        if (g.out_f32) {
-          float* po = g.out_f32 + (size_t)row * g.ldo32 + j * 32;
-          if (j * 32 + 32 <= g.n_valid && (g.ldo32 & 3) == 0) {
+          for (int q = 0; q < 8; ++q)
+            reinterpret_cast<float4*>(po)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+        } else {
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-              reinterpret_cast<float4*>(po)[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (j * 32 + i < g.n_valid) po[i] = v[i];
-          }
+          for (int i = 0; i < 32; ++i)
+            if (j * 32 + i < g.n_valid) po[i] = v[i];
         }
       }
       tc_fence_before();
@@ -311,24 +369,30 @@ __global__ void convert_bf16_kernel(const float* __restrict__ A, int64_t lda, in
   *reinterpret_cast<uint2*>(out + (size_t)m * ldo + c) = o;
 }
 
-template <int K, int N>
-int launch_kn(const TcGemmArgs& g, const CUtensorMap& tm, int tf, cudaStream_t st) {
+template <int K, int N, int TF, bool STAGED>
+int launch_one(const TcGemmArgs& g, const CUtensorMap& tm, const CUtensorMap& to, cudaStream_t st) {
   const int64_t tiles = (g.M + kTileM - 1) / kTileM;
-  int sms = tc_sm_count();
+  const int sms = tc_sm_count();
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  const int smem = smem_bytes(K, N);
-  cudaError_t e;
-  if (tf == TC_TF_SILU) {
-    e = cudaFuncSetAttribute(tc_gemm_kernel<K, N, TC_TF_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return (int)e;
-    tc_gemm_kernel<K, N, TC_TF_SILU><<<grid, kThreads, smem, st>>>(tm, g);
-  } else {
-    e = cudaFuncSetAttribute(tc_gemm_kernel<K, N, TC_TF_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return (int)e;
-    tc_gemm_kernel<K, N, TC_TF_NONE><<<grid, kThreads, smem, st>>>(tm, g);
-  }
+  constexpr int smem = smem_bytes(K, N, STAGED);
+  static_assert(num_slots(K, N, STAGED) >= 2, "pipeline too shallow");
+  cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<K, N, TF, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return (int)e;
+  tc_gemm_kernel<K, N, TF, STAGED><<<grid, kThreads, smem, st>>>(tm, to, g);
   AE_LAUNCH_CHECK();
   return 0;
+}
+
+template <int K, int N>
+int launch_kn(const TcGemmArgs& g, const CUtensorMap& tm, const CUtensorMap& to, int tf, bool staged, cudaStream_t st) {
+  if constexpr (N >= 64) {
+    if (staged) {
+      if (tf == TC_TF_SILU) return launch_one<K, N, TC_TF_SILU, true>(g, tm, to, st);
+      return launch_one<K, N, TC_TF_NONE, true>(g, tm, to, st);
+    }
+  }
+  if (tf == TC_TF_SILU) return launch_one<K, N, TC_TF_SILU, false>(g, tm, to, st);
+  return launch_one<K, N, TC_TF_NONE, false>(g, tm, to, st);
 }
 
 }  // namespace
@@ -396,9 +460,16 @@ bool tc_gemm_supported(int K, int N) {
 int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int tf, cudaStream_t st) {
   if (g.M <= 0) return 0;
   if (!tc_gemm_supported(K, N)) return AETHER_E_UNSUPPORTED;
-  CUtensorMap tm;
+  // exactly one output: bf16 (staged TMA-store epilogue) or fp32 (direct stores)
+  const bool staged = g.out_bf16 != nullptr;
+  if (staged == (g.out_f32 != nullptr)) return AETHER_E_BADARG;
+  if (staged && (N < 64 || g.res || g.dsilu32 || g.emask || g.accumulate)) return AETHER_E_BADARG;
+  if (!staged && (g.gat16 || g.dsilu)) return AETHER_E_BADARG;
+  CUtensorMap tm, to;
+  memset(&to, 0, sizeof(to));
   AE_CHECK(tc_make_tmap_bf16(&tm, A, g.M, K, lda, kTileM));
-#define AE_TC_CASE(KK, NN) if (K == KK && N == NN) return launch_kn<KK, NN>(g, tm, tf, st);
+  if (staged) AE_CHECK(tc_make_tmap_bf16(&to, g.out_bf16, g.M, N, g.ldo, 32));
+#define AE_TC_CASE(KK, NN) if (K == KK && N == NN) return launch_kn<KK, NN>(g, tm, to, tf, staged, st);
   AE_TC_CASE(256, 256) AE_TC_CASE(256, 32) AE_TC_CASE(64, 256)
   AE_TC_CASE(128, 128) AE_TC_CASE(128, 32) AE_TC_CASE(64, 128)
   AE_TC_CASE(64, 64) AE_TC_CASE(64, 32)

@@ -11,12 +11,12 @@ struct TcGemmArgs {
   int64_t M = 0;                       // rows of A / out
   const void* wpack = nullptr;         // packed weight image from tc_pack_weight (N*K*2 bytes)
   const float* bias = nullptr;         // [N] or null
-  // + gat[idx_a[m]*ldg + n] + gat[idx_b[m]*ldg + goff_b + n]
-  const float* gat = nullptr; int64_t ldg = 0;
+  // bf16-output epilogue only: + gat16[idx_a[m]*ldg + n] + gat16[idx_b[m]*ldg + goff_b + n]
+  const __nv_bfloat16* gat16 = nullptr; int64_t ldg = 0;
   const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int goff_b = 0;
-  // * silu'(dsilu[m*ldd + n])
+  // bf16-output epilogue only: * silu'(dsilu[m*ldd + n])
   const __nv_bfloat16* dsilu = nullptr; int64_t ldd = 0;
-  // node-level (fp32) epilogue terms, applied in this order after the ones above:
+  // fp32-output epilogue only (node-level Linears), applied in this order:
   const float* res = nullptr; int64_t ldr = 0;            // + res[m*ldr + n]
   const float* dsilu32 = nullptr; int64_t ldd32 = 0;      // * silu'(dsilu32[m*ldd32 + n])
   const float* emask = nullptr; int64_t ldm = 0;          // * emask[m*ldm + n]

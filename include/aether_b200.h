@@ -154,12 +154,13 @@ int64_t aether_debug_stage(const AetherDims* dims, const void* workspace, uint32
 
 /* ---- test hooks for the tcgen05 building blocks (aether_b200/csrc/tc_gemm.cu, tc_wgrad.cu) -------
  * out[M,N] = epi(tf(A_bf16[M,K]) B^T), B[n][k] = transpose ? W[k*ldw+n] : W[n*ldw + (kmod ? k%kmod : k)],
- * zero outside [n_valid,k_valid]; epi adds bias[n], gat[idx_a[m]*ldg+n] + gat[idx_b[m]*ldg+goff_b+n],
- * multiplies by silu'(dsilu_bf16[m,n]); bf16 and/or fp32 output with leading dimension N.
+ * zero outside [n_valid,k_valid]; epi adds bias[n]; with the bf16 output (exactly one of out_bf16 / out_f32
+ * is given, leading dimension N) it also adds gat_bf16[idx_a[m]*ldg+n] + gat_bf16[idx_b[m]*ldg+goff_b+n] and
+ * multiplies by silu'(dsilu_bf16[m,n]).
  * wpack_scratch: N*K*2 bytes. */
 int aether_dbg_tc_gemm(const void* A_bf16, int64_t M, int32_t K, int64_t lda, const float* W, int64_t ldw,
                        int32_t N, int32_t n_valid, int32_t k_valid, int32_t transpose, int32_t kmod,
-                       int32_t silu_on_load, const float* bias, const float* gat, int64_t ldg,
+                       int32_t silu_on_load, const float* bias, const void* gat_bf16, int64_t ldg,
                        const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, const void* dsilu_bf16,
                        void* out_bf16, float* out_f32, void* wpack_scratch, void* stream);
 /* dW[MG, n_valid] = sum_e G[e,:]^T tf(ACT[e,:]) (fold32: columns j and 32+j summed). */

@@ -29,17 +29,24 @@ def stream():
 
 
 def run_gemm(lib, A, W, N, K, *, n_valid=None, k_valid=None, transpose=0, kmod=0, silu=0, bias=None, gat=None,
-             idx_a=None, idx_b=None, goff_b=0, dsilu=None, f32=False):
+             idx_a=None, idx_b=None, goff_b=0, dsilu=None, f32=False, bf=True):
+    """Returns (bf16 output or None, fp32 output or None); the two epilogues are separate launches."""
     M = A.shape[0]
     n_valid = N if n_valid is None else n_valid
     k_valid = K if k_valid is None else k_valid
-    out_bf = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device="cuda")
-    out_f = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda") if f32 else None
     scratch = torch.empty(N * K * 2, dtype=torch.uint8, device="cuda")
-    rc = lib.aether_dbg_tc_gemm(P(A), M, K, A.stride(0), P(W), W.stride(0), N, n_valid, k_valid, transpose, kmod, silu,
-                                P(bias), P(gat), 0 if gat is None else gat.stride(0), P(idx_a), P(idx_b), goff_b,
-                                P(dsilu), P(out_bf), P(out_f), P(scratch), stream())
-    assert rc == 0, rc
+    out_bf = out_f = None
+    if bf and N >= 64:
+        out_bf = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device="cuda")
+        rc = lib.aether_dbg_tc_gemm(P(A), M, K, A.stride(0), P(W), W.stride(0), N, n_valid, k_valid, transpose, kmod, silu,
+                                    P(bias), P(gat), 0 if gat is None else gat.stride(0), P(idx_a), P(idx_b), goff_b,
+                                    P(dsilu), P(out_bf), None, P(scratch), stream())
+        assert rc == 0, rc
+    if f32:
+        out_f = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda")
+        rc = lib.aether_dbg_tc_gemm(P(A), M, K, A.stride(0), P(W), W.stride(0), N, n_valid, k_valid, transpose, kmod, silu,
+                                    P(bias), None, 0, None, None, 0, None, None, P(out_f), P(scratch), stream())
+        assert rc == 0, rc
     torch.cuda.synchronize()
     return out_bf, out_f
 
@@ -54,7 +61,8 @@ def test_plain_gemm(lib, K, N, M):
     out_bf, out_f = run_gemm(lib, A, W, N, K, bias=bias, f32=True)
     ref = A.float() @ W.bfloat16().float().t() + bias
     assert rel_err(out_f, ref) < 1e-4
-    assert rel_err(out_bf.float(), ref) < 5e-3
+    if N >= 64:
+        assert rel_err(out_bf.float(), ref) < 5e-3
 
 
 def test_transposed_weight_and_padding(lib):
@@ -78,27 +86,30 @@ def test_transposed_weight_and_padding(lib):
     assert rel_err(out2, ref2) < 1e-4
 
 
-def test_silu_on_load_gather_and_dsilu(lib):
+@pytest.mark.parametrize("M,K,N", [(5000, 256, 256), (777, 128, 128), (130, 64, 64), (4000, 256, 128)])
+def test_silu_on_load_gather_and_dsilu(lib, M, K, N):
     torch.manual_seed(5)
-    M, K, N, Nn = 5000, 256, 256, 300
+    Nn = 300
     pre = torch.randn(M, K, device="cuda").bfloat16() * 2
     W = torch.randn(N, K, device="cuda") / K ** 0.5
     bias = torch.randn(N, device="cuda")
-    gat = torch.randn(Nn, 2 * N, device="cuda")
+    gat = torch.randn(Nn, 2 * N, device="cuda").bfloat16()
     ia = torch.randint(0, Nn, (M,), device="cuda", dtype=torch.int32)
     ib = torch.randint(0, Nn, (M,), device="cuda", dtype=torch.int32)
-    out_bf, out_f = run_gemm(lib, pre, W, N, K, silu=1, bias=bias, gat=gat, idx_a=ia, idx_b=ib, goff_b=N, f32=True)
     a = torch.nn.functional.silu(pre.float()).bfloat16().float()
-    ref = a @ W.bfloat16().float().t() + bias + gat[ia.long(), :N] + gat[ib.long(), N:]
-    assert rel_err(out_f, ref) < 5e-3                # tanh.approx SiLU before bf16 rounding
+    _, out_f = run_gemm(lib, pre, W, N, K, silu=1, bias=bias, f32=True, bf=False)
+    ref0 = a @ W.bfloat16().float().t() + bias
+    assert rel_err(out_f, ref0) < 5e-3               # tanh.approx SiLU before bf16 rounding
+    out_bf, _ = run_gemm(lib, pre, W, N, K, silu=1, bias=bias, gat=gat, idx_a=ia, idx_b=ib, goff_b=N)
+    ref = ref0 + gat[ia.long(), :N].float() + gat[ib.long(), N:].float()
     assert rel_err(out_bf.float(), ref) < 1e-2
     # backward epilogue: (A W) * silu'(z)
     z = torch.randn(M, N, device="cuda").bfloat16() * 2
-    _, o2 = run_gemm(lib, pre, W, N, K, dsilu=z, f32=True)
+    o2, _ = run_gemm(lib, pre, W, N, K, dsilu=z)
     zf = z.float()
     s = torch.sigmoid(zf)
     ref2 = (pre.float() @ W.bfloat16().float().t()) * (s * (1 + zf * (1 - s)))
-    assert rel_err(o2, ref2) < 5e-3
+    assert rel_err(o2.float(), ref2) < 1e-2
 
 
 @pytest.mark.parametrize("MG,NA", [(256, 256), (128, 128), (64, 64), (256, 64), (128, 64)])
@@ -135,6 +146,8 @@ def test_gemm_throughput_report(lib):
     lines = []
     for silu in (0, 1):
         run_gemm(lib, A, W, N, K, silu=silu)
+        gat = torch.randn(3000, 2 * N, device="cuda").bfloat16()
+        ia = torch.randint(0, 3000, (M,), device="cuda", dtype=torch.int32)
         out_bf = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
         scratch = torch.empty(N * K * 2, dtype=torch.uint8, device="cuda")
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -147,6 +160,15 @@ def test_gemm_throughput_report(lib):
         ms = a.elapsed_time(b) / 5
         lines.append("tc_gemm M=%d K=%d N=%d silu=%d: %.3f ms, %.1f TFLOP/s, %.0f GB/s" %
                      (M, K, N, silu, ms, 2.0 * M * K * N / ms / 1e9, M * (K + N) * 2 / ms / 1e6))
+        a.record()
+        for _ in range(5):
+            lib.aether_dbg_tc_gemm(P(A), M, K, K, P(W), K, N, N, K, 0, 0, silu, None, P(gat), 2 * N, P(ia), P(ia), N, P(A),
+                                   P(out_bf), None, P(scratch), stream())
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 5
+        lines.append("tc_gemm + gather + dsilu epilogue silu=%d: %.3f ms, %.0f GB/s (in+aux+out)" %
+                     (silu, ms, M * (K + 2 * N) * 2 / ms / 1e6))
     E = M
     G = torch.randn(E, 256, device="cuda").bfloat16()
     nf = lib.aether_dbg_tc_wgrad_partial_floats(256, 256)
