@@ -90,14 +90,15 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
       }
       {
         ProfScope ps(PROF_EDGE_WGRAD, st);
-        AE_CHECK(tc_wgrad(g2, H, H, w.bpre1[l], H, H, TC_TF_SILU, E, G[sl.m2w], H, H, 0, s.partial, s.partial_floats, st));
-        AE_CHECK(colsum_bf16(g2, H, E, H, G[sl.m2b], s.partial, s.partial_floats, st));
-        AE_CHECK(colsum_bf16(g1, H, E, H, G[sl.m0b], s.partial, s.partial_floats, st));
+        // dW2 = g2^T silu(pre1), db2 = colsum(g2) ; dW1e = g1^T silu(pre2_{l-1}) (or g1^T feat), db1 = colsum(g1)
+        AE_CHECK(tc_wgrad(g2, H, H, w.bpre1[l], H, H, TC_TF_SILU, E, G[sl.m2w], H, H, 0, G[sl.m2b], s.partial,
+                          s.partial_floats, st));
         if (l > 1)
-          AE_CHECK(tc_wgrad(g1, H, H, w.bpre2[l - 1], H, H, TC_TF_SILU, E, G[sl.m0w] + 2 * H, 3 * H, H, 0, s.partial,
-                            s.partial_floats, st));
+          AE_CHECK(tc_wgrad(g1, H, H, w.bpre2[l - 1], H, H, TC_TF_SILU, E, G[sl.m0w] + 2 * H, 3 * H, H, 0, G[sl.m0b],
+                            s.partial, s.partial_floats, st));
         else
-          AE_CHECK(tc_wgrad(g1, H, H, w.feat16, 64, 64, TC_TF_NONE, E, G[sl.m0w], Fe, Fe, 1, s.partial, s.partial_floats, st));
+          AE_CHECK(tc_wgrad(g1, H, H, w.feat16, 64, 64, TC_TF_NONE, E, G[sl.m0w], Fe, Fe, 1, G[sl.m0b], s.partial,
+                            s.partial_floats, st));
       }
       if (l > 1) {
         {

@@ -93,7 +93,7 @@ int wgrad_tc(const NodeTc& c, const float* gy, int64_t ldgy, int64_t rows, int n
     for (int n0 = 0; n0 < k_in; n0 += Nc) {
       AE_CHECK(tc_convert_bf16(a + n0, lda, rows, Nc, tf, mask ? mask + n0 : nullptr, c.a16, Nc, st));
       AE_CHECK(tc_wgrad(c.g16, Mc, Mc, c.a16, Nc, Nc, TC_TF_NONE, rows, dW + (size_t)m0 * lddw + n0, lddw, Nc, 0,
-                        c.partial, c.partial_floats, st));
+                        nullptr, c.partial, c.partial_floats, st));
     }
   }
   return 0;

@@ -26,8 +26,8 @@ extern "C" size_t aether_dbg_tc_wgrad_partial_floats(int32_t MG, int32_t NA) { r
 
 extern "C" int aether_dbg_tc_wgrad(const void* G_bf16, int32_t MG, const void* ACT_bf16, int32_t NA,
                                    int32_t silu_on_load, int64_t E, float* dW, int32_t n_valid, int32_t fold32,
-                                   float* partial, size_t partial_floats, void* stream) {
+                                   float* db, float* partial, size_t partial_floats, void* stream) {
   if (!G_bf16 || !ACT_bf16 || !dW) return AETHER_E_BADARG;
   return tc_wgrad(G_bf16, MG, MG, ACT_bf16, NA, NA, silu_on_load ? TC_TF_SILU : TC_TF_NONE, E, dW,
-                  n_valid, n_valid, fold32, partial, partial_floats, (cudaStream_t)stream);
+                  n_valid, n_valid, fold32, db, partial, partial_floats, (cudaStream_t)stream);
 }

@@ -45,6 +45,7 @@ int tc_convert_bf16(const float* A, int64_t lda, int64_t M, int cols, int tf, co
 bool tc_wgrad_supported(int MG, int NA);
 size_t tc_wgrad_partial_floats(int MG, int NA);
 int tc_wgrad(const void* G, int64_t ldg, int MG, const void* ACT, int64_t lda, int NA, int tf, int64_t E, float* dW,
-             int64_t lddw, int n_valid, int fold32, float* partial, size_t partial_floats, cudaStream_t st);
+             int64_t lddw, int n_valid, int fold32, float* db /* [MG] column sums of G, or null */, float* partial,
+             size_t partial_floats, cudaStream_t st);
 
 }  // namespace aether

@@ -40,7 +40,7 @@ __host__ __device__ constexpr int wg_tmem_cols(int MG, int NA) {
 template <int MG, int NA, int TF>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmA, int64_t n_stages,
-                float* __restrict__ partial) {
+                float* __restrict__ partial, float* __restrict__ colsum_partial) {
   static_assert(MG % 64 == 0 && NA % 64 == 0 && MG <= 256 && NA <= 256, "unsupported shape");
   constexpr int S = wg_stages(MG, NA);
   constexpr int MT = wg_mtiles(MG);
@@ -63,7 +63,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__
     for (int s = 0; s < S; ++s) {
       mbar_init(bar_raw + 8 * s, 1);
       mbar_init(bar_rdy + 8 * s, 128);
-      mbar_init(bar_free + 8 * s, 1);
+      mbar_init(bar_free + 8 * s, colsum_partial ? 5 : 1);   // MMA commit (+ the four column-sum warps)
     }
     mbar_init(bar_done, 1);
     fence_mbar_init();
@@ -134,7 +134,44 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__
       }
     }
   } else {
-    // warps 0..3: wait for the last MMA, then write this CTA's partial dW
+    // warps 0..3.  While the pipeline runs they are otherwise idle: optionally accumulate the column sums
+    // of G (the bias gradient of the same Linear) from the landed slabs.  Thread t owns columns 2t, 2t+1:
+    // slab t/32, 16-byte chunk (t%32)/4 (XOR-swizzled by the row), conflict-free 4-byte loads.
+    if (colsum_partial) {
+      const int t = threadIdx.x;
+      float c0 = 0.0f, c1 = 0.0f;
+      if (2 * t < MG) {
+        const uint32_t slab_off = (uint32_t)(t >> 5) * kSlab + (uint32_t)(t & 3) * 4;
+        const uint32_t chunk = (uint32_t)(t & 31) >> 2;
+        uint32_t it = 0;
+        for (int64_t st = s_begin; st < s_end; ++st, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait(bar_raw + 8 * s, ph);
+          const uint32_t a0 = base + s * STAGE + slab_off;
+#pragma unroll 16
+          for (int k = 0; k < kStageRows; ++k) {
+            uint32_t v;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a0 + k * 128 + ((chunk ^ (uint32_t)(k & 7)) << 4)));
+            c0 += bf16_lo(v);
+            c1 += bf16_hi(v);
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_free + 8 * s);
+        }
+        colsum_partial[(size_t)blockIdx.x * MG + 2 * t] = c0;
+        colsum_partial[(size_t)blockIdx.x * MG + 2 * t + 1] = c1;
+      } else {
+        // MG < 256: the upper warps only release the slots
+        uint32_t it = 0;
+        for (int64_t st = s_begin; st < s_end; ++st, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait(bar_raw + 8 * s, ph);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_free + 8 * s);
+        }
+      }
+    }
+    // then wait for the last MMA and write this CTA's partial dW
     float* out = partial + (size_t)blockIdx.x * MG * NA;
     if (s_end > s_begin) {
       mbar_wait(bar_done, 0);
@@ -186,6 +223,14 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int parts
   dW[(size_t)m * ld + n] = s;
 }
 
+__global__ void colsum_reduce_kernel(const float* __restrict__ partial, int parts, int MG, float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= MG) return;
+  float s = 0.0f;
+  for (int b = 0; b < parts; ++b) s += partial[(size_t)b * MG + n];
+  out[n] = s;
+}
+
 int wg_grid(int64_t n_stages) {
   const int sms = tc_sm_count();
   return (int)(n_stages < sms ? (n_stages > 0 ? n_stages : 1) : sms);
@@ -193,17 +238,17 @@ int wg_grid(int64_t n_stages) {
 
 template <int MG, int NA>
 int launch_wg(const CUtensorMap& tg, const CUtensorMap& ta, int tf, int64_t n_stages, int grid, float* partial,
-              cudaStream_t st) {
+              float* cpart, cudaStream_t st) {
   const int smem = wg_smem(MG, NA);
   cudaError_t e;
   if (tf == TC_TF_SILU) {
     e = cudaFuncSetAttribute(tc_wgrad_kernel<MG, NA, TC_TF_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    tc_wgrad_kernel<MG, NA, TC_TF_SILU><<<grid, kThreads, smem, st>>>(tg, ta, n_stages, partial);
+    tc_wgrad_kernel<MG, NA, TC_TF_SILU><<<grid, kThreads, smem, st>>>(tg, ta, n_stages, partial, cpart);
   } else {
     e = cudaFuncSetAttribute(tc_wgrad_kernel<MG, NA, TC_TF_NONE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
-    tc_wgrad_kernel<MG, NA, TC_TF_NONE><<<grid, kThreads, smem, st>>>(tg, ta, n_stages, partial);
+    tc_wgrad_kernel<MG, NA, TC_TF_NONE><<<grid, kThreads, smem, st>>>(tg, ta, n_stages, partial, cpart);
   }
   AE_LAUNCH_CHECK();
   return 0;
@@ -215,20 +260,21 @@ bool tc_wgrad_supported(int MG, int NA) {
   return (MG == 64 || MG == 128 || MG == 256) && (NA == 64 || NA == 128 || NA == 256);
 }
 
-size_t tc_wgrad_partial_floats(int MG, int NA) { return (size_t)tc_sm_count() * MG * NA; }
+size_t tc_wgrad_partial_floats(int MG, int NA) { return (size_t)tc_sm_count() * MG * (NA + 1); }
 
 int tc_wgrad(const void* G, int64_t ldg, int MG, const void* ACT, int64_t lda, int NA, int tf, int64_t E, float* dW,
-             int64_t lddw, int n_valid, int fold32, float* partial, size_t partial_floats, cudaStream_t st) {
+             int64_t lddw, int n_valid, int fold32, float* db, float* partial, size_t partial_floats, cudaStream_t st) {
   if (!tc_wgrad_supported(MG, NA)) return AETHER_E_UNSUPPORTED;
   const int64_t n_stages = (E + kStageRows - 1) / kStageRows;
   const int grid = wg_grid(n_stages);
-  if (!partial || partial_floats < (size_t)grid * MG * NA) return AETHER_E_WORKSPACE;
+  if (!partial || partial_floats < (size_t)grid * MG * (NA + 1)) return AETHER_E_WORKSPACE;
+  float* cpart = db ? partial + (size_t)grid * MG * NA : nullptr;
   if (E > 0) {
     CUtensorMap tg, ta;
     AE_CHECK(tc_make_tmap_bf16(&tg, G, E, MG, ldg, kStageRows));
     AE_CHECK(tc_make_tmap_bf16(&ta, ACT, E, NA, lda, kStageRows));
     int rc = AETHER_E_UNSUPPORTED;
-#define AE_WG_CASE(MM, NN) if (MG == MM && NA == NN) rc = launch_wg<MM, NN>(tg, ta, tf, n_stages, grid, partial, st);
+#define AE_WG_CASE(MM, NN) if (MG == MM && NA == NN) rc = launch_wg<MM, NN>(tg, ta, tf, n_stages, grid, partial, cpart, st);
     AE_WG_CASE(256, 256) AE_WG_CASE(256, 64) AE_WG_CASE(128, 128) AE_WG_CASE(128, 64) AE_WG_CASE(64, 64)
     AE_WG_CASE(256, 128) AE_WG_CASE(128, 256) AE_WG_CASE(64, 128) AE_WG_CASE(64, 256)
 #undef AE_WG_CASE
@@ -237,6 +283,10 @@ int tc_wgrad(const void* G, int64_t ldg, int MG, const void* ACT, int64_t lda, i
   const int tot = MG * n_valid;
   wgrad_reduce_kernel<<<(tot + 255) / 256, 256, 0, st>>>(partial, E > 0 ? grid : 0, MG, NA, n_valid, fold32, dW, lddw);
   AE_LAUNCH_CHECK();
+  if (db) {
+    colsum_reduce_kernel<<<(MG + 255) / 256, 256, 0, st>>>(cpart, E > 0 ? grid : 0, MG, db);
+    AE_LAUNCH_CHECK();
+  }
   return 0;
 }
 

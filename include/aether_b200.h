@@ -163,10 +163,11 @@ int aether_dbg_tc_gemm(const void* A_bf16, int64_t M, int32_t K, int64_t lda, co
                        int32_t silu_on_load, const float* bias, const void* gat_bf16, int64_t ldg,
                        const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, const void* dsilu_bf16,
                        void* out_bf16, float* out_f32, void* wpack_scratch, void* stream);
-/* dW[MG, n_valid] = sum_e G[e,:]^T tf(ACT[e,:]) (fold32: columns j and 32+j summed). */
+/* dW[MG, n_valid] = sum_e G[e,:]^T tf(ACT[e,:]) (fold32: columns j and 32+j summed);
+ * db[MG] = column sums of G when db is not NULL. */
 size_t aether_dbg_tc_wgrad_partial_floats(int32_t MG, int32_t NA);
 int aether_dbg_tc_wgrad(const void* G_bf16, int32_t MG, const void* ACT_bf16, int32_t NA, int32_t silu_on_load,
-                        int64_t E, float* dW, int32_t n_valid, int32_t fold32, float* partial,
+                        int64_t E, float* dW, int32_t n_valid, int32_t fold32, float* db, float* partial,
                         size_t partial_floats, void* stream);
 
 #ifdef __cplusplus

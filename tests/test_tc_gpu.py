@@ -122,15 +122,18 @@ def test_wgrad(lib, MG, NA, E):
     partial = torch.empty(nf, dtype=torch.float32, device="cuda")
     for silu in (0, 1):
         dW = torch.full((MG, NA), float("nan"), device="cuda")
-        rc = lib.aether_dbg_tc_wgrad(P(G), MG, P(ACT), NA, silu, E, P(dW), NA, 0, P(partial), nf, stream())
+        db = torch.full((MG,), float("nan"), device="cuda") if silu else None
+        rc = lib.aether_dbg_tc_wgrad(P(G), MG, P(ACT), NA, silu, E, P(dW), NA, 0, P(db), P(partial), nf, stream())
         assert rc == 0, rc
         torch.cuda.synchronize()
+        if db is not None:
+            assert rel_err(db, G.float().sum(0)) < 1e-4
         act = torch.nn.functional.silu(ACT.float()).bfloat16().float() if silu else ACT.float()
         ref = G.float().t() @ act
         assert rel_err(dW, ref) < (5e-3 if silu else 1e-4)
     if NA == 64:
         dW = torch.full((MG, 17), float("nan"), device="cuda")
-        rc = lib.aether_dbg_tc_wgrad(P(G), MG, P(ACT), NA, 0, E, P(dW), 17, 1, P(partial), nf, stream())
+        rc = lib.aether_dbg_tc_wgrad(P(G), MG, P(ACT), NA, 0, E, P(dW), 17, 1, None, P(partial), nf, stream())
         assert rc == 0
         torch.cuda.synchronize()
         ref = G.float().t() @ ACT.float()
@@ -175,11 +178,11 @@ def test_gemm_throughput_report(lib):
     partial = torch.empty(nf, dtype=torch.float32, device="cuda")
     dW = torch.empty(256, 256, device="cuda")
     for silu in (0, 1):
-        lib.aether_dbg_tc_wgrad(P(G), 256, P(A), 256, silu, E, P(dW), 256, 0, P(partial), nf, stream())
+        lib.aether_dbg_tc_wgrad(P(G), 256, P(A), 256, silu, E, P(dW), 256, 0, P(dW), P(partial), nf, stream())
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for _ in range(5):
-            lib.aether_dbg_tc_wgrad(P(G), 256, P(A), 256, silu, E, P(dW), 256, 0, P(partial), nf, stream())
+            lib.aether_dbg_tc_wgrad(P(G), 256, P(A), 256, silu, E, P(dW), 256, 0, P(dW), P(partial), nf, stream())
         b.record()
         torch.cuda.synchronize()
         ms = a.elapsed_time(b) / 5
