@@ -139,6 +139,8 @@ int launch_segsum_bf16(int64_t Nn, int W, const int32_t* ptr, const int32_t* lis
                        float* out, int64_t ldo, cudaStream_t st);
 int launch_edge_dpre2_bf16(int64_t E, int H, const int32_t* recv, const int32_t* rowptr, const void* ge, const float* gy,
                            const void* pre2, void* g, cudaStream_t st);
+// out16[n,:] = bf16(src[n,:] / max(deg(n), 1))   (the mean's backward, gathered per edge by the next GEMM)
+int launch_node_mean_scale_bf16(int64_t Nn, int H, const int32_t* rowptr, const float* src, void* out16, cudaStream_t st);
 int colsum_bf16(const void* A, int64_t lda, int64_t M, int N, float* out, float* partial, size_t partial_floats,
                 cudaStream_t st);
 size_t colsum_bf16_partial_floats(int64_t M, int N);

@@ -106,6 +106,22 @@ __global__ void edge_dpre2_bf16_kernel(int64_t E, int H, const int32_t* __restri
   *reinterpret_cast<uint4*>(g + (size_t)k * H + c) = w;
 }
 
+__global__ void node_mean_scale_bf16_kernel(int64_t Nn, int H, const int32_t* __restrict__ rowptr,
+                                            const float* __restrict__ src, __nv_bfloat16* __restrict__ out) {
+  const int hq = H / 4;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Nn * hq) return;
+  const int64_t n = i / hq;
+  const int c = (int)(i % hq) * 4;
+  const int deg = rowptr[n + 1] - rowptr[n];
+  const float inv = 1.0f / (float)(deg < 1 ? 1 : deg);
+  const float4 v = *reinterpret_cast<const float4*>(src + (size_t)n * H + c);
+  uint2 o;
+  o.x = tc::pack_bf16(v.x * inv, v.y * inv);
+  o.y = tc::pack_bf16(v.z * inv, v.w * inv);
+  *reinterpret_cast<uint2*>(out + (size_t)n * H + c) = o;
+}
+
 constexpr int CS_ROWS = 4096;
 
 // partial[chunk][n] = sum of rows [chunk*CS_ROWS, ...) ; block = 32 column-octets x 8 row lanes
@@ -178,6 +194,14 @@ int launch_edge_dpre2_bf16(int64_t E, int H, const int32_t* recv, const int32_t*
   const int64_t tot = E * (H / 8);
   edge_dpre2_bf16_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(E, H, recv, rowptr, (const __nv_bfloat16*)ge, gy,
                                                                       (const __nv_bfloat16*)pre2, (__nv_bfloat16*)g);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_node_mean_scale_bf16(int64_t Nn, int H, const int32_t* rowptr, const float* src, void* out16, cudaStream_t st) {
+  if (Nn <= 0) return 0;
+  const int64_t tot = Nn * (H / 4);
+  node_mean_scale_bf16_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(Nn, H, rowptr, src, (__nv_bfloat16*)out16);
   AE_LAUNCH_CHECK();
   return 0;
 }

@@ -38,6 +38,77 @@ struct Bwd {
   }
 };
 
+// Edge part of the backward pass on the bf16 tensor-core path, interleaved with the node-level callbacks.
+// Per layer l (top down), with g2_l = dL/dpre2_l already in s.bg2:
+//   B1   g1 = (g2 W2) * silu'(pre1_l)                                   tc_gemm, silu' epilogue
+//   dW2 = g2^T silu(pre1_l), db2 ; dW1e = g1^T silu(pre2_{l-1}) (layer 1: g1^T feat), db1       tc_wgrad
+//   l > 1: segment sums of g1 by sender / receiver -> node terms -> grad of x_{l-1} -> node update of
+//          layer l-1 -> gy_{l-1}; then ONE GEMM produces the next g2 directly:
+//   B2   g2_{l-1} = (g1 We + gy_{l-1}[recv] / deg) * silu'(pre2_{l-1})   gather + silu' epilogue
+// so dL/de_{l-1} is never written to HBM and the separate elementwise pass exists only for the top layer.
+template <class FA, class FP, class FR>
+int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGraph& Gr, float* const* G,
+                      const Workspace& w, const Scratch& s, cudaStream_t st, FA& node_update_bwd, FP& node_terms_bwd,
+                      FR& node_res_bwd) {
+  const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D);
+  const int64_t Nn = d.n_nodes, E = d.n_edges;
+  void* g2 = s.bg2;
+  void* g1 = s.bg1;
+  AE_CHECK(node_update_bwd(4));
+  {
+    ProfScope ps(PROF_EDGE_BWD_DATA, st);
+    AE_CHECK(launch_edge_dpre2_bf16(E, H, Gr.recv, Gr.rowptr, nullptr, s.gy, w.bpre2[4], g2, st));
+  }
+  for (int l = 4; l >= 1; --l) {
+    const LayerSlots sl = layer_slots(l);
+    {
+      ProfScope ps(PROF_EDGE_BWD_DATA, st);
+      AE_CHECK(tc_pack_weight(P[sl.m2w], H, H, H, H, H, 1, 0, s.wtB, st));
+      TcGemmArgs a;
+      a.M = E; a.wpack = s.wtB; a.dsilu = (const __nv_bfloat16*)w.bpre1[l]; a.ldd = H;
+      a.out_bf16 = (__nv_bfloat16*)g1; a.ldo = H;
+      AE_CHECK(tc_gemm(a, g2, H, H, H, TC_TF_NONE, st));
+    }
+    {
+      ProfScope ps(PROF_EDGE_WGRAD, st);
+      AE_CHECK(tc_wgrad(g2, H, H, w.bpre1[l], H, H, TC_TF_SILU, E, G[sl.m2w], H, H, 0, G[sl.m2b], s.partial,
+                        s.partial_floats, st));
+      if (l > 1)
+        AE_CHECK(tc_wgrad(g1, H, H, w.bpre2[l - 1], H, H, TC_TF_SILU, E, G[sl.m0w] + 2 * H, 3 * H, H, 0, G[sl.m0b],
+                          s.partial, s.partial_floats, st));
+      else
+        AE_CHECK(tc_wgrad(g1, H, H, w.feat16, 64, 64, TC_TF_NONE, E, G[sl.m0w], Fe, Fe, 1, G[sl.m0b], s.partial,
+                          s.partial_floats, st));
+    }
+    if (l > 1) {
+      {
+        ProfScope ps(PROF_SEGMENT, st);
+        AE_CHECK(launch_segsum_bf16(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, st));
+        AE_CHECK(launch_segsum_bf16(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, st));
+      }
+      AE_CHECK(node_terms_bwd(l));
+      AE_CHECK(node_update_bwd(l - 1));
+      ProfScope ps(PROF_EDGE_BWD_DATA, st);
+      AE_CHECK(launch_node_mean_scale_bf16(Nn, H, Gr.rowptr, s.gy, s.gyd16, st));
+      AE_CHECK(tc_pack_weight(P[sl.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, s.wtA, st));
+      TcGemmArgs a;
+      a.M = E; a.wpack = s.wtA;
+      a.gat16 = (const __nv_bfloat16*)s.gyd16; a.ldg = H; a.idx_a = Gr.recv;
+      a.dsilu = (const __nv_bfloat16*)w.bpre2[l - 1]; a.ldd = H;
+      a.out_bf16 = (__nv_bfloat16*)g2; a.ldo = H;
+      AE_CHECK(tc_gemm(a, g1, H, H, H, TC_TF_NONE, st));
+    } else {
+      // gfeat[E, 32] = g1 W1 (fp32, consumed by the geometry backward)
+      AE_CHECK(tc_pack_weight(P[sl.m0w], Fe, 32, H, Fe, H, 1, 0, s.wtA, st));
+      TcGemmArgs a;
+      a.M = E; a.wpack = s.wtA; a.out_f32 = s.gfeat; a.ldo32 = 32; a.n_valid = 32;
+      AE_CHECK(tc_gemm(a, g1, H, H, 32, TC_TF_NONE, st));
+      AE_CHECK(node_res_bwd());
+    }
+  }
+  return 0;
+}
+
 int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, const float* x, const float* vel,
              const float* q, const float* dmask, const float* gout, float* const* G, float* gx_out, float* gvel_out,
              const Workspace& w, const Scratch& s, uint32_t flags, cudaStream_t st) {
@@ -63,66 +134,42 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   AE_CHECK(b.dgrad(s.go1, H, Nn, H, P[P_OUT0_W], H, H, gx, H, nullptr, nullptr, nullptr, 0));
   const float* ge = nullptr;   // gradient w.r.t. e_l from layer l+1 (none for the last layer)
   const bool tc = use_tc(d, flags);
-  bool have_ge = false;
   const int ldgf = tc ? 32 : ldf;   // leading dimension of gfeat
 
-  for (int l = 4; l >= 1; --l) {
+  // node part A of layer l: x_l = y + W4 silu(pre3) + b4 ; pre3 = W3 y + b3   (gx -> s.gy)
+  auto node_update_bwd = [&](int l) -> int {
     const LayerSlots sl = layer_slots(l);
-    // x_l = y + W4 silu(pre3) + b4 ; pre3 = W3 y + b3
     AE_CHECK(b.wgrad(gx, H, Nn, H, w.pre3[l], 2 * H, 2 * H, TF_SILU, nullptr, G[sl.u2w], 2 * H, G[sl.u2b]));
     AE_CHECK(b.dgrad(gx, H, Nn, H, P[sl.u2w], 2 * H, 2 * H, s.gpre3, 2 * H, w.pre3[l], nullptr, nullptr, 0));
     AE_CHECK(b.wgrad(s.gpre3, 2 * H, Nn, 2 * H, w.y[l], H, H, TF_NONE, nullptr, G[sl.u0w], H, G[sl.u0b]));
     AE_CHECK(b.dgrad(s.gpre3, 2 * H, Nn, 2 * H, P[sl.u0w], H, H, s.gy, H, nullptr, nullptr, gx, 0));
-    // y = base + mean_recv(silu(pre2)) : broadcast gy / deg over the segment, add grad from layer l+1
-    if (tc) {
-      // ---- bf16 tensor-core path: edge gradients stored as bf16, GEMMs on tcgen05 ----
-      void* g2 = s.bg2;
-      void* g1 = s.bg1;
-      {
-        ProfScope ps(PROF_EDGE_BWD_DATA, st);
-        // g2 = (ge + gy[recv]/deg) * silu'(pre2) ; g1 = (g2 W2) * silu'(pre1)
-        AE_CHECK(launch_edge_dpre2_bf16(E, H, Gr.recv, Gr.rowptr, have_ge ? s.bge : nullptr, s.gy, w.bpre2[l], g2, st));
-        AE_CHECK(tc_pack_weight(P[sl.m2w], H, H, H, H, H, 1, 0, s.wtB, st));
-        TcGemmArgs a;
-        a.M = E; a.wpack = s.wtB; a.dsilu = (const __nv_bfloat16*)w.bpre1[l]; a.ldd = H;
-        a.out_bf16 = (__nv_bfloat16*)g1; a.ldo = H;
-        AE_CHECK(tc_gemm(a, g2, H, H, H, TC_TF_NONE, st));
-      }
-      {
-        ProfScope ps(PROF_EDGE_WGRAD, st);
-        // dW2 = g2^T silu(pre1), db2 = colsum(g2) ; dW1e = g1^T silu(pre2_{l-1}) (or g1^T feat), db1 = colsum(g1)
-        AE_CHECK(tc_wgrad(g2, H, H, w.bpre1[l], H, H, TC_TF_SILU, E, G[sl.m2w], H, H, 0, G[sl.m2b], s.partial,
-                          s.partial_floats, st));
-        if (l > 1)
-          AE_CHECK(tc_wgrad(g1, H, H, w.bpre2[l - 1], H, H, TC_TF_SILU, E, G[sl.m0w] + 2 * H, 3 * H, H, 0, G[sl.m0b],
-                            s.partial, s.partial_floats, st));
-        else
-          AE_CHECK(tc_wgrad(g1, H, H, w.feat16, 64, 64, TC_TF_NONE, E, G[sl.m0w], Fe, Fe, 1, G[sl.m0b], s.partial,
-                            s.partial_floats, st));
-      }
-      if (l > 1) {
-        {
-          ProfScope ps(PROF_EDGE_BWD_DATA, st);
-          // ge_{l-1} = g1 We
-          AE_CHECK(tc_pack_weight(P[sl.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, s.wtA, st));
-          TcGemmArgs a;
-          a.M = E; a.wpack = s.wtA; a.out_bf16 = (__nv_bfloat16*)s.bge; a.ldo = H;
-          AE_CHECK(tc_gemm(a, g1, H, H, H, TC_TF_NONE, st));
-          have_ge = true;
-        }
-        {
-          ProfScope ps(PROF_SEGMENT, st);
-          AE_CHECK(launch_segsum_bf16(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, st));
-          AE_CHECK(launch_segsum_bf16(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, st));
-        }
-      } else {
-        // gfeat[E, 32] = g1 W1 (fp32, consumed by the geometry backward)
-        AE_CHECK(tc_pack_weight(P[sl.m0w], Fe, 32, H, Fe, H, 1, 0, s.wtA, st));
-        TcGemmArgs a;
-        a.M = E; a.wpack = s.wtA; a.out_f32 = s.gfeat; a.ldo32 = 32; a.n_valid = 32;
-        AE_CHECK(tc_gemm(a, g1, H, H, 32, TC_TF_NONE, st));
-      }
-    } else {
+    return 0;
+  };
+  // node terms of layer l > 1: P = x_{l-1} [Ws; Wr]^T from the segment sums s.gpspr ; gx <- grad of x_{l-1}
+  auto node_terms_bwd = [&](int l) -> int {
+    const LayerSlots sl = layer_slots(l);
+    const float* xin = w.xl[l - 1];
+    AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
+    AE_CHECK(b.wgrad(s.gpspr + H, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w] + H, 3 * H, nullptr));
+    AE_CHECK(b.dgrad(s.gpspr, 2 * H, Nn, H, P[sl.m0w], 3 * H, H, gxn, H, nullptr, nullptr, s.gy, 0));
+    AE_CHECK(b.dgrad(s.gpspr + H, 2 * H, Nn, H, P[sl.m0w] + H, 3 * H, H, gxn, H, nullptr, nullptr, nullptr, 1));
+    float* t = gx; gx = gxn; gxn = t;
+    return 0;
+  };
+  // layer 1: y1 = Wres x0 + bres + agg
+  auto node_res_bwd = [&]() -> int {
+    AE_CHECK(b.wgrad(s.gy, H, Nn, H, w.x0, 3 * D, 3 * D, TF_NONE, nullptr, G[P_L1_RES_W], 3 * D, G[P_L1_RES_B]));
+    AE_CHECK(b.dgrad(s.gy, H, Nn, H, P[P_L1_RES_W], 3 * D, 3 * D, s.gx0, 3 * D, nullptr, nullptr, nullptr, 0));
+    return 0;
+  };
+
+  if (tc) {
+    AE_CHECK(backward_edges_tc(d, P, Gr, G, w, s, st, node_update_bwd, node_terms_bwd, node_res_bwd));
+  } else {
+    for (int l = 4; l >= 1; --l) {
+      const LayerSlots sl = layer_slots(l);
+      AE_CHECK(node_update_bwd(l));
+      // y = base + mean_recv(silu(pre2)) : broadcast gy / deg over the segment, add grad from layer l+1
       float* g2 = s.gA;
       float* g1 = s.gB;
       {
@@ -159,18 +206,8 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
         g.A = g1; g.lda = H; g.B = P[sl.m0w]; g.ldb = Fe; g.C = s.gfeat; g.ldc = ldf; g.M = E; g.N = Fe; g.K = H;
         AE_CHECK(gemm_f32(GEMM_NN, g, st));
       }
-    }
-    if (l > 1) {
-      const float* xin = w.xl[l - 1];
-      AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
-      AE_CHECK(b.wgrad(s.gpspr + H, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w] + H, 3 * H, nullptr));
-      AE_CHECK(b.dgrad(s.gpspr, 2 * H, Nn, H, P[sl.m0w], 3 * H, H, gxn, H, nullptr, nullptr, s.gy, 0));
-      AE_CHECK(b.dgrad(s.gpspr + H, 2 * H, Nn, H, P[sl.m0w] + H, 3 * H, H, gxn, H, nullptr, nullptr, nullptr, 1));
-      float* t = gx; gx = gxn; gxn = t;
-    } else {
-      // y1 = Wres x0 + bres + agg
-      AE_CHECK(b.wgrad(s.gy, H, Nn, H, w.x0, 3 * D, 3 * D, TF_NONE, nullptr, G[P_L1_RES_W], 3 * D, G[P_L1_RES_B]));
-      AE_CHECK(b.dgrad(s.gy, H, Nn, H, P[P_L1_RES_W], 3 * D, 3 * D, s.gx0, 3 * D, nullptr, nullptr, nullptr, 0));
+      if (l > 1) AE_CHECK(node_terms_bwd(l));
+      else AE_CHECK(node_res_bwd());
     }
   }
 

@@ -108,6 +108,22 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_arrive_expect_tx(bar_raw + 8 * s, kSlotBytes);
           tma_load_2d(sA + s * kSlotBytes, &tmA, c * 64, (int)(t * kTileM), bar_raw + 8 * s);
         }
+        if (STAGED && g.dsilu) {
+          // the epilogue of this tile reads the same rows of the aux tensor: pull them into L2 now
+          const int64_t tp = t + gridDim.x;
+          if (tp < n_tiles) {
+            const char* p0 = reinterpret_cast<const char*>(g.dsilu + (size_t)tp * kTileM * g.ldd);
+            const int64_t rows_left = g.M - tp * kTileM;
+            const int nrow = rows_left < kTileM ? (int)rows_left : kTileM;
+            if (g.ldd == N) {
+              asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p0), "r"((uint32_t)(nrow * N * 2)) : "memory");
+            } else {
+              for (int r = 0; r < nrow; ++r)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
+                             :: "l"(p0 + (size_t)r * g.ldd * 2), "r"((uint32_t)(N * 2)) : "memory");
+            }
+          }
+        }
       }
     }
   } else if (warp == 5) {
@@ -172,7 +188,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int64_t row0 = t * kTileM + warp * 32;
       const int64_t row = row0 + lane;
       int ia = 0, ib = 0;
-      if (g.gat16 && row < g.M) { ia = g.idx_a[row]; ib = g.idx_b[row]; }
+      if (g.gat16 && row < g.M) { ia = g.idx_a[row]; ib = g.idx_b ? g.idx_b[row] : 0; }
       const int64_t zrow = row < g.M ? row : g.M - 1;     // rows past the end read valid memory, TMA clips them
 #pragma unroll 1
       for (int jj = 0; jj < N / 64; ++jj, ++nbox) {
@@ -190,28 +206,41 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           float v[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
+          // epilogue operands: 64 contiguous bytes per row and source, all loads issued before use
+          uint4 a4[4], b4[4], z4[4];
+          const bool has_b = g.gat16 && g.idx_b;
           if (g.gat16) {
-            // node terms of the factorised first Linear: 64 contiguous bytes per row and source
             const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia * g.ldg + c0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) a4[q] = __ldg(pa + q);
+          }
+          if (has_b) {
             const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ib * g.ldg + g.goff_b + c0);
-            uint4 a4[4], b4[4];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) { a4[q] = __ldg(pa + q); b4[q] = __ldg(pb + q); }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w}, bb[4] = {b4[q].x, b4[q].y, b4[q].z, b4[q].w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                v[8 * q + 2 * e] += bf16_lo(aa[e]) + bf16_lo(bb[e]);
-                v[8 * q + 2 * e + 1] += bf16_hi(aa[e]) + bf16_hi(bb[e]);
-              }
-            }
+            for (int q = 0; q < 4; ++q) b4[q] = __ldg(pb + q);
           }
           if (g.dsilu) {
             const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow * g.ldd + c0);
-            uint4 z4[4];
 #pragma unroll
             for (int q = 0; q < 4; ++q) z4[q] = __ldg(pd + q);
+          }
+          if (g.gat16) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(aa[e]); v[8 * q + 2 * e + 1] += bf16_hi(aa[e]); }
+            }
+          }
+          if (has_b) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t bb[4] = {b4[q].x, b4[q].y, b4[q].z, b4[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
+            }
+          }
+          if (g.dsilu) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const uint32_t zz[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
