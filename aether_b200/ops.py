@@ -78,7 +78,14 @@ class AetherStepFn(torch.autograd.Function):
         graph = ctx.graph
         dims = _dims(D, H, graph)
         grad_out = _f32c(grad_out)
-        grads = [torch.empty_like(p) for p in params]
+        # all 47 gradients are views of ONE buffer (state_dict order): the data-parallel all-reduce runs on it
+        # in place (aether_b200.dist.allreduce_grads).  Views start 16-byte aligned (float4 stores); the pad words stay zero.
+        offs, tot = [], 0
+        for p in params:
+            offs.append(tot)
+            tot += (p.numel() + 3) // 4 * 4
+        flat = torch.zeros(tot, dtype=torch.float32, device=x.device)
+        grads = [flat[o:o + p.numel()].view_as(p) for o, p in zip(offs, params)]
         gx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
         gv = torch.empty_like(vel) if ctx.needs_input_grad[1] else None
         nbytes = lib.aether_backward_scratch_bytes(ctypes.byref(dims), ctx.flags)

@@ -171,7 +171,7 @@ def main():
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--hidden", type=int, default=0)
     ap.add_argument("--batch", type=int, default=0, help="graphs per GPU (default: the workload's)")
-    ap.add_argument("--precision", default=os.environ.get("AETHER_B200_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("AETHER_B200_PRECISION", "bf16"), choices=["fp32", "bf16"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -220,16 +220,10 @@ def main():
         model.eval()
         roll = ab.Rollout(model, Nn, T, edges=(send, recv), cuda_graph=True)
 
+    from aether_b200 import dist as adist
+
     def allreduce_grads():
-        if world == 1:
-            return
-        flat = torch.cat([p.grad.reshape(-1) for p in params])
-        dist.all_reduce(flat)
-        flat.div_(world)
-        off = 0
-        for p in params:
-            p.grad.copy_(flat[off:off + p.numel()].view_as(p.grad))
-            off += p.numel()
+        adist.allreduce_grads(params, world)     # ONE in-place all-reduce of the flat gradient buffer
 
     def step_resident():
         if not train:
