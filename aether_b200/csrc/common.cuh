@@ -66,7 +66,7 @@ struct GemmArgs {
   // epilogue (NT/NN only; applied in this order)
   const float* bias = nullptr;            // + bias[n]
   const float* gat = nullptr; int64_t ldg = 0;  // + gat[idx_a[m]*ldg + n] + gat[idx_b[m]*ldg + goff_b + n]
-  const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int goff_b = 0;
+  const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int64_t goff_b = 0;
   const float* res = nullptr; int64_t ldr = 0;  // + res[m*ldr + n]
   const float* dsilu = nullptr; int64_t ldd = 0;  // * silu'(dsilu[m*ldd+n])
   const float* emask = nullptr; int64_t ldm = 0;  // * emask[m*ldm+n]

@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(NT, 2) gemm_kernel(GemmArgs g, int64_t k_chunk
         continue;
       }
       if (g.bias) v += g.bias[n];
-      if (g.gat) v += g.gat[(size_t)ia * g.ldg + n] + g.gat[(size_t)ib * g.ldg + g.goff_b + n];
+      if (g.gat) v += g.gat[(size_t)ia * g.ldg + n] + g.gat[(int64_t)ib * g.ldg + g.goff_b + n];
       if (g.res) v += g.res[(size_t)m * g.ldr + n];
       if (g.dsilu) v *= dsilu_f(g.dsilu[(size_t)m * g.ldd + n]);
       if (g.emask) v *= g.emask[(size_t)m * g.ldm + n];

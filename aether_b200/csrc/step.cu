@@ -193,58 +193,67 @@ int linear(const NodeTc& nc, const float* A, int64_t lda, int64_t M, int K, cons
   return gemm_f32(GEMM_NT, g, st);
 }
 
+// Row range and phase selection for the receiver-partitioned step.  Default: everything.
+//   phase p (0..3) = message-passing layer p+1 on the local edges, its node update on the owned rows and -- for
+//   p < 3 -- the node terms of the next layer: P_s[owned] into the exchange buffer (all-gathered by the caller
+//   before the next phase), P_r[owned] locally.  Phase 0 starts with field / frames (all nodes: senders need them)
+//   and the edge features; phase 3 ends with the out MLP, the rotation back and the Euler update of the owned rows.
+struct Part {
+  int64_t n0 = 0, n1 = -1;      // owned node rows [n0, n1); n1 < 0: all
+  int phase_lo = 0, phase_hi = 3;
+  void* xchg = nullptr;         // [>= Nn, H] sender terms P_s (fp32, or bf16 on the bf16 path); null: workspace
+};
+
 int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, const float* x, const float* vel,
             const float* q, const float* orig, const float* dmask, float* out, const Workspace& w, uint32_t flags,
-            cudaStream_t st) {
+            cudaStream_t st, const Part& pt = Part()) {
   const int D = d.num_dims, H = d.hidden, Fe = num_edge_feat(D), ldf = edge_feat_ld(D);
   const int64_t Nn = d.n_nodes, E = d.n_edges;
   const bool bf16 = use_tc(d, flags);
+  const int64_t n0 = pt.n0, n1 = pt.n1 < 0 ? Nn : pt.n1, M = n1 - n0;
   NodeTc nc;
   nc.on = bf16; nc.a16 = w.na16; nc.wp = w.nwp;
-  // neural field at the particles (aether.py:127-134)
-  AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
-  AE_CHECK(linear(nc, w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
-                  nullptr, 0, st));
-  AE_CHECK(linear(nc, w.fz1, 32, Nn, 32, P[P_F2_W], 32, P[P_F2_B], 32, w.fz2, 32, TF_SILU, nullptr, nullptr, 0, st));
-  AE_CHECK(linear(nc, w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
-  // local frames and features (aether.py:33-100,177)
-  AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
-  {
-    ProfScope ps(PROF_EDGE_FEAT, st);
-    if (bf16) AE_CHECK(launch_edge_features_hilo(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat16, st));
-    else AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
-  }
-  if (bf16) {
-    // bf16 shared-memory images of the edge-MLP weights (first Linear: per-edge block only; layer 1: the
-    // feature columns repeated for the hi and lo halves of the operand)
-    AE_CHECK(tc_pack_weight(P[P_L1_M0_W], Fe, H, 64, H, Fe, 0, 32, w.wpA[1], st));
-    for (int l = 1; l <= 4; ++l) {
-      const LayerSlots s = layer_slots(l);
-      if (l > 1) AE_CHECK(tc_pack_weight(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 0, 0, w.wpA[l], st));
-      AE_CHECK(tc_pack_weight(P[s.m2w], H, H, H, H, H, 0, 0, w.wpB[l], st));
+  // node terms of the factorised first Linear: two planes of [Nn, H], gathered by sender / receiver
+  float* ps32 = pt.xchg && !bf16 ? (float*)pt.xchg : w.pspr;
+  float* pr32 = w.pspr + (size_t)Nn * H;
+  __nv_bfloat16* ps16 = pt.xchg && bf16 ? (__nv_bfloat16*)pt.xchg : (__nv_bfloat16*)w.pspr16;
+  __nv_bfloat16* pr16 = (__nv_bfloat16*)w.pspr16 + (size_t)Nn * H;
+  if (pt.phase_lo == 0) {
+    // neural field at the particles (aether.py:127-134)
+    AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
+    AE_CHECK(linear(nc, w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
+                    nullptr, 0, st));
+    AE_CHECK(linear(nc, w.fz1, 32, Nn, 32, P[P_F2_W], 32, P[P_F2_B], 32, w.fz2, 32, TF_SILU, nullptr, nullptr, 0, st));
+    AE_CHECK(linear(nc, w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
+    // local frames and features (aether.py:33-100,177)
+    AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
+    {
+      ProfScope ps(PROF_EDGE_FEAT, st);
+      if (bf16) AE_CHECK(launch_edge_features_hilo(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat16, st));
+      else AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
+    }
+    if (bf16) {
+      // bf16 shared-memory images of the edge-MLP weights (first Linear: per-edge block only; layer 1: the
+      // feature columns repeated for the hi and lo halves of the operand)
+      AE_CHECK(tc_pack_weight(P[P_L1_M0_W], Fe, H, 64, H, Fe, 0, 32, w.wpA[1], st));
+      for (int l = 1; l <= 4; ++l) {
+        const LayerSlots s = layer_slots(l);
+        if (l > 1) AE_CHECK(tc_pack_weight(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 0, 0, w.wpA[l], st));
+        AE_CHECK(tc_pack_weight(P[s.m2w], H, H, H, H, H, 0, 0, w.wpB[l], st));
+      }
     }
   }
   // four message-passing layers (locs.py:187-190, 227-243)
-  for (int l = 1; l <= 4; ++l) {
+  for (int l = pt.phase_lo + 1; l <= pt.phase_hi + 1; ++l) {
     const LayerSlots s = layer_slots(l);
     const float* xin = w.xl[l - 1];
-    if (l > 1) {
-      // node-factorised first Linear: [x_s | x_r | e] W^T = x_s Ws^T + x_r Wr^T + e We^T
-      if (bf16) {
-        AE_CHECK(linear_tc_bf16out(nc, xin, H, Nn, H, P[s.m0w], 3 * H, H, w.pspr16, 2 * H, st));
-        AE_CHECK(linear_tc_bf16out(nc, xin, H, Nn, H, P[s.m0w] + H, 3 * H, H, (__nv_bfloat16*)w.pspr16 + H, 2 * H, st));
-      } else {
-      AE_CHECK(linear(nc, xin, H, Nn, H, P[s.m0w], 3 * H, nullptr, H, w.pspr, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
-      AE_CHECK(linear(nc, xin, H, Nn, H, P[s.m0w] + H, 3 * H, nullptr, H, w.pspr + H, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
-      }
-    }
     {
     ProfScope ps(PROF_EDGE_MLP_FWD, st);
     if (bf16) {
       // pre1 = [silu(pre2_{l-1}) | feat] We^T + b1 (+ P_s[send] + P_r[recv]) ; pre2 = silu(pre1) W2^T + b2
       TcGemmArgs a;
       a.M = E; a.wpack = w.wpA[l]; a.bias = P[s.m0b]; a.out_bf16 = (__nv_bfloat16*)w.bpre1[l]; a.ldo = H;
-      if (l > 1) { a.gat16 = (const __nv_bfloat16*)w.pspr16; a.ldg = 2 * H; a.idx_a = G.send; a.idx_b = G.recv; a.goff_b = H; }
+      if (l > 1) { a.gat16 = ps16; a.ldg = H; a.idx_a = G.send; a.idx_b = G.recv; a.goff_b = pr16 - ps16; }
       if (l == 1) AE_CHECK(tc_gemm(a, w.feat16, 64, 64, H, TC_TF_NONE, st));
       else AE_CHECK(tc_gemm(a, w.bpre2[l - 1], H, H, H, TC_TF_SILU, st));
       TcGemmArgs b;
@@ -256,36 +265,54 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
         g.A = w.feat; g.lda = ldf; g.K = Fe; g.B = P[s.m0w]; g.ldb = Fe; g.tf = TF_NONE;
       } else {
         g.A = w.pre2[l - 1]; g.lda = H; g.K = H; g.B = P[s.m0w] + 2 * H; g.ldb = 3 * H; g.tf = TF_SILU;
-        g.gat = w.pspr; g.ldg = 2 * H; g.idx_a = G.send; g.idx_b = G.recv; g.goff_b = H;
+        g.gat = ps32; g.ldg = H; g.idx_a = G.send; g.idx_b = G.recv; g.goff_b = pr32 - ps32;
       }
       g.C = w.pre1[l]; g.ldc = H; g.M = E; g.N = H; g.bias = P[s.m0b];
       AE_CHECK(gemm_f32(GEMM_NT, g, st));
       AE_CHECK(linear(nc, w.pre1[l], H, E, H, P[s.m2w], H, P[s.m2b], H, w.pre2[l], H, TF_SILU, nullptr, nullptr, 0, st));
     }
     }
-    // y = res(x) + mean_recv(silu(pre2))   (locs.py:236-240)
-    const float* base = xin;
+    // y = res(x) + mean_recv(silu(pre2))   (locs.py:236-240), owned rows only
+    const float* base = xin + (size_t)n0 * H;
+    float* y = w.y[l] + (size_t)n0 * H;
     if (l == 1) {
-      AE_CHECK(linear(nc, w.x0, 3 * D, Nn, 3 * D, P[P_L1_RES_W], 3 * D, P[P_L1_RES_B], H, w.y[1], H, TF_NONE, nullptr,
-                      nullptr, 0, st));
-      base = w.y[1];
+      AE_CHECK(linear(nc, w.x0 + (size_t)n0 * 3 * D, 3 * D, M, 3 * D, P[P_L1_RES_W], 3 * D, P[P_L1_RES_B], H, y, H, TF_NONE,
+                      nullptr, nullptr, 0, st));
+      base = y;
     }
     {
       ProfScope ps(PROF_SEGMENT, st);
-      if (bf16) AE_CHECK(launch_segmean_silu_bf16(Nn, H, G.rowptr, w.bpre2[l], H, base, H, w.y[l], H, st));
-      else AE_CHECK(launch_segmean_silu(Nn, H, G.rowptr, w.pre2[l], H, base, H, w.y[l], H, st));
+      if (bf16) AE_CHECK(launch_segmean_silu_bf16(M, H, G.rowptr + n0, w.bpre2[l], H, base, H, y, H, st));
+      else AE_CHECK(launch_segmean_silu(M, H, G.rowptr + n0, w.pre2[l], H, base, H, y, H, st));
     }
     // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
-    AE_CHECK(linear(nc, w.y[l], H, Nn, H, P[s.u0w], H, P[s.u0b], 2 * H, w.pre3[l], 2 * H, TF_NONE, nullptr, nullptr, 0, st));
-    AE_CHECK(linear(nc, w.pre3[l], 2 * H, Nn, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, w.xl[l], H, TF_SILU, nullptr, w.y[l], H, st));
+    float* pre3 = w.pre3[l] + (size_t)n0 * 2 * H;
+    float* xo = w.xl[l] + (size_t)n0 * H;
+    AE_CHECK(linear(nc, y, H, M, H, P[s.u0w], H, P[s.u0b], 2 * H, pre3, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
+    AE_CHECK(linear(nc, pre3, 2 * H, M, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, xo, H, TF_SILU, nullptr, y, H, st));
+    if (l < 4) {
+      // node-factorised first Linear of the next layer: [x_s | x_r | e] W^T = x_s Ws^T + x_r Wr^T + e We^T
+      const LayerSlots sn = layer_slots(l + 1);
+      if (bf16) {
+        AE_CHECK(linear_tc_bf16out(nc, xo, H, M, H, P[sn.m0w], 3 * H, H, ps16 + (size_t)n0 * H, H, st));
+        AE_CHECK(linear_tc_bf16out(nc, xo, H, M, H, P[sn.m0w] + H, 3 * H, H, pr16 + (size_t)n0 * H, H, st));
+      } else {
+        AE_CHECK(linear(nc, xo, H, M, H, P[sn.m0w], 3 * H, nullptr, H, ps32 + (size_t)n0 * H, H, TF_NONE, nullptr, nullptr, 0, st));
+        AE_CHECK(linear(nc, xo, H, M, H, P[sn.m0w] + H, 3 * H, nullptr, H, pr32 + (size_t)n0 * H, H, TF_NONE, nullptr, nullptr, 0, st));
+      }
+    }
   }
+  if (pt.phase_hi < 3) return 0;
   // out MLP (locs.py:160-168,193), globalize and Euler update (local_to_global.py:12-13, aether.py:185)
-  const float* m1 = dmask;
-  const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
-  AE_CHECK(linear(nc, w.xl[4], H, Nn, H, P[P_OUT0_W], H, P[P_OUT0_B], H, w.o1, H, TF_NONE, nullptr, nullptr, 0, st));
-  AE_CHECK(linear(nc, w.o1, H, Nn, H, P[P_OUT3_W], H, P[P_OUT3_B], H, w.o2, H, m1 ? TF_SILU_MASK : TF_SILU, m1, nullptr, 0, st));
-  AE_CHECK(linear(nc, w.o2, H, Nn, H, P[P_OUT6_W], H, P[P_OUT6_B], D, w.pred, D, m2 ? TF_SILU_MASK : TF_SILU, m2, nullptr, 0, st));
-  AE_CHECK(launch_globalize(D, Nn, x, w.R, w.pred, out, st));
+  const float* m1 = dmask ? dmask + (size_t)n0 * H : nullptr;
+  const float* m2 = dmask ? dmask + (size_t)Nn * H + (size_t)n0 * H : nullptr;
+  float* o1 = w.o1 + (size_t)n0 * H;
+  float* o2 = w.o2 + (size_t)n0 * H;
+  float* pred = w.pred + (size_t)n0 * D;
+  AE_CHECK(linear(nc, w.xl[4] + (size_t)n0 * H, H, M, H, P[P_OUT0_W], H, P[P_OUT0_B], H, o1, H, TF_NONE, nullptr, nullptr, 0, st));
+  AE_CHECK(linear(nc, o1, H, M, H, P[P_OUT3_W], H, P[P_OUT3_B], H, o2, H, m1 ? TF_SILU_MASK : TF_SILU, m1, nullptr, 0, st));
+  AE_CHECK(linear(nc, o2, H, M, H, P[P_OUT6_W], H, P[P_OUT6_B], D, pred, D, m2 ? TF_SILU_MASK : TF_SILU, m2, nullptr, 0, st));
+  AE_CHECK(launch_globalize(D, M, x + (size_t)n0 * D, w.R + (size_t)n0 * D * D, pred, out + (size_t)n0 * D, st));
   return 0;
 }
 

@@ -151,6 +151,34 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+// ---- packed bf16x2 arithmetic (two elements per instruction) ---------------------------------------
+__device__ __forceinline__ uint32_t bf2_add(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("add.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_mul(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_fma(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t bf2_tanh(uint32_t a) {
+  uint32_t d;
+  asm("tanh.approx.bf16x2 %0, %1;" : "=r"(d) : "r"(a));
+  return d;
+}
+// w = 2 silu'(z) - 1 = t + h (1 - t^2) for a pair, h = z/2, t = tanh(h)
+__device__ __forceinline__ uint32_t bf2_dsilu_w(uint32_t z) {
+  const uint32_t h = bf2_mul(z, 0x3F003F00u);
+  const uint32_t t = bf2_tanh(h);
+  const uint32_t u = bf2_fma(t, t ^ 0x80008000u, 0x3F803F80u);
+  return bf2_fma(h, u, t);
+}
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
@@ -158,7 +186,9 @@ __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u 
 
 // ---- host side ---------------------------------------------------------------------------------
 // Row-major bf16 matrix [rows, cols] (leading dimension ld elements) -> tensor map whose box is
-// box_rows x 64 columns with the 128-byte swizzle.  Returns 0 or an error code.
-int tc_make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+// box_rows x box_cols columns: 64 columns with the 128-byte swizzle (operand loads) or 32 columns with the
+// 64-byte swizzle (epilogue stores).  Returns 0 or an error code.
+int tc_make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows,
+                      int box_cols = 64);
 
 }  // namespace aether

@@ -5,15 +5,17 @@
 // This is every Linear of GNNLayer.message_fn (nn/state2state/locs/locs.py:206-212,235) in the bf16
 // path and the data-gradient GEMMs of its backward.  One CTA per SM, warp-specialised:
 //
-//   warp 4      TMA producer : the weight image once (cp.async.bulk), then one 128x64 bf16 box of A
+//   warp 8      TMA producer : the weight image once (cp.async.bulk), then one 128x64 bf16 box of A
 //               per pipeline slot (cp.async.bulk.tensor, 128-byte swizzle = the UMMA K-major layout)
-//   warps 6-9   transform    : optional in-place SiLU on the landed box (the consumer of a stored
+//   warps 10-13 transform    : optional in-place SiLU on the landed box (the consumer of a stored
 //               pre-activation applies the activation, so activations are never written to HBM)
-//   warp 5      MMA issuer   : one thread, tcgen05.mma 128 x N x 16 per instruction, fp32
+//   warp 9      MMA issuer   : one thread, tcgen05.mma 128 x N x 16 per instruction, fp32
 //               accumulators in TMEM, two accumulators ping-pong between MMA and epilogue
-//   warps 0-3   epilogue     : tcgen05.ld (one output row per thread), + bias, + gathered node terms
+//   warps 0-7   epilogue     : two warps per TMEM lane quarter (warp & 3), alternating 32-column chunks;
+//               tcgen05.ld (one output row per thread), + bias, + gathered node terms
 //               P_s[send] + P_r[recv] (node-factorised first Linear), x silu'(saved pre-activation)
-//               for the backward chain, bf16 or fp32 store
+//               for the backward chain, bf16 (32x32 boxes staged in shared memory, TMA store) or fp32 store.
+//               Two warps per scheduler hide each other's TMEM / global-load latency.
 //
 // Shared memory: weights N*K*2 bytes resident for the whole kernel (128 KB at N=K=256), the rest is
 // the A ring (16 KB per slot, 6 slots at N=K=256).  HBM traffic per row: 2K bytes in, 2N bytes out.
@@ -27,14 +29,16 @@ namespace {
 
 using namespace tc;
 
-constexpr int kThreads = 320;
+constexpr int kThreads = 448;
+constexpr int kEpiWarps = 8;
+constexpr int kWarpTma = 8, kWarpMma = 9, kWarpTf0 = 10;
 constexpr int kTileM = 128;
 constexpr int kSlotBytes = kTileM * 128;          // 128 rows x 64 bf16
 constexpr int kSmemMax = 232448;                  // 227 KB
 constexpr int kMiscBytes = 2048;                  // barriers + tmem pointer + bias
 
 __host__ __device__ constexpr int weight_bytes(int K, int N) { return K * N * 2; }
-constexpr int kStageBytes = 4 * 2 * 4096;         // bf16 epilogue: per warp two 32-row x 64-column boxes
+constexpr int kStageBytes = kEpiWarps * 2 * 2048; // bf16 epilogue: per warp two 32-row x 32-column boxes
 __host__ __device__ constexpr int num_slots(int K, int N, bool staged) {
   int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N) - (staged ? kStageBytes : 0)) / kSlotBytes;
   return s > 8 ? 8 : s;
@@ -80,21 +84,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(bar_accf + 8 * a, 1);
-      mbar_init(bar_acce + 8 * a, 4);
+      mbar_init(bar_acce + 8 * a, kEpiWarps);
     }
     mbar_init(bar_w, 1);
     fence_mbar_init();
   }
   if (threadIdx.x < N) sbias[threadIdx.x] = g.bias ? g.bias[threadIdx.x] : 0.0f;
-  if (warp == 5) tmem_alloc(tmem_slot, tmem_cols(N));
-  if (warp == 4 && lane == 0) { tma_prefetch_desc(&tmA); if (STAGED) tma_prefetch_desc(&tmO); }
+  if (warp == kWarpMma) tmem_alloc(tmem_slot, tmem_cols(N));
+  if (warp == kWarpTma && lane == 0) { tma_prefetch_desc(&tmA); if (STAGED) tma_prefetch_desc(&tmO); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  if (warp == 4) {
+  if (warp == kWarpTma) {
     // ===== TMA producer =====
     if (lane == 0) {
       mbar_arrive_expect_tx(bar_w, weight_bytes(K, N));
@@ -108,25 +112,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_arrive_expect_tx(bar_raw + 8 * s, kSlotBytes);
           tma_load_2d(sA + s * kSlotBytes, &tmA, c * 64, (int)(t * kTileM), bar_raw + 8 * s);
         }
-        if (STAGED && g.dsilu) {
-          // the epilogue of this tile reads the same rows of the aux tensor: pull them into L2 now
-          const int64_t tp = t + gridDim.x;
-          if (tp < n_tiles) {
-            const char* p0 = reinterpret_cast<const char*>(g.dsilu + (size_t)tp * kTileM * g.ldd);
-            const int64_t rows_left = g.M - tp * kTileM;
-            const int nrow = rows_left < kTileM ? (int)rows_left : kTileM;
-            if (g.ldd == N) {
-              asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p0), "r"((uint32_t)(nrow * N * 2)) : "memory");
-            } else {
-              for (int r = 0; r < nrow; ++r)
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
-                             :: "l"(p0 + (size_t)r * g.ldd * 2), "r"((uint32_t)(N * 2)) : "memory");
-            }
-          }
-        }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == kWarpMma) {
     // ===== MMA issuer =====
     if (lane == 0) {
       mbar_wait(bar_w, 0);
@@ -151,10 +139,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         umma_commit(bar_accf + 8 * acc);
       }
     }
-  } else if (warp >= 6) {
+  } else if (warp >= kWarpTf0) {
     // ===== transform: in-place SiLU on the landed A box =====
     if (TF != TC_TF_NONE) {
-      const int tt = threadIdx.x - 192;           // 0..127
+      const int tt = threadIdx.x - kWarpTf0 * 32; // 0..127
       uint32_t it = 0;
       for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         for (int c = 0; c < KC; ++c, ++it) {
@@ -178,52 +166,110 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (STAGED) {
     // ===== epilogue, bf16 output: TMEM -> registers (one row per thread) -> swizzled shared staging
     //       -> TMA store; gathered node terms and the silu' factor are applied in registers =====
-    // Each warp owns two 32-row x 64-column staging boxes (4 KB each), so only __syncwarp is needed.
-    const uint32_t sbuf = sStage + warp * 8192;
+    // Each warp owns two 32-row x 32-column staging boxes (2 KB each, 64-byte swizzle), so only
+    // __syncwarp is needed.  Warps w and w+4 share a lane quarter and take alternate column chunks.
+    const int qr = warp & 3, hf = warp >> 2;
+    const uint32_t sbuf = sStage + warp * 4096;
     uint32_t lt = 0, nbox = 0;
+    const bool has_b = g.gat16 && g.idx_b;      // tc_gemm() rejects idx_b together with dsilu: they share a slot
+    // Every epilogue operand of a chunk (64 contiguous bytes per row and source) is requested ONE CHUNK AHEAD,
+    // also across tiles, so its L2 / HBM latency is covered by the previous chunk's work.  Two register slots:
+    // xn = gathered row idx_a, yn = gathered row idx_b or the silu' rows.
+    uint4 xn[4], yn[4];
+    int ia_n = 0, ib_n = 0;
+    auto request = [&](int ia_, int ib_, int64_t zrow_, int c) {
+      if (g.gat16) {
+        const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) xn[q] = __ldg(pa + q);
+      }
+      if (has_b) {
+        const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
+#pragma unroll
+        for (int q = 0; q < 4; ++q) yn[q] = __ldg(pb + q);
+      } else if (g.dsilu) {
+        const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow_ * g.ldd + c);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) yn[q] = __ldg(pd + q);
+      }
+    };
+    if ((int64_t)blockIdx.x < n_tiles) {
+      const int64_t r0 = (int64_t)blockIdx.x * kTileM + qr * 32 + lane;
+      if (g.gat16 && r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b ? g.idx_b[r0] : 0; }
+      request(ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32);
+    }
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
       const uint32_t acc = lt & 1;
+      const int64_t row0 = t * kTileM + qr * 32;
+      const int64_t row = row0 + lane;
+      const int ia = ia_n, ib = ib_n;
+      const int64_t zrow = row < g.M ? row : g.M - 1;     // rows past the end read valid memory, TMA clips them
+      const int64_t tn = t + gridDim.x;
+      const int64_t row_n = row + (int64_t)gridDim.x * kTileM;
+      const int64_t zrow_n = row_n < g.M ? row_n : g.M - 1;
+      ia_n = 0; ib_n = 0;
+      if (g.gat16 && tn < n_tiles && row_n < g.M) { ia_n = g.idx_a[row_n]; ib_n = g.idx_b ? g.idx_b[row_n] : 0; }
       mbar_wait(bar_accf + 8 * acc, (lt >> 1) & 1);
       tc_fence_after();
-      const int64_t row0 = t * kTileM + warp * 32;
-      const int64_t row = row0 + lane;
-      int ia = 0, ib = 0;
-      if (g.gat16 && row < g.M) { ia = g.idx_a[row]; ib = g.idx_b ? g.idx_b[row] : 0; }
-      const int64_t zrow = row < g.M ? row : g.M - 1;     // rows past the end read valid memory, TMA clips them
 #pragma unroll 1
-      for (int jj = 0; jj < N / 64; ++jj, ++nbox) {
-        const uint32_t buf = sbuf + (nbox & 1) * 4096;
+      for (int j = hf; j < N / 32; j += 2, ++nbox) {
+        const uint32_t buf = sbuf + (nbox & 1) * 2048;
+        const int c0 = j * 32;
+        uint4 a4[4], z4[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { a4[q] = xn[q]; z4[q] = yn[q]; }
+        if (j + 2 < N / 32) request(ia, ib, zrow, c0 + 64);
+        else if (tn < n_tiles) request(ia_n, ib_n, zrow_n, hf * 32);
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + c0, r);
         // the TMA store that read this buffer two boxes ago must have finished reading it
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncwarp();
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t r[32];
-          tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + acc * N + jj * 64 + h * 32, r);
-          tmem_ld_wait();
-          const float* bs = sbias + jj * 64 + h * 32;
-          const int c0 = jj * 64 + h * 32;
-          float v[32];
+        tmem_ld_wait();
+        if (j + 2 >= N / 32) {
+          // accumulator fully read by this warp: hand it back to the MMA warp before the slow part
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_acce + 8 * acc);
+        }
+        float v[32];
+        if (g.bias) {
+          const float* bs = sbias + c0;
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
-          // epilogue operands: 64 contiguous bytes per row and source, all loads issued before use
-          uint4 a4[4], b4[4], z4[4];
-          const bool has_b = g.gat16 && g.idx_b;
-          if (g.gat16) {
-            const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia * g.ldg + c0);
+        } else {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) a4[q] = __ldg(pa + q);
-          }
-          if (has_b) {
-            const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ib * g.ldg + g.goff_b + c0);
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+        }
+        if (has_b) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) b4[q] = __ldg(pb + q);
-          }
-          if (g.dsilu) {
-            const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow * g.ldd + c0);
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t bb[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
 #pragma unroll
-            for (int q = 0; q < 4; ++q) z4[q] = __ldg(pd + q);
+            for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
           }
+        }
+        if (g.dsilu) {
+          // backward chain: out = (acc [+ gathered term]) * silu'(z).  w = 2 silu'(z) - 1 = t + h (1 - t^2)
+          // (h = z/2, t = tanh h, |w| <= 1.2) is evaluated two elements per instruction in bf16x2; the product
+          // with the fp32 accumulator stays in fp32: out = v/2 + (v/2) w.
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t zz[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
+            const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+            uint32_t o[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t w = bf2_dsilu_w(zz[e]);
+              float v0 = v[8 * q + 2 * e], v1 = v[8 * q + 2 * e + 1];
+              if (g.gat16) { v0 += bf16_lo(aa[e]); v1 += bf16_hi(aa[e]); }
+              v0 *= 0.5f; v1 *= 0.5f;
+              o[e] = pack_bf16(fmaf(v0, bf16_lo(w), v0), fmaf(v1, bf16_hi(w), v1));
+            }
+            const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+          }
+        } else {
           if (g.gat16) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -232,45 +278,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(aa[e]); v[8 * q + 2 * e + 1] += bf16_hi(aa[e]); }
             }
           }
-          if (has_b) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint32_t bb[4] = {b4[q].x, b4[q].y, b4[q].z, b4[q].w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
-            }
-          }
-          if (g.dsilu) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint32_t zz[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                v[8 * q + 2 * e] *= dsilu_fast(bf16_lo(zz[e]));
-                v[8 * q + 2 * e + 1] *= dsilu_fast(bf16_hi(zz[e]));
-              }
-            }
-          }
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             uint32_t o[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) o[e] = pack_bf16(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
-            const uint32_t addr = buf + lane * 128 + (((h * 4 + q) ^ (lane & 7)) << 4);
+            const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
           }
-        }
-        if (jj == N / 64 - 1) {
-          // accumulator fully read: hand it back to the MMA warp before the slow part
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_acce + 8 * acc);
         }
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0 && row0 < g.M) {
           asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
-                       :: "l"((uint64_t)&tmO), "r"(jj * 64), "r"((int)row0), "r"(buf) : "memory");
+                       :: "l"((uint64_t)&tmO), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
         }
         if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
@@ -283,12 +304,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t acc = lt & 1;
       mbar_wait(bar_accf + 8 * acc, (lt >> 1) & 1);
       tc_fence_after();
-      const int64_t row = t * kTileM + warp * 32 + lane;
+      const int qr = warp & 3;
+      const int64_t row = t * kTileM + qr * 32 + lane;
       const bool live = row < g.M;
 #pragma unroll 1
-      for (int j = 0; j < N / 32; ++j) {
+      for (int j = warp >> 2; j < N / 32; j += 2) {
         uint32_t r[32];
-        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + acc * N + j * 32, r);
+        tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + j * 32, r);
         tmem_ld_wait();
         if (!live) continue;
         float v[32];
@@ -344,7 +366,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == kWarpMma) {
     tc_fence_after();
     tmem_dealloc(tmem_base, tmem_cols(N));
   }
@@ -437,7 +459,8 @@ int tc_sm_count() {
   return sms;
 }
 
-int tc_make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows) {
+int tc_make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_rows,
+                      int box_cols) {
   typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -450,13 +473,15 @@ int tc_make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t 
     if (!p || q != cudaDriverEntryPointSuccess) return AETHER_E_UNSUPPORTED;
     fn = (EncodeFn)p;
   }
-  if (rows <= 0 || cols < 64 || (ld * 2) % 16 || ((uintptr_t)base & 15)) return AETHER_E_BADARG;
+  if (rows <= 0 || (box_cols != 64 && box_cols != 32) || cols < box_cols || (ld * 2) % 16 || ((uintptr_t)base & 15))
+    return AETHER_E_BADARG;
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : AETHER_E_BADARG;
 }
@@ -494,10 +519,11 @@ int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int t
   if (staged == (g.out_f32 != nullptr)) return AETHER_E_BADARG;
   if (staged && (N < 64 || g.res || g.dsilu32 || g.emask || g.accumulate)) return AETHER_E_BADARG;
   if (!staged && (g.gat16 || g.dsilu)) return AETHER_E_BADARG;
+  if (g.idx_b && g.dsilu) return AETHER_E_BADARG;   // the second gathered row and the silu' rows share a register slot
   CUtensorMap tm, to;
   memset(&to, 0, sizeof(to));
   AE_CHECK(tc_make_tmap_bf16(&tm, A, g.M, K, lda, kTileM));
-  if (staged) AE_CHECK(tc_make_tmap_bf16(&to, g.out_bf16, g.M, N, g.ldo, 32));
+  if (staged) AE_CHECK(tc_make_tmap_bf16(&to, g.out_bf16, g.M, N, g.ldo, 32, 32));
 #define AE_TC_CASE(KK, NN) if (K == KK && N == NN) return launch_kn<KK, NN>(g, tm, to, tf, staged, st);
   AE_TC_CASE(256, 256) AE_TC_CASE(256, 32) AE_TC_CASE(64, 256)
   AE_TC_CASE(128, 128) AE_TC_CASE(128, 32) AE_TC_CASE(64, 128)

@@ -13,7 +13,7 @@ struct TcGemmArgs {
   const float* bias = nullptr;         // [N] or null
   // bf16-output epilogue only: + gat16[idx_a[m]*ldg + n] + gat16[idx_b[m]*ldg + goff_b + n]
   const __nv_bfloat16* gat16 = nullptr; int64_t ldg = 0;
-  const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int goff_b = 0;
+  const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int64_t goff_b = 0;  // goff_b: element offset of the second plane
   // bf16-output epilogue only: * silu'(dsilu[m*ldd + n])
   const __nv_bfloat16* dsilu = nullptr; int64_t ldd = 0;
   // fp32-output epilogue only (node-level Linears), applied in this order:

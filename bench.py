@@ -35,7 +35,32 @@ WORKLOADS = {
     "c2b": dict(D=3, N=20, B=128, H=64, mode="train", T=1, name="lorentz dynamic_20body shape, batch 128, train step"),
     "c2": dict(D=3, N=5, B=128, H=64, mode="train", T=1, name="config2: gravitational 3D, 5 particles, batch 128, train step"),
     "c1": dict(D=2, N=5, B=16, H=64, mode="rollout", T=20, name="config1: electrostatic 2D, 5 particles, batch 16, 20-step rollout"),
+    "c3": dict(D=2, N=0, B=256, H=64, mode="rollout", T=12, knn=10,
+               name="config3: inD-style scenes, 10-40 agents (seed 1), kNN k=10 rebuilt every step, 256 scenes per GPU, 12-step rollout"),
 }
+
+
+def scene_sizes(cfg, rank=0):
+    """Agents per scene: N for the fixed-size workloads, U{10..40} (seed 1 + rank) for the inD-style one."""
+    if cfg["N"]:
+        return [cfg["N"]] * cfg["B"]
+    g = torch.Generator().manual_seed(1 + rank)
+    return [int(v) for v in torch.randint(10, 41, (cfg["B"],), generator=g)]
+
+
+def synth_inputs(cfg, sizes, seed):
+    """(x, v, q): the simulators' distributions for the particle workloads; inD-style scenes use positions in the
+    unit square and speeds U(0,1)*0.05 (speed-normalised tracks)."""
+    from oracle import aether_oracle as O
+    D = cfg["D"]
+    if cfg["N"]:
+        return O.synth_state(len(sizes), cfg["N"], D, seed=seed)
+    g = torch.Generator().manual_seed(seed)
+    n = sum(sizes)
+    x = torch.rand(n, D, generator=g)
+    v = (torch.rand(n, D, generator=g) - 0.5) * 0.1
+    q = torch.randint(0, 2, (n, 1), generator=g).float() * 2 - 1
+    return x, v, q
 
 
 def peaks():
@@ -105,7 +130,17 @@ def cpu_step_sample(cfg, H, graphs, seed=1):
     from oracle import aether_oracle as O
     D, N = cfg["D"], cfg["N"]
     p = {k: v.requires_grad_(True) for k, v in O.init_params(D, H, seed).items()}
-    x, v, q = O.synth_state(graphs, N, D, seed=seed)
+    sizes = scene_sizes(cfg)[:graphs]
+    x, v, q = synth_inputs(cfg, sizes, seed)
+    if cfg.get("knn"):
+        k = cfg["knn"]
+        E = sum(n * min(k, max(n - 1, 0)) for n in sizes)
+        T = cfg["T"]
+
+        def kstep():
+            with torch.no_grad():
+                O.rollout(p, x, v, q, lambda xx: O.knn_edges_batched(xx, sizes, k), T)
+        return kstep, E * T
     send, recv = O.fc_edges(N, graphs)
     E = send.numel()
     if cfg["mode"] == "train":
@@ -130,7 +165,7 @@ def cpu_step_sample(cfg, H, graphs, seed=1):
 
 
 def cpu_sample_graphs(cfg, H):
-    E = cfg["N"] * (cfg["N"] - 1)
+    E = cfg["N"] * (cfg["N"] - 1) if cfg["N"] else 25 * cfg.get("knn", 10)
     budget = 4.0e5 * (64.0 / H) ** 2 if cfg["mode"] == "train" else 2.0e6   # edges per sample step
     return int(max(1, min(cfg["B"], budget // max(E, 1))))
 
@@ -168,7 +203,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))   # c5: see --workload c5 below
     ap.add_argument("--hidden", type=int, default=0)
     ap.add_argument("--batch", type=int, default=0, help="graphs per GPU (default: the workload's)")
     ap.add_argument("--precision", default=os.environ.get("AETHER_B200_PRECISION", "bf16"), choices=["fp32", "bf16"])
@@ -201,15 +236,21 @@ def main():
     D, N, B, T = cfg["D"], cfg["N"], cfg["B"], cfg["T"]
     torch.manual_seed(1)
     model = ab.Aether(2 * D, H, 0.0, D, device=dev, precision=args.precision)
-    x, v, q = O.synth_state(B, N, D, seed=1 + rank)
+    sizes = scene_sizes(cfg, rank)
+    x, v, q = synth_inputs(cfg, sizes, 1 + rank)
     target = x + 0.05 * torch.randn(x.shape, generator=torch.Generator().manual_seed(7 + rank))
     Nn = x.shape[0]
     host = [t.pin_memory() for t in (x, v, q, target)]
     xd, vd, qd, td = [t.to(dev) for t in host]
     qd1 = qd.reshape(-1)
-    send, recv = ab.fc_edges(N, B, dev)
-    E = int(send.numel())
-    graph = ab.PreparedGraph(send, recv, Nn)
+    plan = None
+    if cfg.get("knn"):
+        plan = ab.KnnPlan(sizes, cfg["knn"], dev)
+        E, send, recv, graph = plan.n_edges, None, None, None
+    else:
+        send, recv = ab.fc_edges(N, B, dev)
+        E = int(send.numel())
+        graph = ab.PreparedGraph(send, recv, Nn)
     train = cfg["mode"] == "train"
     params = model.param_list()
     flat_n = sum(p.numel() for p in params)
@@ -218,7 +259,7 @@ def main():
         model.train()
     else:
         model.eval()
-        roll = ab.Rollout(model, Nn, T, edges=(send, recv), cuda_graph=True)
+        roll = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=True)
 
     from aether_b200 import dist as adist
 
@@ -301,6 +342,10 @@ def main():
         sampler.start()
     total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
     clocks = sampler.stop() if rank == 0 else None
+    if not train:
+        # graph replays carry no library-side event pairs: time the same kernels once more, launched eagerly
+        eager = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=False)
+        _, _, prof = timed(lambda: eager.run(xd, vd, qd1), max(1, min(args.steps, 3)), 1, profile=True)
     e2e = None
     if not args.no_e2e:
         e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
@@ -330,7 +375,7 @@ def main():
                 "avg_ms_per_launch_group": ms_per_layer}
     step_ms = total / args.steps * 1e3
     share = {k: (prof["ms"][i] / args.steps) / step_ms for i, k in
-             enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment", "edge_feat", "node"])}
+             enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment", "edge_feat", "node"])} if train else None
     line = {"metric": "edge_messages_per_sec", "value": value, "unit": "edge-messages/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",

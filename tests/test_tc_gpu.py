@@ -165,7 +165,7 @@ def test_gemm_throughput_report(lib):
                      (M, K, N, silu, ms, 2.0 * M * K * N / ms / 1e9, M * (K + N) * 2 / ms / 1e6))
         a.record()
         for _ in range(5):
-            lib.aether_dbg_tc_gemm(P(A), M, K, K, P(W), K, N, N, K, 0, 0, silu, None, P(gat), 2 * N, P(ia), P(ia), N, P(A),
+            lib.aether_dbg_tc_gemm(P(A), M, K, K, P(W), K, N, N, K, 0, 0, silu, None, P(gat), 2 * N, P(ia), None, N, P(A),
                                    P(out_bf), None, P(scratch), stream())
         b.record()
         torch.cuda.synchronize()

@@ -11,8 +11,16 @@ timeout 600 python bench.py --hidden 64 --steps 5 --warmup 3 --no-cpu-baseline >
 CMD="python bench.py --batch 64 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e"
 $CMD > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_c4_b64_bf16.csv $CMD > gpurun_out/ncu.log 2>&1
 echo "ncu list rc=$?"; tail -3 gpurun_out/ncu.log
-for k in tc_gemm_kernel tc_wgrad_kernel segreduce_bf16_kernel edge_features_hilo_kernel edge_dpre2_bf16_kernel; do
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k --launch-skip 3 --launch-count 2 -f -o gpurun_out/full_$k $CMD > gpurun_out/ncu_full_$k.log 2>&1
-  echo "ncu full $k rc=$?"
-done
+cap() { # name regex skip   (demangled names: template arguments print as (int)256 / (bool)1)
+  timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:$2" --launch-skip $3 --launch-count 1 -f -o gpurun_out/full_$1 $CMD > gpurun_out/ncu_full_$1.log 2>&1
+  echo "ncu full $1 rc=$?"
+}
+if [ "$1" = "full" ]; then
+CMD="python bench.py --batch 256 --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
+cap gemm_fwd_silu 'tc_gemm_kernel<\(int\)256, \(int\)256, \(int\)1, \(bool\)1>' 3
+cap gemm_bwd_dsilu 'tc_gemm_kernel<\(int\)256, \(int\)256, \(int\)0, \(bool\)1>' 9
+cap wgrad_silu 'tc_wgrad_kernel<\(int\)256, \(int\)256, \(int\)1>' 2
+cap segmean 'segreduce_bf16_kernel' 1
+cap feat 'edge_features_hilo_kernel' 0
+fi
 ls -la gpurun_out

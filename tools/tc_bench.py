@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""Micro-benchmark of the tcgen05 GEMM kernel in the shapes the train step uses (H=256)."""
+import ctypes, os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from aether_b200 import _lib
+lib = _lib.load(build_if_missing=False)
+P = lambda t: None if t is None else ctypes.c_void_p(t.data_ptr())
+stream = lambda: ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+H = int(os.environ.get("H", 256))
+M = 128 * 148 * 64
+A = torch.randn(M, H, device="cuda").bfloat16()
+Z = torch.randn(M, H, device="cuda").bfloat16()
+W = torch.randn(H, H, device="cuda") / 16
+out = torch.empty(M, H, dtype=torch.bfloat16, device="cuda")
+scratch = torch.empty(H * H * 2, dtype=torch.uint8, device="cuda")
+Nn = M // 99 + 1
+gat = torch.randn(Nn, 2 * H, device="cuda").bfloat16()
+recv = torch.arange(M, device="cuda", dtype=torch.int32) // 99
+send = ((torch.arange(M, device="cuda", dtype=torch.int32) % 99) + (recv // 100) * 100).clamp(max=Nn - 1)
+
+def run(name, silu, gat_, ia, ib, z, passes):
+    def call():
+        return lib.aether_dbg_tc_gemm(P(A), M, H, H, P(W), H, H, H, H, 0, 0, silu, None, P(gat_), 2 * H, P(ia), P(ib), H, P(z),
+                                      P(out), None, P(scratch), stream())
+    assert call() == 0
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(5):
+        call()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 5
+    print("%-34s dbg=%s %.3f ms  %.2f us/tile  %.0f GB/s" % (name, os.environ.get("AETHER_TC_DBG", "0"), ms,
+          ms * 1e3 / (M / 128 / 148), M * H * 2 * passes / ms / 1e6), flush=True)
+
+for dbg in os.environ.get("DBGS", "0").split(","):
+    os.environ["AETHER_TC_DBG"] = dbg
+    run("plain", 0, None, None, None, None, 2)
+    run("silu-on-load", 1, None, None, None, None, 2)
+    run("B1: dsilu", 0, None, None, None, Z, 3)
+    run("B2: gather recv + dsilu", 0, gat, recv, None, Z, 3)
+    run("fwdA: silu + gather send,recv", 1, gat, send, recv, None, 2)
