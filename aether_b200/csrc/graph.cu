@@ -174,6 +174,112 @@ __global__ void knn_kernel(const float* __restrict__ pos, int stride, const int3
   }
 }
 
+// ---- radius graph capped at the k nearest, for scenes too large for the brute-force kernel above --------------
+// Uniform cell list with cell edge >= radius: every neighbour within the radius lies in the 3^D cells around the
+// query's cell.  Squared distances are accumulated left to right with separate roundings (no FMA), so they are
+// bit-identical to the numpy restatement in oracle/; candidates are ranked by (d2, index), which makes the result
+// independent of the (atomic) order in which particles were appended to their cells.
+struct CellGrid { float lo[3]; float inv; int dim[3]; int D; };
+
+__device__ __forceinline__ int cell_coord(float p, float lo, float inv, int dim) {
+  int c = (int)floorf(__fmul_rn(__fsub_rn(p, lo), inv));
+  return c < 0 ? 0 : (c >= dim ? dim - 1 : c);
+}
+__device__ __forceinline__ int cell_of(const float* __restrict__ p, const CellGrid& g) {
+  int c = cell_coord(p[0], g.lo[0], g.inv, g.dim[0]) + g.dim[0] * cell_coord(p[1], g.lo[1], g.inv, g.dim[1]);
+  if (g.D == 3) c += g.dim[0] * g.dim[1] * cell_coord(p[2], g.lo[2], g.inv, g.dim[2]);
+  return c;
+}
+
+__global__ void cell_count_kernel(const float* __restrict__ pos, int stride, int64_t n, CellGrid g, int32_t* cell_cnt,
+                                  int32_t* __restrict__ cell_id) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = cell_of(pos + (size_t)i * stride, g);
+  cell_id[i] = c;
+  atomicAdd(&cell_cnt[c], 1);
+}
+
+__global__ void cell_fill_kernel(int64_t n, const int32_t* __restrict__ cell_id, const int32_t* __restrict__ cell_ptr,
+                                 int32_t* fill, int32_t* __restrict__ cell_items) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = cell_id[i];
+  cell_items[cell_ptr[c] + atomicAdd(&fill[c], 1)] = (int32_t)i;
+}
+
+__device__ __forceinline__ bool cand_less(float da, int ja, float db, int jb) { return da < db || (da == db && ja < jb); }
+
+// One warp per query particle; lane l holds the l-th best (d2, index) found so far.
+__global__ void radius_knn_kernel(const float* __restrict__ pos, int stride, int64_t n, CellGrid g, float r2, int k,
+                                  const int32_t* __restrict__ cell_ptr, const int32_t* __restrict__ cell_items,
+                                  int32_t* __restrict__ nbr, int32_t* __restrict__ deg) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (i >= n) return;
+  const float* pi = pos + (size_t)i * stride;
+  const float xi = pi[0], yi = pi[1], zi = g.D == 3 ? pi[2] : 0.0f;
+  const int cx = cell_coord(xi, g.lo[0], g.inv, g.dim[0]);
+  const int cy = cell_coord(yi, g.lo[1], g.inv, g.dim[1]);
+  const int cz = g.D == 3 ? cell_coord(zi, g.lo[2], g.inv, g.dim[2]) : 0;
+  float bd = INFINITY;
+  int bj = 0x7fffffff;
+  const int zlo = g.D == 3 ? cz - 1 : 0, zhi = g.D == 3 ? cz + 1 : 0;
+  for (int z = zlo; z <= zhi; ++z) {
+    if (g.D == 3 && (z < 0 || z >= g.dim[2])) continue;
+    for (int y = cy - 1; y <= cy + 1; ++y) {
+      if (y < 0 || y >= g.dim[1]) continue;
+      // the three x-neighbours are consecutive cells: one contiguous item range
+      const int x0 = cx > 0 ? cx - 1 : 0, x1 = cx + 1 < g.dim[0] ? cx + 1 : g.dim[0] - 1;
+      const int cbase = (z * g.dim[1] + y) * g.dim[0];
+      const int beg = cell_ptr[cbase + x0], end = cell_ptr[cbase + x1 + 1];
+      for (int b = beg; b < end; b += 32) {
+        const int idx = b + lane;
+        float dc = INFINITY;
+        int jc = 0x7fffffff;
+        if (idx < end) {
+          jc = cell_items[idx];
+          const float* pj = pos + (size_t)jc * stride;
+          const float dx = __fsub_rn(xi, pj[0]), dy = __fsub_rn(yi, pj[1]);
+          float d2 = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+          if (g.D == 3) { const float dz = __fsub_rn(zi, pj[2]); d2 = __fadd_rn(d2, __fmul_rn(dz, dz)); }
+          dc = (jc != (int)i && d2 <= r2) ? d2 : INFINITY;
+        }
+        // insert, one at a time, every candidate that beats the current k-th best
+        for (;;) {
+          const float wd = __shfl_sync(0xffffffffu, bd, k - 1);
+          const int wj = __shfl_sync(0xffffffffu, bj, k - 1);
+          const unsigned m = __ballot_sync(0xffffffffu, dc < INFINITY && cand_less(dc, jc, wd, wj));
+          if (!m) break;
+          const int src = __ffs(m) - 1;
+          const float dn = __shfl_sync(0xffffffffu, dc, src);
+          const int jn = __shfl_sync(0xffffffffu, jc, src);
+          if (lane == src) dc = INFINITY;
+          const float du = __shfl_up_sync(0xffffffffu, bd, 1);
+          const int ju = __shfl_up_sync(0xffffffffu, bj, 1);
+          if (cand_less(dn, jn, bd, bj)) {
+            if (lane > 0 && cand_less(dn, jn, du, ju)) { bd = du; bj = ju; }
+            else { bd = dn; bj = jn; }
+          }
+        }
+      }
+    }
+  }
+  const unsigned have = __ballot_sync(0xffffffffu, lane < k && bd < INFINITY);
+  if (lane < k) nbr[(size_t)i * k + lane] = bd < INFINITY ? bj : -1;
+  if (lane == 0) deg[i] = __popc(have);
+}
+
+__global__ void radius_fill_kernel(const int32_t* __restrict__ nbr, const int32_t* __restrict__ off, int64_t n, int k,
+                                   int64_t* __restrict__ send, int64_t* __restrict__ recv) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * k) return;
+  const int64_t i = t / k;
+  const int j = (int)(t % k);
+  const int32_t o = off[i];
+  if (j < off[i + 1] - o) { send[o + j] = i; recv[o + j] = nbr[t]; }
+}
+
 inline unsigned nblk(int64_t n, int b) { return (unsigned)((n + b - 1) / b); }
 
 struct Scratch { int32_t* cnt; int32_t* fill; int32_t* tmp; };
@@ -250,6 +356,77 @@ extern "C" int aether_knn_edges(const float* pos, int32_t pos_stride, const int3
   // shared memory sized for the largest supported scene (1024 agents)
   knn_kernel<<<n_scenes, 64, 1024 * 2 * sizeof(float), (cudaStream_t)stream>>>(pos, pos_stride, node_off, edge_off, k,
                                                                                send, recv);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---- radius graph (large single scenes, BASELINE config 5) ----------------------------------------------------
+namespace {
+struct RadiusScratch { int32_t *cell_cnt, *cell_ptr, *fill, *cell_id, *items, *deg; size_t bytes; };
+RadiusScratch carve_radius(int64_t n, int64_t cells, void* base) {
+  RadiusScratch r;
+  char* p = (char*)base;
+  size_t off = 0;
+  auto take = [&](size_t count) { int32_t* q = (int32_t*)(p + off); off += align_up(count * 4, 256); return q; };
+  r.cell_cnt = take(cells + 1); r.cell_ptr = take(cells + 1); r.fill = take(cells + 1);
+  r.cell_id = take(n > 0 ? n : 1); r.items = take(n > 0 ? n : 1); r.deg = take(n + 1);
+  r.bytes = off;
+  return r;
+}
+bool grid_ok(int32_t D, const int32_t* dim, int64_t* cells) {
+  if (!dim || (D != 2 && D != 3)) return false;
+  int64_t c = 1;
+  for (int a = 0; a < D; ++a) { if (dim[a] < 1) return false; c *= dim[a]; if (c >= ((int64_t)1 << 30)) return false; }
+  *cells = c;
+  return true;
+}
+}  // namespace
+
+extern "C" size_t aether_radius_graph_scratch_bytes(int64_t n, int32_t num_dims, const int32_t* grid_dim) {
+  int64_t cells;
+  if (n < 0 || !grid_ok(num_dims, grid_dim, &cells)) return 0;
+  return carve_radius(n, cells, nullptr).bytes + 256;
+}
+
+extern "C" int aether_radius_graph_neighbors(const float* pos, int32_t pos_stride, int32_t num_dims, int64_t n,
+                                             float radius, float cell_size, int32_t k, const float* box_lo,
+                                             const int32_t* grid_dim, int32_t* nbr, int32_t* off, void* scratch, size_t scratch_bytes,
+                                             void* stream) {
+  int64_t cells;
+  if (n < 0 || n >= ((int64_t)1 << 31) / (k > 0 ? k : 1) || k < 1 || k > 32 || !(radius > 0.0f) || !(cell_size >= radius) || !box_lo ||
+      pos_stride < num_dims || !grid_ok(num_dims, grid_dim, &cells))
+    return AETHER_E_BADARG;
+  if (!scratch || ((uintptr_t)scratch & 255) || scratch_bytes < carve_radius(n, cells, nullptr).bytes) return AETHER_E_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const RadiusScratch s = carve_radius(n, cells, scratch);
+  CellGrid g;
+  g.D = num_dims; g.inv = 1.0f / cell_size;
+  for (int a = 0; a < 3; ++a) { g.lo[a] = a < num_dims ? box_lo[a] : 0.0f; g.dim[a] = a < num_dims ? grid_dim[a] : 1; }
+  AE_CHECK(cudaMemsetAsync(s.cell_cnt, 0, (size_t)(cells + 1) * 4, st));
+  AE_CHECK(cudaMemsetAsync(s.fill, 0, (size_t)(cells + 1) * 4, st));
+  if (n > 0) {
+    cell_count_kernel<<<nblk(n, 256), 256, 0, st>>>(pos, pos_stride, n, g, s.cell_cnt, s.cell_id);
+    AE_LAUNCH_CHECK();
+  }
+  scan_kernel<<<1, 1024, 0, st>>>(s.cell_cnt, cells, s.cell_ptr);
+  AE_LAUNCH_CHECK();
+  if (n > 0) {
+    cell_fill_kernel<<<nblk(n, 256), 256, 0, st>>>(n, s.cell_id, s.cell_ptr, s.fill, s.items);
+    AE_LAUNCH_CHECK();
+    radius_knn_kernel<<<nblk(n * 32, 256), 256, 0, st>>>(pos, pos_stride, n, g, radius * radius, k, s.cell_ptr, s.items,
+                                                         nbr, s.deg);
+    AE_LAUNCH_CHECK();
+  }
+  scan_kernel<<<1, 1024, 0, st>>>(s.deg, n, off);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int aether_radius_graph_fill(const int32_t* nbr, const int32_t* off, int64_t n, int32_t k, int64_t* send,
+                                        int64_t* recv, void* stream) {
+  if (n < 0 || k < 1 || k > 32) return AETHER_E_BADARG;
+  if (n == 0) return 0;
+  radius_fill_kernel<<<nblk(n * k, 256), 256, 0, (cudaStream_t)stream>>>(nbr, off, n, k, send, recv);
   AE_LAUNCH_CHECK();
   return 0;
 }

@@ -201,7 +201,8 @@ int linear(const NodeTc& nc, const float* A, int64_t lda, int64_t M, int K, cons
 struct Part {
   int64_t n0 = 0, n1 = -1;      // owned node rows [n0, n1); n1 < 0: all
   int phase_lo = 0, phase_hi = 3;
-  void* xchg = nullptr;         // [>= Nn, H] sender terms P_s (fp32, or bf16 on the bf16 path); null: workspace
+  const void* xchg_in = nullptr;   // [>= Nn, H] sender terms P_s read by this phase's edge GEMM (fp32 / bf16)
+  void* xchg_out = nullptr;        // ... written (owned rows) for the next phase; null: workspace
 };
 
 int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, const float* x, const float* vel,
@@ -214,9 +215,11 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   NodeTc nc;
   nc.on = bf16; nc.a16 = w.na16; nc.wp = w.nwp;
   // node terms of the factorised first Linear: two planes of [Nn, H], gathered by sender / receiver
-  float* ps32 = pt.xchg && !bf16 ? (float*)pt.xchg : w.pspr;
+  const float* ps32 = pt.xchg_in && !bf16 ? (const float*)pt.xchg_in : w.pspr;
+  float* ps32o = pt.xchg_out && !bf16 ? (float*)pt.xchg_out : w.pspr;
   float* pr32 = w.pspr + (size_t)Nn * H;
-  __nv_bfloat16* ps16 = pt.xchg && bf16 ? (__nv_bfloat16*)pt.xchg : (__nv_bfloat16*)w.pspr16;
+  const __nv_bfloat16* ps16 = pt.xchg_in && bf16 ? (const __nv_bfloat16*)pt.xchg_in : (const __nv_bfloat16*)w.pspr16;
+  __nv_bfloat16* ps16o = pt.xchg_out && bf16 ? (__nv_bfloat16*)pt.xchg_out : (__nv_bfloat16*)w.pspr16;
   __nv_bfloat16* pr16 = (__nv_bfloat16*)w.pspr16 + (size_t)Nn * H;
   if (pt.phase_lo == 0) {
     // neural field at the particles (aether.py:127-134)
@@ -294,10 +297,10 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       // node-factorised first Linear of the next layer: [x_s | x_r | e] W^T = x_s Ws^T + x_r Wr^T + e We^T
       const LayerSlots sn = layer_slots(l + 1);
       if (bf16) {
-        AE_CHECK(linear_tc_bf16out(nc, xo, H, M, H, P[sn.m0w], 3 * H, H, ps16 + (size_t)n0 * H, H, st));
+        AE_CHECK(linear_tc_bf16out(nc, xo, H, M, H, P[sn.m0w], 3 * H, H, ps16o + (size_t)n0 * H, H, st));
         AE_CHECK(linear_tc_bf16out(nc, xo, H, M, H, P[sn.m0w] + H, 3 * H, H, pr16 + (size_t)n0 * H, H, st));
       } else {
-        AE_CHECK(linear(nc, xo, H, M, H, P[sn.m0w], 3 * H, nullptr, H, ps32 + (size_t)n0 * H, H, TF_NONE, nullptr, nullptr, 0, st));
+        AE_CHECK(linear(nc, xo, H, M, H, P[sn.m0w], 3 * H, nullptr, H, ps32o + (size_t)n0 * H, H, TF_NONE, nullptr, nullptr, 0, st));
         AE_CHECK(linear(nc, xo, H, M, H, P[sn.m0w] + H, 3 * H, nullptr, H, pr32 + (size_t)n0 * H, H, TF_NONE, nullptr, nullptr, 0, st));
       }
     }

@@ -62,6 +62,22 @@ extern "C" int aether_step_backward(const AetherDims* dims, const float* const* 
                   flags, (cudaStream_t)stream);
 }
 
+extern "C" int aether_part_forward_phase(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                                         const float* x, const float* vel, const float* charges,
+                                         const float* edge_attr_orig, int64_t own_begin, int64_t own_end, int32_t phase,
+                                         const void* xchg_in, void* xchg_out, float* out, void* workspace, size_t workspace_bytes, uint32_t flags,
+                                         void* stream) {
+  if (!dims_ok(dims) || !params || !graph || phase < 0 || phase > 3 || own_begin < 0 || own_end < own_begin ||
+      own_end > dims->n_nodes || (phase > 0 && !xchg_in) || (phase < 3 && !xchg_out) || (phase == 3 && !out) || (flags & AETHER_F_SAVE_FOR_BACKWARD))
+    return AETHER_E_BADARG;
+  if (!workspace || ((uintptr_t)workspace & 255) || workspace_bytes < carve(*dims, flags, nullptr).bytes)
+    return AETHER_E_WORKSPACE;
+  const Workspace w = carve(*dims, flags, workspace);
+  Part pt;
+  pt.n0 = own_begin; pt.n1 = own_end; pt.phase_lo = pt.phase_hi = phase; pt.xchg_in = xchg_in; pt.xchg_out = xchg_out;
+  return forward(*dims, params, *graph, x, vel, charges, edge_attr_orig, nullptr, out, w, flags, (cudaStream_t)stream, pt);
+}
+
 namespace aether {
 namespace {
 __global__ void silu_copy_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n, int apply) {

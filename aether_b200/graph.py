@@ -117,3 +117,50 @@ def caller_prep(x, vel, charges, send, recv):
                                           _lib.ptr(charges.contiguous()), D, _lib.ptr(send), _lib.ptr(recv), E, Nn,
                                           _lib.ptr(h), _lib.ptr(ea), _stream()), "aether_caller_prep")
     return h, ea
+
+
+def radius_graph(pos: torch.Tensor, radius: float, k: int = 32) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Radius graph capped at the ``k`` nearest neighbours of every sender (k <= 32), sender-major, nearest first
+    (ties toward the lower index), like get_knn_graph_info (experiments/ind/single_ind_data.py:186-217) but built
+    with a uniform cell list so that 100k-particle scenes work (BASELINE config 5).  Returns int64 (send, recv).
+
+    Construction synchronises once (the edge count is read back to size the output)."""
+    lib = _lib.load()
+    if pos.device.type != "cuda":
+        raise RuntimeError("aether_b200 runs on CUDA devices only (no CPU fallback)")
+    pos = pos.contiguous().float()
+    n, D = int(pos.shape[0]), int(pos.shape[1])
+    if D not in (2, 3) or not 1 <= k <= 32:
+        raise ValueError("radius_graph needs 2-D or 3-D positions and 1 <= k <= 32")
+    dev = pos.device
+    if n == 0:
+        z = torch.zeros(0, dtype=torch.int64, device=dev)
+        return z, z.clone()
+    cell = float(radius) * 1.001
+    lo = pos.min(0).values.cpu()
+    hi = pos.max(0).values.cpu()
+    dims = [max(1, int((float(hi[a]) - float(lo[a])) / cell) + 1) for a in range(D)]
+    while True:                                   # keep the cell table small relative to the particle count
+        cells = 1
+        for d in dims:
+            cells *= d
+        if cells <= max(8 * n, 4096):
+            break
+        cell *= 2.0
+        dims = [max(1, int((float(hi[a]) - float(lo[a])) / cell) + 1) for a in range(D)]
+    c_lo = (ctypes.c_float * D)(*[float(v) for v in lo])
+    c_dim = (ctypes.c_int32 * D)(*dims)
+    nbytes = lib.aether_radius_graph_scratch_bytes(n, D, c_dim)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    nbr = torch.empty(n, k, dtype=torch.int32, device=dev)
+    off = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(lib.aether_radius_graph_neighbors(_lib.ptr(pos), pos.stride(0), D, n, float(radius), cell, k, c_lo, c_dim,
+                                                     _lib.ptr(nbr), _lib.ptr(off), _lib.ptr(scratch), nbytes, _stream()),
+                   "aether_radius_graph_neighbors")
+        E = int(off[-1].item())
+        send = torch.empty(E, dtype=torch.int64, device=dev)
+        recv = torch.empty(E, dtype=torch.int64, device=dev)
+        _lib.check(lib.aether_radius_graph_fill(_lib.ptr(nbr), _lib.ptr(off), n, k, _lib.ptr(send), _lib.ptr(recv),
+                                                _stream()), "aether_radius_graph_fill")
+    return send, recv

@@ -1,0 +1,118 @@
+"""Receiver-partitioned inference of ONE large scene across GPUs (BASELINE config 5).
+
+Rank r owns a contiguous block of nodes and every edge whose receiver it owns, so the segmented mean, the node
+MLPs and the output are local.  What crosses ranks is the sender term ``P_s = x W_s^T`` of the node-factorised
+first Linear of layers 2-4 (one all-gather of ``[Nn, H]`` per layer, bf16 on the bf16 path) and the new
+positions (one all-gather of ``[Nn, D]`` per step).  The collective is torch.distributed's (NCCL over NVLink);
+the compute between two exchanges is one C-ABI call (``aether_part_forward_phase``).
+
+``parts > 1`` with ``world == 1`` runs the partitions one after another on one GPU over a shared exchange
+buffer -- the same kernels and the same slicing, used by the single-GPU parity test.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+from .dist import ReceiverPartition
+from .graph import PreparedGraph
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _LocalPart:
+    """Edge slice, CSR and workspace of one partition."""
+
+    def __init__(self, lib, model, full: PreparedGraph, part: ReceiverPartition, flags: int):
+        dev = full.send.device
+        Nn = full.n_nodes
+        e0, e1 = part.edge_begin, part.edge_end
+        self.part = part
+        self.E = e1 - e0
+        self.send = full.send[e0:e1].contiguous() if self.E else torch.zeros(1, dtype=torch.int32, device=dev)
+        self.recv = full.recv[e0:e1].contiguous() if self.E else torch.zeros(1, dtype=torch.int32, device=dev)
+        self.perm = torch.arange(max(self.E, 1), dtype=torch.int32, device=dev)
+        self.rowptr = (full.rowptr.to(torch.int64) - e0).clamp_(0, self.E).to(torch.int32).contiguous()
+        self.send64 = self.send.to(torch.int64)
+        self.recv64 = self.recv.to(torch.int64)
+        self.ea = torch.empty(max(self.E, 1), 2, dtype=torch.float32, device=dev)
+        self.c_graph = _lib.AetherGraphC(self.perm.data_ptr(), self.rowptr.data_ptr(), self.send.data_ptr(),
+                                         self.recv.data_ptr(), 0, 0)
+        self.dims = _lib.AetherDims(model.num_dims, model.hidden_size, Nn, self.E)
+        nbytes = lib.aether_workspace_bytes(ctypes.byref(self.dims), flags)
+        self.ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+
+
+class PartitionedRollout:
+    """Inference rollout of one scene with a static edge list, receiver-partitioned.
+
+    ``run(x0, v0, charges)`` returns positions ``[steps, Nn, D]`` (identical on every rank)."""
+
+    def __init__(self, model, send: torch.Tensor, recv: torch.Tensor, n_nodes: int, steps: int, world: int = 1,
+                 rank: int = 0, parts: Optional[int] = None, group=None):
+        self.lib = _lib.load()
+        self.model, self.steps, self.world, self.rank, self.group = model, int(steps), int(world), int(rank), group
+        self.D, self.H, self.Nn = model.num_dims, model.hidden_size, int(n_nodes)
+        dev = next(model.parameters()).device
+        self.dev = dev
+        self.flags = model.flags()
+        full = PreparedGraph(send.to(dev), recv.to(dev), self.Nn)
+        full.validate()
+        n_parts = world if world > 1 else int(parts or 1)
+        ranks = [rank] if world > 1 else list(range(n_parts))
+        self.local: List[_LocalPart] = [
+            _LocalPart(self.lib, model, full, ReceiverPartition(full.rowptr, self.Nn, n_parts, r), self.flags) for r in ranks]
+        self.padded = self.local[0].part.padded_nodes
+        xdtype = torch.bfloat16 if (self.flags & _lib.F_BF16 and self.H in (64, 128, 256)) else torch.float32
+        f32 = dict(dtype=torch.float32, device=dev)
+        # two exchange buffers: a phase gathers sender terms from one and writes the next layer's into the other
+        self.xchg = [torch.zeros(self.padded, self.H, dtype=xdtype, device=dev) for _ in range(2)]
+        self.xbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]   # positions ping-pong (gathered)
+        self.vbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]
+        self.q = torch.zeros(self.padded, **f32)
+        self.traj = torch.empty(self.steps, self.Nn, self.D, **f32)
+        self.edges_total = full.n_edges
+        self.launch_exchanges = 0
+
+    def _gather(self, buf: torch.Tensor):
+        if self.world > 1:
+            self.local[0].part.all_gather_rows(buf, self.group)
+            self.launch_exchanges += 1
+
+    def _step(self, x, v, xn, vn):
+        lib = self.lib
+        params = [p.detach() for p in self.model.param_list()]
+        parr = _lib.ptr_array(params)
+        for lp in self.local:    # caller prep on the local (receiver-sorted) edges: [q_i q_j, |x_i - x_j|]
+            _lib.check(lib.aether_caller_prep(_lib.ptr(x), _lib.ptr(v), _lib.ptr(self.q), self.D, _lib.ptr(lp.send64),
+                                              _lib.ptr(lp.recv64), lp.E, self.Nn, None, _lib.ptr(lp.ea), _stream()),
+                       "aether_caller_prep")
+        for phase in range(4):
+            for lp in self.local:
+                _lib.check(lib.aether_part_forward_phase(ctypes.byref(lp.dims), parr, ctypes.byref(lp.c_graph), _lib.ptr(x),
+                                                         _lib.ptr(v), _lib.ptr(self.q), _lib.ptr(lp.ea),
+                                                         lp.part.node_begin, lp.part.node_end, phase,
+                                                         _lib.ptr(self.xchg[(phase + 1) & 1]),
+                                                         _lib.ptr(self.xchg[phase & 1]), _lib.ptr(xn), _lib.ptr(lp.ws), lp.ws.numel(), self.flags,
+                                                         _stream()), "aether_part_forward_phase")
+            self._gather(self.xchg[phase & 1] if phase < 3 else xn)
+        torch.sub(xn, x, out=vn)
+
+    @torch.no_grad()
+    def run(self, x0, v0, charges) -> torch.Tensor:
+        with torch.cuda.device(self.dev):
+            x, v = self.xbuf[0], self.vbuf[0]
+            x[:self.Nn].copy_(x0)
+            v[:self.Nn].copy_(v0)
+            self.q[:self.Nn].copy_(charges.reshape(-1))
+            for t in range(self.steps):
+                xn, vn = self.xbuf[(t + 1) & 1], self.vbuf[(t + 1) & 1]
+                self._step(x, v, xn, vn)
+                self.traj[t].copy_(xn[:self.Nn])
+                x, v = xn, vn
+            return self.traj

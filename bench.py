@@ -37,6 +37,9 @@ WORKLOADS = {
     "c1": dict(D=2, N=5, B=16, H=64, mode="rollout", T=20, name="config1: electrostatic 2D, 5 particles, batch 16, 20-step rollout"),
     "c3": dict(D=2, N=0, B=256, H=64, mode="rollout", T=12, knn=10,
                name="config3: inD-style scenes, 10-40 agents (seed 1), kNN k=10 rebuilt every step, 256 scenes per GPU, 12-step rollout"),
+    "c5": dict(D=3, N=100000, B=1, H=64, mode="partitioned-rollout", T=5, k=32, radius=2.25,
+               name="config5: synthetic 3D gravitational scene, 100k particles (unit density), radius graph r=2.25 capped at the "
+                    "32 nearest (~3.2M edges), ONE scene receiver-partitioned over the GPUs, 5-step rollout"),
 }
 
 
@@ -170,6 +173,158 @@ def cpu_sample_graphs(cfg, H):
     return int(max(1, min(cfg["B"], budget // max(E, 1))))
 
 
+def c5_scene(cfg, n, seed=1):
+    """Uniform unit-density particles in a cube, speeds 0.05, charges +-1 (config 5)."""
+    g = torch.Generator().manual_seed(seed)
+    L = float(n) ** (1.0 / 3.0)
+    x = torch.rand(n, 3, generator=g) * L
+    v = torch.randn(n, 3, generator=g)
+    v = 0.05 * v / v.norm(dim=-1, keepdim=True)
+    q = torch.randint(0, 2, (n, 1), generator=g).float() * 2 - 1
+    return x, v, q
+
+
+def c5_cpu_sample(cfg, H, n_sub=6250):
+    """CPU oracle on a same-density sub-scene (graph built once outside the timed region, like the GPU path)."""
+    from oracle import aether_oracle as O
+    p = O.init_params(3, H, 1)
+    x, v, q = c5_scene(cfg, n_sub)
+    send, recv = O.radius_knn_edges(x, cfg["radius"], cfg["k"])
+    T = cfg["T"]
+
+    def step():
+        with torch.no_grad():
+            O.rollout(p, x, v, q, lambda xx: (send, recv), T)
+    return step, int(send.numel()) * T, "%d of %d particles at the same density (%d edges), %d-step rollout" % (
+        n_sub, cfg["N"], int(send.numel()), T)
+
+
+def run_c5(args, cfg, H):
+    """Config 5: one 100k-particle scene, receiver-partitioned over the ranks (strong scaling: fixed total work)."""
+    import aether_b200 as ab
+    from aether_b200 import _lib
+    lib = _lib.load(build_if_missing=False)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    n = cfg["N"] if not args.batch else args.batch          # --batch overrides the particle count for c5
+    T = cfg["T"]
+    torch.manual_seed(1)
+    model = ab.Aether(6, H, 0.0, 3, device=dev, precision=args.precision)
+    model.eval()
+    x, v, q = c5_scene(cfg, n)
+    host = [t.pin_memory() for t in (x, v, q)]
+    xd, vd, qd = [t.to(dev) for t in host]
+    send, recv = ab.radius_graph(xd, cfg["radius"], cfg["k"])          # replicated on every rank, built once
+    E = int(send.numel())
+    roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank)
+
+    def step_resident():
+        roll.run(xd, vd, qd)
+
+    def step_e2e():
+        xs, vs, qs = [t.to(dev, non_blocking=True) for t in host]
+        traj = roll.run(xs, vs, qs)
+        return float(traj[-1].abs().mean().item())
+
+    def timed(fn, steps, warmup, profile=False):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if profile:
+            lib.aether_profile_enable(1)
+        n0 = lib.aether_launch_count()
+        evs = []
+        for _ in range(steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        launches = lib.aether_launch_count() - n0
+        total = sum(a.elapsed_time(b) for a, b in evs) * 1e-3
+        prof = None
+        if profile:
+            lib.aether_profile_enable(0)
+            import ctypes
+            ms = (ctypes.c_double * 6)()
+            cnt = (ctypes.c_int64 * 6)()
+            lib.aether_profile_collect(ms, cnt, 6)
+            prof = {"ms": list(ms), "spans": list(cnt)}
+        if dist is not None:
+            t = torch.tensor([total], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            total = float(t.item())
+        return total, launches, prof
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e = None
+    if not args.no_e2e:
+        e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
+        e2e = 4.0 * E * T * args.steps / e2e_total
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    pk, pk_src = peaks()
+    e_local = roll.local[0].E
+    spans = max(prof["spans"][0], 1)
+    ms_per_layer = prof["ms"][0] / spans
+    alg = algorithmic_flops_edge_mlp(3, H, e_local) / 4.0
+    achieved = alg / (ms_per_layer * 1e-3) / 1e12 if ms_per_layer > 0 else 0.0
+    peak = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
+    line = {"metric": "edge_messages_per_sec", "value": 4.0 * E * T * args.steps / total, "unit": "edge-messages/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
+            "config": {"workload": cfg["name"], "num_dims": 3, "particles": n, "edges": E, "edges_rank0": e_local,
+                       "hidden": H, "mode": cfg["mode"], "rollout_steps": T, "precision": args.precision,
+                       "parallelism": "receiver-partition x%d, all-gather of [Nn,H] sender terms before layers 2-4 "
+                                      "and of [Nn,3] positions per step" % world,
+                       "l2": "working set exceeds L2" if E * H * 2 * 2 > 126e6 * world else "flushed: no (L2-resident edge state)"},
+            "particle_steps_per_sec": n * T * args.steps / total, "gpu_launches": int(launches), "clocks": clocks,
+            "collectives_per_step": 4 * T if world > 1 else 0,
+            "roofline": {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer, rank 0's edges)",
+                         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+                         "traffic": None, "peak_source": pk_src + " bf16 sustained",
+                         "algorithmic_flops_per_launch_group": alg, "avg_ms_per_launch_group": ms_per_layer}}
+    if e2e is not None:
+        h2d = sum(t.numel() * t.element_size() for t in host)
+        line["e2e"] = {"value": e2e, "unit": "edge-messages/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
+    if not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        cstep, e_step, sample = c5_cpu_sample(cfg, H)
+        cstep()
+        t0, it = time.perf_counter(), 0
+        while it < 2 or (time.perf_counter() - t0 < args.cpu_seconds and it < 50):
+            cstep()
+            it += 1
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": 4.0 * e_step * it / dt, "unit": "edge-messages/s", "cores": cores, "kind": "port",
+                                "sample": sample + ", %d repeats, %d host threads" % (it, cores)}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def run_reference(args, cfg, H):
     """--impl reference: the CPU oracle port on the host cores, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
@@ -177,8 +332,13 @@ def run_reference(args, cfg, H):
         return
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    graphs = cpu_sample_graphs(cfg, H)
-    step, e_step = cpu_step_sample(cfg, H, graphs)
+    if cfg["mode"] == "partitioned-rollout":
+        step, e_step, sample0 = c5_cpu_sample(cfg, H)
+        graphs = 1
+    else:
+        graphs = cpu_sample_graphs(cfg, H)
+        step, e_step = cpu_step_sample(cfg, H, graphs)
+        sample0 = None
     for _ in range(args.warmup):
         step()
     t0 = time.perf_counter()
@@ -187,10 +347,12 @@ def run_reference(args, cfg, H):
     dt = time.perf_counter() - t0
     val = 4.0 * e_step * args.steps / dt
     sample = "%d of %d graphs per step (%d edges), all %d host threads" % (graphs, cfg["B"], e_step, cores)
+    if sample0:
+        sample = sample0 + ", all %d host threads" % cores
     line = {"impl": "reference", "metric": "edge_messages_per_sec", "value": val, "unit": "edge-messages/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": cfg["name"], "hidden": H, "mode": cfg["mode"], "sample": sample},
+            "higher_is_better": True, "scaling": "strong" if sample0 else "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": cfg["name"], "hidden": H, "mode": cfg["mode"], "sample": sample},
             "cpu_baseline": {"value": val, "unit": "edge-messages/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "edge-messages/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -217,6 +379,8 @@ def main():
         cfg["B"] = args.batch
     if args.impl == "reference":
         return run_reference(args, cfg, H)
+    if args.workload == "c5":
+        return run_c5(args, cfg, H)
 
     import aether_b200 as ab
     from aether_b200 import _lib

@@ -111,6 +111,22 @@ int aether_caller_prep(const float* x, const float* vel, const float* charges, i
                        const int64_t* send, const int64_t* recv, int64_t n_edges, int64_t n_nodes,
                        float* h /* [Nn] or NULL */, float* edge_attr_orig /* [E,2] */, void* stream);
 
+/* Radius graph capped at the k nearest (k <= 32), for single scenes too large for aether_knn_edges (BASELINE config 5;
+ * the reference only has the O(N^2) cdist + topk of experiments/ind/single_ind_data.py:186-217).  For every sender i the
+ * receivers are the particles j != i with |x_i - x_j|^2 <= radius^2, nearest first, ties toward the lower index;
+ * sender-major like get_knn_graph_info.  Uniform cell list: cell edge cell_size >= radius (a hair larger, so that
+ * rounding never puts a neighbour two cells away), box_lo = lower corner, grid_dim[a] = cells along axis a (host arrays).
+ *   _neighbors: nbr[n,k] (-1 padded), off[n+1] = exclusive scan of the degrees (off[n] = E).  The caller reads off[n]
+ *               on the host (the one synchronisation of graph construction), allocates send/recv[E], then
+ *   _fill:      writes the edge list. */
+size_t aether_radius_graph_scratch_bytes(int64_t n, int32_t num_dims, const int32_t* grid_dim);
+int aether_radius_graph_neighbors(const float* pos, int32_t pos_stride, int32_t num_dims, int64_t n, float radius,
+                                  float cell_size, int32_t k, const float* box_lo /* host [num_dims] */,
+                                  const int32_t* grid_dim /* host [num_dims] */, int32_t* nbr, int32_t* off,
+                                  void* scratch, size_t scratch_bytes, void* stream);
+int aether_radius_graph_fill(const int32_t* nbr, const int32_t* off, int64_t n, int32_t k, int64_t* send, int64_t* recv,
+                             void* stream);
+
 /* ---- the step ------------------------------------------------------------ */
 size_t aether_workspace_bytes(const AetherDims* dims, uint32_t flags);
 size_t aether_backward_scratch_bytes(const AetherDims* dims, uint32_t flags);
@@ -129,6 +145,27 @@ int aether_step_backward(const AetherDims* dims, const float* const* params, con
                          float* grad_x /* [Nn,D] or NULL */, float* grad_vel /* [Nn,D] or NULL */,
                          void* workspace /* the one forward filled */, size_t workspace_bytes,
                          void* scratch, size_t scratch_bytes, uint32_t flags, void* stream);
+
+/* Receiver-partitioned inference step for ONE large scene.  This rank owns the node rows
+ * [own_begin, own_end) and every edge whose receiver it owns: `graph` holds only those edges, receiver-sorted, with
+ * GLOBAL node ids in send/recv, rowptr[n_nodes+1] indexing the local edge array (empty segments outside the owned
+ * rows) and perm mapping local sorted position -> row of edge_attr_orig; sperm/colptr are not used.
+ * dims->n_nodes = nodes of the whole scene, dims->n_edges = local edges.  x / vel / charges hold ALL nodes.
+ * The step is cut where node state must cross ranks:
+ *   phase 0: field + frames (all nodes), features + layer 1 (local edges, owned rows), sender terms of layer 2
+ *   phase 1, 2: layer phase+1, sender terms of the next layer
+ *   phase 3: layer 4, out MLP, rotation back, Euler update -> out rows [own_begin, own_end)
+ * Phases 0-2 end by writing rows [own_begin, own_end) of xchg_out ([>= n_nodes, hidden], fp32, or bf16 with
+ * AETHER_F_BF16_EDGE_MLP): the sender term P_s = x W_s^T of the node-factorised first Linear.  The caller
+ * all-gathers it (NCCL, torch.distributed) and passes it as xchg_in of the next phase, whose edge GEMM gathers
+ * rows of it by sender.  xchg_in and xchg_out may be the same buffer when every rank has its own (the phase reads
+ * before it writes); partitions that share one address space must alternate two buffers.
+ * The workspace (aether_workspace_bytes of the same dims, without SAVE_FOR_BACKWARD) must persist across the phases. */
+int aether_part_forward_phase(const AetherDims* dims, const float* const* params, const AetherGraph* graph,
+                              const float* x, const float* vel, const float* charges, const float* edge_attr_orig,
+                              int64_t own_begin, int64_t own_end, int32_t phase, const void* xchg_in, void* xchg_out,
+                              float* out,
+                              void* workspace, size_t workspace_bytes, uint32_t flags, void* stream);
 
 /* One harness-level rollout step: edge_attr = [q_i q_j, |x_i - x_j|] over the ORIGINAL
  * edge list (send64/recv64, experiments/lorentz/main.py:243-246), x_next = step(x, vel),

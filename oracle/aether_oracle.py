@@ -84,6 +84,43 @@ def knn_edges_batched(pos: Tensor, sizes: Sequence[int], k: int = 10) -> Tuple[T
     return torch.cat(s_all), torch.cat(r_all)
 
 
+def radius_knn_edges(pos: Tensor, radius: float, k: int = 32) -> Tuple[Tensor, Tensor]:
+    """Radius graph capped at the k nearest, brute force (derived oracle for BASELINE config 5).
+
+    Same conventions as ``knn_edges`` above (experiments/ind/single_ind_data.py:186-217: sender = the query
+    particle, receivers = its nearest neighbours in ascending distance, sender-major) with two changes the large
+    scene needs: only neighbours with |x_i - x_j|^2 <= radius^2 count, and ties are broken toward the lower index
+    (torch.topk leaves tie order unspecified).  Squared distances are accumulated left to right in float32
+    (dx*dx + dy*dy [+ dz*dz], each operation rounded), the arithmetic the CUDA builder reproduces bit for bit.
+    """
+    p = pos.numpy().astype(np.float32)
+    n, D = p.shape
+    r2 = np.float32(radius) * np.float32(radius)
+    send, recv = [], []
+    step = max(1, min(n, (1 << 24) // max(n, 1)))
+    ar = np.arange(n)
+    for b in range(0, n, step):
+        q = p[b:b + step]
+        dx = q[:, None, 0] - p[None, :, 0]
+        dy = q[:, None, 1] - p[None, :, 1]
+        d2 = dx * dx + dy * dy
+        if D == 3:
+            dz = q[:, None, 2] - p[None, :, 2]
+            d2 = d2 + dz * dz
+        d2 = d2.astype(np.float32)
+        ok = d2 <= r2
+        ok[np.arange(q.shape[0]), np.arange(b, b + q.shape[0])] = False
+        for i in range(q.shape[0]):
+            cand = ar[ok[i]]
+            order = np.lexsort((cand, d2[i, cand]))[:k]        # by distance, then index
+            recv.append(cand[order])
+            send.append(np.full(order.shape[0], b + i, dtype=np.int64))
+    if not send:
+        z = torch.zeros(0, dtype=torch.int64)
+        return z, z.clone()
+    return torch.from_numpy(np.concatenate(send).astype(np.int64)), torch.from_numpy(np.concatenate(recv).astype(np.int64))
+
+
 def receiver_csr(send: Tensor, recv: Tensor, n_nodes: int):
     """Receiver-sorted view of an edge list (derived oracle).
 

@@ -118,3 +118,24 @@ def test_rollout(case):
     with torch.no_grad():
         xs = O.rollout(p, t("x"), t("vel"), t("charges"), lambda x: edges, g["rollout"].shape[0])
     assert rel_err(xs, g["rollout"]) <= 1e-5
+
+
+def test_radius_knn_oracle_matches_knn_and_properties():
+    """The large-scene builder's oracle: with an unbounded radius it is the reference's kNN list (tie-free inputs),
+    and with a finite radius every edge is within the radius, nearest first, at most k per sender."""
+    g = torch.Generator().manual_seed(3)
+    pos = torch.rand(60, 2, generator=g)
+    s0, r0 = O.knn_edges(pos, 10)
+    s1, r1 = O.radius_knn_edges(pos, 1e3, 10)
+    assert torch.equal(s0, s1) and torch.equal(r0, r1)
+    pos3 = torch.randn(400, 3, generator=g)
+    s, r = O.radius_knn_edges(pos3, 0.9, 8)
+    d = (pos3[s] - pos3[r]).norm(dim=1)
+    assert float(d.max()) <= 0.9 * (1 + 1e-6) and bool((s != r).all())
+    deg = torch.bincount(s, minlength=400)
+    assert int(deg.max()) <= 8
+    for i in (0, 17, 399):
+        di = d[s == i]
+        assert bool((di[1:] >= di[:-1]).all())
+    full = (torch.cdist(pos3, pos3) <= 0.9).sum(1) - 1
+    assert torch.equal(deg, full.clamp(max=8))
