@@ -25,7 +25,7 @@ namespace aether {
 extern unsigned long long g_launch_count;
 // Optional CUDA-event timing of a group of launches; a no-op unless aether_profile_enable(1).
 enum ProfCat { PROF_EDGE_MLP_FWD = 0, PROF_EDGE_BWD_DATA = 1, PROF_EDGE_WGRAD = 2, PROF_SEGMENT = 3,
-               PROF_EDGE_FEAT = 4, PROF_NODE = 5, PROF_NUM = 6 };
+               PROF_EDGE_FEAT = 4, PROF_NODE = 5, PROF_SEGMEAN_FWD = 6, PROF_NUM = 7 };
 struct ProfScope {
   ProfScope(int cat, cudaStream_t st);
   ~ProfScope();
@@ -129,7 +129,8 @@ int launch_segsum(int64_t Nn, int W, const int32_t* ptr, const int32_t* list, co
 int launch_edge_dpre2(int64_t E, int H, const int32_t* recv, const int32_t* rowptr, const float* ge, const float* gy,
                       const float* pre2, float* g, cudaStream_t st);
 // embedding gradient: gemb[r, :] = sum_{n: idx(n)==r} gfin[n, 2D:2D+16]
-int launch_embedding_bwd(int D, int64_t Nn, const float* charges, const float* gfin, float* gemb, cudaStream_t st);
+int launch_embedding_bwd(int D, int64_t Nn, const float* charges, const float* gfin, float* gemb, float* partial,
+                         size_t partial_floats, cudaStream_t st);
 int launch_fill(float* p, size_t n, float v, cudaStream_t st);
 
 // ---- bf16 edge kernels (edge_bf16.cu): [E, W] tensors stored as bf16, W in {64, 128, 256} ----------

@@ -193,28 +193,42 @@ __global__ void edge_features_hilo_kernel(int64_t E, const int32_t* __restrict__
                                           const float* __restrict__ vel, const float* __restrict__ f,
                                           const float* __restrict__ R, const float* __restrict__ x0,
                                           const float* __restrict__ orig, uint4* __restrict__ feat16) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= E) return;
+  // 128 threads = 128 edges per block.  Each thread computes its edge's 128-byte row; the rows go through a
+  // swizzled shared-memory tile so that the global stores are contiguous (512 bytes per warp instruction)
+  // instead of 32 scattered 16-byte pieces.
+  __shared__ uint4 tile[128 * 8];
+  const int t = threadIdx.x;
+  const int64_t e0 = (int64_t)blockIdx.x * 128;
+  const int64_t e = e0 + t;
   constexpr int FE = 7 * D + D * (D - 1) / 2 + 2;
   constexpr int LD = (FE + 3) / 4 * 4;
-  float out[32];
-  edge_features_values<D>(e, send, recv, perm, x, vel, f, R, x0, orig, out);
+  if (e < E) {
+    float out[32];
+    edge_features_values<D>(e, send, recv, perm, x, vel, f, R, x0, orig, out);
 #pragma unroll
-  for (int k = LD; k < 32; ++k) out[k] = 0.0f;
-  uint32_t hi[16], lo[16];
+    for (int k = LD; k < 32; ++k) out[k] = 0.0f;
+    uint32_t hi[16], lo[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const __nv_bfloat16 h0 = __float2bfloat16_rn(out[2 * k]), h1 = __float2bfloat16_rn(out[2 * k + 1]);
-    const __nv_bfloat16 l0 = __float2bfloat16_rn(out[2 * k] - __bfloat162float(h0));
-    const __nv_bfloat16 l1 = __float2bfloat16_rn(out[2 * k + 1] - __bfloat162float(h1));
-    hi[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-    lo[k] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+    for (int k = 0; k < 16; ++k) {
+      const __nv_bfloat16 h0 = __float2bfloat16_rn(out[2 * k]), h1 = __float2bfloat16_rn(out[2 * k + 1]);
+      const __nv_bfloat16 l0 = __float2bfloat16_rn(out[2 * k] - __bfloat162float(h0));
+      const __nv_bfloat16 l1 = __float2bfloat16_rn(out[2 * k + 1] - __bfloat162float(h1));
+      hi[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+      lo[k] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      tile[t * 8 + (k ^ (t & 7))] = make_uint4(hi[4 * k], hi[4 * k + 1], hi[4 * k + 2], hi[4 * k + 3]);
+      tile[t * 8 + ((4 + k) ^ (t & 7))] = make_uint4(lo[4 * k], lo[4 * k + 1], lo[4 * k + 2], lo[4 * k + 3]);
+    }
   }
-  uint4* dst = feat16 + (size_t)e * 8;   // 128 bytes per edge
+  __syncthreads();
+  uint4* dst = feat16 + (size_t)e0 * 8;   // 128 bytes per edge
 #pragma unroll
-  for (int k = 0; k < 4; ++k) dst[k] = make_uint4(hi[4 * k], hi[4 * k + 1], hi[4 * k + 2], hi[4 * k + 3]);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) dst[4 + k] = make_uint4(lo[4 * k], lo[4 * k + 1], lo[4 * k + 2], lo[4 * k + 3]);
+  for (int it = 0; it < 8; ++it) {
+    const int i = it * 128 + t, row = i >> 3, col = i & 7;
+    if (e0 + row < E) dst[i] = tile[row * 8 + (col ^ (row & 7))];
+  }
 }
 #endif
 

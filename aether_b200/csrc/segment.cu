@@ -76,15 +76,17 @@ __global__ void edge_dpre2_kernel(int64_t E, int H, const int32_t* __restrict__ 
   *reinterpret_cast<float4*>(g + (size_t)k * H + c) = o;
 }
 
-// gemb[r, c] = sum over nodes with class r of gfin[n, 2D + c].  One block of 1024 threads: thread (lane, c)
-// walks nodes lane, lane+64, ... keeping one sum per class; lanes are combined in a fixed order.
-__global__ void embedding_bwd_kernel(int D, int64_t Nn, const float* __restrict__ charges,
-                                     const float* __restrict__ gfin, float* __restrict__ gemb) {
+// gemb[r, c] = sum over nodes with class r of gfin[n, 2D + c].  Each block of 1024 threads takes a contiguous
+// slab of nodes: thread (lane, c) walks nodes lane, lane+64, ... of the slab keeping one sum per class; lanes,
+// then blocks, are combined in a fixed order (deterministic, no atomics).
+__global__ void embedding_bwd_kernel(int D, int64_t Nn, int64_t slab, const float* __restrict__ charges,
+                                     const float* __restrict__ gfin, float* __restrict__ partial) {
   __shared__ float part[64][49];
   const int c = threadIdx.x & 15, ln = threadIdx.x >> 4;   // 64 node lanes x 16 columns
   const int W = 2 * D + 16;
+  const int64_t n0 = (int64_t)blockIdx.x * slab, n1 = n0 + slab < Nn ? n0 + slab : Nn;
   float s0 = 0.f, s1 = 0.f, s2 = 0.f;
-  for (int64_t n = ln; n < Nn; n += 64) {
+  for (int64_t n = n0 + ln; n < n1; n += 64) {
     long long idx = (long long)(charges[n] + 1.0f);
     idx = idx < 0 ? 0 : (idx > 2 ? 2 : idx);
     const float v = gfin[(size_t)n * W + 2 * D + c];
@@ -95,6 +97,13 @@ __global__ void embedding_bwd_kernel(int D, int64_t Nn, const float* __restrict_
   if (threadIdx.x < 48) {
     float a = 0.f;
     for (int i = 0; i < 64; ++i) a += part[i][threadIdx.x];
+    partial[(size_t)blockIdx.x * 48 + threadIdx.x] = a;
+  }
+}
+__global__ void embedding_bwd_reduce_kernel(const float* __restrict__ partial, int blocks, float* __restrict__ gemb) {
+  if (threadIdx.x < 48) {
+    float a = 0.f;
+    for (int b = 0; b < blocks; ++b) a += partial[(size_t)b * 48 + threadIdx.x];
     gemb[threadIdx.x] = a;
   }
 }
@@ -134,8 +143,16 @@ int launch_edge_dpre2(int64_t E, int H, const int32_t* recv, const int32_t* rowp
   return 0;
 }
 
-int launch_embedding_bwd(int D, int64_t Nn, const float* charges, const float* gfin, float* gemb, cudaStream_t st) {
-  embedding_bwd_kernel<<<1, 1024, 0, st>>>(D, Nn, charges, gfin, gemb);
+int launch_embedding_bwd(int D, int64_t Nn, const float* charges, const float* gfin, float* gemb, float* partial,
+                         size_t partial_floats, cudaStream_t st) {
+  int blocks = (int)((Nn + 4095) / 4096);
+  if (blocks < 1) blocks = 1;
+  if (blocks > 256) blocks = 256;
+  if (partial_floats < (size_t)blocks * 48) return AETHER_E_WORKSPACE;
+  const int64_t slab = (Nn + blocks - 1) / blocks;
+  embedding_bwd_kernel<<<blocks, 1024, 0, st>>>(D, Nn, slab, charges, gfin, partial);
+  AE_LAUNCH_CHECK();
+  embedding_bwd_reduce_kernel<<<1, 64, 0, st>>>(partial, blocks, gemb);
   AE_LAUNCH_CHECK();
   return 0;
 }

@@ -136,6 +136,7 @@ size_t partial_need(const AetherDims& d, uint32_t flags) {
   up(gemm_tn_partial_floats(32, 32, Nn));
   up(gemm_tn_partial_floats(D, 32, Nn));
   up(colsum_partial_floats(Nn, 2 * H));
+  up(256 * 48);   // embedding gradient: per-block class sums
   return m + 64;
 }
 
@@ -284,7 +285,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       base = y;
     }
     {
-      ProfScope ps(PROF_SEGMENT, st);
+      ProfScope ps(PROF_SEGMEAN_FWD, st);
       if (bf16) AE_CHECK(launch_segmean_silu_bf16(M, H, G.rowptr + n0, w.bpre2[l], H, base, H, y, H, st));
       else AE_CHECK(launch_segmean_silu(M, H, G.rowptr + n0, w.pre2[l], H, base, H, y, H, st));
     }

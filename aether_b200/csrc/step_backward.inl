@@ -227,7 +227,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   const int FI = 2 * D + 16;
   AE_CHECK(b.wgrad(s.gfz1, 32, Nn, 32, w.fin, FI, FI, TF_NONE, nullptr, G[P_F0_W], FI, G[P_F0_B]));
   AE_CHECK(b.dgrad(s.gfz1, 32, Nn, 32, P[P_F0_W], FI, FI, s.gfin, FI, nullptr, nullptr, nullptr, 0));
-  AE_CHECK(launch_embedding_bwd(D, Nn, q, s.gfin, G[P_EMB], st));
+  AE_CHECK(launch_embedding_bwd(D, Nn, q, s.gfin, G[P_EMB], s.partial, s.partial_floats, st));
   if (gx_out || gvel_out) AE_CHECK(launch_add_field_input_grads(D, Nn, s.gfin, gx_out, gvel_out, st));
   return 0;
 }

@@ -79,6 +79,27 @@ def algorithmic_flops_edge_mlp(D, H, E):
     return 2.0 * E * (fe * H + 13 * H * H)
 
 
+def hbm_rooflines(prof, D, H, E, Nn, bf16, pk):
+    """HBM-bound kernels of the path (north_star subsystem 2): the receiver-sorted segmented mean and the
+    gather + frame-transform feature kernel.  achieved = algorithmic bytes per launch / mean CUDA-event time of
+    the launches (library-side event pairs); peak = measured copy bandwidth."""
+    out = {}
+    peak = pk.get("hbm_gbs")
+    esz = 2 if bf16 else 4
+    fe = 7 * D + D * (D - 1) // 2 + 2
+    specs = {"segmented_mean (receiver-sorted, no atomics)": (6, E * H * esz + Nn * H * 4 * 2 + (Nn + 1) * 4),
+             "edge_features (gather + frame transform)": (4, E * (12 + 8 + (128 if bf16 else 4 * ((fe + 3) // 4 * 4))))}
+    for name, (cat, nbytes) in specs.items():
+        n = prof["spans"][cat] if cat < len(prof["spans"]) else 0
+        if not n or prof["ms"][cat] <= 0:
+            continue
+        ms = prof["ms"][cat] / n
+        ach = nbytes / (ms * 1e-3) / 1e9
+        out[name] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak if peak else None,
+                     "algorithmic_bytes_per_launch": nbytes, "avg_ms_per_launch": ms, "launches": n}
+    return out
+
+
 def executed_flops_edge_mlp(D, H, E):
     fe = 7 * D + D * (D - 1) // 2 + 2
     return 2.0 * E * (fe * H + H * H + 3 * 2 * H * H)     # node-factorised: 2 H^2 per edge in layers 2-4
@@ -260,9 +281,9 @@ def run_c5(args, cfg, H):
         if profile:
             lib.aether_profile_enable(0)
             import ctypes
-            ms = (ctypes.c_double * 6)()
-            cnt = (ctypes.c_int64 * 6)()
-            lib.aether_profile_collect(ms, cnt, 6)
+            ms = (ctypes.c_double * 7)()
+            cnt = (ctypes.c_int64 * 7)()
+            lib.aether_profile_collect(ms, cnt, 7)
             prof = {"ms": list(ms), "spans": list(cnt)}
         if dist is not None:
             t = torch.tensor([total], device=dev)
@@ -304,7 +325,9 @@ def run_c5(args, cfg, H):
             "roofline": {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer, rank 0's edges)",
                          "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                          "traffic": None, "peak_source": pk_src + " bf16 sustained",
-                         "algorithmic_flops_per_launch_group": alg, "avg_ms_per_launch_group": ms_per_layer}}
+                         "algorithmic_flops_per_launch_group": alg, "avg_ms_per_launch_group": ms_per_layer},
+            "roofline_hbm": hbm_rooflines(prof, 3, H, e_local, roll.local[0].part.n_own,
+                                          args.precision == "bf16" and H in (64, 128, 256), pk)}
     if e2e is not None:
         h2d = sum(t.numel() * t.element_size() for t in host)
         line["e2e"] = {"value": e2e, "unit": "edge-messages/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
@@ -491,9 +514,9 @@ def main():
         if profile:
             lib.aether_profile_enable(0)
             import ctypes
-            ms = (ctypes.c_double * 6)()
-            cnt = (ctypes.c_int64 * 6)()
-            lib.aether_profile_collect(ms, cnt, 6)
+            ms = (ctypes.c_double * 7)()
+            cnt = (ctypes.c_int64 * 7)()
+            lib.aether_profile_collect(ms, cnt, 7)
             prof = {"ms": list(ms), "spans": list(cnt)}
         if dist is not None:
             t = torch.tensor([total], device=dev)
@@ -529,7 +552,7 @@ def main():
     peak = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload + "_" + args.precision)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("%s_%s_h%d" % (args.workload, args.precision, H))
     except Exception:
         pass
     roofline = {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer)", "achieved": achieved,
@@ -539,7 +562,7 @@ def main():
                 "avg_ms_per_launch_group": ms_per_layer}
     step_ms = total / args.steps * 1e3
     share = {k: (prof["ms"][i] / args.steps) / step_ms for i, k in
-             enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment", "edge_feat", "node"])} if train else None
+             enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment_bwd", "edge_feat", "node", "segment_fwd"])} if train else None
     line = {"metric": "edge_messages_per_sec", "value": value, "unit": "edge-messages/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
@@ -549,7 +572,9 @@ def main():
                        "precision": args.precision, "parallelism": "dp%d" % world,
                        "l2": "flushed between steps" if small else "working set exceeds L2"},
             "particle_steps_per_sec": Nn * T * world * args.steps / total,
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "time_share": share}
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+            "roofline_hbm": hbm_rooflines(prof, D, H, E, Nn, args.precision == "bf16" and H in (64, 128, 256), pk),
+            "time_share": share}
     if e2e is not None:
         h2d = sum(t.numel() * t.element_size() for t in host)
         line["e2e"] = {"value": e2e, "unit": "edge-messages/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}

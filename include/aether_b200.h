@@ -177,7 +177,8 @@ int aether_rollout_step(const AetherDims* dims, const float* const* params, cons
 
 /* Bench support: kernels launched by this library so far; optional per-category CUDA-event timing
  * (categories: 0 edge-MLP forward, 1 edge backward data grads, 2 edge weight grads, 3 segment
- * reductions, 4 edge features, 5 node-level work).  collect() synchronises the device. */
+ * reductions of the backward pass, 4 edge features (gather + frame transform), 5 node-level work, 6 receiver mean of
+ * the forward pass).  collect() synchronises the device. */
 uint64_t aether_launch_count(void);
 int aether_profile_enable(int on);
 int aether_profile_collect(double* ms_by_cat, int64_t* spans_by_cat, int32_t n_cat);
