@@ -12,7 +12,8 @@ Everything computes through aether_b200/lib/libaether_b200.so; there is no CPU o
 from .aether import Aether, AetherLocalizer, FieldNetwork, Globalizer, GNN, GNNLayer  # noqa: F401
 from .graph import KnnPlan, PreparedGraph, caller_prep, fc_edges, knn_edges, radius_graph  # noqa: F401
 from .partition import PartitionedRollout  # noqa: F401
+from .train import GraphedTrainStep  # noqa: F401
 from .rollout import Rollout, rollout  # noqa: F401
 
 __all__ = ["Aether", "PreparedGraph", "KnnPlan", "fc_edges", "knn_edges", "caller_prep", "Rollout", "rollout", "radius_graph",
-           "PartitionedRollout"]
+           "PartitionedRollout", "GraphedTrainStep"]

@@ -61,6 +61,7 @@ class Rollout:
         self.ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         self._graph_exec = None
         self._use_graph = cuda_graph
+        self.launches_per_replay = 0
 
     def _steps(self):
         params = [p.detach() for p in self.model.param_list()]
@@ -98,8 +99,10 @@ class Rollout:
                 torch.cuda.synchronize()
                 self._keep = []
                 g = torch.cuda.CUDAGraph()
+                n0 = self.lib.aether_launch_count()
                 with torch.cuda.graph(g):
                     self._steps()
+                self.launches_per_replay = int(self.lib.aether_launch_count() - n0)   # kernels one replay launches
                 self._graph_exec = g
             self._graph_exec.replay()
             return self.traj

@@ -395,6 +395,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="small training shapes: do not capture the step in a CUDA graph")
     args = ap.parse_args()
     cfg = dict(WORKLOADS[args.workload])
     H = args.hidden or cfg["H"]
@@ -453,7 +454,16 @@ def main():
     def allreduce_grads():
         adist.allreduce_grads(params, world)     # ONE in-place all-reduce of the flat gradient buffer
 
+    # small training shapes are launch-latency bound: replay the whole step as one CUDA graph
+    graphed = None
+    if train and E * H <= 32e6 and not args.no_graph:
+        opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=1e-12, fused=True, capturable=True)
+        graphed = ab.GraphedTrainStep(model, opt, (send, recv), Nn, allreduce=(lambda: adist.allreduce_grads(params, world))
+                                      if world > 1 else None)
+
     def step_resident():
+        if graphed is not None:
+            return graphed.step(xd, vd, qd, td)
         if not train:
             roll.run(xd, vd, qd1)
             return None
@@ -468,6 +478,8 @@ def main():
 
     def step_e2e():
         xs, vs, qs, ts = [t.to(dev, non_blocking=True) for t in host]
+        if graphed is not None:
+            return float(graphed.step(xs, vs, qs, ts).item())
         if not train:
             traj = roll.run(xs, vs, qs.reshape(-1))
             return float(traj[-1].abs().mean().item())
@@ -509,6 +521,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
         launches = lib.aether_launch_count() - n0
+        # kernels launched by graph replays are not seen by the host-side counter: add what each replay launches
+        replayed = graphed if graphed is not None else (roll if not train else None)
+        if replayed is not None and fn is not eager_fn:
+            launches += steps * replayed.launches_per_replay
         total = sum(a.elapsed_time(b) for a, b in evs) * 1e-3
         prof = None
         if profile:
@@ -524,15 +540,23 @@ def main():
             total = float(t.item())
         return total, launches, prof
 
+    eager_fn = None
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
     clocks = sampler.stop() if rank == 0 else None
+    if graphed is not None:
+        # graph replays carry no library-side event pairs: one eager pass of the same step for the kernel timings
+        g_keep, graphed = graphed, None
+        eager_fn = step_resident
+        _, _, prof = timed(step_resident, max(1, min(args.steps, 3)), 1, profile=True)
+        graphed, eager_fn = g_keep, None
     if not train:
         # graph replays carry no library-side event pairs: time the same kernels once more, launched eagerly
         eager = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=False)
-        _, _, prof = timed(lambda: eager.run(xd, vd, qd1), max(1, min(args.steps, 3)), 1, profile=True)
+        eager_fn = lambda: eager.run(xd, vd, qd1)
+        _, _, prof = timed(eager_fn, max(1, min(args.steps, 3)), 1, profile=True)
     e2e = None
     if not args.no_e2e:
         e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
@@ -568,7 +592,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
             "data": "synthetic",
             "config": {"workload": cfg["name"], "num_dims": D, "particles_per_graph": N, "graphs_per_gpu": B,
-                       "hidden": H, "mode": cfg["mode"], "rollout_steps": T, "edges_per_gpu": E, "nodes_per_gpu": Nn,
+                       "hidden": H, "mode": cfg["mode"] + (" (whole step replayed as one CUDA graph, static edge list)" if graphed is not None else ""),
+                       "rollout_steps": T, "edges_per_gpu": E, "nodes_per_gpu": Nn,
                        "precision": args.precision, "parallelism": "dp%d" % world,
                        "l2": "flushed between steps" if small else "working set exceeds L2"},
             "particle_steps_per_sec": Nn * T * world * args.steps / total,

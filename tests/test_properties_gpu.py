@@ -165,3 +165,32 @@ def test_module_dropin(ab):
     o3, _, _ = run_gpu(ab, md, x, v, q, s, r)
     o4, _, _ = run_gpu(ab, md, x, v, q, s, r)
     assert torch.equal(o3, o4)
+
+
+def test_graphed_train_step_matches_eager(ab):
+    """The captured train step (CUDA graph) takes exactly the steps the eager loop takes."""
+    D, N, B, H = 3, 5, 16, 64
+    x, v, q = O.synth_state(B, N, D, seed=21)
+    tgt = x + 0.05
+    send, recv = ab.fc_edges(N, B, "cuda")
+    xs, vs, qs, ts = x.cuda(), v.cuda(), q.cuda(), tgt.cuda()
+    m1, _ = make(ab, D, H, seed=4)
+    m2, _ = make(ab, D, H, seed=4)
+    m1.train(); m2.train()
+    o1 = torch.optim.AdamW(m1.parameters(), lr=5e-4, weight_decay=1e-12, fused=True)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=5e-4, weight_decay=1e-12, fused=True, capturable=True)
+    g = ab.PreparedGraph(send, recv, B * N)
+    losses1 = []
+    for _ in range(4):
+        o1.zero_grad(set_to_none=True)
+        h, ea = ab.caller_prep(xs, vs, qs.reshape(-1), send, recv)
+        loss = torch.nn.functional.mse_loss(m1(h, xs, g, vs, ea, qs), ts)
+        loss.backward()
+        o1.step()
+        losses1.append(float(loss))
+    gs = ab.GraphedTrainStep(m2, o2, (send, recv), B * N)
+    losses2 = [float(gs.step(xs, vs, qs, ts)) for _ in range(4)]
+    assert np.allclose(losses1, losses2, rtol=1e-5, atol=1e-8), (losses1, losses2)
+    assert losses1[-1] < losses1[0]
+    for (k, a), (_, b) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert rel_err(b.detach().cpu(), a.detach().cpu()) <= 1e-5, k

@@ -24,18 +24,25 @@ def run(name, silu, gat_, ia, ib, z, passes):
         return lib.aether_dbg_tc_gemm(P(A), M, H, H, P(W), H, H, H, H, 0, 0, silu, None, P(gat_), 2 * H, P(ia), P(ib), H, P(z),
                                       P(out), None, P(scratch), stream())
     assert call() == 0
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(5):
-        call()
-    b.record()
-    torch.cuda.synchronize()
-    ms = a.elapsed_time(b) / 5
+    best = 1e9
+    for _ in range(4):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(5):
+            call()
+        b.record()
+        torch.cuda.synchronize()
+        best = min(best, a.elapsed_time(b) / 5)
+    ms = best
     print("%-34s dbg=%s %.3f ms  %.2f us/tile  %.0f GB/s" % (name, os.environ.get("AETHER_TC_DBG", "0"), ms,
           ms * 1e3 / (M / 128 / 148), M * H * 2 * passes / ms / 1e6), flush=True)
 
 for dbg in os.environ.get("DBGS", "0").split(","):
     os.environ["AETHER_TC_DBG"] = dbg
+    if os.environ.get("ONLY_B"):
+        run("B1: dsilu", 0, None, None, None, Z, 3)
+        run("B2: gather recv + dsilu", 0, gat, recv, None, Z, 3)
+        continue
     run("plain", 0, None, None, None, None, 2)
     run("silu-on-load", 1, None, None, None, None, 2)
     run("B1: dsilu", 0, None, None, None, Z, 3)
