@@ -583,7 +583,15 @@ def main():
                 "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                 "peak_source": pk_src + " bf16 sustained", "algorithmic_flops_per_launch_group": alg,
                 "executed_flops_per_launch_group": executed_flops_edge_mlp(D, H, E) / 4.0,
-                "avg_ms_per_launch_group": ms_per_layer}
+                "avg_ms_per_launch_group": ms_per_layer,
+                # the same launches against the HBM roofline (they are HBM-bound at H <= 256: H/2 FLOP per byte):
+                # algorithmic bytes = each of the two GEMMs reads and writes one bf16/fp32 [E,H] tensor
+                "hbm_view": (lambda nb: {"algorithmic_bytes_per_launch_group": nb,
+                                         "achieved_gbs": nb / (ms_per_layer * 1e-3) / 1e9 if ms_per_layer > 0 else 0.0,
+                                         "peak_gbs": pk.get("hbm_gbs"),
+                                         "frac": (nb / (ms_per_layer * 1e-3) / 1e9) / pk["hbm_gbs"]
+                                         if ms_per_layer > 0 and pk.get("hbm_gbs") else None})(
+                    4.0 * E * H * (2 if args.precision == "bf16" and H in (64, 128, 256) else 4))}
     step_ms = total / args.steps * 1e3
     share = {k: (prof["ms"][i] / args.steps) / step_ms for i, k in
              enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment_bwd", "edge_feat", "node", "segment_fwd"])} if train else None
