@@ -21,6 +21,8 @@
 // the A ring (16 KB per slot, 6 slots at N=K=256).  HBM traffic per row: 2K bytes in, 2N bytes out.
 #include <string.h>
 
+#include <type_traits>
+
 #include "tc_gemm.cuh"
 
 namespace aether {
@@ -168,134 +170,164 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     //       -> TMA store; gathered node terms and the silu' factor are applied in registers =====
     // Each warp owns two 32-row x 32-column staging boxes (2 KB each, 64-byte swizzle), so only
     // __syncwarp is needed.  Warps w and w+4 share a lane quarter and take alternate column chunks.
-    const int qr = warp & 3, hf = warp >> 2;
-    const uint32_t sbuf = sStage + warp * 4096;
-    uint32_t lt = 0, nbox = 0;
-    const bool has_b = g.gat16 && g.idx_b;      // tc_gemm() rejects idx_b together with dsilu: they share a slot
-    // Every epilogue operand of a chunk (64 contiguous bytes per row and source) is requested ONE CHUNK AHEAD,
-    // also across tiles, so its L2 / HBM latency is covered by the previous chunk's work.  Two register slots:
-    // xn = gathered row idx_a, yn = gathered row idx_b or the silu' rows.
-    uint4 xn[4], yn[4];
-    int ia_n = 0, ib_n = 0;
-    auto request = [&](int ia_, int ib_, int64_t zrow_, int c) {
-      if (g.gat16) {
-        const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
+    // The loop below exists twice: ZDEEP = the epilogue's only operand is the silu' rows (no gathers), which then are
+    // requested TWO chunks ahead (three register slots); otherwise one chunk ahead (gathers + silu' share the register
+    // budget: the two-ahead variant with a gathered row spilled and measured 30 % slower).
+    auto run = [&](auto zdeep_tag) {
+      constexpr bool ZDEEP = decltype(zdeep_tag)::value;
+      const int qr = warp & 3, hf = warp >> 2;
+      const uint32_t sbuf = sStage + warp * 4096;
+      uint32_t lt = 0, nbox = 0;
+      const bool has_b = g.gat16 && g.idx_b;      // tc_gemm() rejects idx_b together with dsilu: they share a slot
+      // Every epilogue operand of a chunk (64 contiguous bytes per row and source) is requested ONE CHUNK AHEAD,
+      // also across tiles, so its L2 / HBM latency is covered by the previous chunk's work.  Two register slots:
+      // xn = gathered row idx_a, yn = gathered row idx_b or the silu' rows.
+      uint4 xn[4], yn[4], y2[4];
+      int ia_n = 0, ib_n = 0;
+      constexpr int CPT = N / 64;                   // chunks per tile and warp
+      // ZDEEP: silu' rows of the chunk d chunks after (tile row `row_`, chunk k_ of its tile) into dst
+      auto zrequest = [&](uint4 (&dst)[4], int64_t t_, int64_t row_, int k_) {
+        const int m = k_ / CPT, kk = k_ % CPT;
+        if (t_ + (int64_t)m * gridDim.x >= n_tiles) return;
+        int64_t rr = row_ + (int64_t)m * gridDim.x * kTileM;
+        rr = rr < g.M ? rr : g.M - 1;
+        const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)rr * g.ldd + hf * 32 + kk * 64);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) xn[q] = __ldg(pa + q);
-      }
-      if (has_b) {
-        const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
+        for (int q = 0; q < 4; ++q) dst[q] = __ldg(pd + q);
+      };
+      auto request = [&](int ia_, int ib_, int64_t zrow_, int c) {
+        if (g.gat16) {
+          const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) yn[q] = __ldg(pb + q);
-      } else if (g.dsilu) {
-        const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow_ * g.ldd + c);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) yn[q] = __ldg(pd + q);
-      }
-    };
-    if ((int64_t)blockIdx.x < n_tiles) {
-      const int64_t r0 = (int64_t)blockIdx.x * kTileM + qr * 32 + lane;
-      if (g.gat16 && r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b ? g.idx_b[r0] : 0; }
-      request(ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32);
-    }
-    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
-      const uint32_t acc = lt & 1;
-      const int64_t row0 = t * kTileM + qr * 32;
-      const int64_t row = row0 + lane;
-      const int ia = ia_n, ib = ib_n;
-      const int64_t zrow = row < g.M ? row : g.M - 1;     // rows past the end read valid memory, TMA clips them
-      const int64_t tn = t + gridDim.x;
-      const int64_t row_n = row + (int64_t)gridDim.x * kTileM;
-      const int64_t zrow_n = row_n < g.M ? row_n : g.M - 1;
-      ia_n = 0; ib_n = 0;
-      if (g.gat16 && tn < n_tiles && row_n < g.M) { ia_n = g.idx_a[row_n]; ib_n = g.idx_b ? g.idx_b[row_n] : 0; }
-      mbar_wait(bar_accf + 8 * acc, (lt >> 1) & 1);
-      tc_fence_after();
-#pragma unroll 1
-      for (int j = hf; j < N / 32; j += 2, ++nbox) {
-        const uint32_t buf = sbuf + (nbox & 1) * 2048;
-        const int c0 = j * 32;
-        uint4 a4[4], z4[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) { a4[q] = xn[q]; z4[q] = yn[q]; }
-        if (j + 2 < N / 32) request(ia, ib, zrow, c0 + 64);
-        else if (tn < n_tiles) request(ia_n, ib_n, zrow_n, hf * 32);
-        uint32_t r[32];
-        tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + c0, r);
-        // the TMA store that read this buffer two boxes ago must have finished reading it
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-        __syncwarp();
-        tmem_ld_wait();
-        if (j + 2 >= N / 32) {
-          // accumulator fully read by this warp: hand it back to the MMA warp before the slow part
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_acce + 8 * acc);
-        }
-        float v[32];
-        if (g.bias) {
-          const float* bs = sbias + c0;
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+          for (int q = 0; q < 4; ++q) xn[q] = __ldg(pa + q);
         }
         if (has_b) {
+          const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint32_t bb[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
+          for (int q = 0; q < 4; ++q) yn[q] = __ldg(pb + q);
+        } else if (g.dsilu) {
+          const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow_ * g.ldd + c);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
-          }
+          for (int q = 0; q < 4; ++q) yn[q] = __ldg(pd + q);
         }
-        if (g.dsilu) {
-          // backward chain: out = (acc [+ gathered term]) * silu'(z).  w = 2 silu'(z) - 1 = t + h (1 - t^2)
-          // (h = z/2, t = tanh h, |w| <= 1.2) is evaluated two elements per instruction in bf16x2; the product
-          // with the fp32 accumulator stays in fp32: out = v/2 + (v/2) w.
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint32_t zz[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
-            const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
-            uint32_t o[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const uint32_t w = bf2_dsilu_w(zz[e]);
-              float v0 = v[8 * q + 2 * e], v1 = v[8 * q + 2 * e + 1];
-              if (g.gat16) { v0 += bf16_lo(aa[e]); v1 += bf16_hi(aa[e]); }
-              v0 *= 0.5f; v1 *= 0.5f;
-              o[e] = pack_bf16(fmaf(v0, bf16_lo(w), v0), fmaf(v1, bf16_hi(w), v1));
-            }
-            const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
-          }
+      };
+      if ((int64_t)blockIdx.x < n_tiles) {
+        const int64_t r0 = (int64_t)blockIdx.x * kTileM + qr * 32 + lane;
+        if constexpr (ZDEEP) {
+          zrequest(yn, blockIdx.x, r0, 0);
+          zrequest(y2, blockIdx.x, r0, 1);
         } else {
-          if (g.gat16) {
+          if (g.gat16 && r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b ? g.idx_b[r0] : 0; }
+          request(ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32);
+        }
+      }
+      for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+        const uint32_t acc = lt & 1;
+        const int64_t row0 = t * kTileM + qr * 32;
+        const int64_t row = row0 + lane;
+        const int ia = ia_n, ib = ib_n;
+        const int64_t zrow = row < g.M ? row : g.M - 1;     // rows past the end read valid memory, TMA clips them
+        const int64_t tn = t + gridDim.x;
+        const int64_t row_n = row + (int64_t)gridDim.x * kTileM;
+        const int64_t zrow_n = row_n < g.M ? row_n : g.M - 1;
+        ia_n = 0; ib_n = 0;
+        if (g.gat16 && tn < n_tiles && row_n < g.M) { ia_n = g.idx_a[row_n]; ib_n = g.idx_b ? g.idx_b[row_n] : 0; }
+        mbar_wait(bar_accf + 8 * acc, (lt >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int j = hf; j < N / 32; j += 2, ++nbox) {
+          const uint32_t buf = sbuf + (nbox & 1) * 2048;
+          const int c0 = j * 32;
+          uint4 a4[4], z4[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) { a4[q] = xn[q]; z4[q] = yn[q]; }
+          if constexpr (ZDEEP) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) yn[q] = y2[q];
+            zrequest(y2, t, row, (j >> 1) + 2);
+          } else {
+            if (j + 2 < N / 32) request(ia, ib, zrow, c0 + 64);
+            else if (tn < n_tiles) request(ia_n, ib_n, zrow_n, hf * 32);
+          }
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + c0, r);
+          // the TMA store that read this buffer two boxes ago must have finished reading it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          tmem_ld_wait();
+          if (j + 2 >= N / 32) {
+            // accumulator fully read by this warp: hand it back to the MMA warp before the slow part
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_acce + 8 * acc);
+          }
+          float v[32];
+          if (g.bias) {
+            const float* bs = sbias + c0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+          }
+          if (has_b) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+              const uint32_t bb[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
 #pragma unroll
-              for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(aa[e]); v[8 * q + 2 * e + 1] += bf16_hi(aa[e]); }
+              for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
             }
           }
+          if (g.dsilu) {
+            // backward chain: out = (acc [+ gathered term]) * silu'(z).  w = 2 silu'(z) - 1 = t + h (1 - t^2)
+            // (h = z/2, t = tanh h, |w| <= 1.2) is evaluated two elements per instruction in bf16x2; the product
+            // with the fp32 accumulator stays in fp32: out = v/2 + (v/2) w.
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint32_t o[4];
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t zz[4] = {z4[q].x, z4[q].y, z4[q].z, z4[q].w};
+              const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+              uint32_t o[4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) o[e] = pack_bf16(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
-            const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+              for (int e = 0; e < 4; ++e) {
+                const uint32_t w = bf2_dsilu_w(zz[e]);
+                float v0 = v[8 * q + 2 * e], v1 = v[8 * q + 2 * e + 1];
+                if (g.gat16) { v0 += bf16_lo(aa[e]); v1 += bf16_hi(aa[e]); }
+                v0 *= 0.5f; v1 *= 0.5f;
+                o[e] = pack_bf16(fmaf(v0, bf16_lo(w), v0), fmaf(v1, bf16_hi(w), v1));
+              }
+              const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+            }
+          } else {
+            if (g.gat16) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(aa[e]); v[8 * q + 2 * e + 1] += bf16_hi(aa[e]); }
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) o[e] = pack_bf16(v[8 * q + 2 * e], v[8 * q + 2 * e + 1]);
+              const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+            }
           }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && row0 < g.M) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                         :: "l"((uint64_t)&tmO), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
+          }
+          if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0 && row0 < g.M) {
-          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
-                       :: "l"((uint64_t)&tmO), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
-        }
-        if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
-    }
+    };
+    if (g.dsilu && !g.gat16) run(std::true_type{});
+    else run(std::false_type{});
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else {
     // ===== epilogue, fp32 output (node-level Linears, layer-1 feature gradients): direct stores =====

@@ -395,6 +395,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="capture the train step in a CUDA graph at any size")
     ap.add_argument("--no-graph", action="store_true", help="small training shapes: do not capture the step in a CUDA graph")
     args = ap.parse_args()
     cfg = dict(WORKLOADS[args.workload])
@@ -456,7 +457,7 @@ def main():
 
     # small training shapes are launch-latency bound: replay the whole step as one CUDA graph
     graphed = None
-    if train and E * H <= 32e6 and not args.no_graph:
+    if train and (E * H <= 32e6 or args.graph) and not args.no_graph:
         opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=1e-12, fused=True, capturable=True)
         graphed = ab.GraphedTrainStep(model, opt, (send, recv), Nn, allreduce=(lambda: adist.allreduce_grads(params, world))
                                       if world > 1 else None)
