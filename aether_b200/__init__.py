@@ -2,6 +2,7 @@
 
 Public surface (mirrors the reference's nn/state2state/aether.py):
     Aether              drop-in nn.Module (same constructor / forward signature / state_dict)
+    LoCS                the field-free variant (nn/state2state/locs/locs.py), same kernels
     PreparedGraph       receiver-sorted CSR of an edge list (device)
     fc_edges, knn_edges, KnnPlan, caller_prep   the reference's edge builders / caller prep on device
     Rollout, rollout    multi-step rollouts (optionally CUDA-graph captured)
@@ -10,10 +11,11 @@ Public surface (mirrors the reference's nn/state2state/aether.py):
 Everything computes through aether_b200/lib/libaether_b200.so; there is no CPU or ATen fallback.
 """
 from .aether import Aether, AetherLocalizer, FieldNetwork, Globalizer, GNN, GNNLayer  # noqa: F401
+from .locs import LoCS  # noqa: F401
 from .graph import KnnPlan, PreparedGraph, caller_prep, fc_edges, knn_edges, radius_graph  # noqa: F401
 from .partition import PartitionedRollout  # noqa: F401
 from .train import GraphedTrainStep  # noqa: F401
 from .rollout import Rollout, rollout  # noqa: F401
 
-__all__ = ["Aether", "PreparedGraph", "KnnPlan", "fc_edges", "knn_edges", "caller_prep", "Rollout", "rollout", "radius_graph",
+__all__ = ["Aether", "LoCS", "PreparedGraph", "KnnPlan", "fc_edges", "knn_edges", "caller_prep", "Rollout", "rollout", "radius_graph",
            "PartitionedRollout", "GraphedTrainStep"]

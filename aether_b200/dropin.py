@@ -12,6 +12,7 @@ import sys
 import types
 
 from .aether import Aether, AetherLocalizer, FieldNetwork
+from .locs import LoCS, Localizer
 
 
 class ParallelAether:  # pragma: no cover - placeholder for the reference's broken ablation
@@ -27,4 +28,10 @@ def install() -> types.ModuleType:
     m.FieldNetwork = FieldNetwork
     m.__doc__ = "aether_b200 drop-in for the reference's nn/state2state/aether.py"
     sys.modules["nn.state2state.aether"] = m
+    # the field-free baseline (experiments import it as nn.state2state.locs.locs.LoCS)
+    ml = types.ModuleType("nn.state2state.locs.locs")
+    ml.LoCS = LoCS
+    ml.Localizer = Localizer
+    ml.__doc__ = "aether_b200 drop-in for the reference's nn/state2state/locs/locs.py (LoCS only)"
+    sys.modules["nn.state2state.locs.locs"] = ml
     return m

@@ -313,6 +313,45 @@ def aether_step(
     return out
 
 
+def localize_locs(x: Tensor, vel: Tensor, send: Tensor, recv: Tensor):
+    """The base Localizer of LoCS (no field columns).  nn/state2state/locs/locs.py:37-99.
+
+    rel_feat [Nn,2D] = [0, R^T v] (:37-46); edge_attr [E,5D+O] =
+    [R_i^T (p_j-p_i) | euler(R_i^T R_j)/pi | |p_j-p_i| | theta(,phi) | R_i^T v_j | rel_feat[recv]] (:48-99).
+    """
+    D = x.shape[-1]
+    R = heading_frame(vel)
+    Rt = R.transpose(-1, -2)
+    rel_feat = torch.cat([torch.zeros_like(vel), apply_rot(Rt, vel)], -1)
+    Rt_i = Rt[recv]
+    d = x[send] - x[recv]
+    d_loc = apply_rot(Rt_i, d)
+    euler = frame_to_euler(Rt_i @ R[send], D)
+    dist = torch.norm(d, p=2, dim=-1, keepdim=True)
+    sph = torch.cat(heading_angles(d_loc, symmetric=True), -1)
+    v_loc = apply_rot(Rt_i, vel[send])
+    edge_attr = torch.cat([d_loc, euler, dist, sph, v_loc, rel_feat[recv]], -1)
+    return rel_feat, R, edge_attr
+
+
+def locs_step(p: Dict[str, Tensor], x: Tensor, edges: Tuple[Tensor, Tensor], vel: Tensor, edge_attr_orig: Tensor,
+              stages: Optional[dict] = None) -> Tensor:
+    """LoCS.forward.  nn/state2state/locs/locs.py:124-139: the same GNN on the field-free local features."""
+    send, recv = edges
+    rel_feat, R, edge_attr = localize_locs(x, vel, send, recv)
+    e = torch.cat([edge_attr, edge_attr_orig], -1)
+    if stages is not None:
+        stages.update(rel_feat=rel_feat, R=R, edge_attr=e)
+    h = rel_feat
+    for l in range(1, 5):
+        h, e = gnn_layer(p, "gnn.layer_%d" % l, h, e, send, recv, first=(l == 1))
+    silu = torch.nn.functional.silu
+    h = silu(_lin(p, "gnn.out_mlp.0", h))
+    h = silu(_lin(p, "gnn.out_mlp.3", h))
+    pred = _lin(p, "gnn.out_mlp.6", h)
+    return x + apply_rot(R, pred)
+
+
 def caller_prep(x: Tensor, vel: Tensor, charges: Tensor, send: Tensor, recv: Tensor):
     """Per-step features the caller builds.  experiments/lorentz/main.py:243-246.
 

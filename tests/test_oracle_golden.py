@@ -139,3 +139,36 @@ def test_radius_knn_oracle_matches_knn_and_properties():
         assert bool((di[1:] >= di[:-1]).all())
     full = (torch.cdist(pos3, pos3) <= 0.9).sum(1) - 1
     assert torch.equal(deg, full.clamp(max=8))
+
+
+@pytest.mark.parametrize("case", ["locs2d_h32", "locs3d_h64"])
+def test_locs_oracle_vs_reference(case):
+    """LoCS (nn/state2state/locs/locs.py:102-139): stages, output, gradients and a 3-step rollout recorded from the
+    unmodified reference (tests/golden/make_golden_locs.py)."""
+    g = load_golden(case)
+    p = {k: v.clone().requires_grad_(True) for k, v in golden_params(g).items()}
+    x = torch.from_numpy(g["x"]).requires_grad_(True)
+    v = torch.from_numpy(g["vel"]).requires_grad_(True)
+    send, recv = torch.from_numpy(g["send"]), torch.from_numpy(g["recv"])
+    ea = torch.from_numpy(g["edge_attr_orig"])
+    st = {}
+    out = O.locs_step(p, x, (send, recv), v, ea, stages=st)
+    for k in ("rel_feat", "R", "edge_attr"):
+        assert float((st[k].detach() - torch.from_numpy(g[k])).abs().max()) <= 2e-6, k
+    assert float((out.detach() - torch.from_numpy(g["out"])).abs().max()) <= 2e-6
+    loss = torch.nn.functional.mse_loss(out, torch.from_numpy(g["target"]))
+    loss.backward()
+    assert abs(float(loss.detach()) - float(g["loss"])) <= 1e-7
+    assert rel_err(x.grad, g["grad/x"]) <= 1e-4 and rel_err(v.grad, g["grad/vel"]) <= 1e-4
+    for k, t in p.items():
+        if float(np.abs(g["grad/" + k]).max()) > 0:
+            assert rel_err(t.grad, g["grad/" + k]) <= 1e-4, k
+    q = torch.from_numpy(g["charges"])
+    xs, xc, vc = [], x.detach(), v.detach()
+    pd = {k: t.detach() for k, t in p.items()}
+    for _ in range(g["rollout"].shape[0]):
+        _, eaa = O.caller_prep(xc, vc, q, send, recv)
+        xn = O.locs_step(pd, xc, (send, recv), vc, eaa)
+        vc, xc = xn - xc, xn
+        xs.append(xc)
+    assert rel_err(torch.stack(xs), g["rollout"]) <= 1e-5
