@@ -40,13 +40,14 @@ constexpr int kSmemMax = 232448;                  // 227 KB
 constexpr int kMiscBytes = 2048;                  // barriers + tmem pointer + bias
 
 __host__ __device__ constexpr int weight_bytes(int K, int N) { return K * N * 2; }
-constexpr int kStageBytes = kEpiWarps * 2 * 2048; // bf16 epilogue: per warp two 32-row x 32-column boxes
+constexpr int kStageBytes = kEpiWarps * 2 * 2048; // per epilogue warp: two 32x32 bf16 boxes, or one 32x32 fp32 tile
 __host__ __device__ constexpr int num_slots(int K, int N, bool staged) {
-  int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N) - (staged ? kStageBytes : 0)) / kSlotBytes;
+  (void)staged;
+  int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N) - kStageBytes) / kSlotBytes;
   return s > 8 ? 8 : s;
 }
 __host__ __device__ constexpr int smem_bytes(int K, int N, bool staged) {
-  return 1024 + weight_bytes(K, N) + num_slots(K, N, staged) * kSlotBytes + (staged ? kStageBytes : 0) + kMiscBytes;
+  return 1024 + weight_bytes(K, N) + num_slots(K, N, staged) * kSlotBytes + kStageBytes + kMiscBytes;
 }
 __host__ __device__ constexpr int tmem_cols(int N) { return 2 * N < 32 ? 32 : 2 * N; }
 
@@ -63,7 +64,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t sW = base;
   const uint32_t sA = base + weight_bytes(K, N);
   const uint32_t sStage = sA + S * kSlotBytes;
-  const uint32_t sMisc = sStage + (STAGED ? kStageBytes : 0);
+  const uint32_t sMisc = sStage + kStageBytes;
   // barriers (8 bytes each)
   const uint32_t bar_raw = sMisc;                 // [S] TMA landed
   const uint32_t bar_rdy = sMisc + 64;            // [S] transform done
@@ -330,7 +331,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     else run(std::false_type{});
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else {
-    // ===== epilogue, fp32 output (node-level Linears, layer-1 feature gradients): direct stores =====
+    // ===== epilogue, fp32 output (node-level Linears, layer-1 feature gradients) =====
+    // Row-per-thread global accesses would touch 32 lines per instruction; instead the accumulator chunk (+ bias) goes
+    // through the warp's swizzled 32x32 fp32 staging tile and is read back 16 bytes per lane in row-major order, so
+    // the residual / silu' / mask / accumulate operands and the store are all 512 contiguous bytes per instruction.
+    const uint32_t sbuf = sStage + warp * 4096;
+    const bool vec = (g.ldo32 & 3) == 0 && (g.n_valid & 3) == 0 && (!g.res || (g.ldr & 3) == 0) &&
+                     (!g.dsilu32 || (g.ldd32 & 3) == 0) && (!g.emask || (g.ldm & 3) == 0);
     uint32_t lt = 0;
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
       const uint32_t acc = lt & 1;
@@ -339,6 +346,53 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int qr = warp & 3;
       const int64_t row = t * kTileM + qr * 32 + lane;
       const bool live = row < g.M;
+      if (vec) {
+#pragma unroll 1
+        for (int j = warp >> 2; j < N / 32; j += 2) {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + j * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sbias + j * 32 + 4 * q);
+            const uint32_t addr = sbuf + lane * 128 + ((q ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "f"(__uint_as_float(r[4 * q]) + b4.x),
+                         "f"(__uint_as_float(r[4 * q + 1]) + b4.y), "f"(__uint_as_float(r[4 * q + 2]) + b4.z),
+                         "f"(__uint_as_float(r[4 * q + 3]) + b4.w) : "memory");
+          }
+          __syncwarp();
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int i = it * 32 + lane, rr = i >> 3, ch = i & 7;
+            const int64_t grow = t * kTileM + qr * 32 + rr;
+            const int col = j * 32 + ch * 4;
+            float4 v;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                         : "r"(sbuf + rr * 128 + ((ch ^ (rr & 7)) << 4)) : "memory");
+            if (grow < g.M && col < g.n_valid) {
+              if (g.res) {
+                const float4 a = *reinterpret_cast<const float4*>(g.res + (size_t)grow * g.ldr + col);
+                v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+              }
+              if (g.dsilu32) {
+                const float4 z = __ldg(reinterpret_cast<const float4*>(g.dsilu32 + (size_t)grow * g.ldd32 + col));
+                v.x *= dsilu_f(z.x); v.y *= dsilu_f(z.y); v.z *= dsilu_f(z.z); v.w *= dsilu_f(z.w);
+              }
+              if (g.emask) {
+                const float4 z = __ldg(reinterpret_cast<const float4*>(g.emask + (size_t)grow * g.ldm + col));
+                v.x *= z.x; v.y *= z.y; v.z *= z.z; v.w *= z.w;
+              }
+              float4* po = reinterpret_cast<float4*>(g.out_f32 + (size_t)grow * g.ldo32 + col);
+              if (g.accumulate) {
+                const float4 a = *po;
+                v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+              }
+              *po = v;
+            }
+          }
+          __syncwarp();
+        }
+      } else {
 #pragma unroll 1
       for (int j = warp >> 2; j < N / 32; j += 2) {
         uint32_t r[32];
@@ -390,6 +444,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int i = 0; i < 32; ++i)
             if (j * 32 + i < g.n_valid) po[i] = v[i];
         }
+      }
       }
       tc_fence_before();
       __syncwarp();

@@ -48,3 +48,23 @@ for dbg in os.environ.get("DBGS", "0").split(","):
     run("B1: dsilu", 0, None, None, None, Z, 3)
     run("B2: gather recv + dsilu", 0, gat, recv, None, Z, 3)
     run("fwdA: silu + gather send,recv", 1, gat, send, recv, None, 2)
+
+# node-level shape: fp32 output (+ residual through the debug hook is not exposed; plain + bias only)
+Mn = 102400
+An = torch.randn(Mn, H, device="cuda").bfloat16()
+outf = torch.empty(Mn, H, dtype=torch.float32, device="cuda")
+bias = torch.randn(H, device="cuda")
+def call_node():
+    return lib.aether_dbg_tc_gemm(P(An), Mn, H, H, P(W), H, H, H, H, 0, 0, 0, P(bias), None, 0, None, None, 0, None,
+                                  None, P(outf), P(scratch), stream())
+assert call_node() == 0
+best = 1e9
+for _ in range(4):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(10):
+        call_node()
+    b.record()
+    torch.cuda.synchronize()
+    best = min(best, a.elapsed_time(b) / 10)
+print("node GEMM fp32 out M=%d: %.1f us (incl. weight pack), %.0f GB/s" % (Mn, best * 1e3, Mn * H * 6 / best / 1e6))
