@@ -48,6 +48,8 @@ for dbg in os.environ.get("DBGS", "0").split(","):
     run("B1: dsilu", 0, None, None, None, Z, 3)
     run("B2: gather recv + dsilu", 0, gat, recv, None, Z, 3)
     run("fwdA: silu + gather send,recv", 1, gat, send, recv, None, 2)
+    run("fwdA': silu + gather recv,recv", 1, gat, recv, recv, None, 2)
+    run("fwdA'': silu + gather send only", 1, gat, send, None, None, 2)
 
 # node-level shape: fp32 output (+ residual through the debug hook is not exposed; plain + bias only)
 Mn = 102400
