@@ -54,7 +54,7 @@ class PartitionedRollout:
     ``run(x0, v0, charges)`` returns positions ``[steps, Nn, D]`` (identical on every rank)."""
 
     def __init__(self, model, send: torch.Tensor, recv: torch.Tensor, n_nodes: int, steps: int, world: int = 1,
-                 rank: int = 0, parts: Optional[int] = None, group=None):
+                 rank: int = 0, parts: Optional[int] = None, group=None, cuda_graph: bool = False):
         self.lib = _lib.load()
         self.model, self.steps, self.world, self.rank, self.group = model, int(steps), int(world), int(rank), group
         self.D, self.H, self.Nn = model.num_dims, model.hidden_size, int(n_nodes)
@@ -72,12 +72,19 @@ class PartitionedRollout:
         f32 = dict(dtype=torch.float32, device=dev)
         # two exchange buffers: a phase gathers sender terms from one and writes the next layer's into the other
         self.xchg = [torch.zeros(self.padded, self.H, dtype=xdtype, device=dev) for _ in range(2)]
+        self.xin = torch.zeros(self.padded, self.D, **f32)                          # static inputs of a run
+        self.vin = torch.zeros(self.padded, self.D, **f32)
         self.xbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]   # positions ping-pong (gathered)
         self.vbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]
         self.q = torch.zeros(self.padded, **f32)
         self.traj = torch.empty(self.steps, self.Nn, self.D, **f32)
         self.edges_total = full.n_edges
         self.launch_exchanges = 0
+        # the whole T-step loop, all-gathers included, as one CUDA graph (NCCL collectives are capturable; every rank
+        # captures and replays the same sequence).  With world > 1, delete the object (and its graph) before
+        # torch.distributed.destroy_process_group(): tearing the communicator down under a live captured graph hung
+        # in our 8-GPU run.
+        self._use_graph, self._g, self.launches_per_replay = bool(cuda_graph), None, 0
 
     def _gather(self, buf: torch.Tensor):
         if self.world > 1:
@@ -103,16 +110,31 @@ class PartitionedRollout:
             self._gather(self.xchg[phase & 1] if phase < 3 else xn)
         torch.sub(xn, x, out=vn)
 
+    def _loop(self):
+        x, v = self.xin, self.vin
+        for t in range(self.steps):
+            xn, vn = self.xbuf[t & 1], self.vbuf[t & 1]
+            self._step(x, v, xn, vn)
+            self.traj[t].copy_(xn[:self.Nn])
+            x, v = xn, vn
+
     @torch.no_grad()
     def run(self, x0, v0, charges) -> torch.Tensor:
         with torch.cuda.device(self.dev):
-            x, v = self.xbuf[0], self.vbuf[0]
-            x[:self.Nn].copy_(x0)
-            v[:self.Nn].copy_(v0)
-            self.q[:self.Nn].copy_(charges.reshape(-1))
-            for t in range(self.steps):
-                xn, vn = self.xbuf[(t + 1) & 1], self.vbuf[(t + 1) & 1]
-                self._step(x, v, xn, vn)
-                self.traj[t].copy_(xn[:self.Nn])
-                x, v = xn, vn
+            self.xin[:self.Nn].copy_(x0, non_blocking=True)
+            self.vin[:self.Nn].copy_(v0, non_blocking=True)
+            self.q[:self.Nn].copy_(charges.reshape(-1), non_blocking=True)
+            if not self._use_graph:
+                self._loop()
+                return self.traj
+            if self._g is None:
+                self._loop()                                   # warm-up outside capture (lazy init, NCCL channels)
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                n0 = self.lib.aether_launch_count()
+                with torch.cuda.graph(g):
+                    self._loop()
+                self.launches_per_replay = int(self.lib.aether_launch_count() - n0)
+                self._g = g
+            self._g.replay()
             return self.traj

@@ -244,7 +244,12 @@ def run_c5(args, cfg, H):
     xd, vd, qd = [t.to(dev) for t in host]
     send, recv = ab.radius_graph(xd, cfg["radius"], cfg["k"])          # replicated on every rank, built once
     E = int(send.numel())
-    roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank)
+    # One GPU: the T-step loop is replayed as one CUDA graph.  Several GPUs: launched eagerly -- capturing the NCCL
+    # all-gathers works and was measured (8 GPUs, H = 256: 11.4 vs 12.6 ms), but the processes did not exit cleanly
+    # afterwards (teardown of the captured communicator), so it stays opt-in (--graph).
+    use_graph = (world == 1 and not args.no_graph) or (world > 1 and args.graph)
+    roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, cuda_graph=use_graph)
+    eager = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank) if use_graph else roll
 
     def step_resident():
         roll.run(xd, vd, qd)
@@ -295,7 +300,10 @@ def run_c5(args, cfg, H):
     if rank == 0:
         sampler.start()
     total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
+    launches += args.steps * roll.launches_per_replay          # kernels launched by graph replays
     clocks = sampler.stop() if rank == 0 else None
+    if eager is not roll:       # graph replays carry no library-side event pairs: time the same kernels launched eagerly
+        _, _, prof = timed(lambda: eager.run(xd, vd, qd), max(1, min(args.steps, 3)), 1, profile=True)
     e2e = None
     if not args.no_e2e:
         e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))

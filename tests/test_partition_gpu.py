@@ -93,3 +93,19 @@ def test_partitioned_rollout_bf16(ab, H):
     with torch.no_grad():
         want = O.rollout(p, x, v, q, lambda xx: (send.cpu(), recv.cpu()), 2)
     assert rel_err(got.cpu(), want) <= 2e-2
+
+
+def test_partitioned_rollout_cuda_graph(ab):
+    D, N, H = 3, 800, 64
+    m, _ = make(ab, D, H)
+    x, v, q = _scene(D, N, 13)
+    send, recv = ab.radius_graph(x.cuda(), 1.0, 12)
+    eager = ab.PartitionedRollout(m, send, recv, N, 3, parts=2).run(x.cuda(), v.cuda(), q.cuda()).clone()
+    gr = ab.PartitionedRollout(m, send, recv, N, 3, parts=2, cuda_graph=True)
+    a = gr.run(x.cuda(), v.cuda(), q.cuda()).clone()
+    b = gr.run(x.cuda(), v.cuda(), q.cuda()).clone()          # second call = pure replay
+    assert torch.equal(a, eager) and torch.equal(b, eager) and gr.launches_per_replay > 0
+    x2 = x + 0.01
+    c = gr.run(x2.cuda(), v.cuda(), q.cuda())
+    want = ab.PartitionedRollout(m, send, recv, N, 3, parts=2).run(x2.cuda(), v.cuda(), q.cuda())
+    assert torch.equal(c, want)
