@@ -18,7 +18,7 @@
 //               Two warps per scheduler hide each other's TMEM / global-load latency.
 //
 // Shared memory: weights N*K*2 bytes resident for the whole kernel (128 KB at N=K=256), the rest is
-// the A ring (16 KB per slot, 6 slots at N=K=256).  HBM traffic per row: 2K bytes in, 2N bytes out.
+// the A ring (16 KB per slot, 4 slots at N=K=256) and 32 KB of epilogue staging.  HBM traffic per row: 2K bytes in, 2N bytes out.
 #include <string.h>
 
 #include <type_traits>
