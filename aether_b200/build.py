@@ -23,6 +23,8 @@ HOSTCHECK_SO = os.path.join(LIB, "libaether_hostcheck.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-I", os.path.join(ROOT, "include")]
+# extra nvcc flags for experiments (e.g. AETHER_NVCC_FLAGS=-DAETHER_TC_REGSPLIT with `-f`); empty for the shipped build
+COMMON += os.environ.get("AETHER_NVCC_FLAGS", "").split()
 
 # (source, extra flags).  The geometry files are built without FMA contraction so that products and
 # sums round separately, like the reference's eager ATen ops.

@@ -31,7 +31,16 @@ namespace {
 
 using namespace tc;
 
+#ifdef AETHER_TC_REGSPLIT
+// EXPERIMENTAL, off by default and not measured yet: 16 warps so that every warpgroup is complete; after
+// the set-up barrier the two epilogue warpgroups raise their register budget with setmaxnreg and the producer / MMA /
+// transform warpgroups give theirs up (8 x 32 x (128 - 56) registers change hands; warps 14-15 idle).  The larger budget
+// holds FOUR operand slots, so gathered rows (and the silu' rows that go with them) are requested two chunks ahead.
+constexpr int kThreads = 512;
+constexpr int kRegsEpi = 200, kRegsAux = 56;
+#else
 constexpr int kThreads = 448;
+#endif
 constexpr int kEpiWarps = 8;
 constexpr int kWarpTma = 8, kWarpMma = 9, kWarpTf0 = 10;
 constexpr int kTileM = 128;
@@ -100,6 +109,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+#ifdef AETHER_TC_REGSPLIT
+  // one instruction for both auxiliary warpgroups; the epilogue warpgroups raise theirs inside their own branch, so
+  // ptxas allocates that branch against the larger budget
+  if (warp >= kEpiWarps) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" :: "n"(kRegsAux));
+#endif
 
   if (warp == kWarpTma) {
     // ===== TMA producer =====
@@ -144,6 +158,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp >= kWarpTf0) {
     // ===== transform: in-place SiLU on the landed A box =====
+#ifdef AETHER_TC_REGSPLIT
+    if (warp >= kWarpTf0 + 4) {
+      // warps 14-15 only complete the last warpgroup
+    } else
+#endif
     if (TF != TC_TF_NONE) {
       const int tt = threadIdx.x - kWarpTf0 * 32; // 0..127
       uint32_t it = 0;
@@ -174,8 +193,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // The loop below exists twice: ZDEEP = the epilogue's only operand is the silu' rows (no gathers), which then are
     // requested TWO chunks ahead (three register slots); otherwise one chunk ahead (gathers + silu' share the register
     // budget: the two-ahead variant with a gathered row spilled and measured 30 % slower).
-    auto run = [&](auto zdeep_tag) {
+    // GDEEP (AETHER_TC_REGSPLIT builds only): gathered rows and their companions two chunks ahead, four slots.
+#ifdef AETHER_TC_REGSPLIT
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" :: "n"(kRegsEpi));
+#endif
+    auto run = [&](auto zdeep_tag, auto gdeep_tag) {
       constexpr bool ZDEEP = decltype(zdeep_tag)::value;
+      constexpr bool GDEEP = decltype(gdeep_tag)::value;
       const int qr = warp & 3, hf = warp >> 2;
       const uint32_t sbuf = sStage + warp * 4096;
       uint32_t lt = 0, nbox = 0;
@@ -183,9 +207,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // Every epilogue operand of a chunk (64 contiguous bytes per row and source) is requested ONE CHUNK AHEAD,
       // also across tiles, so its L2 / HBM latency is covered by the previous chunk's work.  Two register slots:
       // xn = gathered row idx_a, yn = gathered row idx_b or the silu' rows.
-      uint4 xn[4], yn[4], y2[4];
+      uint4 xn[4], yn[4], y2[4], x2[4];
       int ia_n = 0, ib_n = 0;
-      constexpr int CPT = N / 64;                   // chunks per tile and warp
+      constexpr int CPT = N >= 64 ? N / 64 : 1;     // chunks per tile and warp
       // ZDEEP: silu' rows of the chunk d chunks after (tile row `row_`, chunk k_ of its tile) into dst
       auto zrequest = [&](uint4 (&dst)[4], int64_t t_, int64_t row_, int k_) {
         const int m = k_ / CPT, kk = k_ % CPT;
@@ -196,20 +220,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int q = 0; q < 4; ++q) dst[q] = __ldg(pd + q);
       };
-      auto request = [&](int ia_, int ib_, int64_t zrow_, int c) {
+      auto request = [&](uint4 (&dx)[4], uint4 (&dy)[4], int ia_, int ib_, int64_t zrow_, int c) {
         if (g.gat16) {
           const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) xn[q] = __ldg(pa + q);
+          for (int q = 0; q < 4; ++q) dx[q] = __ldg(pa + q);
         }
         if (has_b) {
           const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
 #pragma unroll
-          for (int q = 0; q < 4; ++q) yn[q] = __ldg(pb + q);
+          for (int q = 0; q < 4; ++q) dy[q] = __ldg(pb + q);
         } else if (g.dsilu) {
           const uint4* pd = reinterpret_cast<const uint4*>(g.dsilu + (size_t)zrow_ * g.ldd + c);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) yn[q] = __ldg(pd + q);
+          for (int q = 0; q < 4; ++q) dy[q] = __ldg(pd + q);
         }
       };
       if ((int64_t)blockIdx.x < n_tiles) {
@@ -219,7 +243,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           zrequest(y2, blockIdx.x, r0, 1);
         } else {
           if (g.gat16 && r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b ? g.idx_b[r0] : 0; }
-          request(ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32);
+          request(xn, yn, ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32);
+          if constexpr (GDEEP) request(x2, y2, ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32 + 64);
         }
       }
       for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
@@ -246,9 +271,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int q = 0; q < 4; ++q) yn[q] = y2[q];
             zrequest(y2, t, row, (j >> 1) + 2);
+          } else if constexpr (GDEEP) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { xn[q] = x2[q]; yn[q] = y2[q]; }
+            const int k2 = (j >> 1) + 2;            // this warp's chunk two ahead: same tile, or the next one
+            if (k2 < CPT) request(x2, y2, ia, ib, zrow, c0 + 128);
+            else if (tn < n_tiles) request(x2, y2, ia_n, ib_n, zrow_n, hf * 32 + (k2 - CPT) * 64);
           } else {
-            if (j + 2 < N / 32) request(ia, ib, zrow, c0 + 64);
-            else if (tn < n_tiles) request(ia_n, ib_n, zrow_n, hf * 32);
+            if (j + 2 < N / 32) request(xn, yn, ia, ib, zrow, c0 + 64);
+            else if (tn < n_tiles) request(xn, yn, ia_n, ib_n, zrow_n, hf * 32);
           }
           uint32_t r[32];
           tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + c0, r);
@@ -327,14 +358,24 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     };
-    if (g.dsilu && !g.gat16) run(std::true_type{});
-    else run(std::false_type{});
+    bool done = false;
+#ifdef AETHER_TC_REGSPLIT
+    if constexpr (N >= 256) {
+      if (g.gat16) { run(std::false_type{}, std::true_type{}); done = true; }
+    }
+#endif
+    if (done) {
+    } else if (g.dsilu && !g.gat16) run(std::true_type{}, std::false_type{});
+    else run(std::false_type{}, std::false_type{});
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   } else {
     // ===== epilogue, fp32 output (node-level Linears, layer-1 feature gradients) =====
     // Row-per-thread global accesses would touch 32 lines per instruction; instead the accumulator chunk (+ bias) goes
     // through the warp's swizzled 32x32 fp32 staging tile and is read back 16 bytes per lane in row-major order, so
     // the residual / silu' / mask / accumulate operands and the store are all 512 contiguous bytes per instruction.
+#ifdef AETHER_TC_REGSPLIT
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" :: "n"(kRegsEpi));
+#endif
     const uint32_t sbuf = sStage + warp * 4096;
     const bool vec = (g.ldo32 & 3) == 0 && (g.n_valid & 3) == 0 && (!g.res || (g.ldr & 3) == 0) &&
                      (!g.dsilu32 || (g.ldd32 & 3) == 0) && (!g.emask || (g.ldm & 3) == 0);
