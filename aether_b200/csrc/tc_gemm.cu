@@ -200,6 +200,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     auto run = [&](auto zdeep_tag, auto gdeep_tag) {
       constexpr bool ZDEEP = decltype(zdeep_tag)::value;
       constexpr bool GDEEP = decltype(gdeep_tag)::value;
+#ifdef AETHER_TC_REGSPLIT
+      constexpr bool ZD3 = ZDEEP;                   // with the larger budget the silu' rows go THREE chunks ahead (slot x2)
+#else
+      constexpr bool ZD3 = false;
+#endif
       const int qr = warp & 3, hf = warp >> 2;
       const uint32_t sbuf = sStage + warp * 4096;
       uint32_t lt = 0, nbox = 0;
@@ -241,6 +246,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if constexpr (ZDEEP) {
           zrequest(yn, blockIdx.x, r0, 0);
           zrequest(y2, blockIdx.x, r0, 1);
+          if constexpr (ZD3) zrequest(x2, blockIdx.x, r0, 2);
         } else {
           if (g.gat16 && r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b ? g.idx_b[r0] : 0; }
           request(xn, yn, ia_n, ib_n, r0 < g.M ? r0 : g.M - 1, hf * 32);
@@ -270,7 +276,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if constexpr (ZDEEP) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) yn[q] = y2[q];
-            zrequest(y2, t, row, (j >> 1) + 2);
+            if constexpr (ZD3) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) y2[q] = x2[q];
+              zrequest(x2, t, row, (j >> 1) + 3);
+            } else {
+              zrequest(y2, t, row, (j >> 1) + 2);
+            }
           } else if constexpr (GDEEP) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) { xn[q] = x2[q]; yn[q] = y2[q]; }
