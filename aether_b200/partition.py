@@ -118,6 +118,13 @@ class PartitionedRollout:
             self.traj[t].copy_(xn[:self.Nn])
             x, v = xn, vn
 
+    def release(self) -> None:
+        """Drop the captured graph (it references the communicator's kernels): call before the process group is
+        destroyed; the next ``run`` captures again."""
+        if self._g is not None:
+            torch.cuda.synchronize(self.dev)
+            self._g = None
+
     @torch.no_grad()
     def run(self, x0, v0, charges) -> torch.Tensor:
         with torch.cuda.device(self.dev):

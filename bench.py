@@ -246,7 +246,8 @@ def run_c5(args, cfg, H):
     E = int(send.numel())
     # One GPU: the T-step loop is replayed as one CUDA graph.  Several GPUs: launched eagerly -- capturing the NCCL
     # all-gathers works and was measured (8 GPUs, H = 256: 11.4 vs 12.6 ms), but the processes did not exit cleanly
-    # afterwards (teardown of the captured communicator), so it stays opt-in (--graph).
+    # afterwards (teardown of the captured communicator).  The teardown below now drops the graphs before every rank leaves
+    # the communicator together; until that is confirmed on 8 GPUs the captured form stays opt-in (--graph).
     use_graph = (world == 1 and not args.no_graph) or (world > 1 and args.graph)
     roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, cuda_graph=use_graph)
     eager = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank) if use_graph else roll
@@ -308,9 +309,14 @@ def run_c5(args, cfg, H):
     if not args.no_e2e:
         e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
         e2e = 4.0 * E * T * args.steps / e2e_total
+    if dist is not None:
+        # all ranks leave the communicator together, captured graphs first (rank 0 still has its CPU baseline to run)
+        roll.release()
+        torch.cuda.synchronize()
+        dist.barrier()
+        dist.destroy_process_group()
+        dist = None
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
         return
     pk, pk_src = peaks()
     e_local = roll.local[0].E
@@ -352,8 +358,6 @@ def run_c5(args, cfg, H):
         line["cpu_baseline"] = {"value": 4.0 * e_step * it / dt, "unit": "edge-messages/s", "cores": cores, "kind": "port",
                                 "sample": sample + ", %d repeats, %d host threads" % (it, cores)}
     print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
 
 
 def run_reference(args, cfg, H):
