@@ -75,3 +75,37 @@ def test_module_state_dict_matches_reference_layout():
     with pytest.raises(RuntimeError):
         m(None, torch.zeros(4, 3), [torch.zeros(0, dtype=torch.long)] * 2, torch.zeros(4, 3), torch.zeros(0, 2),
           torch.zeros(4, 1))
+
+
+def test_dropin_alias_and_pickle_on_cpu():
+    """The reference's import line (experiments/lorentz/main.py:16) resolves to this package after install(); the module
+    pickles like the reference's (main.py:187) and `print(model)` keeps the reference's side effect (aether.py:163-167)."""
+    import importlib
+    import io
+    import sys
+
+    import torch
+
+    import aether_b200
+    import aether_b200.dropin as dropin
+    saved = {k: sys.modules.get(k) for k in ("nn.state2state.aether", "nn.state2state.locs.locs")}
+    try:
+        dropin.install()
+        mod = importlib.import_module("nn.state2state.aether")
+        assert mod.Aether is aether_b200.Aether
+        assert importlib.import_module("nn.state2state.locs.locs").LoCS is aether_b200.LoCS
+        with pytest.raises(NotImplementedError):
+            mod.ParallelAether(6, 64, 0.0, 3)
+        m = mod.Aether(input_size=6, hidden_size=64, dropout_prob=0.0, num_dims=3, device="cpu")
+        assert m.params == "132822" and str(m) == "132822"            # SURVEY.md 8a: probed parameter count (D=3, H=64)
+        buf = io.BytesIO()
+        torch.save(m, buf)
+        buf.seek(0)
+        m2 = torch.load(buf, weights_only=False)
+        assert all(torch.equal(a, b) for a, b in zip(m.state_dict().values(), m2.state_dict().values()))
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
