@@ -9,7 +9,7 @@ fallback.  The sub-modules below only hold parameters; they are never called.
 from __future__ import annotations
 
 import os
-from typing import List, Optional
+from typing import List
 
 import numpy as np
 import torch

@@ -16,7 +16,7 @@ Everything here is host logic and works with the ``gloo`` backend on CPU tensors
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
