@@ -9,7 +9,6 @@ no call of the library synchronises or reads device data on the host, and all bu
 """
 from __future__ import annotations
 
-
 import torch
 
 from .graph import PreparedGraph, caller_prep
