@@ -53,6 +53,9 @@ constexpr int kStageBytes = kEpiWarps * 2 * 2048; // per epilogue warp: two 32x3
 __host__ __device__ constexpr int num_slots(int K, int N, bool staged) {
   (void)staged;
   int s = (kSmemMax - 1024 - kMiscBytes - weight_bytes(K, N) - kStageBytes) / kSlotBytes;
+#ifdef AETHER_TC_MAX_SLOTS                          // experiment knob: ring-depth sensitivity (e.g. -DAETHER_TC_MAX_SLOTS=3)
+  if (s > AETHER_TC_MAX_SLOTS) s = AETHER_TC_MAX_SLOTS;
+#endif
   return s > 8 ? 8 : s;
 }
 __host__ __device__ constexpr int smem_bytes(int K, int N, bool staged) {
