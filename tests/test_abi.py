@@ -109,3 +109,23 @@ def test_dropin_alias_and_pickle_on_cpu():
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def test_header_is_plain_c_and_c_caller_links(lib, tmp_path):
+    """include/aether_b200.h compiles as C99 and a C program links against the library (examples/abi_sizes.c)."""
+    import subprocess
+    inc = os.path.join(ROOT, "include")
+    libdir = os.path.join(ROOT, "aether_b200", "lib")
+    r = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-fsyntax-only", "-x", "c",
+                        os.path.join(inc, "aether_b200.h")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    exe = str(tmp_path / "abi_sizes")
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", inc, os.path.join(ROOT, "examples", "abi_sizes.c"),
+                        "-L", libdir, "-laether_b200", "-Wl,-rpath," + libdir, "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe, "2", "256", "102400", "10137600"], capture_output=True, text=True)
+    assert r.returncode == 0 and "abi 1" in r.stdout, r.stdout + r.stderr
+    from aether_b200 import _lib
+    d = _lib.AetherDims(2, 256, 102400, 10137600)
+    assert ("training fp32 %d " % lib.aether_workspace_bytes(ctypes.byref(d), _lib.F_SAVE)) in r.stdout
+    assert subprocess.run([exe, "4", "64", "1", "1"], capture_output=True).returncode == 1      # D = 4 is rejected
