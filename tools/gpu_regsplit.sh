@@ -3,7 +3,7 @@
 # micro-bench of the default build, then rebuild with the flag, GEMM parity tests, micro-bench, config-4 bench,
 # and the default build is restored at the end.  Every step runs under its own timeout.
 mkdir -p gpurun_out
-timeout 300 python tools/tc_bench.py > gpurun_out/tcbench_default.txt 2>&1
+HALF=1 timeout 300 python tools/tc_bench.py > gpurun_out/tcbench_default.txt 2>&1
 AETHER_NVCC_FLAGS=-DAETHER_TC_REGSPLIT timeout 600 python -m aether_b200.build -f > gpurun_out/build_regsplit.txt 2>&1 || { echo "regsplit build failed"; python -m aether_b200.build -f; exit 1; }
 timeout 600 python -m pytest tests/test_tc_gpu.py tests/test_bf16_gpu.py -q -m gpu -x --timeout 300 > gpurun_out/pytest_regsplit.txt 2>&1
 echo "pytest rc=$?"

@@ -19,10 +19,15 @@ gat = torch.randn(Nn, 2 * H, device="cuda").bfloat16()
 recv = torch.arange(M, device="cuda", dtype=torch.int32) // 99
 send = ((torch.arange(M, device="cuda", dtype=torch.int32) % 99) + (recv // 100) * 100).clamp(max=Nn - 1)
 
-def run(name, silu, gat_, ia, ib, z, passes):
+def run(name, silu, gat_, ia, ib, z, passes, N=None):
+    # N < H: the kernel a column-split CTA pair would run (K = H inputs, N output columns, weights N*K*2 bytes in smem)
+    N = N or H
+    Wn = W[:N].contiguous()
+    zn = None if z is None else (z if N == H else z[:, :N].contiguous())
+    outn = out if N == H else torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
     def call():
-        return lib.aether_dbg_tc_gemm(P(A), M, H, H, P(W), H, H, H, H, 0, 0, silu, None, P(gat_), 2 * H, P(ia), P(ib), H, P(z),
-                                      P(out), None, P(scratch), stream())
+        return lib.aether_dbg_tc_gemm(P(A), M, H, H, P(Wn), H, N, N, H, 0, 0, silu, None, P(gat_), 2 * H, P(ia), P(ib), H, P(zn),
+                                      P(outn), None, P(scratch), stream())
     assert call() == 0
     best = 1e9
     for _ in range(4):
@@ -35,7 +40,7 @@ def run(name, silu, gat_, ia, ib, z, passes):
         best = min(best, a.elapsed_time(b) / 5)
     ms = best
     print("%-34s dbg=%s %.3f ms  %.2f us/tile  %.0f GB/s" % (name, os.environ.get("AETHER_TC_DBG", "0"), ms,
-          ms * 1e3 / (M / 128 / 148), M * H * 2 * passes / ms / 1e6), flush=True)
+          ms * 1e3 / (M / 128 / 148), M * 2 * (H + N * (passes - 1)) / ms / 1e6), flush=True)
 
 for dbg in os.environ.get("DBGS", "0").split(","):
     os.environ["AETHER_TC_DBG"] = dbg
@@ -50,6 +55,11 @@ for dbg in os.environ.get("DBGS", "0").split(","):
     run("fwdA: silu + gather send,recv", 1, gat, send, recv, None, 2)
     run("fwdA': silu + gather recv,recv", 1, gat, recv, recv, None, 2)
     run("fwdA'': silu + gather send only", 1, gat, send, None, None, 2)
+    if os.environ.get("HALF"):        # half-width kernels: twice their us/tile is what a column-split CTA pair would cost
+        run("plain N=H/2", 0, None, None, None, None, 2, H // 2)
+        run("B1 N=H/2", 0, None, None, None, Z, 3, H // 2)
+        run("B2 N=H/2", 0, gat, recv, None, Z, 3, H // 2)
+        run("fwdA N=H/2", 1, gat, send, recv, None, 2, H // 2)
 
 # node-level shape: fp32 output (+ residual through the debug hook is not exposed; plain + bias only)
 Mn = 102400
