@@ -30,3 +30,21 @@ def test_reference_arm_other_ranks_exit_quietly():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--workload",
                         "c1", "--steps", "1", "--warmup", "1"], capture_output=True, text=True, timeout=120, cwd=ROOT, env=env)
     assert r.returncode == 0 and not [l for l in r.stdout.splitlines() if l.startswith("{")]
+
+
+def test_roofline_formulas_match_survey():
+    """per-edge MACs Fe*H + 13 H^2 = 54 912 (3D, H=64) / 858 624 (3D, H=256); the node-factorised
+    form executes Fe*H + 7 H^2; HBM bytes per launch of the segmented mean and the feature kernel as stated in DESIGN.md 3."""
+    sys.path.insert(0, ROOT)
+    import bench
+    assert bench.algorithmic_flops_edge_mlp(3, 64, 1) == 2 * 54912
+    assert bench.algorithmic_flops_edge_mlp(3, 256, 1) == 2 * 858624
+    assert bench.executed_flops_edge_mlp(3, 256, 1) == 2 * (26 * 256 + 7 * 256 * 256)
+    prof = {"ms": [0, 0, 0, 0, 1.0, 0, 2.0], "spans": [0, 0, 0, 0, 1, 0, 2]}
+    E, Nn, H = 1000, 100, 256
+    r = bench.hbm_rooflines(prof, 2, H, E, Nn, True, {"hbm_gbs": 1.0})
+    seg = r["segmented_mean (receiver-sorted, no atomics)"]
+    assert seg["algorithmic_bytes_per_launch"] == E * H * 2 + Nn * H * 8 + (Nn + 1) * 4 and seg["launches"] == 2
+    feat = r["edge_features (gather + frame transform)"]
+    assert feat["algorithmic_bytes_per_launch"] == E * (12 + 8 + 128)
+    assert abs(feat["achieved"] - E * 148 / 1e-3 / 1e9) < 1e-9
