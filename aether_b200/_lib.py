@@ -16,7 +16,6 @@ SO_PATH = os.path.join(HERE, "lib", "libaether_b200.so")
 
 F_SAVE = 1
 F_BF16 = 2
-F_INPUT_GRADS = 4
 NUM_PARAMS = 47
 
 

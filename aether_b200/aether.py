@@ -17,7 +17,7 @@ from torch import nn
 
 from . import _lib
 from .graph import PreparedGraph
-from .ops import AetherStepFn
+from .ops import dropout_masks, step_apply
 
 
 class GNNLayer(nn.Module):
@@ -158,9 +158,6 @@ class Aether(nn.Module):
         D, H = self.num_dims, self.hidden_size
         Nn = x.shape[0]
         graph = self.prepare_graph(edges, Nn)
-        mask = None
-        if self.training and self.dropout_prob > 0.0:
-            keep = 1.0 - self.dropout_prob
-            mask = torch.bernoulli(torch.full((2, Nn, H), keep, device=x.device)) / keep   # locs.py:163,166
+        mask = dropout_masks(self.training, self.dropout_prob, Nn, H, x.device)
         charges = charges.reshape(-1)
-        return AetherStepFn.apply(x, vel, charges, edge_attr_orig, graph, D, H, self.flags(), mask, *self.param_list())
+        return step_apply(x, vel, charges, edge_attr_orig, graph, D, H, self.flags(), mask, self.param_list())

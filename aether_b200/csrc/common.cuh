@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stddef.h>
+#include <atomic>
 #include <stdint.h>
 
 #include "../../include/aether_b200.h"
@@ -14,7 +15,7 @@
 
 #define AE_LAUNCH_CHECK()                           \
   do {                                              \
-    ++::aether::g_launch_count;                     \
+    ::aether::g_launch_count.fetch_add(1, std::memory_order_relaxed); \
     cudaError_t _e = cudaPeekAtLastError();         \
     if (_e != cudaSuccess) return (int)_e;          \
   } while (0)
@@ -22,7 +23,7 @@
 namespace aether {
 
 // prof.cu: number of kernels launched by this library (every launch site runs AE_LAUNCH_CHECK)
-extern unsigned long long g_launch_count;
+extern std::atomic<unsigned long long> g_launch_count;
 // Optional CUDA-event timing of a group of launches; a no-op unless aether_profile_enable(1).
 enum ProfCat { PROF_EDGE_MLP_FWD = 0, PROF_EDGE_BWD_DATA = 1, PROF_EDGE_WGRAD = 2, PROF_SEGMENT = 3,
                PROF_EDGE_FEAT = 4, PROF_NODE = 5, PROF_SEGMEAN_FWD = 6, PROF_NUM = 7 };

@@ -113,14 +113,28 @@ __global__ void segsort_block_kernel(int64_t Nn, const int32_t* __restrict__ ptr
   }
 }
 
+// Sorted copies of the edge list.  Memory safety for malformed lists (the reference raises IndexError on them): edges
+// whose receiver is out of range were skipped by count/place, so the tail of `perm` holds the zeros it was cleared to;
+// out-of-range senders are clamped into [0, Nn) and flagged in the status word.  The step then computes garbage for
+// those edges but never reads out of bounds; PreparedGraph.validate() (or AETHER_B200_VALIDATE=1) turns the status
+// word into the IndexError.
 template <typename T>
-__global__ void gather_kernel(int64_t E, const int32_t* __restrict__ perm, const T* __restrict__ a,
-                              const T* __restrict__ b, int32_t* __restrict__ oa, int32_t* __restrict__ ob) {
+__global__ void gather_kernel(int64_t E, int64_t Nn, const int32_t* __restrict__ perm, const T* __restrict__ a,
+                              const T* __restrict__ b, int32_t* __restrict__ oa, int32_t* __restrict__ ob,
+                              int32_t* status) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= E) return;
-  const int32_t p = perm[e];
-  oa[e] = (int32_t)a[p];
-  ob[e] = (int32_t)b[p];
+  int32_t p = perm[e];
+  if (p < 0 || p >= E) p = 0;
+  long long va = (long long)a[p], vb = (long long)b[p];
+  if (va < 0 || va >= Nn || vb < 0 || vb >= Nn) {
+    atomicOr(status, 2);
+    va = va < 0 ? 0 : (va >= Nn ? Nn - 1 : va);
+    vb = vb < 0 ? 0 : (vb >= Nn ? Nn - 1 : vb);
+    if (Nn <= 0) { va = 0; vb = 0; }
+  }
+  oa[e] = (int32_t)va;
+  ob[e] = (int32_t)vb;
 }
 
 __global__ void fc_edges_kernel(int64_t n, int64_t B, int64_t* __restrict__ send, int64_t* __restrict__ recv) {
@@ -330,9 +344,14 @@ extern "C" int aether_graph_prepare(const int64_t* send, const int64_t* recv, in
   s.fill = (int32_t*)p; p += align_up((size_t)(Nn + 1) * 4, 256);
   s.tmp = (int32_t*)p;
   AE_CHECK(cudaMemsetAsync(status, 0, 4, st));
+  if (E > 0) {
+    // defined contents for the slots that edges with an out-of-range key never fill (see gather_kernel)
+    AE_CHECK(cudaMemsetAsync(g->perm, 0, (size_t)E * 4, st));
+    AE_CHECK(cudaMemsetAsync(g->sperm, 0, (size_t)E * 4, st));
+  }
   AE_CHECK(csr_by_key<int64_t>(recv, E, Nn, g->rowptr, g->perm, status, s, st));
   if (E > 0) {
-    gather_kernel<int64_t><<<nblk(E, 256), 256, 0, st>>>(E, g->perm, send, recv, g->send, g->recv);
+    gather_kernel<int64_t><<<nblk(E, 256), 256, 0, st>>>(E, Nn, g->perm, send, recv, g->send, g->recv, status);
     AE_LAUNCH_CHECK();
   }
   AE_CHECK(csr_by_key<int32_t>(g->send, E, Nn, g->colptr, g->sperm, status, s, st));

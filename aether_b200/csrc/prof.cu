@@ -1,5 +1,6 @@
 // Launch counter and optional per-category CUDA-event timing (bench.py's roofline leg).
 // Off by default; when enabled, categories are timed with event pairs on the launching stream.
+#include <atomic>
 #include <mutex>
 #include <vector>
 
@@ -7,7 +8,7 @@
 
 namespace aether {
 
-unsigned long long g_launch_count = 0;
+std::atomic<unsigned long long> g_launch_count{0};
 
 namespace {
 struct Span { cudaEvent_t a, b; int cat; };
@@ -40,7 +41,7 @@ ProfScope::~ProfScope() {
 
 using namespace aether;
 
-extern "C" uint64_t aether_launch_count(void) { return g_launch_count; }
+extern "C" uint64_t aether_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 
 extern "C" int aether_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(g_mu);

@@ -9,6 +9,7 @@ reused by every layer, forward and backward.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -51,6 +52,10 @@ class PreparedGraph:
                                                 _lib.ptr(self.status), _lib.ptr(scratch), nbytes, _stream()),
                        "aether_graph_prepare")
         self._key = None
+        # Out-of-range indices never cause out-of-bounds reads (graph.cu clamps them and sets the status word), but
+        # the reference raises on them; reading the status word synchronises, so the check is opt-in.
+        if os.environ.get("AETHER_B200_VALIDATE", "0") == "1":
+            self.validate()
 
     def c_struct(self) -> "_lib.AetherGraphC":
         return self._c

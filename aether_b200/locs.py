@@ -19,7 +19,7 @@ from torch import nn
 from . import _lib
 from .aether import GNN, Globalizer
 from .graph import PreparedGraph
-from .ops import AetherStepFn
+from .ops import dropout_masks, step_apply
 
 
 class Localizer(nn.Module):
@@ -86,10 +86,7 @@ class LoCS(nn.Module):
             raise RuntimeError("aether_b200.LoCS runs on CUDA devices only (no CPU fallback)")
         Nn = x.shape[0]
         graph = edges if isinstance(edges, PreparedGraph) else PreparedGraph(edges[0], edges[1], Nn)
-        mask = None
-        if self.training and self.dropout_prob > 0.0:
-            keep = 1.0 - self.dropout_prob
-            mask = torch.bernoulli(torch.full((2, Nn, self.hidden_size), keep, device=x.device)) / keep
+        mask = dropout_masks(self.training, self.dropout_prob, Nn, self.hidden_size, x.device)
         charges = torch.zeros(Nn, device=x.device)
-        return AetherStepFn.apply(x, vel, charges, edge_attr_orig, graph, self.num_dims, self.hidden_size, self.flags(),
-                                  mask, *self._aether_params())
+        return step_apply(x, vel, charges, edge_attr_orig, graph, self.num_dims, self.hidden_size, self.flags(), mask,
+                          self._aether_params())

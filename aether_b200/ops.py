@@ -12,6 +12,7 @@ import ctypes
 from typing import Optional, Sequence
 
 import torch
+from torch.autograd.function import once_differentiable
 
 from . import _lib
 from .graph import PreparedGraph
@@ -58,12 +59,19 @@ def step_forward_raw(params: Sequence[torch.Tensor], graph: PreparedGraph, x, ve
 
 
 class AetherStepFn(torch.autograd.Function):
+    """Use ``step_apply``: it decides whether the forward keeps what the backward needs."""
+
     @staticmethod
-    def forward(ctx, x, vel, charges, edge_attr_orig, graph, D, H, flags, dropout_mask, *params):
+    def forward(ctx, x, vel, charges, edge_attr_orig, graph, D, H, flags, dropout_mask, save, *params):
         x, vel, charges, edge_attr_orig = _f32c(x), _f32c(vel), _f32c(charges), _f32c(edge_attr_orig)
         params = [_f32c(p) for p in params]
-        need = any(ctx.needs_input_grad)
-        f = int(flags) | (_lib.F_SAVE if need else 0)
+        # grad mode is always off in here and needs_input_grad stays True under torch.no_grad() (the parameters still
+        # require grad), so the caller passes `save`: without it the forward ping-pongs 3 edge buffers instead of 8
+        need = bool(save) and any(ctx.needs_input_grad)
+        if need and (ctx.needs_input_grad[2] or ctx.needs_input_grad[3]):
+            raise RuntimeError("aether_b200: gradients w.r.t. charges / edge_attr_orig are not implemented; detach "
+                               "them (the reference's caller passes constants, experiments/lorentz/main.py:243-247)")
+        f = (int(flags) & ~_lib.F_SAVE) | (_lib.F_SAVE if need else 0)
         out, ws = step_forward_raw(params, graph, x, vel, charges, edge_attr_orig, D, H, f, dropout_mask)
         if need:
             ctx.save_for_backward(x, vel, charges, edge_attr_orig, *params)
@@ -71,8 +79,12 @@ class AetherStepFn(torch.autograd.Function):
         return out
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, grad_out):
         lib = _lib.load()
+        if getattr(ctx, "ws", None) is None:
+            raise RuntimeError("aether_b200: the step's saved workspace was already consumed; a second backward "
+                               "through the same forward (retain_graph=True) is not supported -- run forward again")
         x, vel, charges, ea, *params = ctx.saved_tensors
         D, H = ctx.dims
         graph = ctx.graph
@@ -98,7 +110,23 @@ class AetherStepFn(torch.autograd.Function):
                                                 _lib.ptr(ctx.ws), ctx.ws.numel(), _lib.ptr(scratch), nbytes,
                                                 ctx.flags, _stream()), "aether_step_backward")
         ctx.ws = None
-        return (gx, gv, None, None, None, None, None, None, None, *grads)
+        return (gx, gv, None, None, None, None, None, None, None, None, *grads)
+
+
+def step_apply(x, vel, charges, edge_attr_orig, graph, D, H, flags, dropout_mask, params):
+    """The differentiable step.  Keeps the per-layer pre-activations only when a backward can follow."""
+    save = torch.is_grad_enabled() and (x.requires_grad or vel.requires_grad or any(p.requires_grad for p in params))
+    return AetherStepFn.apply(x, vel, charges, edge_attr_orig, graph, D, H, flags, dropout_mask, save, *params)
+
+
+def dropout_masks(training: bool, p: float, n_nodes: int, hidden: int, device):
+    """The two inverted-dropout masks of out_mlp (locs.py:163,166) as one [2, Nn, H] tensor, or None."""
+    if not training or p <= 0.0:
+        return None
+    keep = 1.0 - p
+    if keep <= 0.0:
+        return torch.zeros(2, n_nodes, hidden, device=device)        # nn.Dropout(p=1) zeroes everything
+    return torch.bernoulli(torch.full((2, n_nodes, hidden), keep, device=device)) / keep
 
 
 def debug_stage(ws: torch.Tensor, graph: PreparedGraph, D: int, H: int, flags: int, stage: str) -> torch.Tensor:

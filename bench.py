@@ -54,16 +54,11 @@ def scene_sizes(cfg, rank=0):
 def synth_inputs(cfg, sizes, seed):
     """(x, v, q): the simulators' distributions for the particle workloads; inD-style scenes use positions in the
     unit square and speeds U(0,1)*0.05 (speed-normalised tracks)."""
-    from oracle import aether_oracle as O
+    from aether_b200 import synth
     D = cfg["D"]
     if cfg["N"]:
-        return O.synth_state(len(sizes), cfg["N"], D, seed=seed)
-    g = torch.Generator().manual_seed(seed)
-    n = sum(sizes)
-    x = torch.rand(n, D, generator=g)
-    v = (torch.rand(n, D, generator=g) - 0.5) * 0.1
-    q = torch.randint(0, 2, (n, 1), generator=g).float() * 2 - 1
-    return x, v, q
+        return synth.synth_state(len(sizes), cfg["N"], D, seed=seed)
+    return synth.ind_style_scenes(sizes, D, seed=seed)
 
 
 def peaks():
@@ -196,13 +191,8 @@ def cpu_sample_graphs(cfg, H):
 
 def c5_scene(cfg, n, seed=1):
     """Uniform unit-density particles in a cube, speeds 0.05, charges +-1 (config 5)."""
-    g = torch.Generator().manual_seed(seed)
-    L = float(n) ** (1.0 / 3.0)
-    x = torch.rand(n, 3, generator=g) * L
-    v = torch.randn(n, 3, generator=g)
-    v = 0.05 * v / v.norm(dim=-1, keepdim=True)
-    q = torch.randint(0, 2, (n, 1), generator=g).float() * 2 - 1
-    return x, v, q
+    from aether_b200 import synth
+    return synth.unit_density_scene(n, seed)
 
 
 def c5_cpu_sample(cfg, H, n_sub=6250):
@@ -421,7 +411,6 @@ def main():
 
     import aether_b200 as ab
     from aether_b200 import _lib
-    from oracle import aether_oracle as O   # synthetic inputs + the cpu_baseline leg only
     lib = _lib.load(build_if_missing=False)
 
     rank = int(os.environ.get("RANK", "0"))

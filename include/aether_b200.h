@@ -30,8 +30,10 @@
  *   - the caller owns all memory, including the workspace; sizes come from
  *     aether_workspace_bytes / aether_graph_scratch_bytes;
  *   - all work is enqueued on the stream passed in (a cudaStream_t cast to
- *     void*); no call synchronises, reads device data on the host, or keeps
- *     global state, so every call can be captured in a CUDA graph;
+ *     void*); no call synchronises or reads device data on the host, so every
+ *     call can be captured in a CUDA graph.  The only process-wide state is
+ *     diagnostic: an atomic launch counter (aether_launch_count) and the
+ *     mutex-guarded event list of aether_profile_enable / _collect;
  *   - return value: 0 on success, otherwise a cudaError_t value or one of the
  *     negative AETHER_E_* codes; nothing throws or aborts.
  *   - floating point is fp32 at this boundary; indices are int64 on input (as
@@ -57,7 +59,7 @@ extern "C" {
 /* flags for aether_step_forward / aether_workspace_bytes */
 #define AETHER_F_SAVE_FOR_BACKWARD 1u   /* keep activations for aether_step_backward  */
 #define AETHER_F_BF16_EDGE_MLP     2u   /* edge-MLP GEMMs on tcgen05 in bf16 (fp32 accumulate) */
-#define AETHER_F_INPUT_GRADS       4u   /* backward also returns d/dx and d/dvel      */
+/* (d/dx and d/dvel are returned by aether_step_backward whenever gx_out / gvel_out are non-null) */
 
 /* Number of parameter tensors of Aether, in state_dict order
  * (nn/state2state/aether.py:143-159, locs.py:160-181):

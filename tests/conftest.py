@@ -40,3 +40,12 @@ def rel_err(a, b):
     if b.numel() == 0:
         return 0.0
     return float((a - b).abs().max() / b.abs().max().clamp(min=1e-30))
+
+
+def rel_l2(a, b):
+    """||a-b||_2 / ||b||_2 per tensor: unlike the max-norm bar it cannot hide a tensor whose small entries are all wrong."""
+    a = torch.as_tensor(a, dtype=torch.float64)
+    b = torch.as_tensor(b, dtype=torch.float64)
+    if b.numel() == 0:
+        return 0.0
+    return float((a - b).norm() / b.norm().clamp(min=1e-30))

@@ -4,7 +4,7 @@
 #include "../aether_b200/csrc/geom.cu"
 #include "../aether_b200/csrc/geom_bwd.cu"
 
-namespace aether { unsigned long long g_launch_count = 0; }
+namespace aether { std::atomic<unsigned long long> g_launch_count{0}; }
 using namespace aether;
 
 template <int D>

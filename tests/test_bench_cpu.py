@@ -48,3 +48,16 @@ def test_roofline_formulas_match_survey():
     feat = r["edge_features (gather + frame transform)"]
     assert feat["algorithmic_bytes_per_launch"] == E * (12 + 8 + 128)
     assert abs(feat["achieved"] - E * 148 / 1e-3 / 1e9) < 1e-9
+
+
+def test_product_arm_generator_draws_the_oracles_numbers():
+    """bench.py's product arm takes its inputs from aether_b200.synth (nothing from oracle/); both generators must
+    produce the same particles so that the CPU baseline and the GPU arm time the same workload."""
+    import torch
+    sys.path.insert(0, ROOT)
+    from aether_b200 import synth
+    from oracle import aether_oracle as O
+    for (B, N, D, seed) in [(3, 5, 2, 1), (2, 100, 2, 4), (4, [3, 7, 5, 2], 3, 9)]:
+        a = synth.synth_state(B, N, D, seed=seed)
+        b = O.synth_state(B, N, D, seed=seed)
+        assert all(torch.equal(u, w) for u, w in zip(a, b))

@@ -1,12 +1,12 @@
-"""GPU property tests written after round 1's GPU budget was spent; their first run is the round-end suite, hence the
-non-strict xfail (a pass shows as XPASS).  Size-independent property at a size the oracle does not finish in seconds:
+"""GPU property tests (passed on the B200 in the round-1 driver run).  Size-independent property at a size the oracle
+does not finish in seconds:
 LoCS on the GPU is equivariant to translations and to rotations (2D: any; 3D: about z) of the scene."""
 import math
 
 import pytest
 import torch
 
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(reason="first GPU run of this file is the round-end suite", strict=False)]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("D,precision,tol", [(2, "fp32", 2e-4), (3, "fp32", 2e-4), (2, "bf16", 5e-2)])

@@ -194,3 +194,64 @@ def test_graphed_train_step_matches_eager(ab):
     assert losses1[-1] < losses1[0]
     for (k, a), (_, b) in zip(m1.named_parameters(), m2.named_parameters()):
         assert rel_err(b.detach().cpu(), a.detach().cpu()) <= 1e-5, k
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_no_grad_forward_equals_grad_forward(precision):
+    """Under torch.no_grad() the module takes the ping-pong (no save-for-backward) workspace; its output must be
+    bit-identical to the grad-enabled forward, which keeps all eight per-layer pre-activations."""
+    import aether_b200 as ab
+    D, N, B, H = 2, 20, 6, 64
+    torch.manual_seed(5)
+    m = ab.Aether(2 * D, H, 0.0, D, device="cuda", precision=precision)
+    x, v, q = [t.cuda() for t in O.synth_state(B, N, D, seed=12)]
+    send, recv = ab.fc_edges(N, B, "cuda")
+    h, ea = ab.caller_prep(x, v, q.reshape(-1), send, recv)
+    a = m(h, x, [send, recv], v, ea, q)
+    assert a.requires_grad
+    with torch.no_grad():
+        b = m(h, x, [send, recv], v, ea, q)
+    assert not b.requires_grad
+    assert torch.equal(a.detach(), b)
+
+
+def test_backward_edge_cases_raise_clearly():
+    import aether_b200 as ab
+    D, N, B, H = 2, 5, 2, 64
+    m = ab.Aether(2 * D, H, 0.0, D, device="cuda")
+    x, v, q = [t.cuda() for t in O.synth_state(B, N, D, seed=2)]
+    send, recv = ab.fc_edges(N, B, "cuda")
+    h, ea = ab.caller_prep(x, v, q.reshape(-1), send, recv)
+    out = m(h, x, [send, recv], v, ea, q)
+    out.sum().backward(retain_graph=True)
+    with pytest.raises(RuntimeError, match="already consumed"):
+        out.sum().backward()
+    with pytest.raises(RuntimeError, match="edge_attr_orig"):
+        m(h, x, [send, recv], v, ea.clone().requires_grad_(True), q)
+    # dropout_prob == 1: nn.Dropout zeroes everything (no 0/0)
+    m1 = ab.Aether(2 * D, H, 1.0, D, device="cuda")
+    m1.train()
+    o1 = m1(h, x, [send, recv], v, ea, q)
+    assert torch.isfinite(o1).all()
+
+
+def test_out_of_range_edges_are_memory_safe_and_flagged():
+    """The reference raises IndexError on an out-of-range edge; here the list is clamped (never an out-of-bounds read),
+    the status word is set and validate() / AETHER_B200_VALIDATE=1 raises."""
+    import aether_b200 as ab
+    D, N, B, H = 2, 5, 2, 64
+    m = ab.Aether(2 * D, H, 0.0, D, device="cuda")
+    x, v, q = [t.cuda() for t in O.synth_state(B, N, D, seed=2)]
+    send, recv = ab.fc_edges(N, B, "cuda")
+    bad_s, bad_r = send.clone(), recv.clone()
+    bad_r[3] = B * N + 7
+    bad_s[11] = -2
+    g = ab.PreparedGraph(bad_s, bad_r, B * N)
+    with pytest.raises(IndexError):
+        g.validate()
+    h, ea = ab.caller_prep(x, v, q.reshape(-1), send, recv)
+    with torch.no_grad():
+        out = m(h, x, g, v, ea, q)
+    torch.cuda.synchronize()            # a fault would surface here
+    assert out.shape == x.shape
+    assert int(g.send.min()) >= 0 and int(g.send.max()) < B * N and int(g.recv.max()) < B * N

@@ -6,8 +6,7 @@ import torch
 from conftest import rel_err
 from oracle import aether_oracle as O
 
-# Written after round 1's GPU budget was spent: its first run on a GPU is the round-end suite, hence non-strict xfail.
-pytestmark = [pytest.mark.gpu, pytest.mark.xfail(reason="first GPU run of this file is the round-end suite", strict=False)]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-5), ("bf16", 2e-2)])
