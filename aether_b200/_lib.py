@@ -66,6 +66,9 @@ SIGNATURES = {
     "aether_dbg_tc_wgrad_partial_floats": (c_size_t, [c_int32, c_int32]),
     "aether_dbg_tc_wgrad": (c_int, [c_void_p, c_int32, c_void_p, c_int32, c_int32, c_int64, c_void_p, c_int32, c_int32,
                                     c_void_p, c_void_p, c_size_t, c_void_p]),
+    "aether_dbg_tc_chain": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_int64, c_int32, c_int32, c_void_p,
+                                    c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32,
+                                    c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_debug_stage": (c_int64, [POINTER(AetherDims), c_void_p, c_uint32, c_char_p, c_void_p, c_int64, c_void_p]),
 }
 

@@ -35,6 +35,7 @@ SOURCES = [
     ("step.cu", []),
     ("tc_gemm.cu", []),
     ("tc_wgrad.cu", []),
+    ("tc_chain.cu", []),
     ("tc_abi.cu", []),
     ("edge_bf16.cu", []),
     ("prof.cu", []),

@@ -31,3 +31,23 @@ extern "C" int aether_dbg_tc_wgrad(const void* G_bf16, int32_t MG, const void* A
   return tc_wgrad(G_bf16, MG, MG, ACT_bf16, NA, NA, silu_on_load ? TC_TF_SILU : TC_TF_NONE, E, dW,
                   n_valid, n_valid, fold32, db, partial, partial_floats, (cudaStream_t)stream);
 }
+
+// Chained edge MLP (tc_chain.cu): out2 = silu(out1) W2^T + b2, out1 = tf1(A) W1^T + b1 (+ gathered rows).
+// wpack_scratch: (K1 + H) * H * 2 bytes.  out1 may be null (inference: the intermediate is not stored).
+extern "C" int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, const float* W1, int64_t ldw1,
+                                   int32_t k1_valid, int32_t kmod1, const float* W2, int32_t H, int32_t silu_on_load,
+                                   const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
+                                   const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
+                                   void* out2_bf16, void* wpack_scratch, void* stream) {
+  if (!A_bf16 || !W1 || !W2 || !wpack_scratch || !out2_bf16) return AETHER_E_BADARG;
+  if (!tc_chain_supported(K1, H)) return AETHER_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  char* wp2 = (char*)wpack_scratch + tc_weight_pack_bytes(K1, H);
+  AE_CHECK(tc_pack_weight(W1, ldw1, H, K1, H, k1_valid, 0, kmod1, wpack_scratch, st));
+  AE_CHECK(tc_pack_weight(W2, H, H, H, H, H, 0, 0, wp2, st));
+  TcChainArgs g;
+  g.M = M; g.wpack1 = wpack_scratch; g.wpack2 = wp2; g.bias1 = bias1; g.bias2 = bias2;
+  g.gat16 = (const __nv_bfloat16*)gat_bf16; g.ldg = ldg; g.idx_a = idx_a; g.idx_b = idx_b; g.goff_b = goff_b;
+  g.out1 = (__nv_bfloat16*)out1_bf16; g.ldo1 = H; g.out2 = (__nv_bfloat16*)out2_bf16; g.ldo2 = H;
+  return tc_chain(g, A_bf16, lda, K1, H, silu_on_load ? TC_TF_SILU : TC_TF_NONE, st);
+}

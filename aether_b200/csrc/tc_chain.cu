@@ -1,0 +1,430 @@
+// Chained edge MLP of one message-passing layer on a CTA pair (nn/state2state/locs/locs.py:206-212,
+// 232-235):
+//
+//     pre1 = tf(A) We^T + b1 (+ P_s[send] + P_r[recv])          A = stored pre2 of the previous layer (or the features)
+//     pre2 = silu(pre1) W2^T + b2
+//
+// ONE persistent kernel, the intermediate never leaves the SM: accumulator 1 is read from tensor memory, finished in
+// registers, passed through SiLU, packed to bf16 and written BACK into tensor memory over the columns it came from,
+// where it is the A operand of the second tcgen05.mma (A from TMEM).  pre1 goes to HBM only when the backward needs
+// it (SAVE); pre2 always does (it is the layer's edge state).  HBM traffic per edge: 2*K1 bytes in, 2*H (+ 2*H) out,
+// against 2*K1 + 6*H for the two separate GEMMs.
+//
+// Both weight images do not fit one SM at H = 256 (2 x 128 KB), so the kernel runs on CTA PAIRS (cluster of two,
+// tcgen05 cta_group::2): an MMA covers 256 edges (128 per CTA), each CTA holds HALF the rows of W_e and of W_2
+// (64 KB + 64 KB at H = 256) and the tensor cores of both SMs read both halves.  Per CTA:
+//
+//   warp 8      TMA producer : its halves of the two weight images once, then 128x64 bf16 boxes of A (ring)
+//   warps 10-13 transform    : in-place SiLU on the landed box, then "ready" to the LEADER's barrier (remote arrive)
+//   warp 9      MMA issuer   : CTA 0 only; MMA 1 (A, B from shared memory) into accumulator 1, MMA 2 (A from
+//                              tensor memory, B from shared memory) into accumulator 2; completion is multicast
+//                              to the barriers of both CTAs (tcgen05.commit ... multicast::cluster)
+//   warps 0-7   epilogue     : two warps per TMEM lane quarter on alternate 32-column chunks
+//        epilogue 1: tcgen05.ld, + b1 + gathered node terms (requested one chunk ahead), bf16 pre1 -> TMA store
+//                    (SAVE), SiLU, bf16 pair per 32-bit column -> tcgen05.st over columns [32j, 32j+16) of the chunk,
+//                    "piece ready" to the leader after each chunk (MMA 2 starts on the first 64 inputs while the
+//                    rest of the row is still in the epilogue)
+//        epilogue 2: tcgen05.ld, + b2, bf16 pre2 -> TMA store
+//
+// Tensor memory: accumulator 1 at columns [0, H), accumulator 2 at [H, 2H) -- all 512 columns at H = 256, so there
+// is no second accumulator pair; MMA 1 of the next tile runs while epilogue 2 of this one drains.
+// Numerics are those of the two separate kernels (same operands, same rounding points, same K order): the
+// outputs are bit-identical to tc_gemm + tc_gemm, which tests/test_chain_gpu.py checks.
+#include <string.h>
+
+#include "tc_gemm.cuh"
+
+namespace aether {
+
+namespace {
+
+using namespace tc;
+
+constexpr int kThreads = 448;
+constexpr int kEpiWarps = 8;
+constexpr int kWarpTma = 8, kWarpMma = 9, kWarpTf0 = 10;
+constexpr int kTileM = 128;                        // rows per CTA; the pair owns 256
+constexpr int kSlotBytes = kTileM * 128;           // 128 rows x 64 bf16
+constexpr int kSmemMax = 232448;                   // 227 KB
+constexpr int kStageBytes = kEpiWarps * 2 * 2048;  // per epilogue warp: two 32x32 bf16 boxes
+
+__host__ __device__ constexpr int misc_bytes(int H) { return 512 + 2 * H * 4; }      // barriers | b1 | b2
+__host__ __device__ constexpr int w1_bytes(int K1, int H) { return K1 * (H / 2) * 2; }  // this CTA's half of the rows
+__host__ __device__ constexpr int w2_bytes(int H) { return H * (H / 2) * 2; }
+__host__ __device__ constexpr int num_slots(int K1, int H) {
+  int s = (kSmemMax - 1024 - misc_bytes(H) - w1_bytes(K1, H) - w2_bytes(H) - kStageBytes) / kSlotBytes;
+  return s > 8 ? 8 : s;
+}
+__host__ __device__ constexpr int smem_bytes(int K1, int H) {
+  return 1024 + w1_bytes(K1, H) + w2_bytes(H) + num_slots(K1, H) * kSlotBytes + kStageBytes + misc_bytes(H);
+}
+
+template <int K1, int H, int TF1, bool SAVE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmO1,
+                const __grid_constant__ CUtensorMap tmO2, TcChainArgs g) {
+  static_assert(K1 % 64 == 0 && (H == 64 || H == 128 || H == 256), "unsupported shape");
+  constexpr int KC1 = K1 / 64;                     // 64-wide K chunks of the first GEMM = ring slots per tile
+  constexpr int S = num_slots(K1, H);
+  constexpr int NP = H / 64;                       // 64-input pieces of the second GEMM
+  constexpr int NCH = H / 32;                      // 32-column epilogue chunks
+  constexpr uint32_t IDESC = make_idesc(256, H, MAJOR_K, MAJOR_K);
+  constexpr uint32_t TMEM_COLS = 2 * H;            // 128 / 256 / 512
+  constexpr int WROW = (H / 2) * 128;              // bytes of one 64-wide K chunk of this CTA's weight half
+  static_assert(S >= 2, "pipeline too shallow");
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sW1 = base;
+  const uint32_t sW2 = sW1 + w1_bytes(K1, H);
+  const uint32_t sA = sW2 + w2_bytes(H);
+  const uint32_t sStage = sA + S * kSlotBytes;
+  const uint32_t sMisc = sStage + kStageBytes;
+  const uint32_t bar_raw = sMisc;                  // [S] TMA landed                       (this CTA)
+  const uint32_t bar_rdy = sMisc + 64;             // [S] transform done, 8 warps of the pair    (leader's is used)
+  const uint32_t bar_free = sMisc + 128;           // [S] MMA 1 consumed the slot          (multicast to both)
+  const uint32_t bar_a2 = sMisc + 192;             // [NP] piece of A2 in tensor memory, 16 warps of the pair (leader's)
+  const uint32_t bar_acc1f = sMisc + 224;          // accumulator 1 complete               (multicast to both)
+  const uint32_t bar_acc2f = sMisc + 232;          // accumulator 2 complete               (multicast to both)
+  const uint32_t bar_acc2e = sMisc + 240;          // accumulator 2 drained, 16 warps of the pair        (leader's)
+  const uint32_t bar_w = sMisc + 248;              // weights landed                       (this CTA)
+  const uint32_t tmem_slot = sMisc + 256;
+  uint8_t* misc_ptr = smem_raw + (sMisc - smem_u32(smem_raw));
+  float* sb1 = reinterpret_cast<float*>(misc_ptr + 512);
+  float* sb2 = sb1 + H;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int64_t n_pt = (g.M + 2 * kTileM - 1) / (2 * kTileM);     // pair tiles of 256 rows
+  const int64_t cid = blockIdx.x >> 1, ncl = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(bar_raw + 8 * s, 1);
+      mbar_init(bar_rdy + 8 * s, 8);
+      mbar_init(bar_free + 8 * s, 1);
+    }
+    for (int h = 0; h < NP; ++h) mbar_init(bar_a2 + 8 * h, 2 * kEpiWarps);
+    mbar_init(bar_acc1f, 1);
+    mbar_init(bar_acc2f, 1);
+    mbar_init(bar_acc2e, 2 * kEpiWarps);
+    mbar_init(bar_w, 1);
+    fence_mbar_init();
+  }
+  if (threadIdx.x < H) {
+    sb1[threadIdx.x] = g.bias1 ? g.bias1[threadIdx.x] : 0.0f;
+    sb2[threadIdx.x] = g.bias2 ? g.bias2[threadIdx.x] : 0.0f;
+  }
+  __syncthreads();
+  if (warp == kWarpMma) tmem_alloc_2cta(tmem_slot, TMEM_COLS);
+  if (warp == kWarpTma && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmO2);
+    if (SAVE) tma_prefetch_desc(&tmO1);
+    // this CTA's half of the rows of every 64-wide K chunk of both images
+    mbar_arrive_expect_tx(bar_w, w1_bytes(K1, H) + w2_bytes(H));
+    for (int c = 0; c < KC1; ++c)
+      bulk_load(sW1 + c * WROW, (const uint8_t*)g.wpack1 + (size_t)c * (H * 128) + (size_t)rank * WROW, WROW, bar_w);
+    for (int c = 0; c < NP; ++c)
+      bulk_load(sW2 + c * WROW, (const uint8_t*)g.wpack2 + (size_t)c * (H * 128) + (size_t)rank * WROW, WROW, bar_w);
+    mbar_wait(bar_w, 0);
+  }
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();            // barriers initialised, weights resident and TMEM allocated in BOTH CTAs
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == kWarpTma) {
+    // ===== TMA producer (both CTAs, own rows) =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t pt = cid; pt < n_pt; pt += ncl) {
+        const int row0 = (int)(pt * 2 * kTileM + rank * kTileM);
+        for (int c = 0; c < KC1; ++c, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait(bar_free + 8 * s, ph ^ 1);
+          mbar_arrive_expect_tx(bar_raw + 8 * s, kSlotBytes);
+          tma_load_2d(sA + s * kSlotBytes, &tmA, c * 64, row0, bar_raw + 8 * s);
+        }
+      }
+    }
+  } else if (warp == kWarpMma) {
+    // ===== MMA issuer (leader CTA) =====
+    if (rank == 0 && lane == 0) {
+      const uint32_t acc1 = tmem_base, acc2 = tmem_base + H;
+      uint32_t it = 0, lt = 0;
+      for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
+        // accumulator 1 is free: MMA 2 of the previous tile (which read A2 out of its columns) was issued before
+        // this point and the tensor pipe executes in issue order
+        for (int c = 0; c < KC1; ++c, ++it) {
+          const uint32_t s = it % S, ph = (it / S) & 1;
+          mbar_wait_cluster(bar_rdy + 8 * s, ph);
+          tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t ad = make_sdesc(sA + s * kSlotBytes + k * 32, 16, 1024);
+            const uint64_t bd = make_sdesc(sW1 + c * WROW + k * 32, 16, 1024);
+            umma_bf16_2cta(acc1, ad, bd, IDESC, (c | k) != 0);
+          }
+          umma_commit_2cta(bar_free + 8 * s);
+        }
+        umma_commit_2cta(bar_acc1f);
+        mbar_wait_cluster(bar_acc2e, (lt & 1) ^ 1);
+        tc_fence_after();
+        for (int h = 0; h < NP; ++h) {
+          mbar_wait_cluster(bar_a2 + 8 * h, lt & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            // K step ks = 4h + k: 16 inputs = 8 packed columns at the start of 32-column chunk ks/2, second half if odd
+            const uint32_t ks = 4 * h + k;
+            const uint32_t a_t = acc1 + 32 * (ks >> 1) + 8 * (ks & 1);
+            const uint64_t bd = make_sdesc(sW2 + h * WROW + k * 32, 16, 1024);
+            umma_bf16_2cta_ts(acc2, a_t, bd, IDESC, (h | k) != 0);
+          }
+        }
+        umma_commit_2cta(bar_acc2f);
+      }
+    }
+  } else if (warp >= kWarpTf0) {
+    // ===== transform: in-place SiLU on the landed A box, then "ready" to the leader =====
+    const int tt = threadIdx.x - kWarpTf0 * 32;    // 0..127
+    const uint32_t rdy0 = mapa_rank(bar_rdy, 0);
+    uint32_t it = 0;
+    for (int64_t pt = cid; pt < n_pt; pt += ncl) {
+      for (int c = 0; c < KC1; ++c, ++it) {
+        const uint32_t s = it % S, ph = (it / S) & 1;
+        mbar_wait(bar_raw + 8 * s, ph);
+        if (TF1 == TC_TF_SILU) {
+          const uint32_t a0 = sA + s * kSlotBytes + tt * 16;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            uint32_t u[4];
+            const uint32_t addr = a0 + i * 2048;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]) : "r"(addr));
+#pragma unroll
+            for (int q = 0; q < 4; ++q) u[q] = pack_bf16(silu_fast(bf16_lo(u[q])), silu_fast(bf16_hi(u[q])));
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(u[0]), "r"(u[1]), "r"(u[2]), "r"(u[3]) : "memory");
+          }
+          fence_proxy_async_smem();
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(rdy0 + 8 * s);
+      }
+    }
+  } else {
+    // ===== epilogue warps =====
+    const int qr = warp & 3, hf = warp >> 2;
+    const uint32_t sbuf = sStage + warp * 4096;
+    const uint32_t a2bar0 = mapa_rank(bar_a2, 0), acc2e0 = mapa_rank(bar_acc2e, 0);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(qr * 32) << 16);
+    const bool gather = g.gat16 != nullptr;
+    uint32_t lt = 0, nbox = 0;
+    // gathered node terms of a chunk (64 contiguous bytes per row and plane), requested ONE CHUNK AHEAD
+    uint4 xn[4], yn[4];
+    int ia_n = 0, ib_n = 0;
+    auto request = [&](int ia_, int ib_, int c) {
+      const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
+      const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { xn[q] = __ldg(pa + q); yn[q] = __ldg(pb + q); }
+    };
+    if (gather && cid < n_pt) {
+      const int64_t r0 = cid * 2 * kTileM + rank * kTileM + qr * 32 + lane;
+      if (r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b[r0]; }
+      request(ia_n, ib_n, hf * 32);
+    }
+    for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
+      const int64_t row0 = pt * 2 * kTileM + rank * kTileM + qr * 32;
+      const int ia = ia_n, ib = ib_n;
+      const int64_t ptn = pt + ncl;
+      const int64_t row_n = row0 + lane + ncl * 2 * kTileM;
+      ia_n = 0; ib_n = 0;
+      if (gather && ptn < n_pt && row_n < g.M) { ia_n = g.idx_a[row_n]; ib_n = g.idx_b[row_n]; }
+
+      // ---- epilogue 1: accumulator 1 -> pre1 (HBM, SAVE) and A2 = bf16(silu(pre1)) (tensor memory) ----
+      mbar_wait(bar_acc1f, lt & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int j = hf; j < NCH; j += 2) {
+        const int c0 = j * 32;
+        uint4 a4[4], b4[4];
+        if (gather) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) { a4[q] = xn[q]; b4[q] = yn[q]; }
+          if (j + 2 < NCH) request(ia, ib, c0 + 64);     // the next tile's first chunk is requested in epilogue 2
+        }
+        uint32_t r[32];
+        tmem_ld32(lane_base + c0, r);
+        const uint32_t buf = sbuf + (nbox & 1) * 2048;
+        if (SAVE) {
+          // the TMA store that read this staging box two boxes ago must have finished reading it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+        }
+        tmem_ld_wait();
+        float v[32];
+        {
+          const float* bs = sb1 + c0;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
+        }
+        if (gather) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t bb[4] = {b4[q].x, b4[q].y, b4[q].z, b4[q].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(aa[e]); v[8 * q + 2 * e + 1] += bf16_hi(aa[e]); }
+          }
+        }
+        uint32_t o[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) o[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
+        if (SAVE) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[4 * q]), "r"(o[4 * q + 1]),
+                         "r"(o[4 * q + 2]), "r"(o[4 * q + 3]) : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && row0 < g.M) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                         :: "l"((uint64_t)&tmO1), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
+          }
+          if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          ++nbox;
+        }
+        // the second GEMM consumes what the backward will recompute from the STORED pre1: silu of the bf16 value
+#pragma unroll
+        for (int i = 0; i < 16; ++i) o[i] = pack_bf16(silu_fast(bf16_lo(o[i])), silu_fast(bf16_hi(o[i])));
+        tmem_st16(lane_base + c0, o);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(a2bar0 + 8 * (j >> 1));
+      }
+
+      // ---- epilogue 2: accumulator 2 -> pre2 (HBM) ----
+      mbar_wait(bar_acc2f, lt & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int j = hf; j < NCH; j += 2, ++nbox) {
+        const int c0 = j * 32;
+        const uint32_t buf = sbuf + (nbox & 1) * 2048;
+        if (gather && j + 2 >= NCH && ptn < n_pt) request(ia_n, ib_n, hf * 32);
+        uint32_t r[32];
+        tmem_ld32(lane_base + H + c0, r);
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+        tmem_ld_wait();
+        if (j + 2 >= NCH) {
+          // accumulator 2 fully read by this warp: hand it back to the MMA warp before the stores
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(acc2e0);
+        }
+        const float* bs = sb2 + c0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            o[e] = pack_bf16(__uint_as_float(r[8 * q + 2 * e]) + bs[8 * q + 2 * e],
+                             __uint_as_float(r[8 * q + 2 * e + 1]) + bs[8 * q + 2 * e + 1]);
+          const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0 && row0 < g.M) {
+          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                       :: "l"((uint64_t)&tmO2), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  __syncwarp();
+  tc_fence_before();
+  cluster_sync_all();            // nobody leaves (or frees tensor memory) while the peer can still signal it
+  if (warp == kWarpMma) {
+    tc_fence_after();
+    tmem_dealloc_2cta(tmem_base, TMEM_COLS);
+  }
+}
+
+template <int K1, int H, int TF1, bool SAVE>
+int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, cudaStream_t st) {
+  constexpr int smem = smem_bytes(K1, H);
+  static_assert(smem <= kSmemMax, "shared memory budget");
+  auto kern = tc_chain_kernel<K1, H, TF1, SAVE>;
+  static int max_clusters = 0;                     // co-resident CTA pairs (one per TPC): 74 on a full B200
+  if (max_clusters == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(2 * (unsigned)tc_sm_count());
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = 2; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+    cfg.attrs = &at; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) { (void)cudaGetLastError(); n = tc_sm_count() / 2; }
+    max_clusters = n;
+  }
+  const int64_t n_pt = (g.M + 2 * kTileM - 1) / (2 * kTileM);
+  const unsigned ncl = (unsigned)(n_pt < max_clusters ? n_pt : max_clusters);
+  kern<<<2 * ncl, kThreads, smem, st>>>(ta, t1, t2, g);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int K1, int H>
+int launch_kh(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, int tf1, bool save,
+              cudaStream_t st) {
+  if (tf1 == TC_TF_SILU) {
+    if (save) return launch_chain<K1, H, TC_TF_SILU, true>(g, ta, t1, t2, st);
+    return launch_chain<K1, H, TC_TF_SILU, false>(g, ta, t1, t2, st);
+  }
+  if (save) return launch_chain<K1, H, TC_TF_NONE, true>(g, ta, t1, t2, st);
+  return launch_chain<K1, H, TC_TF_NONE, false>(g, ta, t1, t2, st);
+}
+
+}  // namespace
+
+bool tc_chain_supported(int K1, int H) {
+  return (H == 64 || H == 128 || H == 256) && (K1 == 64 || K1 == H);
+}
+
+int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, int tf1, cudaStream_t st) {
+  if (g.M <= 0) return 0;
+  if (!tc_chain_supported(K1, H)) return AETHER_E_UNSUPPORTED;
+  if (!g.wpack1 || !g.wpack2 || !g.out2) return AETHER_E_BADARG;
+  if (g.gat16 && (!g.idx_a || !g.idx_b)) return AETHER_E_BADARG;
+  const bool save = g.out1 != nullptr;
+  CUtensorMap ta, t1, t2;
+  memset(&t1, 0, sizeof(t1));
+  AE_CHECK(tc_make_tmap_bf16(&ta, A, g.M, K1, lda, kTileM));
+  if (save) AE_CHECK(tc_make_tmap_bf16(&t1, g.out1, g.M, H, g.ldo1, 32, 32));
+  AE_CHECK(tc_make_tmap_bf16(&t2, g.out2, g.M, H, g.ldo2, 32, 32));
+#define AE_CH_CASE(KK, HH) if (K1 == KK && H == HH) return launch_kh<KK, HH>(g, ta, t1, t2, tf1, save, st);
+  AE_CH_CASE(256, 256) AE_CH_CASE(64, 256) AE_CH_CASE(128, 128) AE_CH_CASE(64, 128) AE_CH_CASE(64, 64)
+#undef AE_CH_CASE
+  return AETHER_E_UNSUPPORTED;
+}
+
+}  // namespace aether

@@ -34,6 +34,21 @@ int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k
 // out = epi(tf(A) B^T); A is bf16 [M, K] with leading dimension lda (elements)
 int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int tf, cudaStream_t st);
 
+// Chained edge MLP on a CTA pair (tc_chain.cu): out2 = silu(out1) W2^T + b2 with out1 = tf1(A) W1^T + b1
+// (+ gat16[idx_a[m]] + gat16[idx_b[m] + goff_b]); out1 is written only when non-null (save for backward).
+struct TcChainArgs {
+  int64_t M = 0;
+  const void* wpack1 = nullptr;        // tc_pack_weight image, N = H rows, K = K1
+  const void* wpack2 = nullptr;        // tc_pack_weight image, N = H rows, K = H
+  const float* bias1 = nullptr; const float* bias2 = nullptr;
+  const __nv_bfloat16* gat16 = nullptr; int64_t ldg = 0;
+  const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int64_t goff_b = 0;
+  __nv_bfloat16* out1 = nullptr; int64_t ldo1 = 0;
+  __nv_bfloat16* out2 = nullptr; int64_t ldo2 = 0;
+};
+bool tc_chain_supported(int K1, int H);
+int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, int tf1, cudaStream_t st);
+
 // fp32 [M, cols] (leading dimension lda) -> bf16 [M, cols] (leading dimension ldo), optionally through
 // SiLU (tf = TF_SILU) and a dropout mask (TF_SILU_MASK, mask has the layout of A)
 int tc_convert_bf16(const float* A, int64_t lda, int64_t M, int cols, int tf, const float* mask, void* out, int64_t ldo,

@@ -209,6 +209,16 @@ size_t aether_dbg_tc_wgrad_partial_floats(int32_t MG, int32_t NA);
 int aether_dbg_tc_wgrad(const void* G_bf16, int32_t MG, const void* ACT_bf16, int32_t NA, int32_t silu_on_load,
                         int64_t E, float* dW, int32_t n_valid, int32_t fold32, float* db, float* partial,
                         size_t partial_floats, void* stream);
+/* Chained edge MLP of one layer on a CTA pair (csrc/tc_chain.cu; GNNLayer.message_fn, locs.py:206-212,235):
+ * out1[M,H] = tf(A[M,K1]) W1^T + bias1 (+ gat_bf16[idx_a[m]*ldg+n] + gat_bf16[idx_b[m]*ldg+goff_b+n]),
+ * out2[M,H] = silu(out1) W2^T + bias2, both bf16; out1_bf16 may be NULL (intermediate not stored).
+ * W1 is [H, ldw1] fp32 (columns < k1_valid used, column k read at k % kmod1 when kmod1 != 0), W2 is [H, H].
+ * wpack_scratch: (K1 + H) * H * 2 bytes. */
+int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, const float* W1, int64_t ldw1,
+                        int32_t k1_valid, int32_t kmod1, const float* W2, int32_t H, int32_t silu_on_load,
+                        const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
+                        const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
+                        void* out2_bf16, void* wpack_scratch, void* stream);
 
 #ifdef __cplusplus
 }
