@@ -137,15 +137,18 @@ __device__ __forceinline__ uint32_t mapa_rank(uint32_t smem_addr, uint32_t rank)
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
   return r;
 }
-// arrive on a barrier anywhere in the cluster (address from mapa_rank); releases this thread's prior writes cluster-wide
+// arrive on a barrier anywhere in the cluster (address from mapa_rank).  Default semantics (.release.cta), as CUTLASS's
+// ClusterBarrier::arrive: what is handed over lives in tensor memory (ordered by the tcgen05 fences) or was made visible
+// to the async proxy with fence.proxy.async; ".release.cluster" compiles to MEMBAR.ALL.GPU + ERRBAR and measured 20 % of
+// the epilogue warps' time.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;

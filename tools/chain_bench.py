@@ -55,9 +55,11 @@ def timeit(name, fn, passes):
           (name, best, best * 1e3 / (M / 128 / 148), M * H * 2 * passes / best / 1e6, passes, flops / best / 1e9), flush=True)
 
 
-timeit("two GEMMs, gather (incl. 2 weight packs)", lambda: two(True), 4)
-timeit("two GEMMs, no gather", lambda: two(False), 4)
-timeit("chain train  (pre1 stored), gather", lambda: chain(True, True), 3)
-timeit("chain train  (pre1 stored), no gather", lambda: chain(True, False), 3)
-timeit("chain infer  (pre1 not stored), gather", lambda: chain(False, True), 2)
-timeit("chain infer  (pre1 not stored), no gather", lambda: chain(False, False), 2)
+MODES = {"two_g": ("two GEMMs, gather (incl. 2 weight packs)", lambda: two(True), 4),
+         "two": ("two GEMMs, no gather", lambda: two(False), 4),
+         "train_g": ("chain train  (pre1 stored), gather", lambda: chain(True, True), 3),
+         "train": ("chain train  (pre1 stored), no gather", lambda: chain(True, False), 3),
+         "infer_g": ("chain infer  (pre1 not stored), gather", lambda: chain(False, True), 2),
+         "infer": ("chain infer  (pre1 not stored), no gather", lambda: chain(False, False), 2)}
+for m in os.environ.get("MODES", ",".join(MODES)).split(","):
+    timeit(*MODES[m])
