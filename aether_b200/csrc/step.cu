@@ -2,6 +2,7 @@
 //   forward : nn/state2state/aether.py:169-186
 //   backward: autograd of the same (experiments/lorentz/main.py:291)
 // Every launch goes to the caller's stream; nothing synchronises.
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -172,6 +173,14 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   return s;
 }
 
+// The chained edge-MLP kernel is the default; AETHER_B200_NO_CHAIN=1 runs the two separate GEMMs it replaced (A/B
+// measurements only -- the results are bit-identical, tests/test_chain_gpu.py).
+bool use_chain() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("AETHER_B200_NO_CHAIN"); v = (e && e[0] == '1') ? 0 : 1; }
+  return v == 1;
+}
+
 bool dims_ok(const AetherDims* d) {
   return d && (d->num_dims == 2 || d->num_dims == 3) && d->hidden >= 4 && d->hidden % 4 == 0 && d->n_nodes >= 0 &&
          d->n_edges >= 0 && d->n_nodes < ((int64_t)1 << 31) && d->n_edges < ((int64_t)1 << 31);
@@ -255,6 +264,17 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     ProfScope ps(PROF_EDGE_MLP_FWD, st);
     if (bf16) {
       // pre1 = [silu(pre2_{l-1}) | feat] We^T + b1 (+ P_s[send] + P_r[recv]) ; pre2 = silu(pre1) W2^T + b2
+      if (use_chain()) {
+        // ONE launch per layer (tc_chain.cu): the intermediate stays in tensor memory and reaches HBM only when the
+        // backward needs it
+        TcChainArgs c;
+        c.M = E; c.wpack1 = w.wpA[l]; c.wpack2 = w.wpB[l]; c.bias1 = P[s.m0b]; c.bias2 = P[s.m2b];
+        if (l > 1) { c.gat16 = ps16; c.ldg = H; c.idx_a = G.send; c.idx_b = G.recv; c.goff_b = pr16 - ps16; }
+        c.out1 = (flags & AETHER_F_SAVE_FOR_BACKWARD) ? (__nv_bfloat16*)w.bpre1[l] : nullptr; c.ldo1 = H;
+        c.out2 = (__nv_bfloat16*)w.bpre2[l]; c.ldo2 = H;
+        if (l == 1) AE_CHECK(tc_chain(c, w.feat16, 64, 64, H, TC_TF_NONE, st));
+        else AE_CHECK(tc_chain(c, w.bpre2[l - 1], H, H, H, TC_TF_SILU, st));
+      } else {
       TcGemmArgs a;
       a.M = E; a.wpack = w.wpA[l]; a.bias = P[s.m0b]; a.out_bf16 = (__nv_bfloat16*)w.bpre1[l]; a.ldo = H;
       if (l > 1) { a.gat16 = ps16; a.ldg = H; a.idx_a = G.send; a.idx_b = G.recv; a.goff_b = pr16 - ps16; }
@@ -263,6 +283,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       TcGemmArgs b;
       b.M = E; b.wpack = w.wpB[l]; b.bias = P[s.m2b]; b.out_bf16 = (__nv_bfloat16*)w.bpre2[l]; b.ldo = H;
       AE_CHECK(tc_gemm(b, w.bpre1[l], H, H, H, TC_TF_SILU, st));
+      }
     } else {
       GemmArgs g;
       if (l == 1) {

@@ -15,16 +15,23 @@
 // (64 KB + 64 KB at H = 256) and the tensor cores of both SMs read both halves.  Per CTA:
 //
 //   warp 8      TMA producer : its halves of the two weight images once, then 128x64 bf16 boxes of A (ring)
-//   warps 10-13 transform    : in-place SiLU on the landed box, then "ready" to the LEADER's barrier (remote arrive)
+//   warps 12-15 transform    : in-place SiLU on the landed box, then "ready" to the LEADER's barrier (remote arrive)
 //   warp 9      MMA issuer   : CTA 0 only; MMA 1 (A, B from shared memory) into accumulator 1, MMA 2 (A from
 //                              tensor memory, B from shared memory) into accumulator 2; completion is multicast
 //                              to the barriers of both CTAs (tcgen05.commit ... multicast::cluster)
 //   warps 0-7   epilogue     : two warps per TMEM lane quarter on alternate 32-column chunks
-//        epilogue 1: tcgen05.ld, + b1 + gathered node terms (requested one chunk ahead), bf16 pre1 -> TMA store
-//                    (SAVE), SiLU, bf16 pair per 32-bit column -> tcgen05.st over columns [32j, 32j+16) of the chunk,
-//                    "piece ready" to the leader after each chunk (MMA 2 starts on the first 64 inputs while the
-//                    rest of the row is still in the epilogue)
-//        epilogue 2: tcgen05.ld, + b2, bf16 pre2 -> TMA store
+//        epilogue 1: tcgen05.ld, + b1 + gathered node terms, bf16 pre1 -> TMA store (SAVE), SiLU, bf16 pair per
+//                    32-bit column -> tcgen05.st over columns [32j, 32j+16) of the chunk, "piece ready" to the
+//                    leader after each chunk (MMA 2 starts on the first 64 inputs while the rest of the row is
+//                    still in the epilogue)
+//        epilogue 2: tcgen05.ld (the next chunk's load in flight under this chunk's stores), + b2, bf16 pre2 -> TMA store
+//
+// 16 warps = four complete warpgroups, so the register file is re-split after the set-up (setmaxnreg): the two
+// epilogue warpgroups take 192 registers per thread, the producer / MMA / transform warpgroups keep 64.  The larger
+// budget holds one register slot per chunk position for the gathered rows P_s[send], P_r[recv] (64 bytes each per
+// row and chunk), requested TWO chunks ahead -- also across tiles -- with static slot indices (no register copies
+// that would wait on the loads).  profiles/r02_ncu_chain_v1.md: with one chunk ahead the epilogue warps sat on
+// exactly these loads (gather variant 18.4k cycles per tile against 12.3k without).
 //
 // Tensor memory: accumulator 1 at columns [0, H), accumulator 2 at [H, 2H) -- all 512 columns at H = 256, so there
 // is no second accumulator pair; MMA 1 of the next tile runs while epilogue 2 of this one drains.
@@ -40,9 +47,10 @@ namespace {
 
 using namespace tc;
 
-constexpr int kThreads = 448;
+constexpr int kThreads = 512;                      // warpgroups: epilogue x2 | TMA, MMA, 2 idle | transform
 constexpr int kEpiWarps = 8;
-constexpr int kWarpTma = 8, kWarpMma = 9, kWarpTf0 = 10;
+constexpr int kWarpTma = 8, kWarpMma = 9, kWarpTf0 = 12;
+constexpr int kRegsEpi = 192, kRegsAux = 64;       // 8 x 32 x 192 + 8 x 32 x 64 = 64 Ki registers
 constexpr int kTileM = 128;                        // rows per CTA; the pair owns 256
 constexpr int kSlotBytes = kTileM * 128;           // 128 rows x 64 bf16
 constexpr int kSmemMax = 232448;                   // 227 KB
@@ -52,14 +60,14 @@ __host__ __device__ constexpr int misc_bytes(int H) { return 512 + 2 * H * 4; } 
 __host__ __device__ constexpr int w1_bytes(int K1, int H) { return K1 * (H / 2) * 2; }  // this CTA's half of the rows
 __host__ __device__ constexpr int w2_bytes(int H) { return H * (H / 2) * 2; }
 __host__ __device__ constexpr int num_slots(int K1, int H) {
-  int s = (kSmemMax - 1024 - misc_bytes(H) - w1_bytes(K1, H) - w2_bytes(H) - kStageBytes) / kSlotBytes;
+  int s = (kSmemMax - misc_bytes(H) - w1_bytes(K1, H) - w2_bytes(H) - kStageBytes) / kSlotBytes;
   return s > 8 ? 8 : s;
 }
 __host__ __device__ constexpr int smem_bytes(int K1, int H) {
-  return 1024 + w1_bytes(K1, H) + w2_bytes(H) + num_slots(K1, H) * kSlotBytes + kStageBytes + misc_bytes(H);
+  return w1_bytes(K1, H) + w2_bytes(H) + num_slots(K1, H) * kSlotBytes + kStageBytes + misc_bytes(H);
 }
 
-template <int K1, int H, int TF1, bool SAVE>
+template <int K1, int H, int TF1, bool SAVE, bool GATHER>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmO1,
                 const __grid_constant__ CUtensorMap tmO2, TcChainArgs g) {
@@ -73,8 +81,12 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   constexpr int WROW = (H / 2) * 128;              // bytes of one 64-wide K chunk of this CTA's weight half
   static_assert(S >= 2, "pipeline too shallow");
 
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // The dynamic shared memory of a kernel without static shared memory starts 1024-byte aligned (the swizzle atom of
+  // the operand tiles); no slack is reserved for rounding up, which is what makes room for the fourth ring slot at
+  // H = 256 (a whole tile of A in flight: with three, MMA 1 of the next tile waited on its last chunk's TMA + SiLU).
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  if (base & 1023u) __trap();
   const uint32_t sW1 = base;
   const uint32_t sW2 = sW1 + w1_bytes(K1, H);
   const uint32_t sA = sW2 + w2_bytes(H);
@@ -135,6 +147,8 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  // one instruction for both auxiliary warpgroups; the epilogue warpgroups raise theirs inside their own branch
+  if (warp >= kEpiWarps) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" :: "n"(kRegsAux));
 
   if (warp == kWarpTma) {
     // ===== TMA producer (both CTAs, own rows) =====
@@ -214,50 +228,65 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         if (lane == 0) mbar_arrive_cluster(rdy0 + 8 * s);
       }
     }
-  } else {
+  } else if (warp < kEpiWarps) {
     // ===== epilogue warps =====
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" :: "n"(kRegsEpi));
+    constexpr int CPW = NCH / 2;                   // chunks per warp and epilogue phase: 4 / 2 / 1
+    constexpr int D = CPW >= 2 ? 2 : 1;            // the gathered rows are requested D chunks ahead
+    constexpr bool TOP = (D % CPW) != 0;           // the target slot is not the one being consumed: request first
     const int qr = warp & 3, hf = warp >> 2;
     const uint32_t sbuf = sStage + warp * 4096;
     const uint32_t a2bar0 = mapa_rank(bar_a2, 0), acc2e0 = mapa_rank(bar_acc2e, 0);
     const uint32_t lane_base = tmem_base + ((uint32_t)(qr * 32) << 16);
-    const bool gather = g.gat16 != nullptr;
+    const bool has_b1 = g.bias1 != nullptr;
     uint32_t lt = 0, nbox = 0;
-    // gathered node terms of a chunk (64 contiguous bytes per row and plane), requested ONE CHUNK AHEAD
-    uint4 xn[4], yn[4];
-    int ia_n = 0, ib_n = 0;
-    auto request = [&](int ia_, int ib_, int c) {
+    // gathered node terms: slot kk holds the 64-byte pieces of P_s[send] and P_r[recv] for chunk position kk
+    uint4 gs[CPW][4], gr[CPW][4];
+    int ia = 0, ib = 0, ia_n = 0, ib_n = 0;
+    auto request = [&](uint4 (&ds)[4], uint4 (&dr)[4], int ia_, int ib_, int c) {
       const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
       const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { xn[q] = __ldg(pa + q); yn[q] = __ldg(pb + q); }
+      for (int q = 0; q < 4; ++q) { ds[q] = __ldg(pa + q); dr[q] = __ldg(pb + q); }
     };
-    if (gather && cid < n_pt) {
+    if (GATHER && cid < n_pt) {
       const int64_t r0 = cid * 2 * kTileM + rank * kTileM + qr * 32 + lane;
       if (r0 < g.M) { ia_n = g.idx_a[r0]; ib_n = g.idx_b[r0]; }
-      request(ia_n, ib_n, hf * 32);
+#pragma unroll
+      for (int k = 0; k < D; ++k) request(gs[k], gr[k], ia_n, ib_n, (hf + 2 * k) * 32);
     }
     for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
       const int64_t row0 = pt * 2 * kTileM + rank * kTileM + qr * 32;
-      const int ia = ia_n, ib = ib_n;
       const int64_t ptn = pt + ncl;
       const int64_t row_n = row0 + lane + ncl * 2 * kTileM;
+      ia = ia_n; ib = ib_n;
       ia_n = 0; ib_n = 0;
-      if (gather && ptn < n_pt && row_n < g.M) { ia_n = g.idx_a[row_n]; ib_n = g.idx_b[row_n]; }
+      if (GATHER && ptn < n_pt && row_n < g.M) { ia_n = g.idx_a[row_n]; ib_n = g.idx_b[row_n]; }
+      auto prefetch = [&](int kk) {                // rows of the chunk D positions after (this tile, kk)
+        const int kn = kk + D;
+        if (kn < CPW) request(gs[kn % CPW], gr[kn % CPW], ia, ib, (hf + 2 * kn) * 32);
+        else if (ptn < n_pt) request(gs[kn % CPW], gr[kn % CPW], ia_n, ib_n, (hf + 2 * (kn - CPW)) * 32);
+      };
 
       // ---- epilogue 1: accumulator 1 -> pre1 (HBM, SAVE) and A2 = bf16(silu(pre1)) (tensor memory) ----
       mbar_wait(bar_acc1f, lt & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int j = hf; j < NCH; j += 2) {
-        const int c0 = j * 32;
-        uint4 a4[4], b4[4];
-        if (gather) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) { a4[q] = xn[q]; b4[q] = yn[q]; }
-          if (j + 2 < NCH) request(ia, ib, c0 + 64);     // the next tile's first chunk is requested in epilogue 2
-        }
+      for (int kk = 0; kk < CPW; ++kk) {
+        const int j = hf + 2 * kk;
+        const int c0 = j * 32;
+        if (GATHER && TOP) prefetch(kk);
         uint32_t r[32];
         tmem_ld32(lane_base + c0, r);
+        f32x2 bv[16];
+        if (!GATHER) {
+          // bias of the chunk into registers while the tensor-memory load is in flight
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 t4 = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * q);
+            bv[2 * q] = f2_make(t4.x, t4.y); bv[2 * q + 1] = f2_make(t4.z, t4.w);
+          }
+        }
         const uint32_t buf = sbuf + (nbox & 1) * 2048;
         if (SAVE) {
           // the TMA store that read this staging box two boxes ago must have finished reading it
@@ -265,29 +294,34 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           __syncwarp();
         }
         tmem_ld_wait();
-        float v[32];
-        {
-          const float* bs = sb1 + c0;
+        f32x2 v[16];
+        if (!GATHER) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) + bs[i];
-        }
-        if (gather) {
+          for (int i = 0; i < 16; ++i) v[i] = f2_add(f2_make_u(r[2 * i], r[2 * i + 1]), bv[i]);
+        } else {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint32_t bb[4] = {b4[q].x, b4[q].y, b4[q].z, b4[q].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(bb[e]); v[8 * q + 2 * e + 1] += bf16_hi(bb[e]); }
+          for (int q = 0; q < 8; ++q) {
+            const float4 t4 = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * q);
+            v[2 * q] = f2_add(f2_make_u(r[4 * q], r[4 * q + 1]), f2_make(t4.x, t4.y));
+            v[2 * q + 1] = f2_add(f2_make_u(r[4 * q + 2], r[4 * q + 3]), f2_make(t4.z, t4.w));
           }
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+            const uint32_t bb[4] = {gr[kk][q].x, gr[kk][q].y, gr[kk][q].z, gr[kk][q].w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) { v[8 * q + 2 * e] += bf16_lo(aa[e]); v[8 * q + 2 * e + 1] += bf16_hi(aa[e]); }
+            for (int e = 0; e < 4; ++e) v[4 * q + e] = f2_add(v[4 * q + e], f2_from_bf16x2(bb[e]));
           }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t aa[4] = {gs[kk][q].x, gs[kk][q].y, gs[kk][q].z, gs[kk][q].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[4 * q + e] = f2_add(v[4 * q + e], f2_from_bf16x2(aa[e]));
+          }
+          if (!TOP) prefetch(kk);
         }
         uint32_t o[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) o[i] = pack_bf16(v[2 * i], v[2 * i + 1]);
+        for (int i = 0; i < 16; ++i) o[i] = f2_pack_bf16(v[i]);
         if (SAVE) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -306,7 +340,7 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         // the second GEMM consumes what the backward will recompute from the STORED pre1: silu of the bf16 value
 #pragma unroll
-        for (int i = 0; i < 16; ++i) o[i] = pack_bf16(silu_fast(bf16_lo(o[i])), silu_fast(bf16_hi(o[i])));
+        for (int i = 0; i < 16; ++i) o[i] = f2_pack_bf16(f2_silu(f2_from_bf16x2(o[i])));
         tmem_st16(lane_base + c0, o);
         tmem_st_wait();
         tc_fence_before();
@@ -314,43 +348,50 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         if (lane == 0) mbar_arrive_cluster(a2bar0 + 8 * (j >> 1));
       }
 
-      // ---- epilogue 2: accumulator 2 -> pre2 (HBM) ----
+      // ---- epilogue 2: accumulator 2 -> pre2 (HBM); the next chunk's tensor-memory load runs under the stores ----
       mbar_wait(bar_acc2f, lt & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int j = hf; j < NCH; j += 2, ++nbox) {
-        const int c0 = j * 32;
-        const uint32_t buf = sbuf + (nbox & 1) * 2048;
-        if (gather && j + 2 >= NCH && ptn < n_pt) request(ia_n, ib_n, hf * 32);
+      {
         uint32_t r[32];
-        tmem_ld32(lane_base + H + c0, r);
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-        __syncwarp();
-        tmem_ld_wait();
-        if (j + 2 >= NCH) {
-          // accumulator 2 fully read by this warp: hand it back to the MMA warp before the stores
-          tc_fence_before();
+        tmem_ld32(lane_base + H + hf * 32, r);
+#pragma unroll
+        for (int kk = 0; kk < CPW; ++kk, ++nbox) {
+          const int c0 = (hf + 2 * kk) * 32;
+          const uint32_t buf = sbuf + (nbox & 1) * 2048;
+          f32x2 bv[16];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 t4 = *reinterpret_cast<const float4*>(sb2 + c0 + 4 * q);
+            bv[2 * q] = f2_make(t4.x, t4.y); bv[2 * q + 1] = f2_make(t4.z, t4.w);
+          }
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(acc2e0);
-        }
-        const float* bs = sb2 + c0;
+          tmem_ld_wait();
+          uint32_t o[16];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint32_t o[4];
+          for (int i = 0; i < 16; ++i) o[i] = f2_pack_bf16(f2_add(f2_make_u(r[2 * i], r[2 * i + 1]), bv[i]));
+          if (kk + 1 < CPW) {
+            tmem_ld32(lane_base + H + c0 + 64, r);
+          } else {
+            // accumulator 2 fully read by this warp: hand it back to the MMA warp before the stores
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(acc2e0);
+          }
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            o[e] = pack_bf16(__uint_as_float(r[8 * q + 2 * e]) + bs[8 * q + 2 * e],
-                             __uint_as_float(r[8 * q + 2 * e + 1]) + bs[8 * q + 2 * e + 1]);
-          const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t addr = buf + lane * 64 + ((q ^ ((lane >> 1) & 3)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(o[4 * q]), "r"(o[4 * q + 1]),
+                         "r"(o[4 * q + 2]), "r"(o[4 * q + 3]) : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && row0 < g.M) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                         :: "l"((uint64_t)&tmO2), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
+          }
+          if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0 && row0 < g.M) {
-          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
-                       :: "l"((uint64_t)&tmO2), "r"(c0), "r"((int)row0), "r"(buf) : "memory");
-        }
-        if (lane == 0) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -364,11 +405,11 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
 }
 
-template <int K1, int H, int TF1, bool SAVE>
+template <int K1, int H, int TF1, bool SAVE, bool GATHER>
 int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, cudaStream_t st) {
   constexpr int smem = smem_bytes(K1, H);
   static_assert(smem <= kSmemMax, "shared memory budget");
-  auto kern = tc_chain_kernel<K1, H, TF1, SAVE>;
+  auto kern = tc_chain_kernel<K1, H, TF1, SAVE, GATHER>;
   static int max_clusters = 0;                     // co-resident CTA pairs (one per TPC): 74 on a full B200
   if (max_clusters == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -393,15 +434,19 @@ int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap&
   return 0;
 }
 
+template <int K1, int H, int TF1>
+int launch_tf(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, bool save,
+              cudaStream_t st) {
+  const bool gather = g.gat16 != nullptr;
+  if (save) return gather ? launch_chain<K1, H, TF1, true, true>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, true, false>(g, ta, t1, t2, st);
+  return gather ? launch_chain<K1, H, TF1, false, true>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, false, false>(g, ta, t1, t2, st);
+}
+
 template <int K1, int H>
 int launch_kh(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, int tf1, bool save,
               cudaStream_t st) {
-  if (tf1 == TC_TF_SILU) {
-    if (save) return launch_chain<K1, H, TC_TF_SILU, true>(g, ta, t1, t2, st);
-    return launch_chain<K1, H, TC_TF_SILU, false>(g, ta, t1, t2, st);
-  }
-  if (save) return launch_chain<K1, H, TC_TF_NONE, true>(g, ta, t1, t2, st);
-  return launch_chain<K1, H, TC_TF_NONE, false>(g, ta, t1, t2, st);
+  if (tf1 == TC_TF_SILU) return launch_tf<K1, H, TC_TF_SILU>(g, ta, t1, t2, save, st);
+  return launch_tf<K1, H, TC_TF_NONE>(g, ta, t1, t2, save, st);
 }
 
 }  // namespace

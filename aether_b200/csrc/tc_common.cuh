@@ -264,6 +264,53 @@ __device__ __forceinline__ uint32_t bf2_dsilu_w(uint32_t z) {
 }
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
+// ---- packed fp32x2 arithmetic (sm_100 FADD2 / FMUL2 / FFMA2): two IEEE round-to-nearest results per issue slot, the
+// ---- same values as the scalar instructions; a pair lives in an aligned 64-bit register pair ----------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 f2_make(float lo, float hi) {
+  f32x2 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ f32x2 f2_make_u(uint32_t lo, uint32_t hi) {
+  f32x2 d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
+__device__ __forceinline__ float f2_lo(f32x2 a) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a));
+  return lo;
+}
+__device__ __forceinline__ float f2_hi(f32x2 a) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a));
+  return hi;
+}
+__device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 f2_mul(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+// both halves of a bf16 pair as fp32
+__device__ __forceinline__ f32x2 f2_from_bf16x2(uint32_t u) { return f2_make_u(u << 16, u & 0xFFFF0000u); }
+__device__ __forceinline__ uint32_t f2_pack_bf16(f32x2 a) { return pack_bf16(f2_lo(a), f2_hi(a)); }
+// silu of a pair, the scalar silu_fast twice: h = z/2, h tanh(h) + h
+__device__ __forceinline__ f32x2 f2_silu(f32x2 z) {
+  const f32x2 h = f2_mul(z, f2_make(0.5f, 0.5f));
+  const f32x2 t = f2_make(tanh_approx(f2_lo(h)), tanh_approx(f2_hi(h)));
+  return f2_fma(h, t, h);
+}
 
 }  // namespace tc
 

@@ -24,9 +24,13 @@ recv = torch.arange(M, device="cuda", dtype=torch.int32) // 99
 send = ((torch.arange(M, device="cuda", dtype=torch.int32) % 99) + (recv // 100) * 100).clamp(max=Nn - 1)
 
 
-def chain(save, gather):
-    return lib.aether_dbg_tc_chain(P(A), M, H, H, P(W1), H, H, 0, P(W2), H, 1, P(b1), P(b2), P(gat if gather else None), 2 * H,
-                                   P(send if gather else None), P(recv if gather else None), H, P(o1 if save else None), P(o2),
+send_rand = torch.randint(0, Nn, (M,), device="cuda", dtype=torch.int32)
+
+
+def chain(save, gather, snd=None, bias=True):
+    snd = send if snd is None else snd
+    return lib.aether_dbg_tc_chain(P(A), M, H, H, P(W1), H, H, 0, P(W2), H, 1, P(b1 if bias else None), P(b2), P(gat if gather else None), 2 * H,
+                                   P(snd if gather else None), P(recv if gather else None), H, P(o1 if save else None), P(o2),
                                    P(scratch), stream())
 
 
@@ -60,6 +64,9 @@ MODES = {"two_g": ("two GEMMs, gather (incl. 2 weight packs)", lambda: two(True)
          "train_g": ("chain train  (pre1 stored), gather", lambda: chain(True, True), 3),
          "train": ("chain train  (pre1 stored), no gather", lambda: chain(True, False), 3),
          "infer_g": ("chain infer  (pre1 not stored), gather", lambda: chain(False, True), 2),
+         "train_g_bcast": ("chain train, gather with send := recv (warp-uniform rows)", lambda: chain(True, True, recv), 3),
+         "train_g_rand": ("chain train, gather with random senders", lambda: chain(True, True, send_rand), 3),
+         "train_g_nobias": ("chain train, gather, bias folded into P_r", lambda: chain(True, True, None, False), 3),
          "infer": ("chain infer  (pre1 not stored), no gather", lambda: chain(False, False), 2)}
 for m in os.environ.get("MODES", ",".join(MODES)).split(","):
     timeit(*MODES[m])
