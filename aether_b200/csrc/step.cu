@@ -5,6 +5,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <memory>
+
 #include "common.cuh"
 #include "tc_gemm.cuh"
 
@@ -233,6 +235,8 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   __nv_bfloat16* pr16 = (__nv_bfloat16*)w.pspr16 + (size_t)Nn * H;
   if (pt.phase_lo == 0) {
     // neural field at the particles (aether.py:127-134)
+    {
+    ProfScope pn(PROF_NODE, st);
     AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
     AE_CHECK(linear(nc, w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
                     nullptr, 0, st));
@@ -240,6 +244,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     AE_CHECK(linear(nc, w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
     // local frames and features (aether.py:33-100,177)
     AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
+    }
     {
       ProfScope ps(PROF_EDGE_FEAT, st);
       if (bf16) AE_CHECK(launch_edge_features_hilo(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat16, st));
@@ -248,6 +253,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     if (bf16) {
       // bf16 shared-memory images of the edge-MLP weights (first Linear: per-edge block only; layer 1: the
       // feature columns repeated for the hi and lo halves of the operand)
+      ProfScope pn(PROF_NODE, st);
       AE_CHECK(tc_pack_weight(P[P_L1_M0_W], Fe, H, 64, H, Fe, 0, 32, w.wpA[1], st));
       for (int l = 1; l <= 4; ++l) {
         const LayerSlots s = layer_slots(l);
@@ -301,6 +307,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
     const float* base = xin + (size_t)n0 * H;
     float* y = w.y[l] + (size_t)n0 * H;
     if (l == 1) {
+      ProfScope pn(PROF_NODE, st);
       AE_CHECK(linear(nc, w.x0 + (size_t)n0 * 3 * D, 3 * D, M, 3 * D, P[P_L1_RES_W], 3 * D, P[P_L1_RES_B], H, y, H, TF_NONE,
                       nullptr, nullptr, 0, st));
       base = y;
@@ -311,6 +318,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       else AE_CHECK(launch_segmean_silu(M, H, G.rowptr + n0, w.pre2[l], H, base, H, y, H, st));
     }
     // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
+    ProfScope pn(PROF_NODE, st);
     float* pre3 = w.pre3[l] + (size_t)n0 * 2 * H;
     float* xo = w.xl[l] + (size_t)n0 * H;
     AE_CHECK(linear(nc, y, H, M, H, P[s.u0w], H, P[s.u0b], 2 * H, pre3, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
@@ -329,6 +337,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   }
   if (pt.phase_hi < 3) return 0;
   // out MLP (locs.py:160-168,193), globalize and Euler update (local_to_global.py:12-13, aether.py:185)
+  ProfScope pn(PROF_NODE, st);
   const float* m1 = dmask ? dmask + (size_t)n0 * H : nullptr;
   const float* m2 = dmask ? dmask + (size_t)Nn * H + (size_t)n0 * H : nullptr;
   float* o1 = w.o1 + (size_t)n0 * H;

@@ -122,6 +122,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   const float* m2 = dmask ? dmask + (size_t)Nn * H : nullptr;
 
   // out = x + R pred
+  std::unique_ptr<ProfScope> pn(new ProfScope(PROF_NODE, st));   // node-level head of the backward (closed before the edge part)
   AE_CHECK(launch_globalize_bwd(D, Nn, w.R, w.pred, gout, s.gpred, s.gRglob, st));
   // out MLP
   AE_CHECK(b.wgrad(s.gpred, D, Nn, D, w.o2, H, H, m2 ? TF_SILU_MASK : TF_SILU, m2, G[P_OUT6_W], H, G[P_OUT6_B]));
@@ -135,9 +136,11 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   const float* ge = nullptr;   // gradient w.r.t. e_l from layer l+1 (none for the last layer)
   const bool tc = use_tc(d, flags);
   const int ldgf = tc ? 32 : ldf;   // leading dimension of gfeat
+  pn.reset();
 
   // node part A of layer l: x_l = y + W4 silu(pre3) + b4 ; pre3 = W3 y + b3   (gx -> s.gy)
   auto node_update_bwd = [&](int l) -> int {
+    ProfScope pn(PROF_NODE, st);
     const LayerSlots sl = layer_slots(l);
     AE_CHECK(b.wgrad(gx, H, Nn, H, w.pre3[l], 2 * H, 2 * H, TF_SILU, nullptr, G[sl.u2w], 2 * H, G[sl.u2b]));
     AE_CHECK(b.dgrad(gx, H, Nn, H, P[sl.u2w], 2 * H, 2 * H, s.gpre3, 2 * H, w.pre3[l], nullptr, nullptr, 0));
@@ -147,6 +150,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   };
   // node terms of layer l > 1: P = x_{l-1} [Ws; Wr]^T from the segment sums s.gpspr ; gx <- grad of x_{l-1}
   auto node_terms_bwd = [&](int l) -> int {
+    ProfScope pn(PROF_NODE, st);
     const LayerSlots sl = layer_slots(l);
     const float* xin = w.xl[l - 1];
     AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
@@ -158,6 +162,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   };
   // layer 1: y1 = Wres x0 + bres + agg
   auto node_res_bwd = [&]() -> int {
+    ProfScope pn(PROF_NODE, st);
     AE_CHECK(b.wgrad(s.gy, H, Nn, H, w.x0, 3 * D, 3 * D, TF_NONE, nullptr, G[P_L1_RES_W], 3 * D, G[P_L1_RES_B]));
     AE_CHECK(b.dgrad(s.gy, H, Nn, H, P[P_L1_RES_W], 3 * D, 3 * D, s.gx0, 3 * D, nullptr, nullptr, nullptr, 0));
     return 0;
@@ -212,6 +217,7 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   }
 
   // localizer: per-edge partials, then segment sums by receiver (contiguous) and by sender (sperm)
+  ProfScope pn2(PROF_NODE, st);                      // geometry + field backward: counted with the node-level work
   const int GS = geom_gs(D), GR = geom_gr(D);
   AE_CHECK(launch_edge_features_bwd(D, E, Gr.send, Gr.recv, x, vel, w.f, w.R, s.gfeat, ldgf, s.gsend, s.grecv, st));
   AE_CHECK(launch_segsum(Nn, GS, Gr.colptr, Gr.sperm, s.gsend, GS, s.ssend, GS, 0, st));

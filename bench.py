@@ -12,9 +12,14 @@ particles: training workloads run caller prep + forward + MSE + backward + AdamW
           the edge list rebuilt on the device every step and the loss read back
   roofline : edge-MLP kernels, algorithmic FLOPs / CUDA-event time of those launches
   cpu_baseline : the CPU oracle (torch CPU restatement of the reference) on a bounded sample
+  secondary (default c4 run only): config 4 STRONG scaling (1024 graphs split over the ranks), config 5 (one
+          100k-particle scene, receiver-partitioned) at H = 256 and 64 -- the other scaling cases of SURVEY.md 8(d/e) -- and,
+          at N = 1, `gpu_eager_baseline` (the oracle port as eager PyTorch on the same GPU) and `parity` (errors against
+          the oracle at the config-4 shape, 20-step rollout MSE at the config-1 shape)
 `--impl reference` times that CPU path alone.  Nothing here reads /root/reference.
 """
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -41,6 +46,34 @@ WORKLOADS = {
                name="config5: synthetic 3D gravitational scene, 100k particles (unit density), radius graph r=2.25 capped at the "
                     "32 nearest (~3.2M edges), ONE scene receiver-partitioned over the GPUs, 5-step rollout"),
 }
+
+
+class Ctx:
+    """One process per GPU: rank / world / device and the NCCL process group (initialised once per process)."""
+
+    def __init__(self):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+
+    def close(self):
+        if self.dist is not None:
+            torch.cuda.synchronize()
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+            self.dist = None
+
+
+def release_memory():
+    gc.collect()
+    torch.cuda.empty_cache()
 
 
 def scene_sizes(cfg, rank=0):
@@ -185,7 +218,7 @@ def cpu_step_sample(cfg, H, graphs, seed=1):
 
 def cpu_sample_graphs(cfg, H):
     E = cfg["N"] * (cfg["N"] - 1) if cfg["N"] else 25 * cfg.get("knn", 10)
-    budget = 4.0e5 * (64.0 / H) ** 2 if cfg["mode"] == "train" else 2.0e6   # edges per sample step
+    budget = 8.0e5 * (64.0 / H) ** 2 if cfg["mode"] == "train" else 2.0e6   # edges per sample step (c4, H=256: 4 graphs)
     return int(max(1, min(cfg["B"], budget // max(E, 1))))
 
 
@@ -210,20 +243,13 @@ def c5_cpu_sample(cfg, H, n_sub=6250):
         n_sub, cfg["N"], int(send.numel()), T)
 
 
-def run_c5(args, cfg, H):
-    """Config 5: one 100k-particle scene, receiver-partitioned over the ranks (strong scaling: fixed total work)."""
+def run_c5(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True):
+    """Config 5: one 100k-particle scene, receiver-partitioned over the ranks (strong scaling: fixed total work).
+    Returns the JSON line as a dict on rank 0, None elsewhere."""
     import aether_b200 as ab
     from aether_b200 import _lib
     lib = _lib.load(build_if_missing=False)
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+    rank, world, local, dev, dist = ctx.rank, ctx.world, ctx.local, ctx.dev, ctx.dist
     n = cfg["N"] if not args.batch else args.batch          # --batch overrides the particle count for c5
     T = cfg["T"]
     torch.manual_seed(1)
@@ -290,24 +316,22 @@ def run_c5(args, cfg, H):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
-    launches += args.steps * roll.launches_per_replay          # kernels launched by graph replays
+    total, launches, prof = timed(step_resident, steps, warmup, profile=True)
+    launches += steps * roll.launches_per_replay          # kernels launched by graph replays
     clocks = sampler.stop() if rank == 0 else None
     if eager is not roll:       # graph replays carry no library-side event pairs: time the same kernels launched eagerly
-        _, _, prof = timed(lambda: eager.run(xd, vd, qd), max(1, min(args.steps, 3)), 1, profile=True)
+        _, _, prof = timed(lambda: eager.run(xd, vd, qd), max(1, min(steps, 3)), 1, profile=True)
     e2e = None
-    if not args.no_e2e:
-        e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
-        e2e = 4.0 * E * T * args.steps / e2e_total
+    if do_e2e:
+        e2e_total, _, _ = timed(step_e2e, steps, max(1, warmup - 1))
+        e2e = 4.0 * E * T * steps / e2e_total
+    # captured graphs (and the communicator work they hold) are dropped before anything else uses the communicator
+    roll.release()
+    torch.cuda.synchronize()
     if dist is not None:
-        # all ranks leave the communicator together, captured graphs first (rank 0 still has its CPU baseline to run)
-        roll.release()
-        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
-        dist = None
     if rank != 0:
-        return
+        return None
     pk, pk_src = peaks()
     e_local = roll.local[0].E
     spans = max(prof["spans"][0], 1)
@@ -315,8 +339,8 @@ def run_c5(args, cfg, H):
     alg = algorithmic_flops_edge_mlp(3, H, e_local) / 4.0
     achieved = alg / (ms_per_layer * 1e-3) / 1e12 if ms_per_layer > 0 else 0.0
     peak = pk.get("bf16_tflops_sustained", pk.get("bf16_tflops"))
-    line = {"metric": "edge_messages_per_sec", "value": 4.0 * E * T * args.steps / total, "unit": "edge-messages/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / args.steps * 1e3,
+    line = {"metric": "edge_messages_per_sec", "value": 4.0 * E * T * steps / total, "unit": "edge-messages/s",
+            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": total / steps * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
             "config": {"workload": cfg["name"], "num_dims": 3, "particles": n, "edges": E, "edges_rank0": e_local,
@@ -324,7 +348,7 @@ def run_c5(args, cfg, H):
                        "parallelism": "receiver-partition x%d, all-gather of [Nn,H] sender terms before layers 2-4 "
                                       "and of [Nn,3] positions per step" % world,
                        "l2": "working set exceeds L2" if E * H * 2 * 2 > 126e6 * world else "flushed: no (L2-resident edge state)"},
-            "particle_steps_per_sec": n * T * args.steps / total, "gpu_launches": int(launches), "clocks": clocks,
+            "particle_steps_per_sec": n * T * steps / total, "gpu_launches": int(launches), "clocks": clocks,
             "collectives_per_step": 4 * T if world > 1 else 0,
             "roofline": {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer, rank 0's edges)",
                          "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
@@ -335,7 +359,7 @@ def run_c5(args, cfg, H):
     if e2e is not None:
         h2d = sum(t.numel() * t.element_size() for t in host)
         line["e2e"] = {"value": e2e, "unit": "edge-messages/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
-    if not args.no_cpu_baseline:
+    if do_cpu:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         cstep, e_step, sample = c5_cpu_sample(cfg, H)
@@ -347,7 +371,7 @@ def run_c5(args, cfg, H):
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": 4.0 * e_step * it / dt, "unit": "edge-messages/s", "cores": cores, "kind": "port",
                                 "sample": sample + ", %d repeats, %d host threads" % (it, cores)}
-    print(json.dumps(line), flush=True)
+    return line
 
 
 def run_reference(args, cfg, H):
@@ -384,44 +408,14 @@ def run_reference(args, cfg, H):
     print(json.dumps(line), flush=True)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))   # c5: see --workload c5 below
-    ap.add_argument("--hidden", type=int, default=0)
-    ap.add_argument("--batch", type=int, default=0, help="graphs per GPU (default: the workload's)")
-    ap.add_argument("--precision", default=os.environ.get("AETHER_B200_PRECISION", "bf16"), choices=["fp32", "bf16"])
-    ap.add_argument("--cpu-seconds", type=float, default=12.0)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--graph", action="store_true", help="capture the train step in a CUDA graph at any size")
-    ap.add_argument("--no-graph", action="store_true", help="small training shapes: do not capture the step in a CUDA graph")
-    args = ap.parse_args()
-    cfg = dict(WORKLOADS[args.workload])
-    H = args.hidden or cfg["H"]
-    if args.batch:
-        cfg["B"] = args.batch
-    if args.impl == "reference":
-        return run_reference(args, cfg, H)
-    if args.workload == "c5":
-        return run_c5(args, cfg, H)
-
+def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="weak"):
+    """Data-parallel workloads (configs 1-4): cfg["B"] graphs PER GPU, one process per GPU, no data-path collective,
+    one gradient all-reduce per training step.  Returns the JSON line as a dict on rank 0, None elsewhere."""
     import aether_b200 as ab
     from aether_b200 import _lib
     lib = _lib.load(build_if_missing=False)
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+    rank, world, local, dev, dist = ctx.rank, ctx.world, ctx.local, ctx.dev, ctx.dist
 
     D, N, B, T = cfg["D"], cfg["N"], cfg["B"], cfg["T"]
     torch.manual_seed(1)
@@ -546,30 +540,28 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    total, launches, prof = timed(step_resident, args.steps, args.warmup, profile=True)
+    total, launches, prof = timed(step_resident, steps, warmup, profile=True)
     clocks = sampler.stop() if rank == 0 else None
     if graphed is not None:
         # graph replays carry no library-side event pairs: one eager pass of the same step for the kernel timings
         g_keep, graphed = graphed, None
         eager_fn = step_resident
-        _, _, prof = timed(step_resident, max(1, min(args.steps, 3)), 1, profile=True)
+        _, _, prof = timed(step_resident, max(1, min(steps, 3)), 1, profile=True)
         graphed, eager_fn = g_keep, None
     if not train:
         # graph replays carry no library-side event pairs: time the same kernels once more, launched eagerly
         eager = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=False)
         eager_fn = lambda: eager.run(xd, vd, qd1)
-        _, _, prof = timed(eager_fn, max(1, min(args.steps, 3)), 1, profile=True)
+        _, _, prof = timed(eager_fn, max(1, min(steps, 3)), 1, profile=True)
     e2e = None
-    if not args.no_e2e:
-        e2e_total, _, _ = timed(step_e2e, args.steps, max(1, args.warmup - 1))
-        e2e = 4.0 * E * T * world * args.steps / e2e_total
+    if do_e2e:
+        e2e_total, _, _ = timed(step_e2e, steps, max(1, warmup - 1))
+        e2e = 4.0 * E * T * world * steps / e2e_total
 
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
+        return None
     pk, pk_src = peaks()
-    value = 4.0 * E * T * world * args.steps / total
+    value = 4.0 * E * T * world * steps / total
     # roofline of the dominant kernels: the edge-MLP launches of the forward pass (category 0)
     spans = max(prof["spans"][0], 1)
     ms_per_layer = prof["ms"][0] / spans
@@ -581,55 +573,260 @@ def main():
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("%s_%s_h%d" % (args.workload, args.precision, H))
     except Exception:
         pass
-    roofline = {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer)", "achieved": achieved,
+    esz = 2 if args.precision == "bf16" and H in (64, 128, 256) else 4
+    roofline = {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer: ONE chained launch)", "achieved": achieved,
                 "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                 "peak_source": pk_src + " bf16 sustained", "algorithmic_flops_per_launch_group": alg,
                 "executed_flops_per_launch_group": executed_flops_edge_mlp(D, H, E) / 4.0,
                 "avg_ms_per_launch_group": ms_per_layer,
-                # the same launches against the HBM roofline (they are HBM-bound at H <= 256: H/2 FLOP per byte):
-                # algorithmic bytes = each of the two GEMMs reads and writes one bf16/fp32 [E,H] tensor
+                # the same launch against the HBM roofline: the chained kernel reads the previous layer's [E,H] edge state
+                # and writes this layer's (bf16), plus the first Linear's output when the backward needs it -- 3 passes
+                # in training, 2 in inference (layer 1 reads the [E,64] feature operand instead of an [E,H] tensor)
                 "hbm_view": (lambda nb: {"algorithmic_bytes_per_launch_group": nb,
                                          "achieved_gbs": nb / (ms_per_layer * 1e-3) / 1e9 if ms_per_layer > 0 else 0.0,
                                          "peak_gbs": pk.get("hbm_gbs"),
                                          "frac": (nb / (ms_per_layer * 1e-3) / 1e9) / pk["hbm_gbs"]
                                          if ms_per_layer > 0 and pk.get("hbm_gbs") else None})(
-                    4.0 * E * H * (2 if args.precision == "bf16" and H in (64, 128, 256) else 4))}
-    step_ms = total / args.steps * 1e3
-    share = {k: (prof["ms"][i] / args.steps) / step_ms for i, k in
+                    ((3.0 if train else 2.0) * E * H - (E * (H - 64)) / 4.0) * esz)}
+    # backward of the edge MLPs: data-gradient GEMMs (3 [E,H] passes each: dY, the saved pre-activation, dX; 7 of
+    # them + the layer-1 feature gradient + the top layer's elementwise pass) and weight-gradient GEMMs (2 passes each)
+    extra = {}
+    if train and prof["ms"][1] > 0:
+        nb = E * H * esz * (3.0 * 7 + 3.0) + E * (H * esz + 32 * 4)
+        ms = prof["ms"][1] / steps
+        extra["roofline_bwd"] = {"bound": "hbm", "kernel": "edge-MLP backward, data gradients (per step)", "unit": "GB/s",
+                                 "achieved": nb / (ms * 1e-3) / 1e9, "peak": pk.get("hbm_gbs"),
+                                 "frac": nb / (ms * 1e-3) / 1e9 / pk["hbm_gbs"] if pk.get("hbm_gbs") else None,
+                                 "algorithmic_bytes_per_step": nb, "ms_per_step": ms, "traffic": None}
+    if train and prof["ms"][2] > 0:
+        nb = E * H * esz * 2.0 * 7 + E * (H + 64) * esz
+        ms = prof["ms"][2] / steps
+        extra["roofline_wgrad"] = {"bound": "hbm", "kernel": "edge-MLP backward, weight gradients (per step)", "unit": "GB/s",
+                                   "achieved": nb / (ms * 1e-3) / 1e9, "peak": pk.get("hbm_gbs"),
+                                   "frac": nb / (ms * 1e-3) / 1e9 / pk["hbm_gbs"] if pk.get("hbm_gbs") else None,
+                                   "algorithmic_bytes_per_step": nb, "ms_per_step": ms, "traffic": None}
+    step_ms = total / steps * 1e3
+    share = {k: (prof["ms"][i] / steps) / step_ms for i, k in
              enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment_bwd", "edge_feat", "node", "segment_fwd"])} if train else None
     line = {"metric": "edge_messages_per_sec", "value": value, "unit": "edge-messages/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
+            "steps": steps, "warmup": warmup, "ms_per_step": step_ms, "higher_is_better": True,
+            "scaling": scaling, "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
             "data": "synthetic",
             "config": {"workload": cfg["name"], "num_dims": D, "particles_per_graph": N, "graphs_per_gpu": B,
                        "hidden": H, "mode": cfg["mode"] + (" (whole step replayed as one CUDA graph, static edge list)" if graphed is not None else ""),
                        "rollout_steps": T, "edges_per_gpu": E, "nodes_per_gpu": Nn,
                        "precision": args.precision, "parallelism": "dp%d" % world,
                        "l2": "flushed between steps" if small else "working set exceeds L2"},
-            "particle_steps_per_sec": Nn * T * world * args.steps / total,
+            "particle_steps_per_sec": Nn * T * world * steps / total,
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
             "roofline_hbm": hbm_rooflines(prof, D, H, E, Nn, args.precision == "bf16" and H in (64, 128, 256), pk),
             "time_share": share}
+    line.update(extra)
+    if share is not None:
+        share["other (loss, optimizer, caller prep, graph CSR, launch gaps)"] = max(0.0, 1.0 - sum(share.values()))
     if e2e is not None:
         h2d = sum(t.numel() * t.element_size() for t in host)
         line["e2e"] = {"value": e2e, "unit": "edge-messages/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4}
-    if not args.no_cpu_baseline:
+    if do_cpu:
+        # all host threads, 3 warm-up + >= 10 timed iterations (bounded by --cpu-seconds), median and
+        # min; then the same sample on ONE thread (2 iterations)
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         graphs = cpu_sample_graphs(cfg, H)
         cstep, e_step = cpu_step_sample(cfg, H, graphs)
-        cstep()
-        t0, it = time.perf_counter(), 0
-        while it < 2 or (time.perf_counter() - t0 < args.cpu_seconds and it < 50):
+        for _ in range(3):
             cstep()
-            it += 1
-        dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": 4.0 * e_step * it / dt, "unit": "edge-messages/s", "cores": cores, "kind": "port",
-                                "sample": "%d of %d graphs per step (%d edges), %d steps, %d host threads" %
-                                          (graphs, B, e_step, it, cores)}
-    print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+        ts, t_begin = [], time.perf_counter()
+        while len(ts) < 3 or (len(ts) < 10 and time.perf_counter() - t_begin < 2.5 * args.cpu_seconds) or \
+                (time.perf_counter() - t_begin < args.cpu_seconds and len(ts) < 50):
+            t0 = time.perf_counter()
+            cstep()
+            ts.append(time.perf_counter() - t0)
+        med = statistics.median(ts)
+        torch.set_num_threads(1)
+        t1 = []
+        for _ in range(2):
+            t0 = time.perf_counter()
+            cstep()
+            t1.append(time.perf_counter() - t0)
+        torch.set_num_threads(cores)
+        line["cpu_baseline"] = {"value": 4.0 * e_step / med, "unit": "edge-messages/s", "cores": cores, "kind": "port",
+                                "value_best": 4.0 * e_step / min(ts), "value_1_thread": 4.0 * e_step / min(t1),
+                                "sample": "%d of %d graphs per step (%d edges), median of %d steps after 3 warm-up, %d host "
+                                          "threads; 1-thread figure: best of 2 steps" % (graphs, B, e_step, len(ts), cores)}
+    return line
+
+def brief(line):
+    """The fields of a secondary measurement that go into the primary JSON line."""
+    if line is None:
+        return None
+    keep = ("value", "unit", "ms_per_step", "n_gpus", "steps", "scaling", "gpu_launches", "collectives_per_step",
+            "particle_steps_per_sec")
+    out = {k: line[k] for k in keep if k in line}
+    c = line["config"]
+    out["config"] = {k: c[k] for k in ("workload", "hidden", "graphs_per_gpu", "edges_per_gpu", "particles", "edges",
+                                       "edges_rank0", "parallelism", "mode", "rollout_steps") if k in c}
+    out["roofline_frac"] = line["roofline"]["frac"]
+    return out
+
+
+def gpu_eager_baseline(cfg, H, dev, graphs=32, iters=10):
+    """BASELINE.md 4, second baseline: the oracle port (plain eager PyTorch, index_add_ scatter, fp32) with its
+    parameters and inputs on the same GPU, same step definition (forward + MSE + backward + AdamW), on a sub-batch.
+    This is bench.py's baseline leg: the only place besides cpu_baseline that executes oracle/."""
+    from oracle import aether_oracle as O
+    D, N = cfg["D"], cfg["N"]
+    p = {k: v.to(dev).requires_grad_(True) for k, v in O.init_params(D, H, 1).items()}
+    x, v, q = [t.to(dev) for t in synth_inputs(cfg, [N] * graphs, 1)]
+    send, recv = [t.to(dev) for t in O.fc_edges(N, graphs)]
+    E = int(send.numel())
+    opt = torch.optim.AdamW(list(p.values()), lr=5e-4, weight_decay=1e-12)
+    target = x + 0.05
+
+    def step():
+        opt.zero_grad()
+        _, ea = O.caller_prep(x, v, q, send, recv)
+        out = O.aether_step(p, x, (send, recv), v, ea, q)
+        loss = torch.nn.functional.mse_loss(out, target)
+        loss.backward()
+        opt.step()
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step()
+        b.record()
+        torch.cuda.synchronize()
+        ms.append(a.elapsed_time(b))
+    med = statistics.median(ms)
+    return {"value": 4.0 * E / (med * 1e-3), "unit": "edge-messages/s", "ms_per_step_median": med, "ms_per_step_min": min(ms),
+            "kind": "port, eager PyTorch fp32 on the same GPU (device-timed, inputs resident)", "iterations": iters,
+            "sample": "%d of %d graphs per step (%d edges); the eager step keeps [E,3H] concatenations and every "
+                      "activation for autograd, which is what bounds the sub-batch" % (graphs, cfg["B"], E)}
+
+
+def parity_report(dev, precision):
+    """Errors against the oracle, reported next to the throughput (north_star: 'with rollout MSE reported'):
+    one train step at config 4's per-graph shape (2 graphs) and a 20-step rollout at config 1's shape."""
+    import aether_b200 as ab
+    from oracle import aether_oracle as O
+    out = {}
+    # --- config-4 shape, forward + all gradients
+    D, N, B, H = 2, 100, 2, 256
+    torch.manual_seed(1)
+    model = ab.Aether(2 * D, H, 0.0, D, device=dev, precision=precision)
+    p = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    x, v, q = O.synth_state(B, N, D, seed=1)
+    send, recv = ab.fc_edges(N, B, dev)
+    xc = x.to(dev).requires_grad_(True)
+    h, ea = ab.caller_prep(xc.detach(), v.to(dev), q.to(dev).reshape(-1), send, recv)
+    got = model(h, xc, [send, recv], v.to(dev), ea, q.to(dev))
+    torch.nn.functional.mse_loss(got, (x + 0.1).to(dev)).backward()
+    so, ro = O.fc_edges(N, B)
+    po = {k: t.clone().requires_grad_(True) for k, t in p.items()}
+    xo = x.clone().requires_grad_(True)
+    _, eo = O.caller_prep(x, v, q, so, ro)
+    want = O.aether_step(po, xo, (so, ro), v, eo, q)
+    torch.nn.functional.mse_loss(want, x + 0.1).backward()
+
+    def rl2(a, b):
+        return float((a.double() - b.double()).norm() / b.double().norm().clamp(min=1e-30))
+
+    def rmax(a, b):
+        return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp(min=1e-30))
+
+    grads = [(k, prm.grad.cpu(), po[k].grad) for k, prm in model.named_parameters()
+             if po[k].grad is not None and float(po[k].grad.abs().max()) > 0]
+    out["config4_shape_step"] = {
+        "shape": "D=2 N=100 B=2 H=256 %s, train step vs fp32 CPU oracle" % precision,
+        "out_rel_max": rmax(got.detach().cpu(), want.detach()), "displacement_rel_l2": rl2((got.detach().cpu() - x), (want.detach() - x)),
+        "grad_x_rel_l2": rl2(xc.grad.cpu(), xo.grad), "grad_w_rel_max_worst": max(rmax(a, b) for _, a, b in grads),
+        "grad_w_rel_l2_worst": max(rl2(a, b) for _, a, b in grads), "tolerance": 1e-5 if precision == "fp32" else 2e-2}
+    # --- config-1 shape, 20-step rollout
+    D, N, B, H, T = 2, 5, 16, 64, 20
+    torch.manual_seed(1)
+    model = ab.Aether(2 * D, H, 0.0, D, device=dev, precision=precision)
+    model.eval()
+    p = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    x, v, q = O.synth_state(B, N, D, seed=1)
+    send, recv = ab.fc_edges(N, B, dev)
+    traj = ab.rollout(model, x.to(dev), v.to(dev), q.to(dev).reshape(-1), T, edges=(send, recv)).cpu()
+    so, ro = O.fc_edges(N, B)
+    with torch.no_grad():
+        ref = O.rollout(p, x, v, q, lambda xx: (so, ro), T)
+    ref = torch.stack(list(ref)) if not torch.is_tensor(ref) else ref
+    n = min(traj.shape[0], ref.shape[0])
+    mse = [float(((traj[-n:][t] - ref[-n:][t]) ** 2).mean()) for t in range(n)]
+    out["config1_shape_rollout"] = {"shape": "D=2 N=5 B=16 H=64 %s, %d-step rollout vs fp32 CPU oracle" % (precision, T),
+                                    "mse_step_1": mse[0], "mse_step_last": mse[-1], "mse_mean": sum(mse) / len(mse),
+                                    "position_scale_rms": float((ref ** 2).mean().sqrt())}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))   # c5: see --workload c5 below
+    ap.add_argument("--hidden", type=int, default=0)
+    ap.add_argument("--batch", type=int, default=0, help="graphs per GPU (default: the workload's)")
+    ap.add_argument("--precision", default=os.environ.get("AETHER_B200_PRECISION", "bf16"), choices=["fp32", "bf16"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="default c4 run: skip the strong-scaling / config-5 / baseline legs")
+    ap.add_argument("--strong", action="store_true", help="c4: split the workload's batch over the ranks (strong scaling)")
+    ap.add_argument("--graph", action="store_true", help="capture the train step in a CUDA graph at any size")
+    ap.add_argument("--no-graph", action="store_true", help="small training shapes: do not capture the step in a CUDA graph")
+    args = ap.parse_args()
+    cfg = dict(WORKLOADS[args.workload])
+    H = args.hidden or cfg["H"]
+    if args.batch:
+        cfg["B"] = args.batch
+    if args.impl == "reference":
+        return run_reference(args, cfg, H)
+    ctx = Ctx()
+    default_run = args.workload == "c4" and not args.hidden and not args.batch and not args.strong
+    try:
+        if args.workload == "c5":
+            line = run_c5(args, cfg, H, ctx, args.steps, args.warmup, not args.no_e2e, not args.no_cpu_baseline)
+        elif args.strong:
+            cfg["B"] = max(1, cfg["B"] // ctx.world)
+            line = run_dp(args, cfg, H, ctx, args.steps, args.warmup, not args.no_e2e, not args.no_cpu_baseline, "strong")
+        else:
+            line = run_dp(args, cfg, H, ctx, args.steps, args.warmup, not args.no_e2e, not args.no_cpu_baseline, "weak")
+        if default_run and not args.no_secondary:
+            release_memory()
+            sec = {}
+            ssteps, swarm = max(3, min(args.steps, 10)), 3
+            if ctx.world > 1:
+                c4s = dict(WORKLOADS["c4"])
+                c4s["B"] = c4s["B"] // ctx.world
+                c4s["name"] = "config4 STRONG scaling: 1024 graphs in total, %d per GPU, train step" % c4s["B"]
+                sec["c4_strong"] = brief(run_dp(args, c4s, H, ctx, ssteps, swarm, False, False, "strong"))
+                release_memory()
+            for hh in (256, 64):
+                sec["c5_h%d" % hh] = brief(run_c5(args, dict(WORKLOADS["c5"]), hh, ctx, ssteps, swarm, False, False))
+                release_memory()
+            if ctx.rank == 0:
+                line["secondary"] = sec
+                if ctx.world == 1:
+                    try:
+                        line["gpu_eager_baseline"] = gpu_eager_baseline(WORKLOADS["c4"], H, ctx.dev)
+                    except Exception as e:          # an out-of-memory eager baseline must not lose the bench line
+                        line["gpu_eager_baseline"] = {"unavailable": repr(e)[:200]}
+                    release_memory()
+                    line["parity"] = parity_report(ctx.dev, args.precision)
+        if ctx.rank == 0:
+            print(json.dumps(line), flush=True)
+    finally:
+        ctx.close()
 
 
 if __name__ == "__main__":

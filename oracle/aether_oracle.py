@@ -260,8 +260,8 @@ def scatter_mean(src: Tensor, index: Tensor, n_rows: int) -> Tensor:
     the output as max(index)+1; the oracle always uses ``n_rows`` = Nn (superset,
     SURVEY.md 7.2 last bullet).
     """
-    out = torch.zeros(n_rows, src.shape[1], dtype=src.dtype).index_add_(0, index, src)
-    cnt = torch.zeros(n_rows, dtype=src.dtype).index_add_(0, index, torch.ones_like(index, dtype=src.dtype))
+    out = torch.zeros(n_rows, src.shape[1], dtype=src.dtype, device=src.device).index_add_(0, index, src)
+    cnt = torch.zeros(n_rows, dtype=src.dtype, device=src.device).index_add_(0, index, torch.ones_like(index, dtype=src.dtype))
     return out / cnt.clamp(min=1).unsqueeze(1)
 
 
