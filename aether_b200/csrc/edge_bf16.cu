@@ -24,7 +24,7 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&v)[8]) {
 template <int LPR, bool SILU, bool MEAN>
 __global__ void segreduce_bf16_kernel(int64_t Nn, const int32_t* __restrict__ ptr, const int32_t* __restrict__ list,
                                       const __nv_bfloat16* __restrict__ src, int64_t lds, const float* base,
-                                      int64_t ldb, float* y, int64_t ldy) {
+                                      int64_t ldb, float* y, int64_t ldy, __nv_bfloat16* y16, int64_t ldy16) {
   constexpr int G = 32 / LPR;
   const int64_t n = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -72,6 +72,9 @@ __global__ void segreduce_bf16_kernel(int64_t Nn, const int32_t* __restrict__ pt
     float4* po = reinterpret_cast<float4*>(y + (size_t)n * ldy + c);
     po[0] = make_float4(o[0], o[1], o[2], o[3]);
     po[1] = make_float4(o[4], o[5], o[6], o[7]);
+    if (y16)   // operand copy for the tensor-core node GEMM that consumes y
+      *reinterpret_cast<uint4*>(y16 + (size_t)n * ldy16 + c) = make_uint4(tc::pack_bf16(o[0], o[1]), tc::pack_bf16(o[2], o[3]),
+                                                                         tc::pack_bf16(o[4], o[5]), tc::pack_bf16(o[6], o[7]));
   }
 }
 
@@ -164,12 +167,13 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, int chunk
 
 template <bool SILU, bool MEAN>
 int launch_segreduce(int64_t Nn, int W, const int32_t* ptr, const int32_t* list, const __nv_bfloat16* src, int64_t lds,
-                     const float* base, int64_t ldb, float* y, int64_t ldy, cudaStream_t st) {
+                     const float* base, int64_t ldb, float* y, int64_t ldy, cudaStream_t st, __nv_bfloat16* y16 = nullptr,
+                     int64_t ldy16 = 0) {
   if (Nn <= 0) return 0;
   const unsigned blocks = (unsigned)((Nn * 32 + 255) / 256);
-  if (W == 256) segreduce_bf16_kernel<32, SILU, MEAN><<<blocks, 256, 0, st>>>(Nn, ptr, list, src, lds, base, ldb, y, ldy);
-  else if (W == 128) segreduce_bf16_kernel<16, SILU, MEAN><<<blocks, 256, 0, st>>>(Nn, ptr, list, src, lds, base, ldb, y, ldy);
-  else if (W == 64) segreduce_bf16_kernel<8, SILU, MEAN><<<blocks, 256, 0, st>>>(Nn, ptr, list, src, lds, base, ldb, y, ldy);
+  if (W == 256) segreduce_bf16_kernel<32, SILU, MEAN><<<blocks, 256, 0, st>>>(Nn, ptr, list, src, lds, base, ldb, y, ldy, y16, ldy16);
+  else if (W == 128) segreduce_bf16_kernel<16, SILU, MEAN><<<blocks, 256, 0, st>>>(Nn, ptr, list, src, lds, base, ldb, y, ldy, y16, ldy16);
+  else if (W == 64) segreduce_bf16_kernel<8, SILU, MEAN><<<blocks, 256, 0, st>>>(Nn, ptr, list, src, lds, base, ldb, y, ldy, y16, ldy16);
   else return AETHER_E_UNSUPPORTED;
   AE_LAUNCH_CHECK();
   return 0;
@@ -178,8 +182,9 @@ int launch_segreduce(int64_t Nn, int W, const int32_t* ptr, const int32_t* list,
 }  // namespace
 
 int launch_segmean_silu_bf16(int64_t Nn, int H, const int32_t* rowptr, const void* src, int64_t lds, const float* base,
-                             int64_t ldb, float* y, int64_t ldy, cudaStream_t st) {
-  return launch_segreduce<true, true>(Nn, H, rowptr, nullptr, (const __nv_bfloat16*)src, lds, base, ldb, y, ldy, st);
+                             int64_t ldb, float* y, int64_t ldy, cudaStream_t st, void* y16, int64_t ldy16) {
+  return launch_segreduce<true, true>(Nn, H, rowptr, nullptr, (const __nv_bfloat16*)src, lds, base, ldb, y, ldy, st,
+                                      (__nv_bfloat16*)y16, ldy16);
 }
 
 int launch_segsum_bf16(int64_t Nn, int W, const int32_t* ptr, const int32_t* list, const void* src, int64_t lds,

@@ -51,6 +51,9 @@ struct Workspace {
   void* feat16; void *bpre1[5], *bpre2[5]; void *wpA[5], *wpB[5];
   void *na16, *nwp;     // node-level tensor-core scratch: bf16 operand copy [Nn,256], weight image
   void* pspr16;         // [Nn, 2H] bf16 node terms P_s | P_r of the factorised first Linear
+  // node update on the chained kernel: bf16 operand copies y_l, x_l [Nn,H], pre3_l [Nn,2H] and the packed images of
+  // W3 / W4 (two H x H halves each) and of the next layer's W_s, W_r
+  void *y16[5], *x16[5], *pre316[5], *nw3[5][2], *nw4[5][2], *nws[5], *nwr[5];
   size_t bytes;
 };
 
@@ -67,7 +70,11 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
   w.x0 = c.f(Nn * 3 * D);
   w.pre1[0] = w.pre2[0] = nullptr;
   w.feat = nullptr; w.feat16 = nullptr; w.na16 = w.nwp = w.pspr16 = nullptr;
-  for (int l = 0; l <= 4; ++l) { w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr; }
+  for (int l = 0; l <= 4; ++l) {
+    w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr;
+    w.y16[l] = w.x16[l] = w.pre316[l] = w.nws[l] = w.nwr[l] = nullptr;
+    w.nw3[l][0] = w.nw3[l][1] = w.nw4[l][0] = w.nw4[l][1] = nullptr;
+  }
   if (use_tc(d, flags)) {
     w.na16 = c.b(Nn * 256 * 2);
     w.nwp = c.b(tc_weight_pack_bytes(256, 256));
@@ -82,6 +89,11 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
       for (int l = 1; l <= 4; ++l) { w.bpre1[l] = p1; w.bpre2[l] = (l & 1) ? a : b; }
     }
     for (int l = 1; l <= 4; ++l) { w.wpA[l] = c.b(tc_weight_pack_bytes(l == 1 ? 64 : H, H)); w.wpB[l] = c.b(tc_weight_pack_bytes(H, H)); }
+    for (int l = 1; l <= 4; ++l) {
+      w.y16[l] = c.b(Nn * H * 2); w.x16[l] = c.b(Nn * H * 2); w.pre316[l] = c.b(Nn * 2 * H * 2);
+      for (int h = 0; h < 2; ++h) { w.nw3[l][h] = c.b(tc_weight_pack_bytes(H, H)); w.nw4[l][h] = c.b(tc_weight_pack_bytes(H, H)); }
+      w.nws[l] = c.b(tc_weight_pack_bytes(H, H)); w.nwr[l] = c.b(tc_weight_pack_bytes(H, H));
+    }
   } else {
   w.feat = c.f(E * edge_feat_ld(d.num_dims));
   if (save) {
@@ -112,6 +124,7 @@ struct Scratch {
   // bf16 path: edge gradients [E,H] bf16 (ge, g2, g1), transposed weight images
   void *bg2, *bg1, *gyd16; void *wtA, *wtB;   // gyd16: [Nn,H] bf16 = gy / in-degree
   void *na16, *ng16, *nwp;
+  void* gpre316;        // [Nn, 2H] bf16 gradient of the node update's hidden layer
   size_t bytes;
 };
 
@@ -149,9 +162,10 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
   s.gA = s.gB = nullptr;
   s.bg2 = s.bg1 = s.gyd16 = s.wtA = s.wtB = nullptr;
-  s.na16 = s.ng16 = s.nwp = nullptr;
+  s.na16 = s.ng16 = s.nwp = nullptr; s.gpre316 = nullptr;
   if (use_tc(d, flags)) {
     s.na16 = c.b(Nn * 256 * 2); s.ng16 = c.b(Nn * 256 * 2); s.nwp = c.b(tc_weight_pack_bytes(256, 256));
+    s.gpre316 = c.b(Nn * 2 * H * 2);
     s.bg2 = c.b(E * H * 2); s.bg1 = c.b(E * H * 2); s.gyd16 = c.b(Nn * H * 2);
     s.wtA = c.b(tc_weight_pack_bytes(H, H)); s.wtB = c.b(tc_weight_pack_bytes(H, H));
     s.gfeat = c.f(E * 32);
@@ -312,15 +326,46 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
                       nullptr, nullptr, 0, st));
       base = y;
     }
+    const bool node_chain = bf16 && use_chain();
+    __nv_bfloat16* y16 = node_chain ? (__nv_bfloat16*)w.y16[l] + (size_t)n0 * H : nullptr;
     {
       ProfScope ps(PROF_SEGMEAN_FWD, st);
-      if (bf16) AE_CHECK(launch_segmean_silu_bf16(M, H, G.rowptr + n0, w.bpre2[l], H, base, H, y, H, st));
+      if (bf16) AE_CHECK(launch_segmean_silu_bf16(M, H, G.rowptr + n0, w.bpre2[l], H, base, H, y, H, st, y16, H));
       else AE_CHECK(launch_segmean_silu(M, H, G.rowptr + n0, w.pre2[l], H, base, H, y, H, st));
     }
     // x = y + W4 silu(W3 y + b3) + b4   (locs.py:241)
     ProfScope pn(PROF_NODE, st);
     float* pre3 = w.pre3[l] + (size_t)n0 * 2 * H;
     float* xo = w.xl[l] + (size_t)n0 * H;
+    if (node_chain) {
+      // the update MLP is GEMM -> SiLU -> GEMM like the edge MLP: two launches of the chained kernel, one per half of the
+      // 2H-wide hidden layer (x = y + b4 + silu(pre3_a) W4a^T + silu(pre3_b) W4b^T), fp32 residual output, bf16 copies of
+      // pre3 (backward) and x (operand of the next layer's node terms) written by the epilogues
+      __nv_bfloat16* p316 = (__nv_bfloat16*)w.pre316[l] + (size_t)n0 * 2 * H;
+      __nv_bfloat16* x16 = (__nv_bfloat16*)w.x16[l] + (size_t)n0 * H;
+      for (int h = 0; h < 2; ++h) {
+        AE_CHECK(tc_pack_weight(P[s.u0w] + (size_t)h * H * H, H, H, H, H, H, 0, 0, w.nw3[l][h], st));
+        AE_CHECK(tc_pack_weight(P[s.u2w] + (size_t)h * H, 2 * H, H, H, H, H, 0, 0, w.nw4[l][h], st));
+        TcChainArgs c;
+        c.M = M; c.wpack1 = w.nw3[l][h]; c.wpack2 = w.nw4[l][h]; c.bias1 = P[s.u0b] + h * H; c.bias2 = h == 0 ? P[s.u2b] : nullptr;
+        c.out1 = (flags & AETHER_F_SAVE_FOR_BACKWARD) ? p316 + h * H : nullptr; c.ldo1 = 2 * H;
+        c.out2_f32 = xo; c.ldo2f = H; c.res = h == 0 ? y : xo; c.ldr = H;
+        if (h == 1) { c.copy16 = x16; c.ldc16 = H; }
+        AE_CHECK(tc_chain(c, y16, H, H, H, TC_TF_NONE, st));
+      }
+      if (l < 4) {
+        const LayerSlots sn = layer_slots(l + 1);
+        AE_CHECK(tc_pack_weight(P[sn.m0w], 3 * H, H, H, H, H, 0, 0, w.nws[l], st));
+        AE_CHECK(tc_pack_weight(P[sn.m0w] + H, 3 * H, H, H, H, H, 0, 0, w.nwr[l], st));
+        TcGemmArgs a;
+        a.M = M; a.wpack = w.nws[l]; a.out_bf16 = ps16o + (size_t)n0 * H; a.ldo = H;
+        AE_CHECK(tc_gemm(a, x16, H, H, H, TC_TF_NONE, st));
+        TcGemmArgs b;
+        b.M = M; b.wpack = w.nwr[l]; b.out_bf16 = pr16 + (size_t)n0 * H; b.ldo = H;
+        AE_CHECK(tc_gemm(b, x16, H, H, H, TC_TF_NONE, st));
+      }
+      continue;
+    }
     AE_CHECK(linear(nc, y, H, M, H, P[s.u0w], H, P[s.u0b], 2 * H, pre3, 2 * H, TF_NONE, nullptr, nullptr, 0, st));
     AE_CHECK(linear(nc, pre3, 2 * H, M, 2 * H, P[s.u2w], 2 * H, P[s.u2b], H, xo, H, TF_SILU, nullptr, y, H, st));
     if (l < 4) {

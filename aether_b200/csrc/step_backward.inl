@@ -139,9 +139,38 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   pn.reset();
 
   // node part A of layer l: x_l = y + W4 silu(pre3) + b4 ; pre3 = W3 y + b3   (gx -> s.gy)
+  void* gpre316 = s.gpre316;
   auto node_update_bwd = [&](int l) -> int {
     ProfScope pn(PROF_NODE, st);
     const LayerSlots sl = layer_slots(l);
+    if (tc && use_chain()) {
+      // bf16 operands throughout (forward kept y_l and pre3_l as bf16, tc_chain.cu): no conversion passes except gx
+      const __nv_bfloat16* p316 = (const __nv_bfloat16*)w.pre316[l];
+      const __nv_bfloat16* y16 = (const __nv_bfloat16*)w.y16[l];
+      __nv_bfloat16* g316 = (__nv_bfloat16*)gpre316;
+      AE_CHECK(tc_convert_bf16(gx, H, Nn, H, TF_NONE, nullptr, s.na16, H, st));
+      for (int h = 0; h < 2; ++h) {
+        // dW4[:, half] = gx^T silu(pre3[:, half]) ; db4 = colsum(gx)
+        AE_CHECK(tc_wgrad(s.na16, H, H, p316 + h * H, 2 * H, H, TC_TF_SILU, Nn, G[sl.u2w] + h * H, 2 * H, H, 0,
+                          h == 0 ? G[sl.u2b] : nullptr, s.partial, s.partial_floats, st));
+        // gpre3[:, half] = (gx W4[:, half]) * silu'(pre3[:, half])
+        AE_CHECK(tc_pack_weight(P[sl.u2w] + h * H, 2 * H, H, H, H, H, 1, 0, s.nwp, st));
+        TcGemmArgs a;
+        a.M = Nn; a.wpack = s.nwp; a.dsilu = p316 + h * H; a.ldd = 2 * H; a.out_bf16 = g316 + h * H; a.ldo = 2 * H;
+        AE_CHECK(tc_gemm(a, s.na16, H, H, H, TC_TF_NONE, st));
+      }
+      for (int h = 0; h < 2; ++h) {
+        // dW3[half, :] = gpre3[:, half]^T y ; db3[half] = colsum
+        AE_CHECK(tc_wgrad(g316 + h * H, 2 * H, H, y16, H, H, TC_TF_NONE, Nn, G[sl.u0w] + (size_t)h * H * H, H, H, 0,
+                          G[sl.u0b] + h * H, s.partial, s.partial_floats, st));
+        // gy = gx + gpre3 W3   (two K halves, the second accumulates)
+        AE_CHECK(tc_pack_weight(P[sl.u0w] + (size_t)h * H * H, H, H, H, H, H, 1, 0, s.nwp, st));
+        TcGemmArgs a;
+        a.M = Nn; a.wpack = s.nwp; a.res = h == 0 ? gx : s.gy; a.ldr = H; a.out_f32 = s.gy; a.ldo32 = H; a.n_valid = H;
+        AE_CHECK(tc_gemm(a, g316 + h * H, 2 * H, H, H, TC_TF_NONE, st));
+      }
+      return 0;
+    }
     AE_CHECK(b.wgrad(gx, H, Nn, H, w.pre3[l], 2 * H, 2 * H, TF_SILU, nullptr, G[sl.u2w], 2 * H, G[sl.u2b]));
     AE_CHECK(b.dgrad(gx, H, Nn, H, P[sl.u2w], 2 * H, 2 * H, s.gpre3, 2 * H, w.pre3[l], nullptr, nullptr, 0));
     AE_CHECK(b.wgrad(s.gpre3, 2 * H, Nn, 2 * H, w.y[l], H, H, TF_NONE, nullptr, G[sl.u0w], H, G[sl.u0b]));

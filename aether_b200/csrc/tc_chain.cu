@@ -67,7 +67,7 @@ __host__ __device__ constexpr int smem_bytes(int K1, int H) {
   return w1_bytes(K1, H) + w2_bytes(H) + num_slots(K1, H) * kSlotBytes + kStageBytes + misc_bytes(H);
 }
 
-template <int K1, int H, int TF1, bool SAVE, bool GATHER>
+template <int K1, int H, int TF1, bool SAVE, bool GATHER, bool OUT32>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmO1,
                 const __grid_constant__ CUtensorMap tmO2, TcChainArgs g) {
@@ -131,7 +131,7 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp == kWarpMma) tmem_alloc_2cta(tmem_slot, TMEM_COLS);
   if (warp == kWarpTma && lane == 0) {
     tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmO2);
+    if (!OUT32) tma_prefetch_desc(&tmO2);
     if (SAVE) tma_prefetch_desc(&tmO1);
     // this CTA's half of the rows of every 64-wide K chunk of both images
     mbar_arrive_expect_tx(bar_w, w1_bytes(K1, H) + w2_bytes(H));
@@ -364,6 +364,49 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const float4 t4 = *reinterpret_cast<const float4*>(sb2 + c0 + 4 * q);
             bv[2 * q] = f2_make(t4.x, t4.y); bv[2 * q + 1] = f2_make(t4.z, t4.w);
           }
+          if (OUT32) {
+            // fp32 output: the chunk (+ bias) goes through the warp's staging as a swizzled 32x32 fp32 tile and is read
+            // back row-major, so the residual load and the store are 512 contiguous bytes per instruction
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // epilogue 1's pre1 boxes
+            __syncwarp();
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const f32x2 a0 = f2_add(f2_make_u(r[4 * q], r[4 * q + 1]), bv[2 * q]);
+              const f32x2 a1 = f2_add(f2_make_u(r[4 * q + 2], r[4 * q + 3]), bv[2 * q + 1]);
+              const uint32_t addr = sbuf + lane * 128 + ((q ^ (lane & 7)) << 4);
+              asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "f"(f2_lo(a0)), "f"(f2_hi(a0)),
+                           "f"(f2_lo(a1)), "f"(f2_hi(a1)) : "memory");
+            }
+            if (kk + 1 < CPW) {
+              tmem_ld32(lane_base + H + c0 + 64, r);
+            } else {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(acc2e0);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int i = it * 32 + lane, rr = i >> 3, ch = i & 7;
+              const int64_t grow = row0 + rr;
+              const int col = c0 + ch * 4;
+              float4 v;
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                           : "r"(sbuf + rr * 128 + ((ch ^ (rr & 7)) << 4)) : "memory");
+              if (grow < g.M) {
+                if (g.res) {
+                  const float4 a = *reinterpret_cast<const float4*>(g.res + (size_t)grow * g.ldr + col);
+                  v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+                }
+                *reinterpret_cast<float4*>(g.out2_f32 + (size_t)grow * g.ldo2f + col) = v;
+                if (g.copy16)
+                  *reinterpret_cast<uint2*>(g.copy16 + (size_t)grow * g.ldc16 + col) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+              }
+            }
+            __syncwarp();
+            continue;
+          }
           if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
           tmem_ld_wait();
@@ -405,11 +448,11 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
 }
 
-template <int K1, int H, int TF1, bool SAVE, bool GATHER>
+template <int K1, int H, int TF1, bool SAVE, bool GATHER, bool OUT32>
 int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, cudaStream_t st) {
   constexpr int smem = smem_bytes(K1, H);
   static_assert(smem <= kSmemMax, "shared memory budget");
-  auto kern = tc_chain_kernel<K1, H, TF1, SAVE, GATHER>;
+  auto kern = tc_chain_kernel<K1, H, TF1, SAVE, GATHER, OUT32>;
   static int max_clusters = 0;                     // co-resident CTA pairs (one per TPC): 74 on a full B200
   if (max_clusters == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -438,8 +481,18 @@ template <int K1, int H, int TF1>
 int launch_tf(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, bool save,
               cudaStream_t st) {
   const bool gather = g.gat16 != nullptr;
-  if (save) return gather ? launch_chain<K1, H, TF1, true, true>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, true, false>(g, ta, t1, t2, st);
-  return gather ? launch_chain<K1, H, TF1, false, true>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, false, false>(g, ta, t1, t2, st);
+  if (g.out2_f32) {
+    // node update: fp32 output with residual, no gather, plain (already activated / linear) operand
+    if constexpr (K1 == H && TF1 == TC_TF_NONE) {
+      if (gather) return AETHER_E_UNSUPPORTED;
+      return save ? launch_chain<K1, H, TF1, true, false, true>(g, ta, t1, t2, st)
+                  : launch_chain<K1, H, TF1, false, false, true>(g, ta, t1, t2, st);
+    } else {
+      return AETHER_E_UNSUPPORTED;
+    }
+  }
+  if (save) return gather ? launch_chain<K1, H, TF1, true, true, false>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, true, false, false>(g, ta, t1, t2, st);
+  return gather ? launch_chain<K1, H, TF1, false, true, false>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, false, false, false>(g, ta, t1, t2, st);
 }
 
 template <int K1, int H>
@@ -458,14 +511,16 @@ bool tc_chain_supported(int K1, int H) {
 int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, int tf1, cudaStream_t st) {
   if (g.M <= 0) return 0;
   if (!tc_chain_supported(K1, H)) return AETHER_E_UNSUPPORTED;
-  if (!g.wpack1 || !g.wpack2 || !g.out2) return AETHER_E_BADARG;
+  if (!g.wpack1 || !g.wpack2 || ((g.out2 != nullptr) == (g.out2_f32 != nullptr))) return AETHER_E_BADARG;
+  if (g.out2_f32 && ((g.ldo2f & 3) || (g.res && (g.ldr & 3)) || (g.copy16 && (g.ldc16 & 3)))) return AETHER_E_BADARG;
   if (g.gat16 && (!g.idx_a || !g.idx_b)) return AETHER_E_BADARG;
   const bool save = g.out1 != nullptr;
   CUtensorMap ta, t1, t2;
   memset(&t1, 0, sizeof(t1));
   AE_CHECK(tc_make_tmap_bf16(&ta, A, g.M, K1, lda, kTileM));
   if (save) AE_CHECK(tc_make_tmap_bf16(&t1, g.out1, g.M, H, g.ldo1, 32, 32));
-  AE_CHECK(tc_make_tmap_bf16(&t2, g.out2, g.M, H, g.ldo2, 32, 32));
+  memset(&t2, 0, sizeof(t2));
+  if (g.out2) AE_CHECK(tc_make_tmap_bf16(&t2, g.out2, g.M, H, g.ldo2, 32, 32));
 #define AE_CH_CASE(KK, HH) if (K1 == KK && H == HH) return launch_kh<KK, HH>(g, ta, t1, t2, tf1, save, st);
   AE_CH_CASE(256, 256) AE_CH_CASE(64, 256) AE_CH_CASE(128, 128) AE_CH_CASE(64, 128) AE_CH_CASE(64, 64)
 #undef AE_CH_CASE

@@ -45,6 +45,12 @@ struct TcChainArgs {
   const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int64_t goff_b = 0;
   __nv_bfloat16* out1 = nullptr; int64_t ldo1 = 0;
   __nv_bfloat16* out2 = nullptr; int64_t ldo2 = 0;
+  // fp32 second output instead of out2 (node update x = y + W4 silu(W3 y + b3) + b4, locs.py:241):
+  //   out2_f32[m][n] = acc2 + b2[n] + res[m][n]  (res may alias out2_f32: accumulation over K halves), and
+  //   optionally the same value rounded to bf16 in copy16 (operand of the next tensor-core GEMM)
+  float* out2_f32 = nullptr; int64_t ldo2f = 0;
+  const float* res = nullptr; int64_t ldr = 0;
+  __nv_bfloat16* copy16 = nullptr; int64_t ldc16 = 0;
 };
 bool tc_chain_supported(int K1, int H);
 int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, int tf1, cudaStream_t st);
