@@ -244,6 +244,8 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint4 gs[CPW][4], gr[CPW][4];
     int ia = 0, ib = 0, ia_n = 0, ib_n = 0;
     auto request = [&](uint4 (&ds)[4], uint4 (&dr)[4], int ia_, int ib_, int c) {
+      // 128-bit loads: the 256-bit form (ld.global.nc.v8.b32) measured the same on contiguous senders and 16 % slower
+      // on random ones (profiles/r02_chain_bench_v3.txt)
       const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
       const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
 #pragma unroll
@@ -299,11 +301,16 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = f2_add(f2_make_u(r[2 * i], r[2 * i + 1]), bv[i]);
         } else {
+          if (has_b1) {      // the step folds b1 into P_r (node GEMM bias), so the gather variant normally has none
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 t4 = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * q);
-            v[2 * q] = f2_add(f2_make_u(r[4 * q], r[4 * q + 1]), f2_make(t4.x, t4.y));
-            v[2 * q + 1] = f2_add(f2_make_u(r[4 * q + 2], r[4 * q + 3]), f2_make(t4.z, t4.w));
+            for (int q = 0; q < 8; ++q) {
+              const float4 t4 = *reinterpret_cast<const float4*>(sb1 + c0 + 4 * q);
+              v[2 * q] = f2_add(f2_make_u(r[4 * q], r[4 * q + 1]), f2_make(t4.x, t4.y));
+              v[2 * q + 1] = f2_add(f2_make_u(r[4 * q + 2], r[4 * q + 3]), f2_make(t4.z, t4.w));
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = f2_make_u(r[2 * i], r[2 * i + 1]);
           }
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -514,6 +521,7 @@ int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, in
   if (!g.wpack1 || !g.wpack2 || ((g.out2 != nullptr) == (g.out2_f32 != nullptr))) return AETHER_E_BADARG;
   if (g.out2_f32 && ((g.ldo2f & 3) || (g.res && (g.ldr & 3)) || (g.copy16 && (g.ldc16 & 3)))) return AETHER_E_BADARG;
   if (g.gat16 && (!g.idx_a || !g.idx_b)) return AETHER_E_BADARG;
+  if (g.gat16 && (((uintptr_t)g.gat16 & 15) || (g.ldg & 7) || (g.goff_b & 7))) return AETHER_E_BADARG;   // 128-bit row loads
   const bool save = g.out1 != nullptr;
   CUtensorMap ta, t1, t2;
   memset(&t1, 0, sizeof(t1));

@@ -82,6 +82,13 @@ __device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, u
                :: "r"(smem_dst), "l"(gsrc), "r"(bytes), "r"(bar) : "memory");
 }
 
+// 256-bit read-only global load (sm_100): 32 bytes per lane and instruction.  Row-per-thread operand loads touch one
+// line per lane whatever the width, so the wider load halves the L1 wavefronts per byte (p 32-byte aligned).
+__device__ __forceinline__ void ldg256(const void* p, uint4& a, uint4& b) {
+  asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p));
+}
+
 // ---- TMEM ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_result, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_result), "r"(ncols) : "memory");
