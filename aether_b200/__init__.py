@@ -7,6 +7,7 @@ Public surface (mirrors the reference's nn/state2state/aether.py):
     fc_edges, knn_edges, KnnPlan, caller_prep   the reference's edge builders / caller prep on device
     Rollout, rollout    multi-step rollouts (optionally CUDA-graph captured)
     radius_graph        cell-list radius / kNN graph for large single scenes
+    FusedAdamW          torch.optim.AdamW semantics, all parameter tensors in one launch (csrc/optim.cu)
     PartitionedRollout  receiver-partitioned rollout of one large scene across GPUs (aether_b200.dist for the plan)
 Everything computes through aether_b200/lib/libaether_b200.so; there is no CPU or ATen fallback.
 """
@@ -15,7 +16,8 @@ from .locs import LoCS  # noqa: F401
 from .graph import KnnPlan, PreparedGraph, caller_prep, fc_edges, knn_edges, radius_graph  # noqa: F401
 from .partition import PartitionedRollout  # noqa: F401
 from .train import GraphedTrainStep  # noqa: F401
+from .optim import FusedAdamW  # noqa: F401
 from .rollout import Rollout, rollout  # noqa: F401
 
 __all__ = ["Aether", "LoCS", "PreparedGraph", "KnnPlan", "fc_edges", "knn_edges", "caller_prep", "Rollout", "rollout", "radius_graph",
-           "PartitionedRollout", "GraphedTrainStep"]
+           "PartitionedRollout", "GraphedTrainStep", "FusedAdamW"]

@@ -60,6 +60,14 @@ SIGNATURES = {
     "aether_launch_count": (ctypes.c_uint64, []),
     "aether_profile_enable": (c_int, [c_int]),
     "aether_profile_collect": (c_int, [POINTER(ctypes.c_double), POINTER(c_int64), c_int32]),
+    "aether_dynfield_workspace_bytes": (c_size_t, [c_int32, c_int64, c_int32]),
+    "aether_dynfield_scratch_bytes": (c_size_t, [c_int32, c_int64, c_int32]),
+    "aether_dynfield_forward": (c_int, [c_int32, c_int64, c_int32, POINTER(c_void_p), c_void_p, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_size_t, c_void_p]),
+    "aether_dynfield_backward": (c_int, [c_int32, c_int64, c_int32, POINTER(c_void_p), c_void_p, c_void_p, POINTER(c_void_p),
+                                         c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
+    "aether_adamw_step": (c_int, [c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
+                                  POINTER(c_int64), c_void_p, c_float, c_float, c_float, c_float, c_float, c_void_p]),
     "aether_dbg_tc_gemm": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_int64, c_int32, c_int32, c_int32,
                                    c_int32, c_int32, c_int32, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),

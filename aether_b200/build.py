@@ -39,6 +39,8 @@ SOURCES = [
     ("tc_abi.cu", []),
     ("edge_bf16.cu", []),
     ("prof.cu", []),
+    ("optim.cu", []),
+    ("dynfield.cu", []),
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),
 ]

@@ -54,6 +54,8 @@ struct Workspace {
   // node update on the chained kernel: bf16 operand copies y_l, x_l [Nn,H], pre3_l [Nn,2H] and the packed images of
   // W3 / W4 (two H x H halves each) and of the next layer's W_s, W_r
   void *y16[5], *x16[5], *pre316[5], *nw3[5][2], *nw4[5][2], *nws[5], *nwr[5];
+  // transposed images for the backward (packed by the forward's single batched launch when it saves for backward)
+  void *wtA[5], *wtB[5], *nt3[5][2], *nt4[5][2];
   size_t bytes;
 };
 
@@ -74,6 +76,7 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
     w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr;
     w.y16[l] = w.x16[l] = w.pre316[l] = w.nws[l] = w.nwr[l] = nullptr;
     w.nw3[l][0] = w.nw3[l][1] = w.nw4[l][0] = w.nw4[l][1] = nullptr;
+    w.wtA[l] = w.wtB[l] = w.nt3[l][0] = w.nt3[l][1] = w.nt4[l][0] = w.nt4[l][1] = nullptr;
   }
   if (use_tc(d, flags)) {
     w.na16 = c.b(Nn * 256 * 2);
@@ -93,6 +96,12 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
       w.y16[l] = c.b(Nn * H * 2); w.x16[l] = c.b(Nn * H * 2); w.pre316[l] = c.b(Nn * 2 * H * 2);
       for (int h = 0; h < 2; ++h) { w.nw3[l][h] = c.b(tc_weight_pack_bytes(H, H)); w.nw4[l][h] = c.b(tc_weight_pack_bytes(H, H)); }
       w.nws[l] = c.b(tc_weight_pack_bytes(H, H)); w.nwr[l] = c.b(tc_weight_pack_bytes(H, H));
+    }
+    if (save) {
+      for (int l = 1; l <= 4; ++l) {
+        w.wtA[l] = c.b(tc_weight_pack_bytes(H, H)); w.wtB[l] = c.b(tc_weight_pack_bytes(H, H));
+        for (int h = 0; h < 2; ++h) { w.nt3[l][h] = c.b(tc_weight_pack_bytes(H, H)); w.nt4[l][h] = c.b(tc_weight_pack_bytes(H, H)); }
+      }
     }
   } else {
   w.feat = c.f(E * edge_feat_ld(d.num_dims));
@@ -224,6 +233,45 @@ int linear(const NodeTc& nc, const float* A, int64_t lda, int64_t M, int K, cons
 //   p < 3 -- the node terms of the next layer: P_s[owned] into the exchange buffer (all-gathered by the caller
 //   before the next phase), P_r[owned] locally.  Phase 0 starts with field / frames (all nodes: senders need them)
 //   and the edge features; phase 3 ends with the out MLP, the rotation back and the Euler update of the owned rows.
+// Every bf16 weight image of the step in ONE launch: forward (edge + node), and -- when the backward follows --
+// the transposed ones, so that neither pass packs per GEMM (f4: images are built once per step, from the parameters
+// the optimizer last wrote).
+int pack_step_weights(const AetherDims& d, const float* const* P, const Workspace& w, uint32_t flags, cudaStream_t st) {
+  const int H = d.hidden, Fe = num_edge_feat(d.num_dims);
+  TcPackJob jobs[TC_PACK_MAX_JOBS];
+  int n = 0;
+  auto add = [&](const float* W, int ldw, int N, int K, int nv, int kv, int tr, int kmod, void* out) {
+    TcPackJob j; j.W = W; j.out = out; j.ldw = ldw; j.N = N; j.K = K; j.n_valid = nv; j.k_valid = kv;
+    j.transpose = (int16_t)tr; j.kmod = (int16_t)kmod; jobs[n++] = j;
+  };
+  const bool save = flags & AETHER_F_SAVE_FOR_BACKWARD;
+  add(P[P_L1_M0_W], Fe, H, 64, H, Fe, 0, 32, w.wpA[1]);   // layer 1: the feature columns repeated for the hi | lo halves
+  for (int l = 1; l <= 4; ++l) {
+    const LayerSlots s = layer_slots(l);
+    if (l > 1) add(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 0, 0, w.wpA[l]);
+    add(P[s.m2w], H, H, H, H, H, 0, 0, w.wpB[l]);
+    for (int h = 0; h < 2; ++h) {
+      add(P[s.u0w] + (size_t)h * H * H, H, H, H, H, H, 0, 0, w.nw3[l][h]);
+      add(P[s.u2w] + (size_t)h * H, 2 * H, H, H, H, H, 0, 0, w.nw4[l][h]);
+    }
+    if (l < 4) {
+      const LayerSlots sn = layer_slots(l + 1);
+      add(P[sn.m0w], 3 * H, H, H, H, H, 0, 0, w.nws[l]);
+      add(P[sn.m0w] + H, 3 * H, H, H, H, H, 0, 0, w.nwr[l]);
+    }
+    if (save) {
+      add(P[s.m2w], H, H, H, H, H, 1, 0, w.wtB[l]);
+      if (l > 1) add(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, w.wtA[l]);
+      else add(P[s.m0w], Fe, 32, H, Fe, H, 1, 0, w.wtA[1]);          // gfeat[E,32] = g1 W1 (fp32 output)
+      for (int h = 0; h < 2; ++h) {
+        add(P[s.u2w] + (size_t)h * H, 2 * H, H, H, H, H, 1, 0, w.nt4[l][h]);
+        add(P[s.u0w] + (size_t)h * H * H, H, H, H, H, H, 1, 0, w.nt3[l][h]);
+      }
+    }
+  }
+  return tc_pack_weights_batched(jobs, n, st);
+}
+
 struct Part {
   int64_t n0 = 0, n1 = -1;      // owned node rows [n0, n1); n1 < 0: all
   int phase_lo = 0, phase_hi = 3;
@@ -249,7 +297,12 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
   __nv_bfloat16* pr16 = (__nv_bfloat16*)w.pspr16 + (size_t)Nn * H;
   if (pt.phase_lo == 0) {
     // neural field at the particles (aether.py:127-134)
-    {
+    if (flags & AETHER_F_EXTERNAL_FIELD) {
+      // DynamicFieldAether: the field comes from the latent field network (dynfield.cu)
+      ProfScope pn(PROF_NODE, st);
+      AE_CHECK((int)cudaMemcpyAsync(w.f, P[P_F0_W], (size_t)Nn * D * sizeof(float), cudaMemcpyDeviceToDevice, st));
+      AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
+    } else {
     ProfScope pn(PROF_NODE, st);
     AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
     AE_CHECK(linear(nc, w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
@@ -265,15 +318,8 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       else AE_CHECK(launch_edge_features(D, E, G.send, G.recv, G.perm, x, vel, w.f, w.R, w.x0, orig, w.feat, ldf, st));
     }
     if (bf16) {
-      // bf16 shared-memory images of the edge-MLP weights (first Linear: per-edge block only; layer 1: the
-      // feature columns repeated for the hi and lo halves of the operand)
       ProfScope pn(PROF_NODE, st);
-      AE_CHECK(tc_pack_weight(P[P_L1_M0_W], Fe, H, 64, H, Fe, 0, 32, w.wpA[1], st));
-      for (int l = 1; l <= 4; ++l) {
-        const LayerSlots s = layer_slots(l);
-        if (l > 1) AE_CHECK(tc_pack_weight(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 0, 0, w.wpA[l], st));
-        AE_CHECK(tc_pack_weight(P[s.m2w], H, H, H, H, H, 0, 0, w.wpB[l], st));
-      }
+      AE_CHECK(pack_step_weights(d, P, w, flags, st));
     }
   }
   // four message-passing layers (locs.py:187-190, 227-243)
@@ -345,8 +391,6 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       __nv_bfloat16* p316 = (__nv_bfloat16*)w.pre316[l] + (size_t)n0 * 2 * H;
       __nv_bfloat16* x16 = (__nv_bfloat16*)w.x16[l] + (size_t)n0 * H;
       for (int h = 0; h < 2; ++h) {
-        AE_CHECK(tc_pack_weight(P[s.u0w] + (size_t)h * H * H, H, H, H, H, H, 0, 0, w.nw3[l][h], st));
-        AE_CHECK(tc_pack_weight(P[s.u2w] + (size_t)h * H, 2 * H, H, H, H, H, 0, 0, w.nw4[l][h], st));
         TcChainArgs c;
         c.M = M; c.wpack1 = w.nw3[l][h]; c.wpack2 = w.nw4[l][h]; c.bias1 = P[s.u0b] + h * H; c.bias2 = h == 0 ? P[s.u2b] : nullptr;
         c.out1 = (flags & AETHER_F_SAVE_FOR_BACKWARD) ? p316 + h * H : nullptr; c.ldo1 = 2 * H;
@@ -356,8 +400,6 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       }
       if (l < 4) {
         const LayerSlots sn = layer_slots(l + 1);
-        AE_CHECK(tc_pack_weight(P[sn.m0w], 3 * H, H, H, H, H, 0, 0, w.nws[l], st));
-        AE_CHECK(tc_pack_weight(P[sn.m0w] + H, 3 * H, H, H, H, H, 0, 0, w.nwr[l], st));
         TcGemmArgs a;
         a.M = M; a.wpack = w.nws[l]; a.out_bf16 = ps16o + (size_t)n0 * H; a.ldo = H;
         AE_CHECK(tc_gemm(a, x16, H, H, H, TC_TF_NONE, st));

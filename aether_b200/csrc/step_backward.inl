@@ -63,9 +63,8 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
     const LayerSlots sl = layer_slots(l);
     {
       ProfScope ps(PROF_EDGE_BWD_DATA, st);
-      AE_CHECK(tc_pack_weight(P[sl.m2w], H, H, H, H, H, 1, 0, s.wtB, st));
       TcGemmArgs a;
-      a.M = E; a.wpack = s.wtB; a.dsilu = (const __nv_bfloat16*)w.bpre1[l]; a.ldd = H;
+      a.M = E; a.wpack = w.wtB[l]; a.dsilu = (const __nv_bfloat16*)w.bpre1[l]; a.ldd = H;
       a.out_bf16 = (__nv_bfloat16*)g1; a.ldo = H;
       AE_CHECK(tc_gemm(a, g2, H, H, H, TC_TF_NONE, st));
     }
@@ -90,18 +89,16 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
       AE_CHECK(node_update_bwd(l - 1));
       ProfScope ps(PROF_EDGE_BWD_DATA, st);
       AE_CHECK(launch_node_mean_scale_bf16(Nn, H, Gr.rowptr, s.gy, s.gyd16, st));
-      AE_CHECK(tc_pack_weight(P[sl.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, s.wtA, st));
       TcGemmArgs a;
-      a.M = E; a.wpack = s.wtA;
+      a.M = E; a.wpack = w.wtA[l];
       a.gat16 = (const __nv_bfloat16*)s.gyd16; a.ldg = H; a.idx_a = Gr.recv;
       a.dsilu = (const __nv_bfloat16*)w.bpre2[l - 1]; a.ldd = H;
       a.out_bf16 = (__nv_bfloat16*)g2; a.ldo = H;
       AE_CHECK(tc_gemm(a, g1, H, H, H, TC_TF_NONE, st));
     } else {
       // gfeat[E, 32] = g1 W1 (fp32, consumed by the geometry backward)
-      AE_CHECK(tc_pack_weight(P[sl.m0w], Fe, 32, H, Fe, H, 1, 0, s.wtA, st));
       TcGemmArgs a;
-      a.M = E; a.wpack = s.wtA; a.out_f32 = s.gfeat; a.ldo32 = 32; a.n_valid = 32;
+      a.M = E; a.wpack = w.wtA[1]; a.out_f32 = s.gfeat; a.ldo32 = 32; a.n_valid = 32;
       AE_CHECK(tc_gemm(a, g1, H, H, 32, TC_TF_NONE, st));
       AE_CHECK(node_res_bwd());
     }
@@ -154,9 +151,8 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
         AE_CHECK(tc_wgrad(s.na16, H, H, p316 + h * H, 2 * H, H, TC_TF_SILU, Nn, G[sl.u2w] + h * H, 2 * H, H, 0,
                           h == 0 ? G[sl.u2b] : nullptr, s.partial, s.partial_floats, st));
         // gpre3[:, half] = (gx W4[:, half]) * silu'(pre3[:, half])
-        AE_CHECK(tc_pack_weight(P[sl.u2w] + h * H, 2 * H, H, H, H, H, 1, 0, s.nwp, st));
         TcGemmArgs a;
-        a.M = Nn; a.wpack = s.nwp; a.dsilu = p316 + h * H; a.ldd = 2 * H; a.out_bf16 = g316 + h * H; a.ldo = 2 * H;
+        a.M = Nn; a.wpack = w.nt4[l][h]; a.dsilu = p316 + h * H; a.ldd = 2 * H; a.out_bf16 = g316 + h * H; a.ldo = 2 * H;
         AE_CHECK(tc_gemm(a, s.na16, H, H, H, TC_TF_NONE, st));
       }
       for (int h = 0; h < 2; ++h) {
@@ -164,9 +160,8 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
         AE_CHECK(tc_wgrad(g316 + h * H, 2 * H, H, y16, H, H, TC_TF_NONE, Nn, G[sl.u0w] + (size_t)h * H * H, H, H, 0,
                           G[sl.u0b] + h * H, s.partial, s.partial_floats, st));
         // gy = gx + gpre3 W3   (two K halves, the second accumulates)
-        AE_CHECK(tc_pack_weight(P[sl.u0w] + (size_t)h * H * H, H, H, H, H, H, 1, 0, s.nwp, st));
         TcGemmArgs a;
-        a.M = Nn; a.wpack = s.nwp; a.res = h == 0 ? gx : s.gy; a.ldr = H; a.out_f32 = s.gy; a.ldo32 = H; a.n_valid = H;
+        a.M = Nn; a.wpack = w.nt3[l][h]; a.res = h == 0 ? gx : s.gy; a.ldr = H; a.out_f32 = s.gy; a.ldo32 = H; a.n_valid = H;
         AE_CHECK(tc_gemm(a, g316 + h * H, 2 * H, H, H, TC_TF_NONE, st));
       }
       return 0;
@@ -254,6 +249,10 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
   float* gxin = gx_out ? gx_out : s.gxin;
   float* gvin = gvel_out ? gvel_out : s.gvin;
   AE_CHECK(launch_node_frame_bwd(D, Nn, vel, w.f, w.R, s.gx0, s.ssend, s.srecv, s.gRglob, gout, s.gf, gxin, gvin, st));
+  if (flags & AETHER_F_EXTERNAL_FIELD) {
+    // the field was an input: hand its gradient to the caller (dynfield.cu continues from there)
+    return (int)cudaMemcpyAsync(G[P_F0_W], s.gf, (size_t)Nn * D * sizeof(float), cudaMemcpyDeviceToDevice, st);
+  }
   // field network (aether.py:113-119,127-134)
   AE_CHECK(b.wgrad(s.gf, D, Nn, D, w.fz2, 32, 32, TF_SILU, nullptr, G[P_F4_W], 32, G[P_F4_B]));
   AE_CHECK(b.dgrad(s.gf, D, Nn, D, P[P_F4_W], 32, 32, s.gfz2, 32, w.fz2, nullptr, nullptr, 0));

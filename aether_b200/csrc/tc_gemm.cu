@@ -542,6 +542,42 @@ __global__ void pack_weight_kernel(const float* __restrict__ W, int64_t ldw, int
   *reinterpret_cast<uint4*>(out + off) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
+struct PackTable {
+  TcPackJob job[TC_PACK_MAX_JOBS];
+  int32_t unit_end[TC_PACK_MAX_JOBS];     // exclusive prefix end of each job's 16-byte units
+  int32_t n;
+};
+
+__global__ void pack_weights_batched_kernel(const __grid_constant__ PackTable t) {
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= t.unit_end[t.n - 1]) return;
+  int lo = 0, hi = t.n - 1;                // first job whose end is past u
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (u < t.unit_end[mid]) hi = mid; else lo = mid + 1;
+  }
+  const TcPackJob& j = t.job[lo];
+  const int lu = u - (lo ? t.unit_end[lo - 1] : 0);
+  const int n = lu % j.N, kb = lu / j.N;
+  uint32_t w[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    float f[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = kb * 8 + 2 * e + h;
+      const int ks = j.kmod ? k % j.kmod : k;
+      float x = 0.0f;
+      if (n < j.n_valid && ks < j.k_valid) x = j.transpose ? j.W[(size_t)ks * j.ldw + n] : j.W[(size_t)n * j.ldw + ks];
+      f[h] = x;
+    }
+    w[e] = tc::pack_bf16(f[0], f[1]);
+  }
+  const int c = kb / 8, jj = kb % 8;
+  const size_t off = (size_t)c * j.N * 128 + (size_t)n * 128 + (size_t)((jj ^ (n & 7)) * 16);
+  *reinterpret_cast<uint4*>((uint8_t*)j.out + off) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 __global__ void convert_bf16_kernel(const float* __restrict__ A, int64_t lda, int64_t M, int cols, int tf,
                                     const float* __restrict__ mask, __nv_bfloat16* __restrict__ out, int64_t ldo) {
   const int cq = cols / 4;
@@ -636,6 +672,25 @@ int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k
   if (K % 64 || N % 8 || ((uintptr_t)out & 15)) return AETHER_E_BADARG;
   const int units = N * K / 8;
   pack_weight_kernel<<<(units + 255) / 256, 256, 0, st>>>(W, ldw, N, K, n_valid, k_valid, transpose, kmod, (uint8_t*)out);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int tc_pack_weights_batched(const TcPackJob* jobs, int n_jobs, cudaStream_t st) {
+  if (n_jobs <= 0) return 0;
+  if (n_jobs > TC_PACK_MAX_JOBS) return AETHER_E_BADARG;
+  PackTable t;
+  memset(&t, 0, sizeof(t));
+  int tot = 0;
+  for (int i = 0; i < n_jobs; ++i) {
+    const TcPackJob& j = jobs[i];
+    if (j.K % 64 || j.N % 8 || ((uintptr_t)j.out & 15) || !j.W) return AETHER_E_BADARG;
+    t.job[i] = j;
+    tot += j.N * j.K / 8;
+    t.unit_end[i] = tot;
+  }
+  t.n = n_jobs;
+  pack_weights_batched_kernel<<<(tot + 255) / 256, 256, 0, st>>>(t);
   AE_LAUNCH_CHECK();
   return 0;
 }

@@ -31,6 +31,13 @@ size_t tc_weight_pack_bytes(int K, int N);
 // B[n][k] = transpose ? W[k*ldw+n] : W[n*ldw + (kmod ? k%kmod : k)], zero outside [n_valid,k_valid]
 int tc_pack_weight(const float* W, int64_t ldw, int N, int K, int n_valid, int k_valid, int transpose, int kmod,
                    void* out, cudaStream_t st);
+// The same for up to TC_PACK_MAX_JOBS images in ONE launch (every weight image of a step: forward, transposed for the
+// backward, node-level), so that the step packs once instead of once per GEMM.
+constexpr int TC_PACK_MAX_JOBS = 64;
+struct TcPackJob {
+  const float* W; void* out; int32_t ldw, N, K, n_valid, k_valid; int16_t transpose, kmod;
+};
+int tc_pack_weights_batched(const TcPackJob* jobs, int n_jobs, cudaStream_t st);
 // out = epi(tf(A) B^T); A is bf16 [M, K] with leading dimension lda (elements)
 int tc_gemm(const TcGemmArgs& g, const void* A, int64_t lda, int K, int N, int tf, cudaStream_t st);
 

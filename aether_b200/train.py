@@ -18,7 +18,7 @@ class GraphedTrainStep:
     """``step(x, vel, charges, target) -> loss`` (a device scalar; read it when you need it).
 
     ``edges``: (send, recv) int64 device tensors, static across steps.  The optimizer must be capturable
-    (``torch.optim.AdamW(..., fused=True, capturable=True)``).  ``allreduce``: optional callable run after backward
+    (``aether_b200.FusedAdamW``, or ``torch.optim.AdamW(..., fused=True, capturable=True)``).  ``allreduce``: optional callable run after backward
     (data-parallel gradient averaging; NCCL collectives are capturable)."""
 
     def __init__(self, model, optimizer, edges, n_nodes: int, allreduce=None, warmup: int = 3):
@@ -68,6 +68,9 @@ class GraphedTrainStep:
                 for v in st.values():                    # zero-fill into every replay)
                     if torch.is_tensor(v):
                         v.zero_()
+            for group in self.opt.param_groups:          # FusedAdamW keeps its step count per group, on the device
+                if torch.is_tensor(group.get("_step_dev")):
+                    group["_step_dev"].zero_()
         torch.cuda.synchronize()
         from . import _lib
         lib = _lib.load()

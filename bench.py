@@ -439,7 +439,7 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
     params = model.param_list()
     flat_n = sum(p.numel() for p in params)
     if train:
-        opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=1e-12, fused=True)
+        opt = ab.FusedAdamW(model.parameters(), lr=5e-4, weight_decay=1e-12)       # one launch for all 47 tensors
         model.train()
     else:
         model.eval()
@@ -453,7 +453,7 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
     # small training shapes are launch-latency bound: replay the whole step as one CUDA graph
     graphed = None
     if train and (E * H <= 32e6 or args.graph) and not args.no_graph:
-        opt = torch.optim.AdamW(model.parameters(), lr=5e-4, weight_decay=1e-12, fused=True, capturable=True)
+        opt = ab.FusedAdamW(model.parameters(), lr=5e-4, weight_decay=1e-12)       # capturable: the step count is on the device
         graphed = ab.GraphedTrainStep(model, opt, (send, recv), Nn, allreduce=(lambda: adist.allreduce_grads(params, world))
                                       if world > 1 else None)
 

@@ -59,6 +59,11 @@ extern "C" {
 /* flags for aether_step_forward / aether_workspace_bytes */
 #define AETHER_F_SAVE_FOR_BACKWARD 1u   /* keep activations for aether_step_backward  */
 #define AETHER_F_BF16_EDGE_MLP     2u   /* edge-MLP GEMMs on tcgen05 in bf16 (fp32 accumulate) */
+#define AETHER_F_EXTERNAL_FIELD    4u   /* the field at the particles is an INPUT (DynamicFieldAether,
+                                         * nn/state2state/dynamic_field_aether.py:84-88): params[40] is a device pointer
+                                         * to field[Nn, D] instead of field_net.net.0.weight, params[41..46] and
+                                         * `charges` are not read; aether_step_backward writes d loss / d field to
+                                         * param_grads[40] ([Nn, D]) and leaves param_grads[41..46] untouched */
 /* (d/dx and d/dvel are returned by aether_step_backward whenever gx_out / gvel_out are non-null) */
 
 /* Number of parameter tensors of Aether, in state_dict order
@@ -191,6 +196,38 @@ int aether_profile_collect(double* ms_by_cat, int64_t* spans_by_cat, int32_t n_c
  * floats written, or a negative error. */
 int64_t aether_debug_stage(const AetherDims* dims, const void* workspace, uint32_t flags, const char* stage,
                            float* dst, int64_t dst_floats, void* stream);
+
+/* ---- latent field network of DynamicFieldAether (nn/state2state/dynamic_field_aether.py:11-47; csrc/dynfield.cu) -------
+ * field[Nn, D] = FilmedNetwork([x, v, emb(q)], z[graph]) with z = attention pooling of the graph's nodes
+ * (graph_pool.py:6-29, film.py:5-60).  Graphs are blocks of num_nodes consecutive nodes (Nn % num_nodes == 0).
+ * params / param_grads: AETHER_DYNFIELD_NUM_PARAMS fp32 tensors in the state_dict order of `field_net`:
+ *   0..3   summary_net.summary_net.gate_nn.{0,2}.{weight,bias}     4..7   summary_net.summary_net.nn.{0,2}.{weight,bias}
+ *   8..13  wrapper.linear_{1,2,3}.{weight,bias}
+ *   14..19 wrapper.film_1.modulator.{0,2,4}.{weight,bias}          20..25 wrapper.film_2.modulator.(same)
+ *   26     class_embedding.weight
+ * The step itself then runs with AETHER_F_EXTERNAL_FIELD.  aether_dynfield_backward takes d loss / d field (what
+ * aether_step_backward left in param_grads[40]), writes every parameter gradient and ADDS the field's dependence on the
+ * inputs to grad_x / grad_vel (either may be NULL). */
+#define AETHER_DYNFIELD_NUM_PARAMS 27
+size_t aether_dynfield_workspace_bytes(int32_t num_dims, int64_t n_nodes, int32_t num_nodes);
+size_t aether_dynfield_scratch_bytes(int32_t num_dims, int64_t n_nodes, int32_t num_nodes);
+int aether_dynfield_forward(int32_t num_dims, int64_t n_nodes, int32_t num_nodes, const float* const* params,
+                            const float* x, const float* vel, const float* charges, float* field, void* workspace,
+                            size_t workspace_bytes, void* stream);
+int aether_dynfield_backward(int32_t num_dims, int64_t n_nodes, int32_t num_nodes, const float* const* params,
+                             const float* charges, const float* grad_field, float* const* param_grads, float* grad_x,
+                             float* grad_vel, const void* workspace, size_t workspace_bytes, void* scratch,
+                             size_t scratch_bytes, void* stream);
+
+/* ---- optimizer step of the reference's caller (torch.optim.AdamW, experiments/lorentz/main.py:164,292) ----------
+ * One fused update of n_tensors parameter tensors (host arrays of device pointers; numel[i] elements each, n_tensors <= 64):
+ *   p <- p (1 - lr wd);  m <- b1 m + (1-b1) g;  v <- b2 v + (1-b2) g^2;  p <- p - lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
+ * step_dev: ONE float on the device holding the step count t; it is advanced by 1 before the update (a 1-thread launch),
+ * so the call is capturable in a CUDA graph.  Same semantics and operation order as torch.optim.AdamW (not amsgrad,
+ * not maximize). */
+int aether_adamw_step(int32_t n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                      float* const* exp_avg_sq, const int64_t* numel, float* step_dev, float lr, float beta1,
+                      float beta2, float eps, float weight_decay, void* stream);
 
 /* ---- test hooks for the tcgen05 building blocks (aether_b200/csrc/tc_gemm.cu, tc_wgrad.cu) -------
  * out[M,N] = epi(tf(A_bf16[M,K]) B^T), B[n][k] = transpose ? W[k*ldw+n] : W[n*ldw + (kmod ? k%kmod : k)],

@@ -313,6 +313,65 @@ def aether_step(
     return out
 
 
+def latent_field_forward(p: Dict[str, Tensor], x: Tensor, vel: Tensor, charges: Tensor, num_nodes: int,
+                         stages: Optional[dict] = None) -> Tensor:
+    """LatentFieldNetwork.forward.  nn/state2state/dynamic_field_aether.py:29-47.
+
+    Graph summary (graph_pool.py:6-29): torch_geometric's AttentionalAggregation is an un-vendored dependency
+    (requirements of the reference, README.md:31; not installed here) -- parity UNPINNED at that boundary.  Its published
+    semantics are restated: gate = gate_nn(x); alpha = softmax of the gate over the nodes of a graph
+    (exp(g - max) / (sum + 1e-16)); summary = sum_n alpha_n * nn(x_n).  FiLM (film.py:40-60): (1 + gamma) y + beta with
+    [gamma | beta] = modulator(z); FilmedNetwork (film.py:24-37).
+    """
+    silu = torch.nn.functional.silu
+    inp = torch.cat([x, vel], -1)                                            # dynamic_field_aether.py:84
+    pre = "field_net.summary_net.summary_net."
+    gate = _lin(p, pre + "gate_nn.2", silu(_lin(p, pre + "gate_nn.0", inp)))  # [Nn, 1]
+    val = _lin(p, pre + "nn.2", silu(_lin(p, pre + "nn.0", inp)))             # [Nn, 32]
+    g = gate.reshape(-1, num_nodes, 1)
+    a = torch.exp(g - g.max(dim=1, keepdim=True).values)
+    alpha = a / (a.sum(dim=1, keepdim=True) + 1e-16)
+    z = (alpha * val.reshape(-1, num_nodes, val.shape[-1])).sum(dim=1)       # [B, 32]
+    zb = z.repeat_interleave(num_nodes, dim=0)                               # :33-39
+
+    def film(name, y):
+        m = _lin(p, name + ".modulator.4", silu(_lin(p, name + ".modulator.2", silu(_lin(p, name + ".modulator.0", zb)))))
+        gamma, beta = torch.chunk(m, 2, dim=-1)
+        return (1.0 + gamma) * y + beta
+
+    idx = (charges + 1).long().reshape(-1)
+    emb = p["field_net.class_embedding.weight"][idx]
+    y = _lin(p, "field_net.wrapper.linear_1", torch.cat([x, vel, emb], -1))  # :41-42
+    y = silu(film("field_net.wrapper.film_1", y))
+    y = _lin(p, "field_net.wrapper.linear_2", y)
+    y = silu(film("field_net.wrapper.film_2", y))
+    f = _lin(p, "field_net.wrapper.linear_3", y)
+    if stages is not None:
+        stages.update(summary=z, alpha=alpha.reshape(-1), field=f)
+    return f
+
+
+def dynamic_field_step(p: Dict[str, Tensor], x: Tensor, edges: Tuple[Tensor, Tensor], vel: Tensor, edge_attr_orig: Tensor,
+                       charges: Tensor, num_nodes: int, stages: Optional[dict] = None) -> Tensor:
+    """DynamicFieldAether.forward.  nn/state2state/dynamic_field_aether.py:79-100: Aether's step with the field predicted
+    by the latent field network."""
+    send, recv = edges
+    f = latent_field_forward(p, x, vel, charges, num_nodes, stages)
+    rel_feat, R, edge_attr = localize(x, vel, f, send, recv)
+    e = torch.cat([edge_attr, edge_attr_orig], -1)
+    h = rel_feat
+    for l in range(1, 5):
+        h, e = gnn_layer(p, "gnn.layer_%d" % l, h, e, send, recv, first=(l == 1))
+    silu = torch.nn.functional.silu
+    h = silu(_lin(p, "gnn.out_mlp.0", h))
+    h = silu(_lin(p, "gnn.out_mlp.3", h))
+    pred = _lin(p, "gnn.out_mlp.6", h)
+    out = x + apply_rot(R, pred)
+    if stages is not None:
+        stages.update(pred=pred, out=out)
+    return out
+
+
 def localize_locs(x: Tensor, vel: Tensor, send: Tensor, recv: Tensor):
     """The base Localizer of LoCS (no field columns).  nn/state2state/locs/locs.py:37-99.
 
