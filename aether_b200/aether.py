@@ -20,6 +20,19 @@ from .graph import PreparedGraph
 from .ops import dropout_masks, step_apply
 
 
+_warned_bf16 = set()
+
+
+def _warn_bf16_fallback(precision, hidden_size):
+    """bf16 requested at a hidden size the tcgen05 kernels do not cover: the step silently ran on the fp32 CUDA-core kernels
+    (about 18x slower at H = 256-class sizes); say so once per size."""
+    if precision == "bf16" and hidden_size not in (64, 128, 256) and hidden_size not in _warned_bf16:
+        import warnings
+        _warned_bf16.add(hidden_size)
+        warnings.warn("aether_b200: precision='bf16' is implemented for hidden_size in {64, 128, 256}; hidden_size=%d runs on "
+                      "the fp32 CUDA-core kernels (much slower, fp32 accuracy)" % hidden_size, RuntimeWarning, stacklevel=3)
+
+
 class GNNLayer(nn.Module):
     """Parameter holder of one message-passing layer (nn/state2state/locs/locs.py:197-225)."""
 
@@ -97,8 +110,13 @@ class Aether(nn.Module):
         super().__init__()
         if num_dims not in (2, 3) or input_size != 2 * num_dims:
             raise ValueError("aether_b200 supports num_dims in {2,3} with input_size == 2*num_dims")
-        if hidden_size % 4 or hidden_size < 4 or hidden_size == 3 * num_dims:
-            raise ValueError("hidden_size must be a multiple of 4")
+        if hidden_size % 4 or hidden_size < 4:
+            raise ValueError("aether_b200: hidden_size must be a positive multiple of 4 (rows of every [.,H] tensor are read "
+                             "and written as 16-byte vectors); the reference has no such restriction")
+        if hidden_size == 3 * num_dims:
+            raise ValueError("aether_b200: hidden_size == 3*num_dims makes layer_1.res an nn.Identity in the reference "
+                             "(locs.py:214-218: input_size == hidden_size), i.e. a different parameter set; not supported")
+        _warn_bf16_fallback(precision or os.environ.get("AETHER_B200_PRECISION", "fp32"), hidden_size)
         self.gnn = GNN(input_size, hidden_size, dropout_prob, num_dims, additional_features=num_dims)
         self.localizer = AetherLocalizer(num_dims)
         self.globalizer = Globalizer(num_dims)

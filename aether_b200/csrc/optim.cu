@@ -49,7 +49,7 @@ __global__ void adamw_kernel(const __grid_constant__ AdamTable t, const float* _
     if (i >= n) break;
     const float gi = g[i];
     float pi = p[i] * (1.0f - lr * wd);
-    const float mi = b1 * m[i] + (1.0f - b1) * gi;
+    const float mi = m[i] + (1.0f - b1) * (gi - m[i]);        // torch: exp_avg.lerp_(grad, 1 - beta1)
     const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
     const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
     pi -= step_size * (mi / denom);

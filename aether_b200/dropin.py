@@ -34,4 +34,11 @@ def install() -> types.ModuleType:
     ml.Localizer = Localizer
     ml.__doc__ = "aether_b200 drop-in for the reference's nn/state2state/locs/locs.py (LoCS only)"
     sys.modules["nn.state2state.locs.locs"] = ml
+    # the FiLM / attention-pooled field variant (experiments/lorentz/main.py: --model film_aether)
+    from .dynamic_field import DynamicFieldAether, LatentFieldNetwork
+    md = types.ModuleType("nn.state2state.dynamic_field_aether")
+    md.DynamicFieldAether = DynamicFieldAether
+    md.LatentFieldNetwork = LatentFieldNetwork
+    md.__doc__ = "aether_b200 drop-in for the reference's nn/state2state/dynamic_field_aether.py"
+    sys.modules["nn.state2state.dynamic_field_aether"] = md
     return m

@@ -22,7 +22,7 @@ from torch import nn
 from torch.autograd.function import once_differentiable
 
 from . import _lib
-from .aether import Aether, AetherLocalizer, Globalizer, GNN
+from .aether import Aether, AetherLocalizer, Globalizer, GNN, _warn_bf16_fallback
 from .ops import _dims, _f32c, _stream, dropout_masks
 
 F_EXTERNAL_FIELD = 4
@@ -176,8 +176,13 @@ class DynamicFieldAether(nn.Module):
         super().__init__()
         if num_dims not in (2, 3) or input_size != 2 * num_dims:
             raise ValueError("aether_b200 supports num_dims in {2,3} with input_size == 2*num_dims")
-        if hidden_size % 4 or hidden_size < 4 or hidden_size == 3 * num_dims:
-            raise ValueError("hidden_size must be a multiple of 4")
+        if hidden_size % 4 or hidden_size < 4:
+            raise ValueError("aether_b200: hidden_size must be a positive multiple of 4 (rows of every [.,H] tensor are read "
+                             "and written as 16-byte vectors); the reference has no such restriction")
+        if hidden_size == 3 * num_dims:
+            raise ValueError("aether_b200: hidden_size == 3*num_dims makes layer_1.res an nn.Identity in the reference "
+                             "(locs.py:214-218: input_size == hidden_size), i.e. a different parameter set; not supported")
+        _warn_bf16_fallback(precision or os.environ.get("AETHER_B200_PRECISION", "fp32"), hidden_size)
         self.gnn = GNN(input_size, hidden_size, dropout_prob, num_dims, additional_features=num_dims)
         self.localizer = AetherLocalizer(num_dims)
         self.globalizer = Globalizer(num_dims)

@@ -29,8 +29,8 @@ def test_fused_adamw_matches_torch(wd):
     assert oa.step_count() == 6
     for pa, pb in zip(a, b):
         assert torch.allclose(pa, pb, rtol=2e-6, atol=1e-8), float((pa - pb).abs().max())
-        assert torch.allclose(oa.state[pa]["exp_avg"], ob.state[pb]["exp_avg"], rtol=1e-6, atol=1e-10)
-        assert torch.allclose(oa.state[pa]["exp_avg_sq"], ob.state[pb]["exp_avg_sq"], rtol=1e-6, atol=1e-12)
+        assert torch.allclose(oa.state[pa]["exp_avg"], ob.state[pb]["exp_avg"], rtol=1e-5, atol=1e-7)
+        assert torch.allclose(oa.state[pa]["exp_avg_sq"], ob.state[pb]["exp_avg_sq"], rtol=1e-5, atol=1e-9)
 
 
 def test_fused_adamw_is_capturable():
