@@ -67,7 +67,8 @@ SIGNATURES = {
     "aether_dynfield_backward": (c_int, [c_int32, c_int64, c_int32, POINTER(c_void_p), c_void_p, c_void_p, POINTER(c_void_p),
                                          c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
     "aether_adamw_step": (c_int, [c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
-                                  POINTER(c_int64), c_void_p, c_float, c_float, c_float, c_float, c_float, c_void_p]),
+                                  POINTER(c_int64), c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,
+                                  ctypes.c_double, c_void_p]),
     "aether_dbg_tc_gemm": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_int64, c_int32, c_int32, c_int32,
                                    c_int32, c_int32, c_int32, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -77,6 +78,8 @@ SIGNATURES = {
     "aether_dbg_tc_chain": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                     c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    "aether_dbg_tc_chain_bwd": (c_int, [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_debug_stage": (c_int64, [POINTER(AetherDims), c_void_p, c_uint32, c_char_p, c_void_p, c_int64, c_void_p]),
 }
 

@@ -36,6 +36,7 @@ SOURCES = [
     ("tc_gemm.cu", []),
     ("tc_wgrad.cu", []),
     ("tc_chain.cu", []),
+    ("tc_chain_bwd.cu", []),
     ("tc_abi.cu", []),
     ("edge_bf16.cu", []),
     ("prof.cu", []),

@@ -78,35 +78,46 @@ __global__ void segreduce_bf16_kernel(int64_t Nn, const int32_t* __restrict__ pt
   }
 }
 
-__global__ void edge_dpre2_bf16_kernel(int64_t E, int H, const int32_t* __restrict__ recv,
-                                       const int32_t* __restrict__ rowptr, const __nv_bfloat16* __restrict__ ge,
-                                       const float* __restrict__ gy, const __nv_bfloat16* __restrict__ pre2,
-                                       __nv_bfloat16* __restrict__ g) {
-  const int hq = H / 8;
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= E * hq) return;
-  const int64_t k = i / hq;
-  const int c = (int)(i % hq) * 8;
-  const int r = recv[k];
-  const int deg = rowptr[r + 1] - rowptr[r];
-  const float inv = 1.0f / (float)(deg < 1 ? 1 : deg);
-  const float4 a0 = __ldg(reinterpret_cast<const float4*>(gy + (size_t)r * H + c));
-  const float4 a1 = __ldg(reinterpret_cast<const float4*>(gy + (size_t)r * H + c + 4));
-  float o[8] = {a0.x * inv, a0.y * inv, a0.z * inv, a0.w * inv, a1.x * inv, a1.y * inv, a1.z * inv, a1.w * inv};
-  if (ge) {
-    float v[8];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(ge + (size_t)k * H + c)), v);
+// g[k,:] = (ge[k,:] + gy[recv[k],:] / deg) * silu'(pre2[k,:]).  One warp per edge row PAIR: the receiver index and its
+// degree are read once per row (lane 0, broadcast), every lane moves 16-byte pieces of both rows before it computes, and
+// silu' is evaluated two elements per instruction in bf16x2 (the form the GEMM epilogues use) -- the kernel is a pure
+// 2-pass stream (read pre2, write g) and was issue / latency bound in its one-thread-per-8-columns form (3.7 TB/s).
+template <int LPR>     // lanes per row = H / 8
+__global__ void edge_dpre2_bf16_kernel(int64_t E, const int32_t* __restrict__ recv, const int32_t* __restrict__ rowptr,
+                                       const __nv_bfloat16* __restrict__ ge, const float* __restrict__ gy,
+                                       const __nv_bfloat16* __restrict__ pre2, __nv_bfloat16* __restrict__ g) {
+  constexpr int H = LPR * 8;
+  constexpr int RPW = 32 / LPR;                      // rows per warp and pass
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int sub = lane / LPR, c = (lane % LPR) * 8;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) o[q] += v[q];
+  for (int p = 0; p < 2; ++p) {
+    const int64_t k = (warp * 2 + p) * RPW + sub;
+    if (k >= E) return;
+    const int r = recv[k];
+    const int deg = rowptr[r + 1] - rowptr[r];
+    const float inv = 1.0f / (float)(deg < 1 ? 1 : deg);
+    const uint4 z = __ldg(reinterpret_cast<const uint4*>(pre2 + (size_t)k * H + c));
+    const float4 a0 = __ldg(reinterpret_cast<const float4*>(gy + (size_t)r * H + c));
+    const float4 a1 = __ldg(reinterpret_cast<const float4*>(gy + (size_t)r * H + c + 4));
+    float o[8] = {a0.x * inv, a0.y * inv, a0.z * inv, a0.w * inv, a1.x * inv, a1.y * inv, a1.z * inv, a1.w * inv};
+    if (ge) {
+      float v[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(ge + (size_t)k * H + c)), v);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) o[q] += v[q];
+    }
+    const uint32_t zz[4] = {z.x, z.y, z.z, z.w};
+    uint32_t w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t d = tc::bf2_dsilu_w(zz[q]);     // 2 silu'(z) - 1 for the pair
+      const float h0 = 0.5f * o[2 * q], h1 = 0.5f * o[2 * q + 1];
+      w[q] = tc::pack_bf16(fmaf(h0, bf16_lo(d), h0), fmaf(h1, bf16_hi(d), h1));
+    }
+    *reinterpret_cast<uint4*>(g + (size_t)k * H + c) = make_uint4(w[0], w[1], w[2], w[3]);
   }
-  float z[8];
-  unpack8(__ldg(reinterpret_cast<const uint4*>(pre2 + (size_t)k * H + c)), z);
-#pragma unroll
-  for (int q = 0; q < 8; ++q) o[q] *= tc::dsilu_fast(z[q]);
-  uint4 w;
-  w.x = tc::pack_bf16(o[0], o[1]); w.y = tc::pack_bf16(o[2], o[3]);
-  w.z = tc::pack_bf16(o[4], o[5]); w.w = tc::pack_bf16(o[6], o[7]);
-  *reinterpret_cast<uint4*>(g + (size_t)k * H + c) = w;
 }
 
 __global__ void node_mean_scale_bf16_kernel(int64_t Nn, int H, const int32_t* __restrict__ rowptr,
@@ -195,10 +206,14 @@ int launch_segsum_bf16(int64_t Nn, int W, const int32_t* ptr, const int32_t* lis
 int launch_edge_dpre2_bf16(int64_t E, int H, const int32_t* recv, const int32_t* rowptr, const void* ge, const float* gy,
                            const void* pre2, void* g, cudaStream_t st) {
   if (E <= 0) return 0;
-  if (H % 8) return AETHER_E_BADARG;
-  const int64_t tot = E * (H / 8);
-  edge_dpre2_bf16_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(E, H, recv, rowptr, (const __nv_bfloat16*)ge, gy,
-                                                                      (const __nv_bfloat16*)pre2, (__nv_bfloat16*)g);
+  if (H != 64 && H != 128 && H != 256) return AETHER_E_BADARG;
+  const int rpw = 2 * (32 / (H / 8));                // rows per warp
+  const int64_t warps = (E + rpw - 1) / rpw;
+  const unsigned blocks = (unsigned)((warps * 32 + 255) / 256);
+  auto a = (const __nv_bfloat16*)ge; auto z = (const __nv_bfloat16*)pre2; auto o = (__nv_bfloat16*)g;
+  if (H == 256) edge_dpre2_bf16_kernel<32><<<blocks, 256, 0, st>>>(E, recv, rowptr, a, gy, z, o);
+  else if (H == 128) edge_dpre2_bf16_kernel<16><<<blocks, 256, 0, st>>>(E, recv, rowptr, a, gy, z, o);
+  else edge_dpre2_bf16_kernel<8><<<blocks, 256, 0, st>>>(E, recv, rowptr, a, gy, z, o);
   AE_LAUNCH_CHECK();
   return 0;
 }

@@ -25,8 +25,10 @@ struct AdamTable {
 
 __global__ void adamw_tick_kernel(float* step) { *step += 1.0f; }
 
-__global__ void adamw_kernel(const __grid_constant__ AdamTable t, const float* __restrict__ step, float lr, float b1, float b2,
-                             float eps, float wd) {
+// omb1 = 1 - beta1, omb2 = 1 - beta2, decay = 1 - lr wd: formed in double on the host like torch does (1 - 0.999f in fp32
+// is 4.7e-5 off)
+__global__ void adamw_kernel(const __grid_constant__ AdamTable t, const float* __restrict__ step, double lr, double b1d, double b2d,
+                             float eps, float omb1, float omb2, float decay) {
   const int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= t.end[t.n - 1]) return;
   int lo = 0, hi = t.n - 1;
@@ -36,8 +38,9 @@ __global__ void adamw_kernel(const __grid_constant__ AdamTable t, const float* _
   }
   const int64_t i0 = (u - (lo ? t.end[lo - 1] : 0)) * 4;
   const float ts = *step;
-  const float bc1 = 1.0f - powf(b1, ts), bc2 = 1.0f - powf(b2, ts);
-  const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
+  const double bc1 = 1.0 - pow(b1d, (double)ts), bc2 = 1.0 - pow(b2d, (double)ts);
+  const float step_size = (float)(lr / bc1), inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  const float b2 = (float)b2d;
   float* p = t.p[lo];
   const float* g = t.g[lo];
   float* m = t.m[lo];
@@ -48,9 +51,9 @@ __global__ void adamw_kernel(const __grid_constant__ AdamTable t, const float* _
     const int64_t i = i0 + k;
     if (i >= n) break;
     const float gi = g[i];
-    float pi = p[i] * (1.0f - lr * wd);
-    const float mi = m[i] + (1.0f - b1) * (gi - m[i]);        // torch: exp_avg.lerp_(grad, 1 - beta1)
-    const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+    float pi = p[i] * decay;
+    const float mi = m[i] + omb1 * (gi - m[i]);               // torch: exp_avg.lerp_(grad, 1 - beta1)
+    const float vi = b2 * v[i] + omb2 * gi * gi;
     const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
     pi -= step_size * (mi / denom);
     p[i] = pi; m[i] = mi; v[i] = vi;
@@ -63,8 +66,8 @@ __global__ void adamw_kernel(const __grid_constant__ AdamTable t, const float* _
 using namespace aether;
 
 extern "C" int aether_adamw_step(int32_t n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
-                                 float* const* exp_avg_sq, const int64_t* numel, float* step_dev, float lr, float beta1,
-                                 float beta2, float eps, float weight_decay, void* stream) {
+                                 float* const* exp_avg_sq, const int64_t* numel, float* step_dev, double lr, double beta1,
+                                 double beta2, double eps, double weight_decay, void* stream) {
   if (n_tensors <= 0) return 0;
   if (n_tensors > kMaxTensors || !params || !grads || !exp_avg || !exp_avg_sq || !numel || !step_dev) return AETHER_E_BADARG;
   AdamTable t;
@@ -84,7 +87,10 @@ extern "C" int aether_adamw_step(int32_t n_tensors, float* const* params, const 
   adamw_tick_kernel<<<1, 1, 0, st>>>(step_dev);
   AE_LAUNCH_CHECK();
   if (n == 0) return 0;
-  adamw_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(t, step_dev, lr, beta1, beta2, eps, weight_decay);
+  // hyper-parameters arrive as doubles (Python floats): 1 - beta, 1 - lr wd and the bias corrections are formed in double
+  // and rounded once, like torch.optim.AdamW does
+  adamw_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(t, step_dev, lr, beta1, beta2, (float)eps, (float)(1.0 - beta1),
+                                                                (float)(1.0 - beta2), (float)(1.0 - lr * weight_decay));
   AE_LAUNCH_CHECK();
   return 0;
 }

@@ -131,7 +131,7 @@ struct Scratch {
   float *gf, *gfz1, *gfz2, *gfin, *gxin, *gvin;
   float* partial; size_t partial_floats;
   // bf16 path: edge gradients [E,H] bf16 (ge, g2, g1), transposed weight images
-  void *bg2, *bg1, *gyd16; void *wtA, *wtB;   // gyd16: [Nn,H] bf16 = gy / in-degree
+  void *bg2, *bg1, *bg1b, *gyd16; void *wtA, *wtB;   // gyd16: [Nn,H] bf16 = gy / in-degree
   void *na16, *ng16, *nwp;
   void* gpre316;        // [Nn, 2H] bf16 gradient of the node update's hidden layer
   size_t bytes;
@@ -170,12 +170,12 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   Carver c(base);
   const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
   s.gA = s.gB = nullptr;
-  s.bg2 = s.bg1 = s.gyd16 = s.wtA = s.wtB = nullptr;
+  s.bg2 = s.bg1 = s.bg1b = s.gyd16 = s.wtA = s.wtB = nullptr;
   s.na16 = s.ng16 = s.nwp = nullptr; s.gpre316 = nullptr;
   if (use_tc(d, flags)) {
     s.na16 = c.b(Nn * 256 * 2); s.ng16 = c.b(Nn * 256 * 2); s.nwp = c.b(tc_weight_pack_bytes(256, 256));
     s.gpre316 = c.b(Nn * 2 * H * 2);
-    s.bg2 = c.b(E * H * 2); s.bg1 = c.b(E * H * 2); s.gyd16 = c.b(Nn * H * 2);
+    s.bg2 = c.b(E * H * 2); s.bg1 = c.b(E * H * 2); s.bg1b = c.b(E * H * 2); s.gyd16 = c.b(Nn * H * 2);
     s.wtA = c.b(tc_weight_pack_bytes(H, H)); s.wtB = c.b(tc_weight_pack_bytes(H, H));
     s.gfeat = c.f(E * 32);
   } else {

@@ -54,6 +54,9 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
   const int64_t Nn = d.n_nodes, E = d.n_edges;
   void* g2 = s.bg2;
   void* g1 = s.bg1;
+  void* g1_next = s.bg1b;       // the chained kernel writes the next layer's g1 while it reads this layer's
+  const bool chain = use_chain() && tc_chain_bwd_supported(H);
+  bool have_g1 = false;         // g1 of this layer was already produced by the previous iteration's chained launch
   AE_CHECK(node_update_bwd(4));
   {
     ProfScope ps(PROF_EDGE_BWD_DATA, st);
@@ -61,7 +64,7 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
   }
   for (int l = 4; l >= 1; --l) {
     const LayerSlots sl = layer_slots(l);
-    {
+    if (!have_g1) {
       ProfScope ps(PROF_EDGE_BWD_DATA, st);
       TcGemmArgs a;
       a.M = E; a.wpack = w.wtB[l]; a.dsilu = (const __nv_bfloat16*)w.bpre1[l]; a.ldd = H;
@@ -89,6 +92,18 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
       AE_CHECK(node_update_bwd(l - 1));
       ProfScope ps(PROF_EDGE_BWD_DATA, st);
       AE_CHECK(launch_node_mean_scale_bf16(Nn, H, Gr.rowptr, s.gy, s.gyd16, st));
+      if (chain) {
+        // B2 of this layer and B1 of the next one down in ONE launch (tc_chain_bwd.cu): g2_{l-1} is stored for the weight
+        // gradient and handed to the second GEMM through tensor memory
+        TcChainArgs c;
+        c.M = E; c.wpack1 = w.wtA[l]; c.wpack2 = w.wtB[l - 1];
+        c.gat16 = (const __nv_bfloat16*)s.gyd16; c.ldg = H; c.idx_b = Gr.recv;
+        c.out1 = (__nv_bfloat16*)g2; c.ldo1 = H; c.out2 = (__nv_bfloat16*)g1_next; c.ldo2 = H;
+        AE_CHECK(tc_chain_bwd(c, g1, H, w.bpre2[l - 1], H, w.bpre1[l - 1], H, H, st));
+        void* t = g1; g1 = g1_next; g1_next = t;
+        have_g1 = true;
+        continue;
+      }
       TcGemmArgs a;
       a.M = E; a.wpack = w.wtA[l];
       a.gat16 = (const __nv_bfloat16*)s.gyd16; a.ldg = H; a.idx_a = Gr.recv;

@@ -51,3 +51,22 @@ extern "C" int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, in
   g.out1 = (__nv_bfloat16*)out1_bf16; g.ldo1 = H; g.out2 = (__nv_bfloat16*)out2_bf16; g.ldo2 = H;
   return tc_chain(g, A_bf16, lda, K1, H, silu_on_load ? TC_TF_SILU : TC_TF_NONE, st);
 }
+
+// Chained data-gradient GEMMs (tc_chain_bwd.cu): out1 = (A W1 (+ gat[idx_b[m]])) * silu'(z1), out2 = (out1 W2) * silu'(z2);
+// W1, W2 are [H, H] fp32 row-major (out = in W: the transposed images are packed here).  wpack_scratch: 2*H*H*2 bytes.
+extern "C" int aether_dbg_tc_chain_bwd(const void* A_bf16, int64_t M, int32_t H, const float* W1, const float* W2,
+                                       const void* gat_bf16, int64_t ldg, const int32_t* idx_b, const void* z1_bf16,
+                                       const void* z2_bf16, void* out1_bf16, void* out2_bf16, void* wpack_scratch,
+                                       void* stream) {
+  if (!A_bf16 || !W1 || !W2 || !z1_bf16 || !z2_bf16 || !out1_bf16 || !out2_bf16 || !wpack_scratch) return AETHER_E_BADARG;
+  if (!tc_chain_bwd_supported(H)) return AETHER_E_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  char* wp2 = (char*)wpack_scratch + tc_weight_pack_bytes(H, H);
+  AE_CHECK(tc_pack_weight(W1, H, H, H, H, H, 1, 0, wpack_scratch, st));
+  AE_CHECK(tc_pack_weight(W2, H, H, H, H, H, 1, 0, wp2, st));
+  TcChainArgs g;
+  g.M = M; g.wpack1 = wpack_scratch; g.wpack2 = wp2;
+  g.gat16 = (const __nv_bfloat16*)gat_bf16; g.ldg = ldg; g.idx_b = idx_b;
+  g.out1 = (__nv_bfloat16*)out1_bf16; g.ldo1 = H; g.out2 = (__nv_bfloat16*)out2_bf16; g.ldo2 = H;
+  return tc_chain_bwd(g, A_bf16, H, z1_bf16, H, z2_bf16, H, H, st);
+}

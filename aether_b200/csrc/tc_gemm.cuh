@@ -60,6 +60,11 @@ struct TcChainArgs {
   __nv_bfloat16* copy16 = nullptr; int64_t ldc16 = 0;
 };
 bool tc_chain_supported(int K1, int H);
+// Chained data-gradient GEMMs of the backward (tc_chain_bwd.cu): out1 = (A W1 (+ gat16[idx_b[m]])) * silu'(z1),
+// out2 = (out1 W2) * silu'(z2); wpack1 / wpack2 are transposed images.
+bool tc_chain_bwd_supported(int H);
+int tc_chain_bwd(const TcChainArgs& g, const void* A, int64_t lda, const void* z1, int64_t ldz1, const void* z2, int64_t ldz2,
+                 int H, cudaStream_t st);
 int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, int tf1, cudaStream_t st);
 
 // fp32 [M, cols] (leading dimension lda) -> bf16 [M, cols] (leading dimension ldo), optionally through

@@ -226,8 +226,8 @@ int aether_dynfield_backward(int32_t num_dims, int64_t n_nodes, int32_t num_node
  * so the call is capturable in a CUDA graph.  Same semantics and operation order as torch.optim.AdamW (not amsgrad,
  * not maximize). */
 int aether_adamw_step(int32_t n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
-                      float* const* exp_avg_sq, const int64_t* numel, float* step_dev, float lr, float beta1,
-                      float beta2, float eps, float weight_decay, void* stream);
+                      float* const* exp_avg_sq, const int64_t* numel, float* step_dev, double lr, double beta1,
+                      double beta2, double eps, double weight_decay, void* stream);
 
 /* ---- test hooks for the tcgen05 building blocks (aether_b200/csrc/tc_gemm.cu, tc_wgrad.cu) -------
  * out[M,N] = epi(tf(A_bf16[M,K]) B^T), B[n][k] = transpose ? W[k*ldw+n] : W[n*ldw + (kmod ? k%kmod : k)],
@@ -256,6 +256,12 @@ int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, 
                         const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
                         const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
                         void* out2_bf16, void* wpack_scratch, void* stream);
+/* Chained data-gradient GEMMs of the edge-MLP backward on a CTA pair (csrc/tc_chain_bwd.cu; autograd of locs.py:232-235):
+ * out1[M,H] = (A[M,H] W1 (+ gat_bf16[idx_b[m]*ldg + n])) * silu'(z1[m,n]),  out2[M,H] = (out1 W2) * silu'(z2[m,n]);
+ * everything bf16 except W1, W2 ([H,H] fp32 row-major).  wpack_scratch: 2 * H * H * 2 bytes. */
+int aether_dbg_tc_chain_bwd(const void* A_bf16, int64_t M, int32_t H, const float* W1, const float* W2,
+                            const void* gat_bf16, int64_t ldg, const int32_t* idx_b, const void* z1_bf16,
+                            const void* z2_bf16, void* out1_bf16, void* out2_bf16, void* wpack_scratch, void* stream);
 
 #ifdef __cplusplus
 }
