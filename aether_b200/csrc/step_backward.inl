@@ -58,7 +58,18 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
   const bool chain = use_chain() && tc_chain_bwd_supported(H);
   bool have_g1 = false;         // g1 of this layer was already produced by the previous iteration's chained launch
   AE_CHECK(node_update_bwd(4));
-  {
+  if (chain) {
+    // top layer: g2 = gyd[recv] * silu'(pre2_4) and g1 = (g2 W2) * silu'(pre1_4) in one launch of the chained kernel
+    // without its first GEMM (no standalone elementwise pass, no re-read of g2)
+    ProfScope ps(PROF_EDGE_BWD_DATA, st);
+    AE_CHECK(launch_node_mean_scale_bf16(Nn, H, Gr.rowptr, s.gy, s.gyd16, st));
+    TcChainArgs c;
+    c.M = E; c.wpack2 = w.wtB[4];
+    c.gat16 = (const __nv_bfloat16*)s.gyd16; c.ldg = H; c.idx_b = Gr.recv;
+    c.out1 = (__nv_bfloat16*)g2; c.ldo1 = H; c.out2 = (__nv_bfloat16*)g1; c.ldo2 = H;
+    AE_CHECK(tc_chain_bwd(c, nullptr, 0, w.bpre2[4], H, w.bpre1[4], H, H, st));
+    have_g1 = true;
+  } else {
     ProfScope ps(PROF_EDGE_BWD_DATA, st);
     AE_CHECK(launch_edge_dpre2_bf16(E, H, Gr.recv, Gr.rowptr, nullptr, s.gy, w.bpre2[4], g2, st));
   }

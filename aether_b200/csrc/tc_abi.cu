@@ -58,11 +58,11 @@ extern "C" int aether_dbg_tc_chain_bwd(const void* A_bf16, int64_t M, int32_t H,
                                        const void* gat_bf16, int64_t ldg, const int32_t* idx_b, const void* z1_bf16,
                                        const void* z2_bf16, void* out1_bf16, void* out2_bf16, void* wpack_scratch,
                                        void* stream) {
-  if (!A_bf16 || !W1 || !W2 || !z1_bf16 || !z2_bf16 || !out1_bf16 || !out2_bf16 || !wpack_scratch) return AETHER_E_BADARG;
+  if ((A_bf16 && !W1) || !W2 || !z1_bf16 || !z2_bf16 || !out1_bf16 || !out2_bf16 || !wpack_scratch) return AETHER_E_BADARG;
   if (!tc_chain_bwd_supported(H)) return AETHER_E_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
   char* wp2 = (char*)wpack_scratch + tc_weight_pack_bytes(H, H);
-  AE_CHECK(tc_pack_weight(W1, H, H, H, H, H, 1, 0, wpack_scratch, st));
+  if (A_bf16) AE_CHECK(tc_pack_weight(W1, H, H, H, H, H, 1, 0, wpack_scratch, st));
   AE_CHECK(tc_pack_weight(W2, H, H, H, H, H, 1, 0, wp2, st));
   TcChainArgs g;
   g.M = M; g.wpack1 = wpack_scratch; g.wpack2 = wp2;

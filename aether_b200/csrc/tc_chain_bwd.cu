@@ -54,7 +54,7 @@ __device__ __forceinline__ uint32_t dsilu_mul_pack(float v0, float v1, uint32_t 
   return pack_bf16(fmaf(v0, bf16_lo(w), v0), fmaf(v1, bf16_hi(w), v1));
 }
 
-template <int H, bool GATHER>
+template <int H, bool GATHER, bool MMA1>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmZ1,
                     const __grid_constant__ CUtensorMap tmZ2, const __grid_constant__ CUtensorMap tmO1,
@@ -67,6 +67,7 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr uint32_t IDESC = make_idesc(256, H, MAJOR_K, MAJOR_K);
   constexpr uint32_t TMEM_COLS = 2 * H;
   constexpr int WROW = (H / 2) * 128;
+  constexpr int NOPS = MMA1 ? 3 : 2;               // operand tiles per edge tile in the ring: (A,) Z1, Z2
   static_assert(S >= 2, "pipeline too shallow");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -114,9 +115,9 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == kWarpTma && lane == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmZ1); tma_prefetch_desc(&tmZ2);
     tma_prefetch_desc(&tmO1); tma_prefetch_desc(&tmO2);
-    mbar_arrive_expect_tx(bar_w, 2 * w_bytes(H));
+    mbar_arrive_expect_tx(bar_w, (MMA1 ? 2 : 1) * w_bytes(H));
     for (int c = 0; c < KC; ++c) {
-      bulk_load(sW1 + c * WROW, (const uint8_t*)g.wpack1 + (size_t)c * (H * 128) + (size_t)rank * WROW, WROW, bar_w);
+      if (MMA1) bulk_load(sW1 + c * WROW, (const uint8_t*)g.wpack1 + (size_t)c * (H * 128) + (size_t)rank * WROW, WROW, bar_w);
       bulk_load(sW2 + c * WROW, (const uint8_t*)g.wpack2 + (size_t)c * (H * 128) + (size_t)rank * WROW, WROW, bar_w);
     }
     mbar_wait(bar_w, 0);
@@ -136,7 +137,7 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int64_t pt = cid; pt < n_pt; pt += ncl) {
         const int row0 = (int)(pt * 2 * kTileM + rank * kTileM);
 #pragma unroll 1
-        for (int op = 0; op < 3; ++op) {
+        for (int op = MMA1 ? 0 : 1; op < 3; ++op) {
           const CUtensorMap* tm = op == 0 ? &tmA : (op == 1 ? &tmZ1 : &tmZ2);
           for (int c = 0; c < KC; ++c, ++it) {
             const uint32_t s = it % S, bit = 1u << s;
@@ -158,8 +159,8 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t acc1 = tmem_base, acc2 = tmem_base + H;
       uint32_t lt = 0, nA = 0;
       for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
-        for (int c = 0; c < KC; ++c) {
-          const uint32_t it = lt * 3 * KC + c, s = it % S;
+        for (int c = 0; MMA1 && c < KC; ++c) {
+          const uint32_t it = lt * NOPS * KC + c, s = it % S;
           mbar_wait_cluster(bar_rdy + 8 * s, (nA >> s) & 1);
           nA ^= 1u << s;
           tc_fence_after();
@@ -171,7 +172,7 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           umma_commit_2cta(bar_free + 8 * s);
         }
-        umma_commit_2cta(bar_acc1f);
+        if (MMA1) umma_commit_2cta(bar_acc1f);
         mbar_wait_cluster(bar_acc2e, (lt & 1) ^ 1);
         tc_fence_after();
         for (int h = 0; h < NP; ++h) {
@@ -193,8 +194,8 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t rdy0 = mapa_rank(bar_rdy, 0);
     uint32_t lt = 0, nA = 0;
     for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
-      for (int c = 0; c < KC; ++c) {
-        const uint32_t it = lt * 3 * KC + c, s = it % S;
+      for (int c = 0; MMA1 && c < KC; ++c) {
+        const uint32_t it = lt * NOPS * KC + c, s = it % S;
         mbar_wait(bar_raw + 8 * s, (nA >> s) & 1);
         nA ^= 1u << s;
         __syncwarp();
@@ -249,7 +250,9 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       };
 
       // ---- epilogue 1: g2 = (acc1 + gyd[recv]) * silu'(Z1) -> HBM and, as bf16, back into tensor memory (A2) ----
-      mbar_wait(bar_acc1f, lt & 1);
+      // (without the first MMA -- the top layer, g2 = gyd[recv] * silu'(Z1) -- accumulator 1's columns are free once MMA 2 of
+      // the previous tile has completed, which epilogue 2 of that tile already waited for)
+      if (MMA1) mbar_wait(bar_acc1f, lt & 1);
       tc_fence_after();
 #pragma unroll
       for (int kk = 0; kk < CPW; ++kk) {
@@ -257,8 +260,13 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int c0 = j * 32;
         if (GATHER && TOP) prefetch(kk);
         uint32_t r[32];
-        tmem_ld32(lane_base + c0, r);
-        const uint32_t itz = lt * 3 * KC + KC + kk, zs = itz % S;
+        if (MMA1) {
+          tmem_ld32(lane_base + c0, r);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = 0u;
+        }
+        const uint32_t itz = lt * NOPS * KC + (NOPS - 2) * KC + kk, zs = itz % S;
         mbar_wait(bar_rawz + 8 * zs, (nZ >> zs) & 1);
         nZ ^= 1u << zs;
         uint4 z[4];
@@ -313,7 +321,7 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kk = 0; kk < CPW; ++kk, ++nbox) {
           const int c0 = (hf + 2 * kk) * 32;
           const uint32_t buf = sbuf + (nbox & 1) * 2048;
-          const uint32_t itz = lt * 3 * KC + 2 * KC + kk, zs = itz % S;
+          const uint32_t itz = lt * NOPS * KC + (NOPS - 1) * KC + kk, zs = itz % S;
           mbar_wait(bar_rawz + 8 * zs, (nZ >> zs) & 1);
           nZ ^= 1u << zs;
           uint4 z[4];
@@ -367,12 +375,12 @@ tc_chain_bwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
 }
 
-template <int H, bool GATHER>
+template <int H, bool GATHER, bool MMA1>
 int launch_bwd(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& z1, const CUtensorMap& z2, const CUtensorMap& o1,
                const CUtensorMap& o2, cudaStream_t st) {
   constexpr int smem = smem_bytes(H);
   static_assert(smem <= kSmemMax, "shared memory budget");
-  auto kern = tc_chain_bwd_kernel<H, GATHER>;
+  auto kern = tc_chain_bwd_kernel<H, GATHER, MMA1>;
   static int max_clusters = 0;
   if (max_clusters == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -403,20 +411,26 @@ bool tc_chain_bwd_supported(int H) { return H == 64 || H == 128 || H == 256; }
 
 // g.wpack1 / g.wpack2: TRANSPOSED images (tc_pack_weight transpose = 1) of W_e,l and W_2,{l-1}; g.gat16 + g.idx_b: the
 // receiver-indexed node term (optional); z1 / z2: saved pre-activations; g.out1 = g2, g.out2 = g1 (both required).
+// A == nullptr: no first GEMM (top layer): out1 = gat16[idx_b[m]] * silu'(z1), g.wpack1 is not read.
 int tc_chain_bwd(const TcChainArgs& g, const void* A, int64_t lda, const void* z1, int64_t ldz1, const void* z2, int64_t ldz2,
                  int H, cudaStream_t st) {
   if (g.M <= 0) return 0;
   if (!tc_chain_bwd_supported(H)) return AETHER_E_UNSUPPORTED;
-  if (!g.wpack1 || !g.wpack2 || !g.out1 || !g.out2 || !A || !z1 || !z2 || g.bias1 || g.bias2 || g.out2_f32) return AETHER_E_BADARG;
+  if (!g.wpack2 || !g.out1 || !g.out2 || !z1 || !z2 || g.bias1 || g.bias2 || g.out2_f32) return AETHER_E_BADARG;
+  if (A ? !g.wpack1 : !g.gat16) return AETHER_E_BADARG;
   if (g.gat16 && (!g.idx_b || ((uintptr_t)g.gat16 & 15) || (g.ldg & 7))) return AETHER_E_BADARG;
   CUtensorMap ta, tz1, tz2, t1, t2;
-  AE_CHECK(tc_make_tmap_bf16(&ta, A, g.M, H, lda, kTileM));
+  AE_CHECK(tc_make_tmap_bf16(&ta, A ? A : z1, g.M, H, A ? lda : ldz1, kTileM));
   AE_CHECK(tc_make_tmap_bf16(&tz1, z1, g.M, H, ldz1, kTileM));
   AE_CHECK(tc_make_tmap_bf16(&tz2, z2, g.M, H, ldz2, kTileM));
   AE_CHECK(tc_make_tmap_bf16(&t1, g.out1, g.M, H, g.ldo1, 32, 32));
   AE_CHECK(tc_make_tmap_bf16(&t2, g.out2, g.M, H, g.ldo2, 32, 32));
   const bool gather = g.gat16 != nullptr;
-#define AE_CB_CASE(HH) if (H == HH) return gather ? launch_bwd<HH, true>(g, ta, tz1, tz2, t1, t2, st) : launch_bwd<HH, false>(g, ta, tz1, tz2, t1, t2, st);
+#define AE_CB_CASE(HH)                                                                                                  \
+  if (H == HH) {                                                                                                        \
+    if (!A) return launch_bwd<HH, true, false>(g, ta, tz1, tz2, t1, t2, st);                                            \
+    return gather ? launch_bwd<HH, true, true>(g, ta, tz1, tz2, t1, t2, st) : launch_bwd<HH, false, true>(g, ta, tz1, tz2, t1, t2, st); \
+  }
   AE_CB_CASE(256) AE_CB_CASE(128) AE_CB_CASE(64)
 #undef AE_CB_CASE
   return AETHER_E_UNSUPPORTED;

@@ -70,3 +70,30 @@ def test_chain_bwd(lib, H, M, gather):
     p1 = p1 * dsilu(z1.float())
     p2 = (p1.bfloat16().float() @ W2.bfloat16().float()) * dsilu(z2.float())
     assert rel_err(o1.float(), p1) < 2e-2 and rel_err(o2.float(), p2) < 2e-2
+
+
+@pytest.mark.parametrize("H", [64, 128, 256])
+@pytest.mark.parametrize("M", [100, 5000, 74 * 256 * 2 + 77])
+def test_chain_bwd_top_layer(lib, H, M):
+    """No first GEMM: out1 = gyd[recv] * silu'(z1) (the mean's backward), out2 = (out1 W2) * silu'(z2)."""
+    torch.manual_seed(3 + H + M)
+    W2 = torch.randn(H, H, device="cuda") / H ** 0.5
+    z1 = (torch.randn(M, H, device="cuda") * 2).bfloat16()
+    z2 = (torch.randn(M, H, device="cuda") * 2).bfloat16()
+    Nn = max(M // 9, 1) + 1
+    gat = (torch.randn(Nn, H, device="cuda") * 0.5).bfloat16()
+    recv = torch.arange(M, device="cuda", dtype=torch.int32) // 9
+    scratch = torch.empty(2 * H * H * 2, dtype=torch.uint8, device="cuda")
+    o1 = torch.full((M, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+    o2 = torch.full((M, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rc = lib.aether_dbg_tc_chain_bwd(None, M, H, None, P(W2), P(gat), H, P(recv), P(z1), P(z2), P(o1), P(o2), P(scratch), stream())
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    p1 = gat.float()[recv.long()] * dsilu(z1.float())
+    assert rel_err(o1.float(), p1) < 2e-2
+    u2 = torch.full((M, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rc = lib.aether_dbg_tc_gemm(P(o1), M, H, H, P(W2), H, H, H, H, 1, 0, 0, None, None, 0, None, None, 0, P(z2), P(u2), None,
+                                P(scratch), stream())
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+    assert torch.equal(o2, u2), "g1 differs from the separate GEMM on the same g2"
