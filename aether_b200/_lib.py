@@ -80,6 +80,7 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_dbg_tc_chain_bwd": (c_int, [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "aether_dbg_gather4_probe": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_int32, c_void_p, c_int32, c_void_p, c_void_p]),
     "aether_debug_stage": (c_int64, [POINTER(AetherDims), c_void_p, c_uint32, c_char_p, c_void_p, c_int64, c_void_p]),
 }
 

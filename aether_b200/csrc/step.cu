@@ -336,7 +336,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
         TcChainArgs c;
         c.M = E; c.wpack1 = w.wpA[l]; c.wpack2 = w.wpB[l]; c.bias1 = P[s.m0b]; c.bias2 = P[s.m2b];
         // layers 2-4: b1 is already inside P_r (bias of the node GEMM that produced it)
-        if (l > 1) { c.gat16 = ps16; c.ldg = H; c.idx_a = G.send; c.idx_b = G.recv; c.goff_b = pr16 - ps16; c.bias1 = nullptr; }
+        if (l > 1) { c.gat16 = ps16; c.ldg = H; c.idx_a = G.send; c.idx_b = G.recv; c.goff_b = pr16 - ps16; c.bias1 = nullptr; c.gat_rows = Nn; }
         c.out1 = (flags & AETHER_F_SAVE_FOR_BACKWARD) ? (__nv_bfloat16*)w.bpre1[l] : nullptr; c.ldo1 = H;
         c.out2 = (__nv_bfloat16*)w.bpre2[l]; c.ldo2 = H;
         if (l == 1) AE_CHECK(tc_chain(c, w.feat16, 64, 64, H, TC_TF_NONE, st));

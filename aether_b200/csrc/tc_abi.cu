@@ -70,3 +70,43 @@ extern "C" int aether_dbg_tc_chain_bwd(const void* A_bf16, int64_t M, int32_t H,
   g.out1 = (__nv_bfloat16*)out1_bf16; g.ldo1 = H; g.out2 = (__nv_bfloat16*)out2_bf16; g.ldo2 = H;
   return tc_chain_bwd(g, A_bf16, H, z1_bf16, H, z2_bf16, H, H, st);
 }
+
+// Probe of the TMA row gather (cp.async.bulk.tensor.2d.tile::gather4): 128 rows idx[0..127] of a bf16 table [Nn, ld], columns
+// [col0, col0 + 64), land in one 16 KB operand slot exactly like a 128 x 64 box load (128-byte swizzle); the raw slot is
+// copied to raw_out (16384 bytes) for the test to decode.  box_rows: the row extent the tensor map is encoded with.
+namespace {
+__global__ void gather4_probe_kernel(const __grid_constant__ CUtensorMap tm, const int32_t* __restrict__ idx, int col0,
+                                     uint8_t* __restrict__ raw_out) {
+  extern __shared__ __align__(1024) uint8_t smem_probe[];
+  __shared__ uint64_t bar;
+  const uint32_t b = aether::tc::smem_u32(&bar), d = aether::tc::smem_u32(smem_probe);
+  if (threadIdx.x == 0) {
+    aether::tc::mbar_init(b, 1);
+    aether::tc::fence_mbar_init();
+    aether::tc::mbar_arrive_expect_tx(b, 128 * 128);
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int i = threadIdx.x;
+    asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+                 :: "r"(d + 512u * i), "l"((uint64_t)&tm), "r"(col0), "r"(idx[4 * i]), "r"(idx[4 * i + 1]), "r"(idx[4 * i + 2]),
+                    "r"(idx[4 * i + 3]), "r"(b) : "memory");
+  }
+  aether::tc::mbar_wait(b, 0);
+  for (int k = threadIdx.x; k < 16384 / 16; k += blockDim.x)
+    reinterpret_cast<uint4*>(raw_out)[k] = reinterpret_cast<const uint4*>(smem_probe)[k];
+}
+}  // namespace
+
+extern "C" int aether_dbg_gather4_probe(const void* table_bf16, int64_t n_rows, int32_t n_cols, int64_t ld, int32_t box_rows,
+                                        const int32_t* idx128, int32_t col0, void* raw_out, void* stream) {
+  if (!table_bf16 || !idx128 || !raw_out) return AETHER_E_BADARG;
+  CUtensorMap tm;
+  AE_CHECK(tc_make_tmap_bf16(&tm, table_bf16, n_rows, n_cols, ld, box_rows));
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaFuncSetAttribute(gather4_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 + 1024);
+  if (e != cudaSuccess) return (int)e;
+  gather4_probe_kernel<<<1, 128, 16384, st>>>(tm, idx128, col0, (uint8_t*)raw_out);
+  AE_LAUNCH_CHECK();
+  return 0;
+}

@@ -245,7 +245,11 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     int ia = 0, ib = 0, ia_n = 0, ib_n = 0;
     auto request = [&](uint4 (&ds)[4], uint4 (&dr)[4], int ia_, int ib_, int c) {
       // 128-bit loads: the 256-bit form (ld.global.nc.v8.b32) measured the same on contiguous senders and 16 % slower
-      // on random ones (profiles/r02_chain_bench_v3.txt)
+      // on random ones (profiles/r02_chain_bench_v3.txt).  Feeding P_s[send] through the A ring with the TMA row gather
+      // (cp.async.bulk.tensor tile::gather4, 32 instructions per 128 x 64 box; it works -- tools/gather4_probe.py -- and
+      // the results were bit-identical) measured SLOWER, 9.8 vs 8.6 us per tile whatever the index pattern
+      // (profiles/r02_chain_bench_gather4.txt): ~58 cycles per gather4, and the boxes can only be requested once MMA 1
+      // has freed the slots.  The dense silu' operands of the backward kernel do go through the ring (tc_chain_bwd.cu).
       const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
       const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
 #pragma unroll

@@ -262,6 +262,10 @@ int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, 
 int aether_dbg_tc_chain_bwd(const void* A_bf16, int64_t M, int32_t H, const float* W1, const float* W2,
                             const void* gat_bf16, int64_t ldg, const int32_t* idx_b, const void* z1_bf16,
                             const void* z2_bf16, void* out1_bf16, void* out2_bf16, void* wpack_scratch, void* stream);
+/* Probe of the TMA row gather (tile::gather4): rows idx128[0..127] of a bf16 table, columns [col0, col0+64), into one
+ * 128-byte-swizzled 16 KB operand slot; raw_out receives the slot's 16384 bytes. */
+int aether_dbg_gather4_probe(const void* table_bf16, int64_t n_rows, int32_t n_cols, int64_t ld, int32_t box_rows,
+                             const int32_t* idx128, int32_t col0, void* raw_out, void* stream);
 
 #ifdef __cplusplus
 }
