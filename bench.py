@@ -260,11 +260,10 @@ def run_c5(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True):
     xd, vd, qd = [t.to(dev) for t in host]
     send, recv = ab.radius_graph(xd, cfg["radius"], cfg["k"])          # replicated on every rank, built once
     E = int(send.numel())
-    # One GPU: the T-step loop is replayed as one CUDA graph.  Several GPUs: launched eagerly -- capturing the NCCL
-    # all-gathers works and was measured (8 GPUs, H = 256: 11.4 vs 12.6 ms), but the processes did not exit cleanly
-    # afterwards (teardown of the captured communicator).  The teardown below now drops the graphs before every rank leaves
-    # the communicator together; until that is confirmed on 8 GPUs the captured form stays opt-in (--graph).
-    use_graph = (world == 1 and not args.no_graph) or (world > 1 and args.graph)
+    # The T-step loop -- on several GPUs including its NCCL all-gathers -- is replayed as ONE CUDA graph (8 GPUs, H = 256:
+    # 9.5 vs 10.4 ms per 5-step rollout eager; H = 64: 3.95 vs 4.85 ms; profiles/r02_c5_8gpu.md).  The captured graphs are
+    # released before the communicator is torn down (roll.release() below); --no-graph launches eagerly.
+    use_graph = not args.no_graph
     roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, cuda_graph=use_graph)
     eager = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank) if use_graph else roll
 
