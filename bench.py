@@ -451,7 +451,9 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
 
     # small training shapes are launch-latency bound: replay the whole step as one CUDA graph
     graphed = None
-    if train and (E * H <= 32e6 or args.graph) and not args.no_graph:
+    # (up to ~1.5 M edges at H = 256 -- config 4's strong-scaling share at 8 GPUs -- replay still beats eager launches:
+    # 10.4 vs 10.8 ms per step at 128 graphs)
+    if train and (E * H <= 400e6 or args.graph) and not args.no_graph:
         opt = ab.FusedAdamW(model.parameters(), lr=5e-4, weight_decay=1e-12)       # capturable: the step count is on the device
         graphed = ab.GraphedTrainStep(model, opt, (send, recv), Nn, allreduce=(lambda: adist.allreduce_grads(params, world))
                                       if world > 1 else None)
