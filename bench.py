@@ -589,11 +589,11 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
                                          "frac": (nb / (ms_per_layer * 1e-3) / 1e9) / pk["hbm_gbs"]
                                          if ms_per_layer > 0 and pk.get("hbm_gbs") else None})(
                     ((3.0 if train else 2.0) * E * H - (E * (H - 64)) / 4.0) * esz)}
-    # backward of the edge MLPs: data-gradient GEMMs (3 [E,H] passes each: dY, the saved pre-activation, dX; 7 of
-    # them + the layer-1 feature gradient + the top layer's elementwise pass) and weight-gradient GEMMs (2 passes each)
+    # backward of the edge MLPs: data gradients = 3 chained layer pairs (5 [E,H] passes each: g1, pre2, pre1 in; g2, g1 out),
+    # the top layer (4 passes) and the layer-1 feature gradient (reads g1, writes [E,32] fp32); weight gradients 2 passes each
     extra = {}
     if train and prof["ms"][1] > 0:
-        nb = E * H * esz * (3.0 * 7 + 3.0) + E * (H * esz + 32 * 4)
+        nb = E * H * esz * (3 * 5.0 + 4.0) + E * (H * esz + 32 * 4)
         ms = prof["ms"][1] / steps
         extra["roofline_bwd"] = {"bound": "hbm", "kernel": "edge-MLP backward, data gradients (per step)", "unit": "GB/s",
                                  "achieved": nb / (ms * 1e-3) / 1e9, "peak": pk.get("hbm_gbs"),
