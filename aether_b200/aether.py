@@ -33,6 +33,15 @@ def _warn_bf16_fallback(precision, hidden_size):
                       "the fp32 CUDA-core kernels (much slower, fp32 accuracy)" % hidden_size, RuntimeWarning, stacklevel=3)
 
 
+def check_charges(charges):
+    """The reference indexes ``nn.Embedding(3, .)`` with ``(charges + 1).long()`` (aether.py:123-125) and raises on a class
+    outside 0..2; the kernels clamp the index for memory safety.  With AETHER_B200_VALIDATE=1 the modules check it here (a
+    host read: synchronises)."""
+    idx = (charges + 1).long()
+    if idx.numel() and (int(idx.min()) < 0 or int(idx.max()) > 2):
+        raise IndexError("aether_b200: charge class (charges + 1).long() outside 0..2")
+
+
 class GNNLayer(nn.Module):
     """Parameter holder of one message-passing layer (nn/state2state/locs/locs.py:197-225)."""
 
@@ -178,4 +187,6 @@ class Aether(nn.Module):
         graph = self.prepare_graph(edges, Nn)
         mask = dropout_masks(self.training, self.dropout_prob, Nn, H, x.device)
         charges = charges.reshape(-1)
+        if os.environ.get("AETHER_B200_VALIDATE", "0") == "1":
+            check_charges(charges)
         return step_apply(x, vel, charges, edge_attr_orig, graph, D, H, self.flags(), mask, self.param_list())

@@ -22,7 +22,7 @@ from torch import nn
 from torch.autograd.function import once_differentiable
 
 from . import _lib
-from .aether import Aether, AetherLocalizer, Globalizer, GNN, _warn_bf16_fallback
+from .aether import Aether, AetherLocalizer, Globalizer, GNN, _warn_bf16_fallback, check_charges
 from .ops import _dims, _f32c, _stream, dropout_masks
 
 F_EXTERNAL_FIELD = 4
@@ -221,6 +221,8 @@ class DynamicFieldAether(nn.Module):
         graph = self.prepare_graph(edges, Nn)
         mask = dropout_masks(self.training, self.dropout_prob, Nn, H, x.device)
         params = self.param_list()
+        if os.environ.get("AETHER_B200_VALIDATE", "0") == "1":
+            check_charges(charges.reshape(-1))
         save = torch.is_grad_enabled() and (x.requires_grad or vel.requires_grad or any(p.requires_grad for p in params))
         return _DynStepFn.apply(x, vel, charges.reshape(-1), edge_attr_orig, graph, D, H, self.flags(), num_nodes, mask,
                                 save, *params)
