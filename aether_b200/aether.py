@@ -189,4 +189,8 @@ class Aether(nn.Module):
         charges = charges.reshape(-1)
         if os.environ.get("AETHER_B200_VALIDATE", "0") == "1":
             check_charges(charges)
+        if mask is None and torch.is_grad_enabled() and (getattr(self, "use_registered_ops", False) or
+                                                          os.environ.get("AETHER_B200_TORCH_OPS", "0") == "1"):
+            from . import torch_ops          # the same step as registered torch.library operators (step_fwd / step_bwd)
+            return torch_ops.train_step_from_model(self, graph, x, vel, charges, edge_attr_orig)
         return step_apply(x, vel, charges, edge_attr_orig, graph, D, H, self.flags(), mask, self.param_list())
