@@ -41,6 +41,7 @@ SOURCES = [
     ("edge_bf16.cu", []),
     ("prof.cu", []),
     ("optim.cu", []),
+    ("field.cu", []),
     ("dynfield.cu", []),
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),

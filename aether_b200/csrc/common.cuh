@@ -94,6 +94,14 @@ struct NodeBufs {
 };
 int launch_field_input(int D, int64_t Nn, const float* x, const float* vel, const float* charges,
                        const float* emb /*[3,16]*/, float* fin, cudaStream_t st);
+// the whole field MLP in one launch (field.cu): fin, the two pre-activations [Nn,32] and the field [Nn,D]
+int launch_field_mlp_fwd(int D, int64_t Nn, const float* x, const float* vel, const float* charges, const float* emb,
+                         const float* W0, const float* b0, const float* W2, const float* b2, const float* W4, const float* b4,
+                         float* fin, float* z1, float* z2, float* f, cudaStream_t st);
+size_t field_mlp_bwd_partial_floats(int D, int64_t Nn);
+int launch_field_mlp_bwd(int D, int64_t Nn, const float* gf, const float* fin, const float* z1, const float* z2, const float* W0,
+                         const float* W2, const float* W4, float* gfin, float* dW0, float* db0, float* dW2, float* db2,
+                         float* dW4, float* db4, float* partial, size_t partial_floats, cudaStream_t st);
 int launch_node_frame(int D, int64_t Nn, const float* vel, const float* f, float* R, float* x0, cudaStream_t st);
 int launch_edge_features(int D, int64_t E, const int32_t* send, const int32_t* recv, const int32_t* perm,
                          const float* x, const float* vel, const float* f, const float* R, const float* x0,

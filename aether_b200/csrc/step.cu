@@ -162,6 +162,7 @@ size_t partial_need(const AetherDims& d, uint32_t flags) {
   up(gemm_tn_partial_floats(D, 32, Nn));
   up(colsum_partial_floats(Nn, 2 * H));
   up(256 * 48);   // embedding gradient: per-block class sums
+  up(field_mlp_bwd_partial_floats(D, Nn));
   return m + 64;
 }
 
@@ -304,11 +305,8 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
       AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
     } else {
     ProfScope pn(PROF_NODE, st);
-    AE_CHECK(launch_field_input(D, Nn, x, vel, q, P[P_EMB], w.fin, st));
-    AE_CHECK(linear(nc, w.fin, 2 * D + 16, Nn, 2 * D + 16, P[P_F0_W], 2 * D + 16, P[P_F0_B], 32, w.fz1, 32, TF_NONE, nullptr,
-                    nullptr, 0, st));
-    AE_CHECK(linear(nc, w.fz1, 32, Nn, 32, P[P_F2_W], 32, P[P_F2_B], 32, w.fz2, 32, TF_SILU, nullptr, nullptr, 0, st));
-    AE_CHECK(linear(nc, w.fz2, 32, Nn, 32, P[P_F4_W], 32, P[P_F4_B], D, w.f, D, TF_SILU, nullptr, nullptr, 0, st));
+    AE_CHECK(launch_field_mlp_fwd(D, Nn, x, vel, q, P[P_EMB], P[P_F0_W], P[P_F0_B], P[P_F2_W], P[P_F2_B], P[P_F4_W], P[P_F4_B],
+                                  w.fin, w.fz1, w.fz2, w.f, st));
     // local frames and features (aether.py:33-100,177)
     AE_CHECK(launch_node_frame(D, Nn, vel, w.f, w.R, w.x0, st));
     }

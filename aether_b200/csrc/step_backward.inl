@@ -279,14 +279,9 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
     // the field was an input: hand its gradient to the caller (dynfield.cu continues from there)
     return (int)cudaMemcpyAsync(G[P_F0_W], s.gf, (size_t)Nn * D * sizeof(float), cudaMemcpyDeviceToDevice, st);
   }
-  // field network (aether.py:113-119,127-134)
-  AE_CHECK(b.wgrad(s.gf, D, Nn, D, w.fz2, 32, 32, TF_SILU, nullptr, G[P_F4_W], 32, G[P_F4_B]));
-  AE_CHECK(b.dgrad(s.gf, D, Nn, D, P[P_F4_W], 32, 32, s.gfz2, 32, w.fz2, nullptr, nullptr, 0));
-  AE_CHECK(b.wgrad(s.gfz2, 32, Nn, 32, w.fz1, 32, 32, TF_SILU, nullptr, G[P_F2_W], 32, G[P_F2_B]));
-  AE_CHECK(b.dgrad(s.gfz2, 32, Nn, 32, P[P_F2_W], 32, 32, s.gfz1, 32, w.fz1, nullptr, nullptr, 0));
-  const int FI = 2 * D + 16;
-  AE_CHECK(b.wgrad(s.gfz1, 32, Nn, 32, w.fin, FI, FI, TF_NONE, nullptr, G[P_F0_W], FI, G[P_F0_B]));
-  AE_CHECK(b.dgrad(s.gfz1, 32, Nn, 32, P[P_F0_W], FI, FI, s.gfin, FI, nullptr, nullptr, nullptr, 0));
+  // field network (aether.py:113-119,127-134): input gradient and all six parameter gradients in two launches (field.cu)
+  AE_CHECK(launch_field_mlp_bwd(D, Nn, s.gf, w.fin, w.fz1, w.fz2, P[P_F0_W], P[P_F2_W], P[P_F4_W], s.gfin, G[P_F0_W], G[P_F0_B],
+                                G[P_F2_W], G[P_F2_B], G[P_F4_W], G[P_F4_B], s.partial, s.partial_floats, st));
   AE_CHECK(launch_embedding_bwd(D, Nn, q, s.gfin, G[P_EMB], s.partial, s.partial_floats, st));
   if (gx_out || gvel_out) AE_CHECK(launch_add_field_input_grads(D, Nn, s.gfin, gx_out, gvel_out, st));
   return 0;

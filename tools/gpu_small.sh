@@ -1,20 +1,11 @@
 #!/bin/bash
-for mode in "--no-graph" "--graph"; do
-timeout 300 python bench.py --batch 128 $mode --steps 20 --warmup 5 --no-cpu-baseline --no-e2e --no-secondary 2>/dev/null | python -c "
+# per-rank share of config 5 at 8 GPUs, without the exchange: a 12.5k-particle scene (same density) on one GPU
+for H in 256 64; do
+timeout 300 python bench.py --workload c5 --batch 12500 --hidden $H --steps 20 --warmup 5 --no-cpu-baseline --no-e2e 2>/dev/null | python -c "
 import json,sys
 for l in sys.stdin:
     if l.startswith('{'):
-        d=json.loads(l); print('b128 $mode', d['ms_per_step'], d['gpu_launches'], d['config']['mode'][:40])
+        d=json.loads(l); print('c5 12.5k h$H', d['ms_per_step'], d['gpu_launches'], d['config']['edges'])
 "; done
-timeout 300 python bench.py --workload c5 --hidden 256 --steps 10 --warmup 3 --no-cpu-baseline --no-e2e 2>/dev/null | python -c "
-import json,sys
-for l in sys.stdin:
-    if l.startswith('{'):
-        d=json.loads(l); print('c5 h256 1gpu', d['ms_per_step'], d['gpu_launches'])
-"
-timeout 300 python bench.py --workload c5 --hidden 64 --steps 10 --warmup 3 --no-cpu-baseline --no-e2e 2>/dev/null | python -c "
-import json,sys
-for l in sys.stdin:
-    if l.startswith('{'):
-        d=json.loads(l); print('c5 h64 1gpu', d['ms_per_step'], d['gpu_launches'])
-"
+CMD="python bench.py --workload c5 --batch 12500 --hidden 256 --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --no-graph"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_c5_12k.csv $CMD > gpurun_out/ncu_c5.log 2>&1; echo "ncu rc=$?"
