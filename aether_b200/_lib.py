@@ -78,6 +78,9 @@ SIGNATURES = {
     "aether_dbg_tc_chain": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                     c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    "aether_dbg_tc_chain_ex": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_int64, c_int32, c_int32, c_void_p,
+                                       c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32,
+                                       c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "aether_dbg_tc_chain_bwd": (c_int, [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_dbg_gather4_probe": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_int32, c_void_p, c_int32, c_void_p, c_void_p]),

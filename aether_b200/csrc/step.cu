@@ -207,6 +207,16 @@ bool use_chain() {
   return v == 1;
 }
 
+// AETHER_B200_BOX_GATHER=1: the caller asserts that (nearly) every 128-edge tile of the receiver-sorted list has senders
+// within 128 consecutive node rows (batched small graphs); the forward then feeds P_s by TMA boxes.  Off by default: it
+// measured 8.8 vs 9.1 us per tile (profiles/r02_chain_bench_box.txt) -- the gather variant's cost is the epilogue's
+// instruction count, not the sender loads -- and tiles that do not fit take an unprefetched path.
+int box_gather_hint() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("AETHER_B200_BOX_GATHER"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v;
+}
+
 bool dims_ok(const AetherDims* d) {
   return d && (d->num_dims == 2 || d->num_dims == 3) && d->hidden >= 4 && d->hidden % 4 == 0 && d->n_nodes >= 0 &&
          d->n_edges >= 0 && d->n_nodes < ((int64_t)1 << 31) && d->n_edges < ((int64_t)1 << 31);
@@ -334,7 +344,7 @@ int forward(const AetherDims& d, const float* const* P, const AetherGraph& G, co
         TcChainArgs c;
         c.M = E; c.wpack1 = w.wpA[l]; c.wpack2 = w.wpB[l]; c.bias1 = P[s.m0b]; c.bias2 = P[s.m2b];
         // layers 2-4: b1 is already inside P_r (bias of the node GEMM that produced it)
-        if (l > 1) { c.gat16 = ps16; c.ldg = H; c.idx_a = G.send; c.idx_b = G.recv; c.goff_b = pr16 - ps16; c.bias1 = nullptr; c.gat_rows = Nn; }
+        if (l > 1) { c.gat16 = ps16; c.ldg = H; c.idx_a = G.send; c.idx_b = G.recv; c.goff_b = pr16 - ps16; c.bias1 = nullptr; c.gat_rows = Nn; c.box_gather = box_gather_hint(); }
         c.out1 = (flags & AETHER_F_SAVE_FOR_BACKWARD) ? (__nv_bfloat16*)w.bpre1[l] : nullptr; c.ldo1 = H;
         c.out2 = (__nv_bfloat16*)w.bpre2[l]; c.ldo2 = H;
         if (l == 1) AE_CHECK(tc_chain(c, w.feat16, 64, 64, H, TC_TF_NONE, st));

@@ -34,11 +34,11 @@ extern "C" int aether_dbg_tc_wgrad(const void* G_bf16, int32_t MG, const void* A
 
 // Chained edge MLP (tc_chain.cu): out2 = silu(out1) W2^T + b2, out1 = tf1(A) W1^T + b1 (+ gathered rows).
 // wpack_scratch: (K1 + H) * H * 2 bytes.  out1 may be null (inference: the intermediate is not stored).
-extern "C" int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, const float* W1, int64_t ldw1,
-                                   int32_t k1_valid, int32_t kmod1, const float* W2, int32_t H, int32_t silu_on_load,
-                                   const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
-                                   const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
-                                   void* out2_bf16, void* wpack_scratch, void* stream) {
+extern "C" int aether_dbg_tc_chain_ex(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, const float* W1, int64_t ldw1,
+                                      int32_t k1_valid, int32_t kmod1, const float* W2, int32_t H, int32_t silu_on_load,
+                                      const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
+                                      const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
+                                      void* out2_bf16, void* wpack_scratch, int64_t gat_rows, int32_t box_gather, void* stream) {
   if (!A_bf16 || !W1 || !W2 || !wpack_scratch || !out2_bf16) return AETHER_E_BADARG;
   if (!tc_chain_supported(K1, H)) return AETHER_E_UNSUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
@@ -48,8 +48,18 @@ extern "C" int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, in
   TcChainArgs g;
   g.M = M; g.wpack1 = wpack_scratch; g.wpack2 = wp2; g.bias1 = bias1; g.bias2 = bias2;
   g.gat16 = (const __nv_bfloat16*)gat_bf16; g.ldg = ldg; g.idx_a = idx_a; g.idx_b = idx_b; g.goff_b = goff_b;
+  g.gat_rows = gat_rows; g.box_gather = box_gather;
   g.out1 = (__nv_bfloat16*)out1_bf16; g.ldo1 = H; g.out2 = (__nv_bfloat16*)out2_bf16; g.ldo2 = H;
   return tc_chain(g, A_bf16, lda, K1, H, silu_on_load ? TC_TF_SILU : TC_TF_NONE, st);
+}
+
+extern "C" int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, const float* W1, int64_t ldw1,
+                                   int32_t k1_valid, int32_t kmod1, const float* W2, int32_t H, int32_t silu_on_load,
+                                   const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
+                                   const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
+                                   void* out2_bf16, void* wpack_scratch, void* stream) {
+  return aether_dbg_tc_chain_ex(A_bf16, M, K1, lda, W1, ldw1, k1_valid, kmod1, W2, H, silu_on_load, bias1, bias2, gat_bf16, ldg,
+                                idx_a, idx_b, goff_b, out1_bf16, out2_bf16, wpack_scratch, 0, 0, stream);
 }
 
 // Chained data-gradient GEMMs (tc_chain_bwd.cu): out1 = (A W1 (+ gat[idx_b[m]])) * silu'(z1), out2 = (out1 W2) * silu'(z2);

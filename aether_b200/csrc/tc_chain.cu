@@ -67,10 +67,11 @@ __host__ __device__ constexpr int smem_bytes(int K1, int H) {
   return w1_bytes(K1, H) + w2_bytes(H) + num_slots(K1, H) * kSlotBytes + kStageBytes + misc_bytes(H);
 }
 
-template <int K1, int H, int TF1, bool SAVE, bool GATHER, bool OUT32>
+template <int K1, int H, int TF1, bool SAVE, bool GATHER, bool OUT32, bool BOX>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmO1,
-                const __grid_constant__ CUtensorMap tmO2, TcChainArgs g) {
+                const __grid_constant__ CUtensorMap tmO2, const __grid_constant__ CUtensorMap tmG, TcChainArgs g) {
+  static_assert(!BOX || GATHER, "the box feed is a form of the gather variant");
   static_assert(K1 % 64 == 0 && (H == 64 || H == 128 || H == 256), "unsupported shape");
   constexpr int KC1 = K1 / 64;                     // 64-wide K chunks of the first GEMM = ring slots per tile
   constexpr int S = num_slots(K1, H);
@@ -79,6 +80,12 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   constexpr uint32_t IDESC = make_idesc(256, H, MAJOR_K, MAJOR_K);
   constexpr uint32_t TMEM_COLS = 2 * H;            // 128 / 256 / 512
   constexpr int WROW = (H / 2) * 128;              // bytes of one 64-wide K chunk of this CTA's weight half
+  // BOX: the sender term P_s[send] of a tile whose senders span fewer than 128 node rows (batched small graphs: a tile
+  // lies inside one graph) is ONE 128-row box of the node-term table per 64 columns, loaded by TMA into the same ring
+  // after the A boxes; the epilogue reads row (send - base) of the box.  Tiles that do not fit (graph boundaries) fall
+  // back to direct loads.  Chosen per launch from the graph's statistics (TcChainArgs::box_gather).
+  constexpr int NG = BOX ? H / 64 : 0;             // sender-term boxes per tile
+  constexpr int LPT = KC1 + NG;                    // ring loads per tile
   static_assert(S >= 2, "pipeline too shallow");
 
   // The dynamic shared memory of a kernel without static shared memory starts 1024-byte aligned (the swizzle atom of
@@ -101,6 +108,9 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const uint32_t bar_acc2e = sMisc + 240;          // accumulator 2 drained, 16 warps of the pair        (leader's)
   const uint32_t bar_w = sMisc + 248;              // weights landed                       (this CTA)
   const uint32_t tmem_slot = sMisc + 256;
+  const uint32_t bar_zfree = sMisc + 320;          // [S] the 8 epilogue warps read the sender-term box   (this CTA)
+  const uint32_t bar_rawz = sMisc + 384;           // [S] sender-term box landed (or: tile falls back)    (this CTA)
+  const uint32_t sBase = sMisc + 448;              // [S] int32: first node row of the box in the slot, -1 = fall back
   uint8_t* misc_ptr = smem_raw + (sMisc - smem_u32(smem_raw));
   float* sb1 = reinterpret_cast<float*>(misc_ptr + 512);
   float* sb2 = sb1 + H;
@@ -115,6 +125,8 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_init(bar_raw + 8 * s, 1);
       mbar_init(bar_rdy + 8 * s, 8);
       mbar_init(bar_free + 8 * s, 1);
+      mbar_init(bar_zfree + 8 * s, kEpiWarps);
+      mbar_init(bar_rawz + 8 * s, 1);
     }
     for (int h = 0; h < NP; ++h) mbar_init(bar_a2 + 8 * h, 2 * kEpiWarps);
     mbar_init(bar_acc1f, 1);
@@ -131,6 +143,7 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp == kWarpMma) tmem_alloc_2cta(tmem_slot, TMEM_COLS);
   if (warp == kWarpTma && lane == 0) {
     tma_prefetch_desc(&tmA);
+    if (BOX) tma_prefetch_desc(&tmG);
     if (!OUT32) tma_prefetch_desc(&tmO2);
     if (SAVE) tma_prefetch_desc(&tmO1);
     // this CTA's half of the rows of every 64-wide K chunk of both images
@@ -151,16 +164,50 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp >= kEpiWarps) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" :: "n"(kRegsAux));
 
   if (warp == kWarpTma) {
-    // ===== TMA producer (both CTAs, own rows) =====
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (int64_t pt = cid; pt < n_pt; pt += ncl) {
-        const int row0 = (int)(pt * 2 * kTileM + rank * kTileM);
-        for (int c = 0; c < KC1; ++c, ++it) {
-          const uint32_t s = it % S, ph = (it / S) & 1;
-          mbar_wait(bar_free + 8 * s, ph ^ 1);
-          mbar_arrive_expect_tx(bar_raw + 8 * s, kSlotBytes);
-          tma_load_2d(sA + s * kSlotBytes, &tmA, c * 64, row0, bar_raw + 8 * s);
+    // ===== TMA producer (both CTAs, own rows): per tile the A boxes, then (BOX) the sender-term boxes.  Ring protocol as
+    // in tc_chain_bwd.cu: before reusing a slot the producer waits on the barrier of the slot's previous use (MMA commit
+    // for A boxes, the eight epilogue warps for sender-term boxes); separate landing barriers per kind. =====
+    uint32_t it = 0, nA = 0, nZ = 0, lastZ = 0;
+    for (int64_t pt = cid; pt < n_pt; pt += ncl) {
+      const int row0 = (int)(pt * 2 * kTileM + rank * kTileM);
+      int base = -1;
+      if (BOX) {
+        // senders of this CTA's 128 rows: 4 per lane; the box fits if they span fewer than 128 node rows
+        int lo = 0x7fffffff, hi = -1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int64_t r = (int64_t)row0 + 4 * lane + q;
+          if (r < g.M) { const int v = g.idx_a[r]; lo = v < lo ? v : lo; hi = v > hi ? v : hi; }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+          const int l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+          lo = l2 < lo ? l2 : lo; hi = h2 > hi ? h2 : hi;
+        }
+        if (hi >= 0 && hi - lo < kTileM) base = lo;
+      }
+      if (lane == 0) {
+        for (int c = 0; c < LPT; ++c, ++it) {
+          const uint32_t s = it % S, bit = 1u << s;
+          const bool isA = c < KC1;
+          if (it >= (uint32_t)S) {
+            if (lastZ & bit) mbar_wait(bar_zfree + 8 * s, ((nZ >> s) & 1) ^ 1);
+            else mbar_wait(bar_free + 8 * s, ((nA >> s) & 1) ^ 1);
+          }
+          if (isA) {
+            mbar_arrive_expect_tx(bar_raw + 8 * s, kSlotBytes);
+            tma_load_2d(sA + s * kSlotBytes, &tmA, c * 64, row0, bar_raw + 8 * s);
+            nA ^= bit; lastZ &= ~bit;
+          } else {
+            asm volatile("st.shared.b32 [%0], %1;" :: "r"(sBase + 4 * s), "r"(base) : "memory");
+            if (base >= 0) {
+              mbar_arrive_expect_tx(bar_rawz + 8 * s, kSlotBytes);
+              tma_load_2d(sA + s * kSlotBytes, &tmG, (c - KC1) * 64, base, bar_rawz + 8 * s);
+            } else {
+              mbar_arrive(bar_rawz + 8 * s);       // nothing to land: the epilogue loads this tile's rows itself
+            }
+            nZ ^= bit; lastZ |= bit;
+          }
         }
       }
     }
@@ -168,13 +215,14 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===== MMA issuer (leader CTA) =====
     if (rank == 0 && lane == 0) {
       const uint32_t acc1 = tmem_base, acc2 = tmem_base + H;
-      uint32_t it = 0, lt = 0;
+      uint32_t lt = 0, nA = 0;
       for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
         // accumulator 1 is free: MMA 2 of the previous tile (which read A2 out of its columns) was issued before
         // this point and the tensor pipe executes in issue order
-        for (int c = 0; c < KC1; ++c, ++it) {
-          const uint32_t s = it % S, ph = (it / S) & 1;
-          mbar_wait_cluster(bar_rdy + 8 * s, ph);
+        for (int c = 0; c < KC1; ++c) {
+          const uint32_t s = (lt * LPT + c) % S;
+          mbar_wait_cluster(bar_rdy + 8 * s, (nA >> s) & 1);
+          nA ^= 1u << s;
           tc_fence_after();
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
@@ -206,11 +254,12 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===== transform: in-place SiLU on the landed A box, then "ready" to the leader =====
     const int tt = threadIdx.x - kWarpTf0 * 32;    // 0..127
     const uint32_t rdy0 = mapa_rank(bar_rdy, 0);
-    uint32_t it = 0;
-    for (int64_t pt = cid; pt < n_pt; pt += ncl) {
-      for (int c = 0; c < KC1; ++c, ++it) {
-        const uint32_t s = it % S, ph = (it / S) & 1;
-        mbar_wait(bar_raw + 8 * s, ph);
+    uint32_t lt = 0, nA = 0;
+    for (int64_t pt = cid; pt < n_pt; pt += ncl, ++lt) {
+      for (int c = 0; c < KC1; ++c) {
+        const uint32_t s = (lt * LPT + c) % S;
+        mbar_wait(bar_raw + 8 * s, (nA >> s) & 1);
+        nA ^= 1u << s;
         if (TF1 == TC_TF_SILU) {
           const uint32_t a0 = sA + s * kSlotBytes + tt * 16;
 #pragma unroll
@@ -239,7 +288,7 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t a2bar0 = mapa_rank(bar_a2, 0), acc2e0 = mapa_rank(bar_acc2e, 0);
     const uint32_t lane_base = tmem_base + ((uint32_t)(qr * 32) << 16);
     const bool has_b1 = g.bias1 != nullptr;
-    uint32_t lt = 0, nbox = 0;
+    uint32_t lt = 0, nbox = 0, nZ = 0;             // nZ bit s: parity of the sender-term boxes this warp took from slot s
     // gathered node terms: slot kk holds the 64-byte pieces of P_s[send] and P_r[recv] for chunk position kk
     uint4 gs[CPW][4], gr[CPW][4];
     int ia = 0, ib = 0, ia_n = 0, ib_n = 0;
@@ -253,7 +302,7 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia_ * g.ldg + c);
       const uint4* pb = reinterpret_cast<const uint4*>(g.gat16 + ((int64_t)ib_ * g.ldg + g.goff_b + c));
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { ds[q] = __ldg(pa + q); dr[q] = __ldg(pb + q); }
+      for (int q = 0; q < 4; ++q) { if (!BOX) ds[q] = __ldg(pa + q); dr[q] = __ldg(pb + q); }
     };
     if (GATHER && cid < n_pt) {
       const int64_t r0 = cid * 2 * kTileM + rank * kTileM + qr * 32 + lane;
@@ -322,11 +371,43 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
             for (int e = 0; e < 4; ++e) v[4 * q + e] = f2_add(v[4 * q + e], f2_from_bf16x2(bb[e]));
           }
+          if (BOX) {
+            // sender term out of the box in ring slot zs (this thread's row is node `ia`, box row ia - base), or -- tiles
+            // whose senders span 128 rows or more -- straight from the table
+            const uint32_t zs = (lt * LPT + KC1 + kk) % S;
+            mbar_wait(bar_rawz + 8 * zs, (nZ >> zs) & 1);
+            nZ ^= 1u << zs;
+            int base;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(base) : "r"(sBase + 4 * zs) : "memory");
+            uint4 a4[4];
+            if (base >= 0) {
+              int lr = ia - base;
+              lr = lr < 0 ? 0 : (lr > kTileM - 1 ? kTileM - 1 : lr);          // rows past M carry no valid index
+              const uint32_t za = sA + zs * kSlotBytes + (uint32_t)((lr >> 3) * 1024 + (lr & 7) * 128);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint32_t aa[4] = {gs[kk][q].x, gs[kk][q].y, gs[kk][q].z, gs[kk][q].w};
+              for (int q = 0; q < 4; ++q)
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a4[q].x), "=r"(a4[q].y), "=r"(a4[q].z), "=r"(a4[q].w)
+                             : "r"(za + (uint32_t)(((4 * hf + q) ^ (lr & 7)) << 4)));
+            } else {
+              const uint4* pa = reinterpret_cast<const uint4*>(g.gat16 + (size_t)ia * g.ldg + c0);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) v[4 * q + e] = f2_add(v[4 * q + e], f2_from_bf16x2(aa[e]));
+              for (int q = 0; q < 4; ++q) a4[q] = __ldg(pa + q);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t aa[4] = {a4[q].x, a4[q].y, a4[q].z, a4[q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) v[4 * q + e] = f2_add(v[4 * q + e], f2_from_bf16x2(aa[e]));
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_zfree + 8 * zs);      // the adds above consumed every lane's loads
+          } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t aa[4] = {gs[kk][q].x, gs[kk][q].y, gs[kk][q].z, gs[kk][q].w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) v[4 * q + e] = f2_add(v[4 * q + e], f2_from_bf16x2(aa[e]));
+            }
           }
           if (!TOP) prefetch(kk);
         }
@@ -459,11 +540,12 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
 }
 
-template <int K1, int H, int TF1, bool SAVE, bool GATHER, bool OUT32>
-int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, cudaStream_t st) {
+template <int K1, int H, int TF1, bool SAVE, bool GATHER, bool OUT32, bool BOX = false>
+int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, const CUtensorMap& tg,
+                 cudaStream_t st) {
   constexpr int smem = smem_bytes(K1, H);
   static_assert(smem <= kSmemMax, "shared memory budget");
-  auto kern = tc_chain_kernel<K1, H, TF1, SAVE, GATHER, OUT32>;
+  auto kern = tc_chain_kernel<K1, H, TF1, SAVE, GATHER, OUT32, BOX>;
   static int max_clusters = 0;                     // co-resident CTA pairs (one per TPC): 74 on a full B200
   if (max_clusters == 0) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -483,34 +565,39 @@ int launch_chain(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap&
   }
   const int64_t n_pt = (g.M + 2 * kTileM - 1) / (2 * kTileM);
   const unsigned ncl = (unsigned)(n_pt < max_clusters ? n_pt : max_clusters);
-  kern<<<2 * ncl, kThreads, smem, st>>>(ta, t1, t2, g);
+  kern<<<2 * ncl, kThreads, smem, st>>>(ta, t1, t2, tg, g);
   AE_LAUNCH_CHECK();
   return 0;
 }
 
 template <int K1, int H, int TF1>
-int launch_tf(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, bool save,
-              cudaStream_t st) {
+int launch_tf(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, const CUtensorMap& tg,
+              bool save, cudaStream_t st) {
   const bool gather = g.gat16 != nullptr;
   if (g.out2_f32) {
     // node update: fp32 output with residual, no gather, plain (already activated / linear) operand
     if constexpr (K1 == H && TF1 == TC_TF_NONE) {
       if (gather) return AETHER_E_UNSUPPORTED;
-      return save ? launch_chain<K1, H, TF1, true, false, true>(g, ta, t1, t2, st)
-                  : launch_chain<K1, H, TF1, false, false, true>(g, ta, t1, t2, st);
+      return save ? launch_chain<K1, H, TF1, true, false, true>(g, ta, t1, t2, tg, st)
+                  : launch_chain<K1, H, TF1, false, false, true>(g, ta, t1, t2, tg, st);
     } else {
       return AETHER_E_UNSUPPORTED;
     }
   }
-  if (save) return gather ? launch_chain<K1, H, TF1, true, true, false>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, true, false, false>(g, ta, t1, t2, st);
-  return gather ? launch_chain<K1, H, TF1, false, true, false>(g, ta, t1, t2, st) : launch_chain<K1, H, TF1, false, false, false>(g, ta, t1, t2, st);
+  if constexpr (K1 == H && TF1 == TC_TF_SILU) {
+    if (gather && g.box_gather)
+      return save ? launch_chain<K1, H, TF1, true, true, false, true>(g, ta, t1, t2, tg, st)
+                  : launch_chain<K1, H, TF1, false, true, false, true>(g, ta, t1, t2, tg, st);
+  }
+  if (save) return gather ? launch_chain<K1, H, TF1, true, true, false>(g, ta, t1, t2, tg, st) : launch_chain<K1, H, TF1, true, false, false>(g, ta, t1, t2, tg, st);
+  return gather ? launch_chain<K1, H, TF1, false, true, false>(g, ta, t1, t2, tg, st) : launch_chain<K1, H, TF1, false, false, false>(g, ta, t1, t2, tg, st);
 }
 
 template <int K1, int H>
-int launch_kh(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, int tf1, bool save,
-              cudaStream_t st) {
-  if (tf1 == TC_TF_SILU) return launch_tf<K1, H, TC_TF_SILU>(g, ta, t1, t2, save, st);
-  return launch_tf<K1, H, TC_TF_NONE>(g, ta, t1, t2, save, st);
+int launch_kh(const TcChainArgs& g, const CUtensorMap& ta, const CUtensorMap& t1, const CUtensorMap& t2, const CUtensorMap& tg,
+              int tf1, bool save, cudaStream_t st) {
+  if (tf1 == TC_TF_SILU) return launch_tf<K1, H, TC_TF_SILU>(g, ta, t1, t2, tg, save, st);
+  return launch_tf<K1, H, TC_TF_NONE>(g, ta, t1, t2, tg, save, st);
 }
 
 }  // namespace
@@ -527,13 +614,18 @@ int tc_chain(const TcChainArgs& g, const void* A, int64_t lda, int K1, int H, in
   if (g.gat16 && (!g.idx_a || !g.idx_b)) return AETHER_E_BADARG;
   if (g.gat16 && (((uintptr_t)g.gat16 & 15) || (g.ldg & 7) || (g.goff_b & 7))) return AETHER_E_BADARG;   // 128-bit row loads
   const bool save = g.out1 != nullptr;
-  CUtensorMap ta, t1, t2;
+  CUtensorMap ta, t1, t2, tg;
   memset(&t1, 0, sizeof(t1));
+  memset(&tg, 0, sizeof(tg));
+  if (g.gat16 && g.box_gather) {
+    if (g.gat_rows <= 0) return AETHER_E_BADARG;
+    AE_CHECK(tc_make_tmap_bf16(&tg, g.gat16, g.gat_rows, H, g.ldg, kTileM));
+  }
   AE_CHECK(tc_make_tmap_bf16(&ta, A, g.M, K1, lda, kTileM));
   if (save) AE_CHECK(tc_make_tmap_bf16(&t1, g.out1, g.M, H, g.ldo1, 32, 32));
   memset(&t2, 0, sizeof(t2));
   if (g.out2) AE_CHECK(tc_make_tmap_bf16(&t2, g.out2, g.M, H, g.ldo2, 32, 32));
-#define AE_CH_CASE(KK, HH) if (K1 == KK && H == HH) return launch_kh<KK, HH>(g, ta, t1, t2, tf1, save, st);
+#define AE_CH_CASE(KK, HH) if (K1 == KK && H == HH) return launch_kh<KK, HH>(g, ta, t1, t2, tg, tf1, save, st);
   AE_CH_CASE(256, 256) AE_CH_CASE(64, 256) AE_CH_CASE(128, 128) AE_CH_CASE(64, 128) AE_CH_CASE(64, 64)
 #undef AE_CH_CASE
   return AETHER_E_UNSUPPORTED;

@@ -50,7 +50,8 @@ struct TcChainArgs {
   const float* bias1 = nullptr; const float* bias2 = nullptr;
   const __nv_bfloat16* gat16 = nullptr; int64_t ldg = 0;
   const int32_t* idx_a = nullptr; const int32_t* idx_b = nullptr; int64_t goff_b = 0;
-  int64_t gat_rows = 0;                // rows of the idx_a plane of gat16 (bound of the TMA row gather; 0: unknown)
+  int64_t gat_rows = 0;                // rows of the idx_a plane of gat16 (needed with box_gather)
+  int box_gather = 0;                  // senders of (nearly) every 128-row tile span < 128 node rows: feed P_s by TMA boxes
   __nv_bfloat16* out1 = nullptr; int64_t ldo1 = 0;
   __nv_bfloat16* out2 = nullptr; int64_t ldo2 = 0;
   // fp32 second output instead of out2 (node update x = y + W4 silu(W3 y + b3) + b4, locs.py:241):

@@ -256,6 +256,13 @@ int aether_dbg_tc_chain(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, 
                         const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
                         const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
                         void* out2_bf16, void* wpack_scratch, void* stream);
+/* The same with the sender term fed by TMA boxes (box_gather != 0; gat_rows = rows of the idx_a plane of gat_bf16): tiles
+ * whose idx_a values span fewer than 128 rows read P_s from one 128-row box per 64 columns, the others load directly. */
+int aether_dbg_tc_chain_ex(const void* A_bf16, int64_t M, int32_t K1, int64_t lda, const float* W1, int64_t ldw1,
+                           int32_t k1_valid, int32_t kmod1, const float* W2, int32_t H, int32_t silu_on_load,
+                           const float* bias1, const float* bias2, const void* gat_bf16, int64_t ldg,
+                           const int32_t* idx_a, const int32_t* idx_b, int32_t goff_b, void* out1_bf16,
+                           void* out2_bf16, void* wpack_scratch, int64_t gat_rows, int32_t box_gather, void* stream);
 /* Chained data-gradient GEMMs of the edge-MLP backward on a CTA pair (csrc/tc_chain_bwd.cu; autograd of locs.py:232-235):
  * out1[M,H] = (A[M,H] W1 (+ gat_bf16[idx_b[m]*ldg + n])) * silu'(z1[m,n]),  out2[M,H] = (out1 W2) * silu'(z2[m,n]);
  * everything bf16 except W1, W2 ([H,H] fp32 row-major).  wpack_scratch: 2 * H * H * 2 bytes. */

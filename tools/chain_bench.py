@@ -34,6 +34,11 @@ def chain(save, gather, snd=None, bias=True):
                                    P(scratch), stream())
 
 
+def chain_box(save, snd):
+    return lib.aether_dbg_tc_chain_ex(P(A), M, H, H, P(W1), H, H, 0, P(W2), H, 1, None, P(b2), P(gat), 2 * H, P(snd), P(recv), H,
+                                      P(o1 if save else None), P(o2), P(scratch), Nn, 1, stream())
+
+
 def two(gather):
     rc = lib.aether_dbg_tc_gemm(P(A), M, H, H, P(W1), H, H, H, H, 0, 0, 1, P(b1), P(gat if gather else None), 2 * H,
                                 P(send if gather else None), P(recv if gather else None), H, None, P(o1), None, P(scratch), stream())
@@ -67,6 +72,9 @@ MODES = {"two_g": ("two GEMMs, gather (incl. 2 weight packs)", lambda: two(True)
          "train_g_bcast": ("chain train, gather with send := recv (warp-uniform rows)", lambda: chain(True, True, recv), 3),
          "train_g_rand": ("chain train, gather with random senders", lambda: chain(True, True, send_rand), 3),
          "train_g_nobias": ("chain train, gather, bias folded into P_r", lambda: chain(True, True, None, False), 3),
+         "train_box": ("chain train, sender term by TMA boxes (contiguous senders)", lambda: chain_box(True, send), 3),
+         "infer_box": ("chain infer, sender term by TMA boxes (contiguous senders)", lambda: chain_box(False, send), 2),
+         "train_box_rand": ("chain train, box variant on random senders (all tiles fall back)", lambda: chain_box(True, send_rand), 3),
          "infer": ("chain infer  (pre1 not stored), no gather", lambda: chain(False, False), 2)}
 for m in os.environ.get("MODES", ",".join(MODES)).split(","):
     timeit(*MODES[m])
