@@ -167,8 +167,10 @@ def test_module_dropin(ab):
     assert torch.equal(o3, o4)
 
 
-def test_graphed_train_step_matches_eager(ab):
-    """The captured train step (CUDA graph) takes exactly the steps the eager loop takes."""
+@pytest.mark.parametrize("fused", [False, True])
+def test_graphed_train_step_matches_eager(ab, fused):
+    """The captured train step (CUDA graph) takes exactly the steps the eager loop takes -- with torch's capturable AdamW
+    and with the library's FusedAdamW (csrc/optim.cu) inside the graph; the eager side is always torch.optim.AdamW."""
     D, N, B, H = 3, 5, 16, 64
     x, v, q = O.synth_state(B, N, D, seed=21)
     tgt = x + 0.05
@@ -178,7 +180,8 @@ def test_graphed_train_step_matches_eager(ab):
     m2, _ = make(ab, D, H, seed=4)
     m1.train(); m2.train()
     o1 = torch.optim.AdamW(m1.parameters(), lr=5e-4, weight_decay=1e-12, fused=True)
-    o2 = torch.optim.AdamW(m2.parameters(), lr=5e-4, weight_decay=1e-12, fused=True, capturable=True)
+    o2 = (ab.FusedAdamW(m2.parameters(), lr=5e-4, weight_decay=1e-12) if fused else
+          torch.optim.AdamW(m2.parameters(), lr=5e-4, weight_decay=1e-12, fused=True, capturable=True))
     g = ab.PreparedGraph(send, recv, B * N)
     losses1 = []
     for _ in range(4):
