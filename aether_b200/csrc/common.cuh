@@ -146,7 +146,7 @@ int launch_fill(float* p, size_t n, float v, cudaStream_t st);
 int launch_segmean_silu_bf16(int64_t Nn, int H, const int32_t* rowptr, const void* src, int64_t lds, const float* base,
                              int64_t ldb, float* y, int64_t ldy, cudaStream_t st, void* y16 = nullptr, int64_t ldy16 = 0);
 int launch_segsum_bf16(int64_t Nn, int W, const int32_t* ptr, const int32_t* list, const void* src, int64_t lds,
-                       float* out, int64_t ldo, cudaStream_t st);
+                       float* out, int64_t ldo, cudaStream_t st, void* out16 = nullptr, int64_t ldo16 = 0);
 int launch_edge_dpre2_bf16(int64_t E, int H, const int32_t* recv, const int32_t* rowptr, const void* ge, const float* gy,
                            const void* pre2, void* g, cudaStream_t st);
 // out16[n,:] = bf16(src[n,:] / max(deg(n), 1))   (the mean's backward, gathered per edge by the next GEMM)

@@ -199,8 +199,9 @@ int launch_segmean_silu_bf16(int64_t Nn, int H, const int32_t* rowptr, const voi
 }
 
 int launch_segsum_bf16(int64_t Nn, int W, const int32_t* ptr, const int32_t* list, const void* src, int64_t lds,
-                       float* out, int64_t ldo, cudaStream_t st) {
-  return launch_segreduce<false, false>(Nn, W, ptr, list, (const __nv_bfloat16*)src, lds, nullptr, 0, out, ldo, st);
+                       float* out, int64_t ldo, cudaStream_t st, void* out16, int64_t ldo16) {
+  return launch_segreduce<false, false>(Nn, W, ptr, list, (const __nv_bfloat16*)src, lds, nullptr, 0, out, ldo, st,
+                                        (__nv_bfloat16*)out16, ldo16);
 }
 
 int launch_edge_dpre2_bf16(int64_t E, int H, const int32_t* recv, const int32_t* rowptr, const void* ge, const float* gy,

@@ -55,7 +55,7 @@ struct Workspace {
   // W3 / W4 (two H x H halves each) and of the next layer's W_s, W_r
   void *y16[5], *x16[5], *pre316[5], *nw3[5][2], *nw4[5][2], *nws[5], *nwr[5];
   // transposed images for the backward (packed by the forward's single batched launch when it saves for backward)
-  void *wtA[5], *wtB[5], *nt3[5][2], *nt4[5][2];
+  void *wtA[5], *wtB[5], *nt3[5][2], *nt4[5][2], *nts[5], *ntr[5];   // nts / ntr: W_s^T, W_r^T of layer l's first Linear
   size_t bytes;
 };
 
@@ -76,7 +76,7 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
     w.bpre1[l] = w.bpre2[l] = w.wpA[l] = w.wpB[l] = nullptr; w.pre1[l] = w.pre2[l] = nullptr;
     w.y16[l] = w.x16[l] = w.pre316[l] = w.nws[l] = w.nwr[l] = nullptr;
     w.nw3[l][0] = w.nw3[l][1] = w.nw4[l][0] = w.nw4[l][1] = nullptr;
-    w.wtA[l] = w.wtB[l] = w.nt3[l][0] = w.nt3[l][1] = w.nt4[l][0] = w.nt4[l][1] = nullptr;
+    w.wtA[l] = w.wtB[l] = w.nt3[l][0] = w.nt3[l][1] = w.nt4[l][0] = w.nt4[l][1] = w.nts[l] = w.ntr[l] = nullptr;
   }
   if (use_tc(d, flags)) {
     w.na16 = c.b(Nn * 256 * 2);
@@ -101,6 +101,7 @@ Workspace carve(const AetherDims& d, uint32_t flags, void* base) {
       for (int l = 1; l <= 4; ++l) {
         w.wtA[l] = c.b(tc_weight_pack_bytes(H, H)); w.wtB[l] = c.b(tc_weight_pack_bytes(H, H));
         for (int h = 0; h < 2; ++h) { w.nt3[l][h] = c.b(tc_weight_pack_bytes(H, H)); w.nt4[l][h] = c.b(tc_weight_pack_bytes(H, H)); }
+        if (l > 1) { w.nts[l] = c.b(tc_weight_pack_bytes(H, H)); w.ntr[l] = c.b(tc_weight_pack_bytes(H, H)); }
       }
     }
   } else {
@@ -134,6 +135,7 @@ struct Scratch {
   void *bg2, *bg1, *bg1b, *gyd16; void *wtA, *wtB;   // gyd16: [Nn,H] bf16 = gy / in-degree
   void *na16, *ng16, *nwp;
   void* gpre316;        // [Nn, 2H] bf16 gradient of the node update's hidden layer
+  void* gpspr16;        // [Nn, 2H] bf16 copy of the node terms' gradients (segment sums of g1)
   size_t bytes;
 };
 
@@ -172,10 +174,10 @@ Scratch carve_scratch(const AetherDims& d, uint32_t flags, void* base) {
   const size_t Nn = (size_t)d.n_nodes, E = (size_t)d.n_edges, D = d.num_dims, H = d.hidden;
   s.gA = s.gB = nullptr;
   s.bg2 = s.bg1 = s.bg1b = s.gyd16 = s.wtA = s.wtB = nullptr;
-  s.na16 = s.ng16 = s.nwp = nullptr; s.gpre316 = nullptr;
+  s.na16 = s.ng16 = s.nwp = nullptr; s.gpre316 = s.gpspr16 = nullptr;
   if (use_tc(d, flags)) {
     s.na16 = c.b(Nn * 256 * 2); s.ng16 = c.b(Nn * 256 * 2); s.nwp = c.b(tc_weight_pack_bytes(256, 256));
-    s.gpre316 = c.b(Nn * 2 * H * 2);
+    s.gpre316 = c.b(Nn * 2 * H * 2); s.gpspr16 = c.b(Nn * 2 * H * 2);
     s.bg2 = c.b(E * H * 2); s.bg1 = c.b(E * H * 2); s.bg1b = c.b(E * H * 2); s.gyd16 = c.b(Nn * H * 2);
     s.wtA = c.b(tc_weight_pack_bytes(H, H)); s.wtB = c.b(tc_weight_pack_bytes(H, H));
     s.gfeat = c.f(E * 32);
@@ -272,8 +274,11 @@ int pack_step_weights(const AetherDims& d, const float* const* P, const Workspac
     }
     if (save) {
       add(P[s.m2w], H, H, H, H, H, 1, 0, w.wtB[l]);
-      if (l > 1) add(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, w.wtA[l]);
-      else add(P[s.m0w], Fe, 32, H, Fe, H, 1, 0, w.wtA[1]);          // gfeat[E,32] = g1 W1 (fp32 output)
+      if (l > 1) {
+        add(P[s.m0w] + 2 * H, 3 * H, H, H, H, H, 1, 0, w.wtA[l]);
+        add(P[s.m0w], 3 * H, H, H, H, H, 1, 0, w.nts[l]);            // node terms' data gradients
+        add(P[s.m0w] + H, 3 * H, H, H, H, H, 1, 0, w.ntr[l]);
+      } else add(P[s.m0w], Fe, 32, H, Fe, H, 1, 0, w.wtA[1]);        // gfeat[E,32] = g1 W1 (fp32 output)
       for (int h = 0; h < 2; ++h) {
         add(P[s.u2w] + (size_t)h * H, 2 * H, H, H, H, H, 1, 0, w.nt4[l][h]);
         add(P[s.u0w] + (size_t)h * H * H, H, H, H, H, H, 1, 0, w.nt3[l][h]);

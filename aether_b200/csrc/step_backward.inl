@@ -96,8 +96,9 @@ int backward_edges_tc(const AetherDims& d, const float* const* P, const AetherGr
     if (l > 1) {
       {
         ProfScope ps(PROF_SEGMENT, st);
-        AE_CHECK(launch_segsum_bf16(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, st));
-        AE_CHECK(launch_segsum_bf16(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, st));
+        __nv_bfloat16* gp16 = (__nv_bfloat16*)s.gpspr16;     // bf16 copies: operands of the node terms' tensor-core GEMMs
+        AE_CHECK(launch_segsum_bf16(Nn, H, Gr.colptr, Gr.sperm, g1, H, s.gpspr, 2 * H, st, gp16, 2 * H));
+        AE_CHECK(launch_segsum_bf16(Nn, H, Gr.rowptr, nullptr, g1, H, s.gpspr + H, 2 * H, st, gp16 + H, 2 * H));
       }
       AE_CHECK(node_terms_bwd(l));
       AE_CHECK(node_update_bwd(l - 1));
@@ -203,6 +204,23 @@ int backward(const AetherDims& d, const float* const* P, const AetherGraph& Gr, 
     ProfScope pn(PROF_NODE, st);
     const LayerSlots sl = layer_slots(l);
     const float* xin = w.xl[l - 1];
+    if (tc && use_chain()) {
+      // bf16 operands from the producers (segment sums wrote gpspr16, the forward's node update wrote x16): no
+      // conversion or packing launches
+      const __nv_bfloat16* gp16 = (const __nv_bfloat16*)s.gpspr16;
+      const __nv_bfloat16* x16 = (const __nv_bfloat16*)w.x16[l - 1];
+      AE_CHECK(tc_wgrad(gp16, 2 * H, H, x16, H, H, TC_TF_NONE, Nn, G[sl.m0w], 3 * H, H, 0, nullptr, s.partial, s.partial_floats, st));
+      AE_CHECK(tc_wgrad(gp16 + H, 2 * H, H, x16, H, H, TC_TF_NONE, Nn, G[sl.m0w] + H, 3 * H, H, 0, nullptr, s.partial,
+                        s.partial_floats, st));
+      TcGemmArgs a;
+      a.M = Nn; a.wpack = w.nts[l]; a.res = s.gy; a.ldr = H; a.out_f32 = gxn; a.ldo32 = H; a.n_valid = H;
+      AE_CHECK(tc_gemm(a, gp16, 2 * H, H, H, TC_TF_NONE, st));
+      TcGemmArgs c;
+      c.M = Nn; c.wpack = w.ntr[l]; c.accumulate = 1; c.out_f32 = gxn; c.ldo32 = H; c.n_valid = H;
+      AE_CHECK(tc_gemm(c, gp16 + H, 2 * H, H, H, TC_TF_NONE, st));
+      float* t = gx; gx = gxn; gxn = t;
+      return 0;
+    }
     AE_CHECK(b.wgrad(s.gpspr, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w], 3 * H, nullptr));
     AE_CHECK(b.wgrad(s.gpspr + H, 2 * H, Nn, H, xin, H, H, TF_NONE, nullptr, G[sl.m0w] + H, 3 * H, nullptr));
     AE_CHECK(b.dgrad(s.gpspr, 2 * H, Nn, H, P[sl.m0w], 3 * H, H, gxn, H, nullptr, nullptr, s.gy, 0));
