@@ -459,6 +459,15 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (OUT32) {
             // fp32 output: the chunk (+ bias) goes through the warp's staging as a swizzled 32x32 fp32 tile and is read
             // back row-major, so the residual load and the store are 512 contiguous bytes per instruction
+            // residual rows of the whole chunk requested before anything waits (see tc_gemm.cu's fp32 epilogue)
+            float4 pre[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int i = it * 32 + lane, rr = i >> 3, ch = i & 7;
+              pre[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (g.res && row0 + rr < g.M)
+                pre[it] = *reinterpret_cast<const float4*>(g.res + (size_t)(row0 + rr) * g.ldr + c0 + ch * 4);
+            }
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // epilogue 1's pre1 boxes
             __syncwarp();
             tmem_ld_wait();
@@ -487,10 +496,7 @@ tc_chain_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                            : "r"(sbuf + rr * 128 + ((ch ^ (rr & 7)) << 4)) : "memory");
               if (grow < g.M) {
-                if (g.res) {
-                  const float4 a = *reinterpret_cast<const float4*>(g.res + (size_t)grow * g.ldr + col);
-                  v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
-                }
+                if (g.res) { v.x += pre[it].x; v.y += pre[it].y; v.z += pre[it].z; v.w += pre[it].w; }
                 *reinterpret_cast<float4*>(g.out2_f32 + (size_t)grow * g.ldo2f + col) = v;
                 if (g.copy16)
                   *reinterpret_cast<uint2*>(g.copy16 + (size_t)grow * g.ldc16 + col) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));

@@ -407,6 +407,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int j = warp >> 2; j < N / 32; j += 2) {
           uint32_t r[32];
           tmem_ld32(tmem_base + ((uint32_t)(qr * 32) << 16) + acc * N + j * 32, r);
+          // the residual / accumulate operands of the whole chunk are requested before anything waits (they used to be
+          // loaded one by one right in front of their use: 8 exposed global-load latencies per chunk, 50 k cycles per
+          // tile -- profiles/r02_ncu_node_gemm.md)
+          float4 pre[8];
+          const float* psrc = g.res ? g.res : (g.accumulate ? g.out_f32 : nullptr);
+          const int64_t pld = g.res ? g.ldr : g.ldo32;
+          const bool both = g.res && g.accumulate;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int i = it * 32 + lane, rr = i >> 3, ch = i & 7;
+            const int64_t grow = t * kTileM + qr * 32 + rr;
+            const int col = j * 32 + ch * 4;
+            pre[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (psrc && grow < g.M && col < g.n_valid) pre[it] = *reinterpret_cast<const float4*>(psrc + (size_t)grow * pld + col);
+          }
           tmem_ld_wait();
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -426,10 +441,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                          : "r"(sbuf + rr * 128 + ((ch ^ (rr & 7)) << 4)) : "memory");
             if (grow < g.M && col < g.n_valid) {
-              if (g.res) {
-                const float4 a = *reinterpret_cast<const float4*>(g.res + (size_t)grow * g.ldr + col);
-                v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
-              }
+              if (g.res) { v.x += pre[it].x; v.y += pre[it].y; v.z += pre[it].z; v.w += pre[it].w; }
               if (g.dsilu32) {
                 const float4 z = __ldg(reinterpret_cast<const float4*>(g.dsilu32 + (size_t)grow * g.ldd32 + col));
                 v.x *= dsilu_f(z.x); v.y *= dsilu_f(z.y); v.z *= dsilu_f(z.z); v.w *= dsilu_f(z.w);
@@ -440,7 +452,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
               float4* po = reinterpret_cast<float4*>(g.out_f32 + (size_t)grow * g.ldo32 + col);
               if (g.accumulate) {
-                const float4 a = *po;
+                const float4 a = both ? *po : pre[it];
                 v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
               }
               *po = v;
