@@ -45,6 +45,7 @@ SOURCES = [
     ("dynfield.cu", []),
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),
+    ("small.cu", ["-fmad=false"]),
 ]
 
 

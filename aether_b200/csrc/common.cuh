@@ -49,6 +49,13 @@ __device__ __forceinline__ float dsilu_f(float z) {
   return s * (1.0f + z * (1.0f - s));
 }
 
+// Planar distance of the kNN builders (graph.cu, small.cu): one definition with the roundings spelled out, so that both
+// kernels pick bit-identical neighbours whatever the file's contraction flags are.
+__device__ __forceinline__ float knn_dist(float xi, float yi, float xj, float yj) {
+  const float dx = __fsub_rn(xi, xj), dy = __fsub_rn(yi, yj);
+  return sqrtf(__fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+}
+
 // ---- generic fp32 GEMM family (gemm_f32.cu) ---------------------------------
 enum GemmLayout { GEMM_NT = 0, GEMM_NN = 1, GEMM_TN = 2 };
 enum LoadTf { TF_NONE = 0, TF_SILU = 1, TF_SILU_MASK = 2 };

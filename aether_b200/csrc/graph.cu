@@ -175,8 +175,7 @@ __global__ void knn_kernel(const float* __restrict__ pos, int stride, const int3
       int bj = -1;
       for (int j = 0; j < n; ++j) {
         if (j == i) continue;
-        const float dx = xi - sp[2 * j], dy = yi - sp[2 * j + 1];
-        const float d = sqrtf(dx * dx + dy * dy);
+        const float d = knn_dist(xi, yi, sp[2 * j], sp[2 * j + 1]);
         const bool after = d > last_d || (d == last_d && j > last_j);
         if (after && (d < best || (d == best && j < bj) || bj < 0)) { best = d; bj = j; }
       }

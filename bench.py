@@ -442,7 +442,10 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
         model.train()
     else:
         model.eval()
-        roll = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=True)
+        # scenes that fit one SM take the single-launch kernel (csrc/small.cu); --multi-launch keeps the graph of
+        # per-step launches for comparison
+        roll = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=True, sizes=sizes,
+                          persistent=False if args.multi_launch else None)
 
     from aether_b200 import dist as adist
 
@@ -551,9 +554,17 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
         graphed, eager_fn = g_keep, None
     if not train:
         # graph replays carry no library-side event pairs: time the same kernels once more, launched eagerly
-        eager = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=False)
+        eager = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=False, persistent=False)
         eager_fn = lambda: eager.run(xd, vd, qd1)
         _, _, prof = timed(eager_fn, max(1, min(steps, 3)), 1, profile=True)
+        multi_ms = None
+        if roll.persistent:
+            # the path the single launch replaces, measured in the same run: the T steps' launches replayed as one graph
+            alt = ab.Rollout(model, Nn, T, edges=None if plan else (send, recv), knn_plan=plan, cuda_graph=True, persistent=False)
+            eager_fn = lambda: alt.run(xd, vd, qd1)
+            t_alt, _, _ = timed(eager_fn, steps, warmup)
+            multi_ms = t_alt / steps * 1e3
+        eager_fn = None
     e2e = None
     if do_e2e:
         e2e_total, _, _ = timed(step_e2e, steps, max(1, warmup - 1))
@@ -606,15 +617,33 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
                                    "achieved": nb / (ms * 1e-3) / 1e9, "peak": pk.get("hbm_gbs"),
                                    "frac": nb / (ms * 1e-3) / 1e9 / pk["hbm_gbs"] if pk.get("hbm_gbs") else None,
                                    "algorithmic_bytes_per_step": nb, "ms_per_step": ms, "traffic": None}
+    if not train and roll.persistent:
+        # single-launch rollout: nothing but inputs, weights and the trajectory crosses HBM, so the roofline SURVEY 8(d)
+        # asks for is the compulsory traffic; what bounds the kernel is fp32 FMA issue and per-scene latency (fp32_view)
+        n_par = sum(p.numel() for p in params)
+        nb = 4.0 * (Nn * (2 * D + 1) + T * Nn * D + n_par)
+        ms = total / steps * 1e3
+        fl = 2.0 * T * (E * ((7 * D + D * (D - 1) // 2 + 2) * H + 7 * H * H) + Nn * (4 * 4 * H * H + 6 * H * H + 2 * H * H))
+        cc_peak = 148 * 128 * 2 * (clocks["sm_mhz"] if clocks and clocks.get("sm_mhz") else 1800.0) * 1e6 / 1e12
+        roofline = {"bound": "hbm", "kernel": "small_rollout_kernel (all %d steps of every scene in one launch)" % T,
+                    "achieved": nb / (ms * 1e-3) / 1e9, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
+                    "frac": nb / (ms * 1e-3) / 1e9 / pk["hbm_gbs"] if pk.get("hbm_gbs") else None, "traffic": None,
+                    "algorithmic_bytes_per_launch": nb, "peak_source": pk_src,
+                    "note": "compulsory traffic only (inputs + weights + trajectory); the kernel is latency / fp32-issue bound",
+                    "fp32_view": {"executed_tflops": fl / (ms * 1e-3) / 1e12, "cuda_core_peak_tflops": cc_peak,
+                                  "frac": fl / (ms * 1e-3) / 1e12 / cc_peak, "ctas": len(sizes), "sms": 148},
+                    "multi_launch_graph_ms_per_step": multi_ms}
     step_ms = total / steps * 1e3
     share = {k: (prof["ms"][i] / steps) / step_ms for i, k in
              enumerate(["edge_mlp_fwd", "edge_bwd_data", "edge_wgrad", "segment_bwd", "edge_feat", "node", "segment_fwd"])} if train else None
     line = {"metric": "edge_messages_per_sec", "value": value, "unit": "edge-messages/s", "n_gpus": world,
             "steps": steps, "warmup": warmup, "ms_per_step": step_ms, "higher_is_better": True,
-            "scaling": scaling, "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16",
+            "scaling": scaling, "vs_baseline": None,
+            "dtype": "f32" if args.precision == "fp32" or (not train and roll.persistent) else "bf16",
             "data": "synthetic",
             "config": {"workload": cfg["name"], "num_dims": D, "particles_per_graph": N, "graphs_per_gpu": B,
-                       "hidden": H, "mode": cfg["mode"] + (" (whole step replayed as one CUDA graph, static edge list)" if graphed is not None else ""),
+                       "hidden": H, "mode": cfg["mode"] + (" (whole step replayed as one CUDA graph, static edge list)" if graphed is not None else "")
+                       + (" (single launch: one CTA per scene for all steps, fp32)" if not train and roll.persistent else ""),
                        "rollout_steps": T, "edges_per_gpu": E, "nodes_per_gpu": Nn,
                        "precision": args.precision, "parallelism": "dp%d" % world,
                        "l2": "flushed between steps" if small else "working set exceeds L2"},
@@ -782,6 +811,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="default c4 run: skip the strong-scaling / config-5 / baseline legs")
+    ap.add_argument("--multi-launch", action="store_true", help="rollout workloads: per-step launches instead of the single-launch kernel")
     ap.add_argument("--strong", action="store_true", help="c4: split the workload's batch over the ranks (strong scaling)")
     ap.add_argument("--graph", action="store_true", help="capture the train step in a CUDA graph at any size")
     ap.add_argument("--no-graph", action="store_true", help="small training shapes: do not capture the step in a CUDA graph")

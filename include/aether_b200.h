@@ -24,6 +24,10 @@
  *                             experiments/lorentz/main.py:291
  *   aether_rollout_step       one harness-level rollout step:
  *                             caller prep + forward + v' = x' - x
+ *   aether_small_rollout      T such steps of a batch of small scenes in ONE
+ *                             launch (the eval loops of experiments/lorentz/
+ *                             main.py:243-247 and, with per-step kNN edges,
+ *                             experiments/ind/single_ind_data.py:186-217)
  *
  * Conventions
  *   - every pointer is a DEVICE pointer unless the name ends in _host;
@@ -181,6 +185,29 @@ int aether_rollout_step(const AetherDims* dims, const float* const* params, cons
                         const int64_t* send64, const int64_t* recv64, const float* x, const float* vel,
                         const float* charges, float* x_next, float* vel_next, float* edge_attr_scratch /* [E,2] */,
                         void* workspace, size_t workspace_bytes, uint32_t flags, void* stream);
+
+/* T rollout steps of a batch of small scenes in one launch (csrc/small.cu): one CTA keeps a whole scene -- edge state,
+ * node state, frames, edge list -- in shared memory for all steps; per step it does what aether_rollout_step does
+ * (inference only, fp32 arithmetic whatever the precision flag of the multi-launch path would be).  A small pack
+ * launch in front writes the step's 32 weight tiles (64 x 64, transposed) into `scratch`
+ * (aether_small_rollout_scratch_bytes, 128-byte aligned); the rollout kernel streams them from there (L2) by bulk copies.
+ *   node_off [n_scenes+1] (int32), edge_off [n_scenes+1] (int64): first particle / first edge of every scene;
+ *   order [n_scenes] (int32, optional): the scene CTA i works on -- largest scenes first balances the SMs;
+ *   send/recv: int64 edge list with global particle ids whose edges are grouped by scene (edge_off) and stay inside
+ *   their scene, or both NULL: the knn_k nearest neighbours of every agent are rebuilt from the positions every step
+ *   (edge_off then has to be the kNN plan's: n_s * min(knn_k, n_s - 1) edges per scene);
+ *   max_nodes / max_edges: upper bounds over the scenes (host-known; they size the shared memory);
+ *   traj [steps, n_nodes, D]: positions after every step; send_out/recv_out (optional, kNN): the last step's edge list.
+ * aether_small_rollout_supported says whether a shape fits (hidden 64, <= 64 particles per scene, edge state plus a
+ * three-tile weight ring within one SM's shared memory); unsupported shapes -- and parameter tensors that are not
+ * 16-byte aligned -- return AETHER_E_UNSUPPORTED and the caller uses aether_rollout_step. */
+size_t aether_small_rollout_scratch_bytes(void);
+int aether_small_rollout_supported(int32_t num_dims, int32_t hidden, int32_t max_nodes, int32_t max_edges);
+int aether_small_rollout(const AetherDims* dims, const float* const* params, int32_t n_scenes, const int32_t* node_off,
+                         const int64_t* edge_off, const int32_t* order, const int64_t* send, const int64_t* recv,
+                         int32_t knn_k, int32_t max_nodes, int32_t max_edges, const float* x0, const float* v0,
+                         const float* charges, int32_t steps, float* traj, int64_t* send_out, int64_t* recv_out,
+                         void* scratch, size_t scratch_bytes, void* stream);
 
 /* Bench support: kernels launched by this library so far; optional per-category CUDA-event timing
  * (categories: 0 edge-MLP forward, 1 edge backward data grads, 2 edge weight grads, 3 segment
