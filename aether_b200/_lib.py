@@ -49,11 +49,11 @@ SIGNATURES = {
     "aether_rollout_step": (c_int, [POINTER(AetherDims), POINTER(c_void_p), POINTER(AetherGraphC), c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,
                                     c_uint32, c_void_p]),
-    "aether_small_rollout_supported": (c_int, [c_int32, c_int32, c_int32, c_int32]),
+    "aether_small_rollout_supported": (c_int, [c_int32, c_int32, c_int32, c_int32, c_uint32]),
     "aether_small_rollout_scratch_bytes": (c_size_t, []),
     "aether_small_rollout": (c_int, [POINTER(AetherDims), POINTER(c_void_p), c_int32, c_void_p, c_void_p, c_void_p, c_void_p,
                                      c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_int32, c_void_p,
-                                     c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+                                     c_void_p, c_void_p, c_void_p, c_size_t, c_uint32, c_void_p]),
     "aether_part_forward_phase": (c_int, [POINTER(AetherDims), POINTER(c_void_p), POINTER(AetherGraphC), c_void_p, c_void_p,
                                           c_void_p, c_void_p, c_int64, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_size_t, c_uint32, c_void_p]),

@@ -58,22 +58,29 @@ struct SmallArgs {
   int32_t steps, knn_k, max_nodes, max_edges, ring;
 };
 
+// bytes of packed tile i: the edge MLP's tiles (W_e, W_2 of every layer) are 64 x 64 bf16 in the tensor-core mode
+__host__ __device__ inline bool small_edge_tile(int i) { return i < 30 && (i & 7) < 2; }
+__host__ __device__ inline uint32_t small_tile_bytes(int i, bool bf16) { return bf16 && small_edge_tile(i) ? kTile * 2 : kTile * 4; }
+
 // shared-memory plan, in floats (all regions 16-byte aligned)
 struct SmallPlan {
-  int S, T1, ring, X, PS, PR, x, v, xn, f, pred, R, x0, q, send, recv, elist, rowptr, bars, total, nb;
+  int S, T1, ring, X, PS, PR, x, v, xn, f, pred, R, x0, q, send, recv, elist, rowptr, bars, bias, total, nb;
 };
 __host__ __device__ inline int up4(int v) { return (v + 3) & ~3; }
-__host__ __device__ inline SmallPlan small_plan(int nmax, int emax, int nb) {
+// bf16 = 1: edge state and chunk temporary as bf16 (128-byte rows: half the floats), T1 then holds 256 rows
+__host__ __device__ inline SmallPlan small_plan(int nmax, int emax, int nb, int bf16) {
   SmallPlan p;
   int o = 0;
-  auto take = [&](int n) { const int r = o; o += up4(n); return r; };
-  p.S = take((emax > 0 ? emax : 1) * SH);
+  auto take = [&](int n) { const int r = (o + 31) & ~31; o = r + up4(n); return r; };     // 128-byte aligned regions
+  p.S = take((emax > 0 ? emax : 1) * (bf16 ? SH / 2 : SH));
   p.T1 = take(CH * SH);
   p.X = take(nmax * SH); p.PS = take(nmax * SH); p.PR = take(nmax * SH);
   p.x = take(nmax * 3); p.v = take(nmax * 3); p.xn = take(nmax * 3); p.f = take(nmax * 3); p.pred = take(nmax * 3);
   p.R = take(nmax * 9); p.x0 = take(nmax * 9); p.q = take(nmax);
   p.send = take(emax); p.recv = take(emax); p.elist = take(emax); p.rowptr = take(nmax + 1);
   p.bars = take(2 * kMaxRing);
+  p.bias = take(2 * SH);
+  o = (o + 31) & ~31;
   p.ring = o;
   if (nb <= 0) {                    // as many ring buffers as fit
     nb = (kSmemLimit / 4 - o) / kTile;
@@ -104,9 +111,22 @@ __host__ __device__ inline TileDesc small_tile(const SmallParams& P, int i, int 
 }
 
 // tiles[i][k][n] = W_i[n][k] (zero rows for k >= K): one block per tile, transposed through shared memory
-__global__ void __launch_bounds__(256) small_pack_kernel(const __grid_constant__ SmallParams P, int FE, float* __restrict__ tiles) {
+// Tensor-core mode: the edge tiles are written as bf16 [n][k] rows of 128 bytes with their 16-byte chunks XOR-swizzled by
+// n & 7 -- exactly the shared-memory image ldmatrix reads -- and layer 1's W_e as [W | W] against the [hi | lo] features.
+__global__ void __launch_bounds__(256) small_pack_kernel(const __grid_constant__ SmallParams P, int FE, float* __restrict__ tiles,
+                                                         int bf16) {
   __shared__ float t[SH][SH + 1];
   const TileDesc d = small_tile(P, blockIdx.x, FE);
+  if (bf16 && small_edge_tile(blockIdx.x)) {
+    __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(tiles + (size_t)blockIdx.x * kTile);
+    const bool first = blockIdx.x == 0;
+    for (int i = threadIdx.x; i < kTile; i += 256) {
+      const int n = i >> 6, k = i & 63, ks = first ? (k & 31) : k;
+      const float v = ks < d.K ? d.W[(size_t)n * d.ldw + ks] : 0.0f;
+      o16[n * 64 + ((((k >> 3) ^ (n & 7)) << 3) | (k & 7))] = __float2bfloat16_rn(v);
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < kTile; i += 256) {
     const int n = i >> 6, k = i & 63;
     t[k][n] = k < d.K ? d.W[(size_t)n * d.ldw + k] : 0.0f;
@@ -116,7 +136,9 @@ __global__ void __launch_bounds__(256) small_pack_kernel(const __grid_constant__
   for (int i = threadIdx.x; i < kTile; i += 256) out[i] = t[i >> 6][i & 63];
 }
 
-__device__ __forceinline__ float silu_s(float z) { return z / (1.0f + expf(-z)); }
+// SiLU through the fast exponential and division (ex2.approx / rcp.approx paths, ~2 ulp each): the IEEE forms cost ~35
+// instructions per element and were a quarter of all instructions of the kernel
+__device__ __forceinline__ float silu_s(float z) { return __fdividef(z, 1.0f + __expf(-z)); }
 __device__ __forceinline__ float4 silu4(float4 v) { return make_float4(silu_s(v.x), silu_s(v.y), silu_s(v.z), silu_s(v.w)); }
 __device__ __forceinline__ float4 add4(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 // column of element (r, c) in an A-operand array: 16-byte chunks swizzled by the row parity
@@ -136,7 +158,7 @@ __device__ __forceinline__ void gemm_acc(float (&acc)[RW][4], const float* __res
   }
   const int sx = gi << 2;
   const float* w = Wt + (lane & 15) * 4;
-#pragma unroll 2
+#pragma unroll (RW == 1 ? 4 : 2)
   for (int k = 0; k < K; k += 4) {
     float4 wv[4];
 #pragma unroll
@@ -192,11 +214,46 @@ __device__ __forceinline__ void chunk_gemm(const float* A, int lda, int K, const
   else gemm_rows<4>(A, lda, K, Wt, row0, M, epi);
 }
 
-template <int D>
+// ---- tensor-core mode (models with precision = "bf16"): the edge MLP on mma.sync m16n8k16, bf16 operands, fp32 accumulate --
+// Edge state and chunk temporary are [rows][64] bf16 with 128-byte rows whose 16-byte chunks are XOR-swizzled by row & 7
+// (conflict-free ldmatrix); the weight tiles arrive in the same layout from the pack kernel.
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// byte offset of 16-byte chunk c of row r
+__device__ __forceinline__ uint32_t sw16(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+
+// acc[j][:] (n-tile j = columns 8j .. 8j+7) = A[r0 .. r0+15][0 .. 63] W^T; rows past rmax are clamped (results dropped).
+// Fragment of lane (g = lane / 4, t = lane % 4): acc[j][0..1] = row r0 + g, columns 8j + 2t, +1; acc[j][2..3] = row r0 + g + 8.
+__device__ __forceinline__ void mma_rows16(float (&acc)[8][4], uint32_t aBase, int r0, int rmax, uint32_t wBase, int lane) {
+  int ar = r0 + (lane & 7) + ((lane >> 3) & 1) * 8;
+  ar = ar < rmax ? ar : rmax;
+  const int ac = lane >> 4;
+  const int bn = (lane & 7) + ((lane >> 4) << 3), bc = (lane >> 3) & 1;
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks) {
+    uint32_t af[4];
+    ldsm_x4(aBase + sw16(ar, 2 * ks + ac), af);
+#pragma unroll
+    for (int jp = 0; jp < 4; ++jp) {
+      uint32_t bf[4];
+      ldsm_x4(wBase + sw16(16 * jp + bn, 2 * ks + bc), bf);
+      mma_bf16(acc[2 * jp], af, bf[0], bf[1]);
+      mma_bf16(acc[2 * jp + 1], af, bf[2], bf[3]);
+    }
+  }
+}
+
+template <int D, bool BF16>
 __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_constant__ SmallParams P, const SmallArgs a) {
   constexpr int O = D * (D - 1) / 2, FE = 7 * D + O + 2, LD = (FE + 3) / 4 * 4, FI = 2 * D + EMB;
   extern __shared__ __align__(128) float sm[];
-  const SmallPlan pl = small_plan(a.max_nodes, a.max_edges, a.ring);
+  const SmallPlan pl = small_plan(a.max_nodes, a.max_edges, a.ring, BF16 ? 1 : 0);
   float* const S = sm + pl.S;            // [E, 64] edge state: features (layer 1), then silu(pre2_l)      (swizzled rows)
   float* const T1 = sm + pl.T1;          // chunk temporary [128, 64] (swizzled); kNN distances; field hidden layers
   float* const Y = T1;                   // y_l [n, 64] (swizzled): live from the aggregation to the node update, when
@@ -218,6 +275,7 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
   int* const sRecv = reinterpret_cast<int*>(sm + pl.recv);
   int* const elist = reinterpret_cast<int*>(sm + pl.elist);
   int* const rowptr = reinterpret_cast<int*>(sm + pl.rowptr);
+  float* const sBias = sm + pl.bias;
   float* const ringbuf = sm + pl.ring;
   const uint32_t bar0 = smem_u32(sm + pl.bars);
   const int NB = pl.nb;
@@ -246,8 +304,9 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
     if (tid == 0)
       for (int g = issued; g < lim; ++g) {
         const int b = g % NB;
-        tc::mbar_arrive_expect_tx(bar0 + 8 * b, kTile * 4);
-        tc::bulk_load(smem_u32(ringbuf + b * kTile), a.tiles + (size_t)(g % kTilesPerStep) * kTile, kTile * 4, bar0 + 8 * b);
+        const uint32_t nbytes = small_tile_bytes(g % kTilesPerStep, BF16);
+        tc::mbar_arrive_expect_tx(bar0 + 8 * b, nbytes);
+        tc::bulk_load(smem_u32(ringbuf + b * kTile), a.tiles + (size_t)(g % kTilesPerStep) * kTile, nbytes, bar0 + 8 * b);
       }
     if (lim > issued) issued = lim;
   };
@@ -329,40 +388,51 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
       build_csr();
     }
 
-    // ---- neural field at the particles (aether.py:108-134), same accumulation order as field.cu -----------------------
+    // ---- neural field at the particles (aether.py:108-134).  Its weights (7.6 KB) go through the free upper half of T1,
+    //      first Linears transposed, so that the lanes (one output unit each) read consecutive words -----------------------
     {
       float* a1 = T1;
       float* a2 = T1 + kSmallMaxNodes * FH;
-      const float* W0 = P.p[P_F0_W]; const float* W2 = P.p[P_F2_W]; const float* W4 = P.p[P_F4_W];
+      float* W0t = T1 + 2 * kSmallMaxNodes * FH;        // [FI][32]
+      float* W2t = W0t + FI * FH;                       // [32][32]
+      float* W4s = W2t + FH * FH;                       // [D][32]
+      float* fb = W4s + D * FH;                         // b0 | b2 | b4
+      float* emb = fb + 2 * FH + 4;                     // [3][16]
+      for (int i = tid; i < FH * FI; i += ST) { const int o = i / FI, k = i - o * FI; W0t[k * FH + o] = __ldg(P.p[P_F0_W] + i); }
+      for (int i = tid; i < FH * FH; i += ST) W2t[(i & 31) * FH + (i >> 5)] = __ldg(P.p[P_F2_W] + i);
+      for (int i = tid; i < D * FH; i += ST) W4s[i] = __ldg(P.p[P_F4_W] + i);
+      if (tid < FH) { fb[tid] = __ldg(P.p[P_F0_B] + tid); fb[FH + tid] = __ldg(P.p[P_F2_B] + tid); }
+      if (tid < D) fb[2 * FH + tid] = __ldg(P.p[P_F4_B] + tid);
+      if (tid < 3 * EMB) emb[tid] = __ldg(P.p[P_EMB] + tid);
+      __syncthreads();
       for (int idx = tid; idx < n * FH; idx += ST) {
         const int node = idx >> 5, o = idx & 31;
         long long ci = (long long)(sq[node] + 1.0f);
         ci = ci < 0 ? 0 : (ci > 2 ? 2 : ci);
-        const float* em = P.p[P_EMB] + ci * EMB;
-        const float* w = W0 + o * FI;
-        float s = __ldg(P.p[P_F0_B] + o);
+        const float* em = emb + ci * EMB;
+        float s = fb[o];
 #pragma unroll
-        for (int k = 0; k < D; ++k) s = fmaf(sx[node * D + k], __ldg(w + k), s);
+        for (int k = 0; k < D; ++k) s = fmaf(sx[node * D + k], W0t[k * FH + o], s);
 #pragma unroll
-        for (int k = 0; k < D; ++k) s = fmaf(sv[node * D + k], __ldg(w + D + k), s);
+        for (int k = 0; k < D; ++k) s = fmaf(sv[node * D + k], W0t[(D + k) * FH + o], s);
 #pragma unroll
-        for (int k = 0; k < EMB; ++k) s = fmaf(__ldg(em + k), __ldg(w + 2 * D + k), s);
+        for (int k = 0; k < EMB; ++k) s = fmaf(em[k], W0t[(2 * D + k) * FH + o], s);
         a1[idx] = silu_s(s);
       }
       __syncthreads();
       for (int idx = tid; idx < n * FH; idx += ST) {
         const int node = idx >> 5, o = idx & 31;
-        float s = __ldg(P.p[P_F2_B] + o);
+        float s = fb[FH + o];
 #pragma unroll
-        for (int k = 0; k < FH; ++k) s = fmaf(a1[node * FH + k], __ldg(W2 + o * FH + k), s);
+        for (int k = 0; k < FH; ++k) s = fmaf(a1[node * FH + k], W2t[k * FH + o], s);
         a2[idx] = silu_s(s);
       }
       __syncthreads();
       for (int idx = tid; idx < n * D; idx += ST) {
         const int node = idx / D, d = idx - node * D;
-        float s = __ldg(P.p[P_F4_B] + d);
+        float s = fb[2 * FH + d];
 #pragma unroll
-        for (int k = 0; k < FH; ++k) s = fmaf(a2[node * FH + k], __ldg(W4 + d * FH + k), s);
+        for (int k = 0; k < FH; ++k) s = fmaf(a2[node * FH + k], W4s[d * FH + k], s);
         sf[idx] = s;
       }
       __syncthreads();
@@ -380,9 +450,28 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
       edge_features_core<D>(j, i, sx, sv, sf, sR, sx0, sq[j] * sq[i], sqrtf(ss), out);
 #pragma unroll
       for (int k = LD; k < 32; ++k) out[k] = 0.0f;
+      if constexpr (BF16) {
+        // [hi(32) | lo(32)] bf16, hi = bf16(v), lo = bf16(v - hi): ~16 bits of every feature reach the GEMM (geom.cu)
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const __nv_bfloat16 h0 = __float2bfloat16_rn(out[2 * k]), h1 = __float2bfloat16_rn(out[2 * k + 1]);
+          const __nv_bfloat16 l0 = __float2bfloat16_rn(out[2 * k] - __bfloat162float(h0));
+          const __nv_bfloat16 l1 = __float2bfloat16_rn(out[2 * k + 1] - __bfloat162float(h1));
+          hi[k] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          lo[k] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+        }
+        char* row = reinterpret_cast<char*>(S);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          *reinterpret_cast<uint4*>(row + sw16(e, k)) = make_uint4(hi[4 * k], hi[4 * k + 1], hi[4 * k + 2], hi[4 * k + 3]);
+          *reinterpret_cast<uint4*>(row + sw16(e, 4 + k)) = make_uint4(lo[4 * k], lo[4 * k + 1], lo[4 * k + 2], lo[4 * k + 3]);
+        }
+      } else {
       float4* dst = reinterpret_cast<float4*>(S + e * SH);
 #pragma unroll
       for (int k = 0; k < 8; ++k) dst[k ^ (e & 1)] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+      }
     }
     // (the barrier of the first acquire below orders these writes)
 
@@ -392,6 +481,66 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
     for (int l = 1; l <= 4; ++l) {
       const LayerSlots sl = layer_slots(l);
       const int b = g0 + 8 * (l - 1);   // tiles b .. b+7 (b+5 for the last layer)
+      if constexpr (BF16) {
+        // tensor-core mode: 256-edge chunks, 16 rows per warp, both GEMMs on mma.sync; biases through shared memory
+        if (tid < SH) { sBias[tid] = __ldg(P.p[sl.m0b] + tid); sBias[SH + tid] = __ldg(P.p[sl.m2b] + tid); }
+        wait_tile(b);
+        acquire(b + 1);
+        if (b > 0) ring_fill(b);
+        const uint32_t we = smem_u32(tile(b)), w2 = smem_u32(tile(b + 1));
+        const uint32_t s16 = smem_u32(S), t16 = smem_u32(T1);
+        char* const Sb = reinterpret_cast<char*>(S);
+        char* const Tb = reinterpret_cast<char*>(T1);
+        const int g = lane >> 2, tq = lane & 3;
+        for (int row0 = 0; row0 < E; row0 += 2 * CH) {
+          const int rows = E - row0 < 2 * CH ? E - row0 : 2 * CH;
+          const int lr0 = 16 * warp, r0 = row0 + lr0;
+          float acc[8][4];
+          if (lr0 < rows) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0f;
+            mma_rows16(acc, s16, r0, E - 1, we, lane);
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              const int lr = lr0 + g + 8 * hf, r = row0 + lr;
+              if (r < E) {
+                const float* ps = PS + sSend[r] * SH + 2 * tq;
+                const float* pr = PR + sRecv[r] * SH + 2 * tq;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  float v0 = acc[j][2 * hf], v1 = acc[j][2 * hf + 1];
+                  if (l == 1) { v0 += sBias[8 * j + 2 * tq]; v1 += sBias[8 * j + 2 * tq + 1]; }
+                  else {
+                    const float2 a2 = *reinterpret_cast<const float2*>(ps + 8 * j);
+                    const float2 c2 = *reinterpret_cast<const float2*>(pr + 8 * j);
+                    v0 += a2.x + c2.x; v1 += a2.y + c2.y;
+                  }
+                  *reinterpret_cast<uint32_t*>(Tb + sw16(lr, j) + 4 * tq) = tc::pack_bf16(tc::silu_fast(v0), tc::silu_fast(v1));
+                }
+              }
+            }
+          }
+          __syncthreads();
+          if (lr0 < rows) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0f;
+            mma_rows16(acc, t16, lr0, rows - 1, w2, lane);
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              const int r = r0 + g + 8 * hf;
+              if (r < E) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float v0 = acc[j][2 * hf] + sBias[SH + 8 * j + 2 * tq], v1 = acc[j][2 * hf + 1] + sBias[SH + 8 * j + 2 * tq + 1];
+                  *reinterpret_cast<uint32_t*>(Sb + sw16(r, j) + 4 * tq) = tc::pack_bf16(tc::silu_fast(v0), tc::silu_fast(v1));
+                }
+              }
+            }
+          }
+          __syncthreads();
+        }
+        ring_fill(b + 2);
+      } else
       {
         const float4 b1 = ld4(P.p[sl.m0b]), b2 = ld4(P.p[sl.m2b]);
         wait_tile(b);
@@ -425,7 +574,15 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
         const int node = idx >> 6, c = idx & 63;
         const int pb = rowptr[node], pe = rowptr[node + 1];
         float s = 0.0f;
+        if constexpr (BF16) {
+          const char* Sb = reinterpret_cast<const char*>(S);
+          for (int p = pb; p < pe; ++p) {
+            const int e = elist[p];
+            s += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(Sb + sw16(e, c >> 3) + 2 * (c & 7)));
+          }
+        } else {
         for (int p = pb; p < pe; ++p) { const int e = elist[p]; s += S[e * SH + swz(e, c)]; }
+        }
         s = s / (float)(pe - pb < 1 ? 1 : pe - pb);
         float base;
         if (l == 1) {
@@ -527,11 +684,20 @@ using namespace aether;
 
 extern "C" size_t aether_small_rollout_scratch_bytes(void) { return (size_t)kTilesPerStep * kTile * sizeof(float); }
 
-extern "C" int aether_small_rollout_supported(int32_t num_dims, int32_t hidden, int32_t max_nodes, int32_t max_edges) {
+extern "C" int aether_small_rollout_supported(int32_t num_dims, int32_t hidden, int32_t max_nodes, int32_t max_edges,
+                                              uint32_t flags) {
   if ((num_dims != 2 && num_dims != 3) || hidden != SH || max_nodes < 1 || max_nodes > kSmallMaxNodes || max_edges < 0 ||
       max_edges > (1 << 16))
     return 0;
-  return small_plan(max_nodes, max_edges, 0).nb >= 3 ? 1 : 0;
+  return small_plan(max_nodes, max_edges, 0, (flags & AETHER_F_BF16_EDGE_MLP) ? 1 : 0).nb >= 3 ? 1 : 0;
+}
+
+template <int D, bool BF16>
+static int launch_small(const SmallParams& P, const SmallArgs& a, int n_scenes, size_t smem, cudaStream_t st) {
+  AE_CHECK((int)cudaFuncSetAttribute(small_rollout_kernel<D, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  small_rollout_kernel<D, BF16><<<n_scenes, ST, smem, st>>>(P, a);
+  AE_LAUNCH_CHECK();
+  return 0;
 }
 
 extern "C" int aether_small_rollout(const AetherDims* dims, const float* const* params, int32_t n_scenes,
@@ -539,11 +705,11 @@ extern "C" int aether_small_rollout(const AetherDims* dims, const float* const* 
                                     const int64_t* send, const int64_t* recv, int32_t knn_k, int32_t max_nodes,
                                     int32_t max_edges, const float* x0, const float* v0, const float* charges, int32_t steps,
                                     float* traj, int64_t* send_out, int64_t* recv_out, void* scratch, size_t scratch_bytes,
-                                    void* stream) {
+                                    uint32_t flags, void* stream) {
   if (!dims || !params || !node_off || !edge_off || !x0 || !v0 || !charges || !traj || n_scenes < 0 || steps < 0 ||
       (send == nullptr) != (recv == nullptr) || (send == nullptr && knn_k < 0) || (send_out == nullptr) != (recv_out == nullptr))
     return AETHER_E_BADARG;
-  if (!aether_small_rollout_supported(dims->num_dims, dims->hidden, max_nodes, max_edges)) return AETHER_E_UNSUPPORTED;
+  if (!aether_small_rollout_supported(dims->num_dims, dims->hidden, max_nodes, max_edges, flags)) return AETHER_E_UNSUPPORTED;
   if (!scratch || ((uintptr_t)scratch & 127) || scratch_bytes < aether_small_rollout_scratch_bytes()) return AETHER_E_WORKSPACE;
   SmallParams P;
   for (int i = 0; i < P_NUM; ++i) {
@@ -553,22 +719,16 @@ extern "C" int aether_small_rollout(const AetherDims* dims, const float* const* 
   }
   if (n_scenes == 0 || steps == 0) return 0;
   const int D = dims->num_dims;
+  const bool bf16 = flags & AETHER_F_BF16_EDGE_MLP;
   cudaStream_t st = (cudaStream_t)stream;
-  small_pack_kernel<<<kTilesPerStep, 256, 0, st>>>(P, num_edge_feat(D), (float*)scratch);
+  small_pack_kernel<<<kTilesPerStep, 256, 0, st>>>(P, num_edge_feat(D), (float*)scratch, bf16 ? 1 : 0);
   AE_LAUNCH_CHECK();
-  const SmallPlan pl = small_plan(max_nodes, max_edges, 0);
+  const SmallPlan pl = small_plan(max_nodes, max_edges, 0, bf16 ? 1 : 0);
   SmallArgs a;
   a.node_off = node_off; a.edge_off = edge_off; a.order = order; a.send = send; a.recv = recv; a.x0 = x0; a.v0 = v0;
   a.q = charges; a.tiles = (const float*)scratch; a.traj = traj; a.send_out = send_out; a.recv_out = recv_out;
   a.n_nodes = dims->n_nodes; a.steps = steps; a.knn_k = knn_k; a.max_nodes = max_nodes; a.max_edges = max_edges; a.ring = pl.nb;
   const size_t smem = (size_t)pl.total * sizeof(float);
-  if (D == 2) {
-    AE_CHECK((int)cudaFuncSetAttribute(small_rollout_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_rollout_kernel<2><<<n_scenes, ST, smem, st>>>(P, a);
-  } else {
-    AE_CHECK((int)cudaFuncSetAttribute(small_rollout_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_rollout_kernel<3><<<n_scenes, ST, smem, st>>>(P, a);
-  }
-  AE_LAUNCH_CHECK();
-  return 0;
+  if (D == 2) return bf16 ? launch_small<2, true>(P, a, n_scenes, smem, st) : launch_small<2, false>(P, a, n_scenes, smem, st);
+  return bf16 ? launch_small<3, true>(P, a, n_scenes, smem, st) : launch_small<3, false>(P, a, n_scenes, smem, st);
 }

@@ -107,7 +107,7 @@ class Rollout:
         per_edges = (edge_off[1:] - edge_off[:-1])
         self._max_nodes = max(max(sizes), 1) if sizes else 1
         self._max_edges = int(per_edges.max()) if len(sizes) else 0
-        if not self.lib.aether_small_rollout_supported(self.D, self.H, self._max_nodes, self._max_edges):
+        if not self.lib.aether_small_rollout_supported(self.D, self.H, self._max_nodes, self._max_edges, self.flags):
             return "shape not supported by the single-launch kernel (hidden 64, <= 64 particles, edge state in shared memory)"
         self._n_scenes = len(sizes)
         self._node_off = node_off.to(torch.int32).to(dev)
@@ -134,7 +134,7 @@ class Rollout:
                                            _lib.ptr(self.send if static else None), _lib.ptr(self.recv if static else None),
                                            self._knn_k, self._max_nodes, self._max_edges, _lib.ptr(self.x), _lib.ptr(self.v),
                                            _lib.ptr(self.q), self.steps, _lib.ptr(self.traj), _lib.ptr(so), _lib.ptr(ro),
-                                           _lib.ptr(self._scratch), self._scratch.numel(), _stream())
+                                           _lib.ptr(self._scratch), self._scratch.numel(), self.flags, _stream())
         if rc == -3:            # parameter tensors not 16-byte aligned (views into a flat buffer): multi-launch path
             return False
         _lib.check(rc, "aether_small_rollout")

@@ -629,7 +629,8 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
                     "achieved": nb / (ms * 1e-3) / 1e9, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
                     "frac": nb / (ms * 1e-3) / 1e9 / pk["hbm_gbs"] if pk.get("hbm_gbs") else None, "traffic": None,
                     "algorithmic_bytes_per_launch": nb, "peak_source": pk_src,
-                    "note": "compulsory traffic only (inputs + weights + trajectory); the kernel is latency / fp32-issue bound",
+                    "note": "compulsory traffic only (inputs + weights + trajectory); the kernel is bound by per-scene latency "
+                            "(barriers between its phases) and, in fp32 mode, by CUDA-core issue",
                     "fp32_view": {"executed_tflops": fl / (ms * 1e-3) / 1e12, "cuda_core_peak_tflops": cc_peak,
                                   "frac": fl / (ms * 1e-3) / 1e12 / cc_peak, "ctas": len(sizes), "sms": 148},
                     "multi_launch_graph_ms_per_step": multi_ms}
@@ -639,11 +640,11 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
     line = {"metric": "edge_messages_per_sec", "value": value, "unit": "edge-messages/s", "n_gpus": world,
             "steps": steps, "warmup": warmup, "ms_per_step": step_ms, "higher_is_better": True,
             "scaling": scaling, "vs_baseline": None,
-            "dtype": "f32" if args.precision == "fp32" or (not train and roll.persistent) else "bf16",
+            "dtype": "f32" if args.precision == "fp32" else "bf16",
             "data": "synthetic",
             "config": {"workload": cfg["name"], "num_dims": D, "particles_per_graph": N, "graphs_per_gpu": B,
                        "hidden": H, "mode": cfg["mode"] + (" (whole step replayed as one CUDA graph, static edge list)" if graphed is not None else "")
-                       + (" (single launch: one CTA per scene for all steps, fp32)" if not train and roll.persistent else ""),
+                       + (" (single launch: one CTA per scene for all steps)" if not train and roll.persistent else ""),
                        "rollout_steps": T, "edges_per_gpu": E, "nodes_per_gpu": Nn,
                        "precision": args.precision, "parallelism": "dp%d" % world,
                        "l2": "flushed between steps" if small else "working set exceeds L2"},

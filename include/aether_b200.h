@@ -188,7 +188,9 @@ int aether_rollout_step(const AetherDims* dims, const float* const* params, cons
 
 /* T rollout steps of a batch of small scenes in one launch (csrc/small.cu): one CTA keeps a whole scene -- edge state,
  * node state, frames, edge list -- in shared memory for all steps; per step it does what aether_rollout_step does
- * (inference only, fp32 arithmetic whatever the precision flag of the multi-launch path would be).  A small pack
+ * (inference only).  flags = 0: fp32 arithmetic on the CUDA cores (the fp32 tolerance); AETHER_F_BF16_EDGE_MLP: the
+ * edge MLP on the tensor cores (mma.sync, bf16 operands, fp32 accumulate; edge state kept as bf16 in shared memory:
+ * the bf16 tolerance, twice the edges per scene), everything else still fp32.  A small pack
  * launch in front writes the step's 32 weight tiles (64 x 64, transposed) into `scratch`
  * (aether_small_rollout_scratch_bytes, 128-byte aligned); the rollout kernel streams them from there (L2) by bulk copies.
  *   node_off [n_scenes+1] (int32), edge_off [n_scenes+1] (int64): first particle / first edge of every scene;
@@ -202,12 +204,12 @@ int aether_rollout_step(const AetherDims* dims, const float* const* params, cons
  * three-tile weight ring within one SM's shared memory); unsupported shapes -- and parameter tensors that are not
  * 16-byte aligned -- return AETHER_E_UNSUPPORTED and the caller uses aether_rollout_step. */
 size_t aether_small_rollout_scratch_bytes(void);
-int aether_small_rollout_supported(int32_t num_dims, int32_t hidden, int32_t max_nodes, int32_t max_edges);
+int aether_small_rollout_supported(int32_t num_dims, int32_t hidden, int32_t max_nodes, int32_t max_edges, uint32_t flags);
 int aether_small_rollout(const AetherDims* dims, const float* const* params, int32_t n_scenes, const int32_t* node_off,
                          const int64_t* edge_off, const int32_t* order, const int64_t* send, const int64_t* recv,
                          int32_t knn_k, int32_t max_nodes, int32_t max_edges, const float* x0, const float* v0,
                          const float* charges, int32_t steps, float* traj, int64_t* send_out, int64_t* recv_out,
-                         void* scratch, size_t scratch_bytes, void* stream);
+                         void* scratch, size_t scratch_bytes, uint32_t flags, void* stream);
 
 /* Bench support: kernels launched by this library so far; optional per-category CUDA-event timing
  * (categories: 0 edge-MLP forward, 1 edge backward data grads, 2 edge weight grads, 3 segment

@@ -52,23 +52,23 @@ def test_size_queries(lib):
 def test_small_rollout_shape_query(lib):
     """Host-side logic of the single-launch rollout (no GPU work): which shapes fit one SM's shared memory."""
     ok = lib.aether_small_rollout_supported
-    assert ok(2, 64, 5, 20) == 1 and ok(3, 64, 40, 400) == 1 and ok(2, 64, 21, 420) == 1
-    assert ok(2, 32, 5, 20) == 0 and ok(2, 128, 5, 20) == 0           # built for hidden 64
-    assert ok(2, 64, 65, 100) == 0                                     # more than 64 particles per scene
-    assert ok(2, 64, 40, 1560) == 0                                    # fully connected 40: edge state beyond 227 KB
-    assert ok(4, 64, 5, 20) == 0 and ok(2, 64, 0, 0) == 0
+    assert ok(2, 64, 5, 20, 0) == 1 and ok(3, 64, 40, 400, 0) == 1 and ok(2, 64, 21, 420, 0) == 1
+    assert ok(2, 32, 5, 20, 0) == 0 and ok(2, 128, 5, 20, 0) == 0           # built for hidden 64
+    assert ok(2, 64, 65, 100, 0) == 0                                     # more than 64 particles per scene
+    assert ok(2, 64, 40, 1560, 0) == 0 and ok(2, 64, 40, 1560, 2) == 0 and ok(2, 64, 30, 870, 2) == 1                                  # fully connected 40: edge state beyond 227 KB
+    assert ok(4, 64, 5, 20, 0) == 0 and ok(2, 64, 0, 0, 0) == 0
     d = __import__("aether_b200")._lib.AetherDims(2, 32, 10, 40)
     arr = (ctypes.c_void_p * 47)()
     one = ctypes.c_void_p(256)
     rc = lib.aether_small_rollout(ctypes.byref(d), arr, 2, one, one, None, one, one, 0, 5, 20, one, one, one, 3, one, None, None,
-                                  one, 1 << 20, None)
+                                  one, 1 << 20, 0, None)
     assert rc == -3                                                    # AETHER_E_UNSUPPORTED, before any launch
     rc = lib.aether_small_rollout(ctypes.byref(d), arr, 2, one, one, None, one, None, 0, 5, 20, one, one, one, 3, one, None, None,
-                                  one, 1 << 20, None)
+                                  one, 1 << 20, 0, None)
     assert rc == -1                                                    # send without recv
     d64 = __import__("aether_b200")._lib.AetherDims(2, 64, 10, 40)
     rc = lib.aether_small_rollout(ctypes.byref(d64), arr, 2, one, one, None, one, one, 0, 5, 20, one, one, one, 3, one, None, None,
-                                  one, 16, None)
+                                  one, 16, 0, None)
     assert rc == -2                                                    # scratch too small
     assert lib.aether_small_rollout_scratch_bytes() == 32 * 64 * 64 * 4
 

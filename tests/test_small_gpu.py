@@ -20,9 +20,9 @@ def ab():
     return aether_b200
 
 
-def make(ab, D, H=64, seed=1):
+def make(ab, D, H=64, seed=1, precision="fp32"):
     torch.manual_seed(seed)
-    m = ab.Aether(2 * D, H, 0.0, D, device="cuda").eval()
+    m = ab.Aether(2 * D, H, 0.0, D, device="cuda", precision=precision).eval()
     p = {k: v.detach().cpu() for k, v in m.state_dict().items()}
     return m, p
 
@@ -126,6 +126,56 @@ def test_small_rollout_edge_cases(ab):
     assert rel_err(xs.cpu(), want) <= 2e-5
 
 
+@pytest.mark.parametrize("D,N,B,T", [(2, 5, 16, 20), (3, 5, 7, 6), (2, 24, 2, 4), (3, 29, 2, 3)])
+def test_small_rollout_bf16_fc(ab, D, N, B, T):
+    """Tensor-core mode (precision="bf16": edge MLP on mma.sync, bf16 edge state in shared memory) against the fp32 oracle
+    at the bf16 bar (2e-2); 24 and 29 particles: 552 / 812 edges per scene, three / four 256-row chunks -- more than the
+    fp32 mode holds."""
+    m, p = make(ab, D, precision="bf16")
+    x, v, q = O.synth_state(B, N, D, seed=3)
+    send, recv = O.fc_edges(N, B)
+    r = ab.Rollout(m, N * B, T, edges=(send.cuda(), recv.cuda()), sizes=[N] * B, persistent=True)
+    xs = r.run(x.cuda(), v.cuda(), q.cuda()).clone()
+    ref = ab.rollout(m, x.cuda(), v.cuda(), q.cuda(), T, edges=(send.cuda(), recv.cuda()), persistent=False)
+    with torch.no_grad():
+        want = O.rollout(p, x, v, q, lambda xx: (send, recv), T)
+    e_or, e_ml = rel_err(xs.cpu(), want), rel_err(ref.cpu(), want)
+    print("bf16 single-launch vs oracle %.2e; multi-launch bf16 vs oracle %.2e" % (e_or, e_ml))
+    assert e_or <= 2e-2
+    assert torch.equal(xs, r.run(x.cuda(), v.cuda(), q.cuda()))
+
+
+def test_small_rollout_bf16_golden_and_knn(ab):
+    """Tensor-core mode on the reference's golden rollouts (2e-2) and on ragged kNN scenes (edge lists stay bit-identical:
+    they depend on positions only through the fp32 distances)."""
+    for case, sizes in [("step3d_h64", [5, 5]), ("step2d_h64_n12", [24])]:
+        g = load_golden(case)
+        D, H = int(g["D"]), int(g["H"])
+        m = ab.Aether(2 * D, H, 0.0, D, device="cuda", precision="bf16").eval()
+        m.load_state_dict(golden_params(g))
+        T = g["rollout"].shape[0]
+        xs = ab.rollout(m, dev(g["x"]), dev(g["vel"]), dev(g["charges"]), T, edges=(dev(g["send"]), dev(g["recv"])), sizes=sizes,
+                        persistent=True)
+        assert rel_err(xs.cpu(), g["rollout"]) <= 2e-2
+    D, k, T = 2, 10, 5
+    sizes = [10, 40, 17, 3, 25, 1, 2, 33]
+    m, p = make(ab, D, precision="bf16")
+    gen = torch.Generator().manual_seed(5)
+    n = sum(sizes)
+    x = torch.rand(n, D, generator=gen)
+    v = (torch.rand(n, D, generator=gen) - 0.5) * 0.1
+    q = torch.randint(0, 2, (n, 1), generator=gen).float() * 2 - 1
+    plan = ab.KnnPlan(sizes, k, "cuda")
+    r = ab.Rollout(m, n, T, knn_plan=plan, persistent=True)
+    xs = r.run(x.cuda(), v.cuda(), q.cuda(), dump_edges=True).clone()
+    s, rr = ab.knn_edges(xs[T - 2].contiguous(), plan)
+    assert torch.equal(r.last_edges[0], s) and torch.equal(r.last_edges[1], rr)
+    # one step from the same state: no neighbour flips between the two arithmetic modes
+    with torch.no_grad():
+        want = O.rollout(p, x, v, q, lambda xx: O.knn_edges_batched(xx, sizes, k), 1)
+    assert rel_err(xs[:1].cpu(), want) <= 2e-2
+
+
 def test_small_rollout_selection(ab):
     """The single-launch path is chosen only where it applies; persistent=True says why when it does not."""
     m32, _ = make(ab, 2, H=32)
@@ -146,4 +196,4 @@ def test_small_rollout_selection(ab):
     with pytest.raises(ValueError):                                               # 1560 edges do not fit one SM
         ab.Rollout(m, 40, 2, edges=(big[0].cuda(), big[1].cuda()), sizes=[40], persistent=True)
     lib = ab._lib.load()
-    assert lib.aether_small_rollout_supported(2, 64, 40, 400) == 1
+    assert lib.aether_small_rollout_supported(2, 64, 40, 400, 0) == 1

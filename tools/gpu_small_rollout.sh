@@ -10,10 +10,10 @@ if [ "$1" = "memcheck" ]; then
 timeout 900 compute-sanitizer --tool memcheck --print-limit 20 python -m pytest tests/test_small_gpu.py -q -m gpu -x -k "golden or edge_cases" > gpurun_out/memcheck_small.log 2>&1; echo "memcheck rc=$?"
 grep -E "ERROR SUMMARY|Invalid|passed|failed" gpurun_out/memcheck_small.log | head -20
 fi
-for w in c1 c3; do for f in "" "--multi-launch"; do timeout 300 python bench.py --workload $w --steps 20 --warmup 5 --no-cpu-baseline --no-e2e $f 2> gpurun_out/bench_small.err | python -c "
+for w in c1 c3; do for f in "" "--precision fp32" "--multi-launch"; do timeout 300 python bench.py --workload $w --steps 20 --warmup 5 --no-cpu-baseline --no-e2e $f 2> gpurun_out/bench_small.err | python -c "
 import json,sys
 for l in sys.stdin:
     if l.startswith('{'):
         d=json.loads(l); print('$w $f', d['ms_per_step'], d['value'], d['gpu_launches'], d['roofline'].get('fp32_view'), d['roofline'].get('multi_launch_graph_ms_per_step'))
-        open('gpurun_out/bench_${w}${f}.json','w').write(l)
+        open('gpurun_out/bench_${w}$(echo $f | tr -d " -").json','w').write(l)
 "; tail -2 gpurun_out/bench_small.err; done; done

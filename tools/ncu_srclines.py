@@ -28,5 +28,5 @@ for r in rows:
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 30
 S = sum(v[0] for v in tot.values()); I = sum(v[1] for v in tot.values())
 print("samples", S, "instructions", I)
-for k, v in sorted(tot.items(), key=lambda kv: -kv[1][1])[:n]:
+for k, v in sorted(tot.items(), key=lambda kv: -kv[1][1 if len(sys.argv) > 3 else 0])[:n]:
     print("%-14s %5d  smp %6d  inst %10d (%4.1f%%)  %s" % (k[0], k[1], v[0], v[1], 100.0 * v[1] / max(I, 1), v[2][:90]))
