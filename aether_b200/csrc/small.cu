@@ -58,13 +58,12 @@ struct SmallArgs {
   int32_t steps, knn_k, max_nodes, max_edges, ring;
 };
 
-// bytes of packed tile i: the edge MLP's tiles (W_e, W_2 of every layer) are 64 x 64 bf16 in the tensor-core mode
-__host__ __device__ inline bool small_edge_tile(int i) { return i < 30 && (i & 7) < 2; }
-__host__ __device__ inline uint32_t small_tile_bytes(int i, bool bf16) { return bf16 && small_edge_tile(i) ? kTile * 2 : kTile * 4; }
+// bytes of a packed tile: 64 x 64 fp32, or bf16 in the tensor-core mode
+__host__ __device__ inline uint32_t small_tile_bytes(bool bf16) { return bf16 ? kTile * 2 : kTile * 4; }
 
 // shared-memory plan, in floats (all regions 16-byte aligned)
 struct SmallPlan {
-  int S, T1, ring, X, PS, PR, x, v, xn, f, pred, R, x0, q, send, recv, elist, rowptr, bars, bias, total, nb;
+  int S, T1, ring, X, PS, PR, x, v, xn, f, pred, R, x0, q, send, recv, elist, rowptr, bars, bias, n16, total, nb, slot;
 };
 __host__ __device__ inline int up4(int v) { return (v + 3) & ~3; }
 // bf16 = 1: edge state and chunk temporary as bf16 (128-byte rows: half the floats), T1 then holds 256 rows
@@ -80,14 +79,16 @@ __host__ __device__ inline SmallPlan small_plan(int nmax, int emax, int nb, int 
   p.send = take(emax); p.recv = take(emax); p.elist = take(emax); p.rowptr = take(nmax + 1);
   p.bars = take(2 * kMaxRing);
   p.bias = take(2 * SH);
+  p.n16 = take(bf16 ? 4 * nmax * (SH / 2) : 0);      // bf16 A operands of the node GEMMs: y, x, two hidden halves
   o = (o + 31) & ~31;
   p.ring = o;
+  p.slot = bf16 ? kTile / 2 : kTile;                  // floats per ring buffer (bf16 tiles are 8 KB)
   if (nb <= 0) {                    // as many ring buffers as fit
-    nb = (kSmemLimit / 4 - o) / kTile;
+    nb = (kSmemLimit / 4 - o) / p.slot;
     if (nb > kMaxRing) nb = kMaxRing;
   }
   p.nb = nb;
-  p.total = o + (nb > 0 ? nb : 0) * kTile;
+  p.total = o + (nb > 0 ? nb : 0) * p.slot;
   return p;
 }
 
@@ -111,13 +112,13 @@ __host__ __device__ inline TileDesc small_tile(const SmallParams& P, int i, int 
 }
 
 // tiles[i][k][n] = W_i[n][k] (zero rows for k >= K): one block per tile, transposed through shared memory
-// Tensor-core mode: the edge tiles are written as bf16 [n][k] rows of 128 bytes with their 16-byte chunks XOR-swizzled by
+// Tensor-core mode: the tiles are written as bf16 [n][k] rows of 128 bytes with their 16-byte chunks XOR-swizzled by
 // n & 7 -- exactly the shared-memory image ldmatrix reads -- and layer 1's W_e as [W | W] against the [hi | lo] features.
 __global__ void __launch_bounds__(256) small_pack_kernel(const __grid_constant__ SmallParams P, int FE, float* __restrict__ tiles,
                                                          int bf16) {
   __shared__ float t[SH][SH + 1];
   const TileDesc d = small_tile(P, blockIdx.x, FE);
-  if (bf16 && small_edge_tile(blockIdx.x)) {
+  if (bf16) {
     __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(tiles + (size_t)blockIdx.x * kTile);
     const bool first = blockIdx.x == 0;
     for (int i = threadIdx.x; i < kTile; i += 256) {
@@ -279,6 +280,12 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
   float* const ringbuf = sm + pl.ring;
   const uint32_t bar0 = smem_u32(sm + pl.bars);
   const int NB = pl.nb;
+  constexpr int SLOT = BF16 ? kTile / 2 : kTile;
+  // tensor-core mode: bf16 copies of the node GEMMs' A operands, [n][64] with the 128-byte swizzle
+  char* const Y16 = reinterpret_cast<char*>(sm + pl.n16);
+  char* const X16 = Y16 + a.max_nodes * 128;
+  char* const HA16 = X16 + a.max_nodes * 128;
+  char* const HB16 = HA16 + a.max_nodes * 128;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int sc = a.order ? a.order[blockIdx.x] : blockIdx.x;
@@ -304,13 +311,13 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
     if (tid == 0)
       for (int g = issued; g < lim; ++g) {
         const int b = g % NB;
-        const uint32_t nbytes = small_tile_bytes(g % kTilesPerStep, BF16);
+        const uint32_t nbytes = small_tile_bytes(BF16);
         tc::mbar_arrive_expect_tx(bar0 + 8 * b, nbytes);
-        tc::bulk_load(smem_u32(ringbuf + b * kTile), a.tiles + (size_t)(g % kTilesPerStep) * kTile, nbytes, bar0 + 8 * b);
+        tc::bulk_load(smem_u32(ringbuf + b * SLOT), a.tiles + (size_t)(g % kTilesPerStep) * kTile, nbytes, bar0 + 8 * b);
       }
     if (lim > issued) issued = lim;
   };
-  auto tile = [&](int g) -> const float* { return ringbuf + (g % NB) * kTile; };
+  auto tile = [&](int g) -> const float* { return ringbuf + (g % NB) * SLOT; };
   // wait until tile g has landed, then barrier (which also orders the shared-memory writes of the phase before)
   auto wait_tile = [&](int g) { tc::mbar_wait(bar0 + 8 * (g % NB), (uint32_t)((g / NB) & 1)); };
   auto acquire = [&](int g) {
@@ -359,6 +366,39 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
     __syncthreads();
   };
   if (!knn) build_csr();
+
+  // tensor-core node GEMMs: warp = (row tile nrt of 16 particles, column quarter ncq of 16 outputs); acc[j] = n-tile j of
+  // the quarter.  Lane (g, tq): acc[j][0..1] = row 16 nrt + g, columns 16 ncq + 8 j + 2 tq, +1; acc[j][2..3] = row + 8.
+  const int nrt = warp & 3, ncq = warp >> 2;
+  const bool nact = nrt * 16 < n;
+  auto node_mma = [&](float (&acc)[2][4], uint32_t aBase, uint32_t wBase, bool zero) {
+    if (zero) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.0f;
+    }
+    int ar = nrt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+    ar = ar < n - 1 ? ar : n - 1;
+    const int ac = lane >> 4, bn = 16 * ncq + (lane & 7) + ((lane >> 4) << 3), bc = (lane >> 3) & 1;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      uint32_t af[4], bf[4];
+      ldsm_x4(aBase + sw16(ar, 2 * ks + ac), af);
+      ldsm_x4(wBase + sw16(bn, 2 * ks + bc), bf);
+      mma_bf16(acc[0], af, bf[0], bf[1]);
+      mma_bf16(acc[1], af, bf[2], bf[3]);
+    }
+  };
+  auto node_each = [&](const float (&acc)[2][4], auto&& f) {
+    const int g = lane >> 2, tq = lane & 3;
+#pragma unroll
+    for (int hf = 0; hf < 2; ++hf) {
+      const int r = nrt * 16 + g + 8 * hf;
+      if (r < n) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) f(r, 16 * ncq + 8 * j + 2 * tq, acc[j][2 * hf], acc[j][2 * hf + 1]);
+      }
+    }
+  };
 
   for (int t = 0; t < a.steps; ++t) {
     const int g0 = t * kTilesPerStep;   // first tile of this step
@@ -592,7 +632,66 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
           for (int k = 0; k < 3 * D; ++k) base = fmaf(sx0[node * 3 * D + k], __ldg(w + k), base);
         } else base = X[node * SH + swz(node, c)];
         Y[node * SH + swz(node, c)] = base + s;
+        if constexpr (BF16) *reinterpret_cast<__nv_bfloat16*>(Y16 + sw16(node, c >> 3) + 2 * (c & 7)) = __float2bfloat16_rn(base + s);
       }
+      if constexpr (BF16) {
+        // tensor-core mode: x = y + W4 silu(W3 y + b3) + b4 and the next layer's node terms on mma.sync; warp = (16-row
+        // tile, 16-column quarter), A operands are the bf16 copies written by the producing phases
+        const float* b3 = P.p[sl.u0b];
+        const float* b4 = P.p[sl.u2b];
+        float acc[2][4];
+        acquire(b + 2);                 // orders the y writes
+        if (nact) {
+          node_mma(acc, smem_u32(Y16), smem_u32(tile(b + 2)), true);
+          node_each(acc, [&](int r, int c, float v0, float v1) {
+            const float2 bb = __ldg(reinterpret_cast<const float2*>(b3 + c));
+            *reinterpret_cast<uint32_t*>(HA16 + sw16(r, c >> 3) + 2 * (c & 7)) = tc::pack_bf16(silu_s(v0 + bb.x), silu_s(v1 + bb.y));
+          });
+        }
+        acquire(b + 3);
+        ring_fill(b + 3);
+        if (nact) {
+          node_mma(acc, smem_u32(Y16), smem_u32(tile(b + 3)), true);
+          node_each(acc, [&](int r, int c, float v0, float v1) {
+            const float2 bb = __ldg(reinterpret_cast<const float2*>(b3 + SH + c));
+            *reinterpret_cast<uint32_t*>(HB16 + sw16(r, c >> 3) + 2 * (c & 7)) = tc::pack_bf16(silu_s(v0 + bb.x), silu_s(v1 + bb.y));
+          });
+        }
+        acquire(b + 4);                 // orders the hidden-layer writes
+        ring_fill(b + 4);
+        if (nact) node_mma(acc, smem_u32(HA16), smem_u32(tile(b + 4)), true);
+        acquire(b + 5);
+        ring_fill(b + 5);
+        if (nact) {
+          node_mma(acc, smem_u32(HB16), smem_u32(tile(b + 5)), false);
+          node_each(acc, [&](int r, int c, float v0, float v1) {
+            const float2 bb = __ldg(reinterpret_cast<const float2*>(b4 + c));
+            const int i = r * SH + swz(r, c);
+            const float2 y = *reinterpret_cast<const float2*>(Y + i);
+            const float x0v = y.x + (v0 + bb.x), x1v = y.y + (v1 + bb.y);
+            *reinterpret_cast<float2*>(X + i) = make_float2(x0v, x1v);
+            *reinterpret_cast<uint32_t*>(X16 + sw16(r, c >> 3) + 2 * (c & 7)) = tc::pack_bf16(x0v, x1v);
+          });
+        }
+        if (l < 4) {
+          const float* bn = P.p[layer_slots(l + 1).m0b];
+          acquire(b + 6);               // orders the x writes
+          ring_fill(b + 6);
+          if (nact) {
+            node_mma(acc, smem_u32(X16), smem_u32(tile(b + 6)), true);
+            node_each(acc, [&](int r, int c, float v0, float v1) { *reinterpret_cast<float2*>(PS + r * SH + c) = make_float2(v0, v1); });
+          }
+          acquire(b + 7);
+          ring_fill(b + 7);
+          if (nact) {
+            node_mma(acc, smem_u32(X16), smem_u32(tile(b + 7)), true);
+            node_each(acc, [&](int r, int c, float v0, float v1) {
+              const float2 bb = __ldg(reinterpret_cast<const float2*>(bn + c));
+              *reinterpret_cast<float2*>(PR + r * SH + c) = make_float2(v0 + bb.x, v1 + bb.y);
+            });
+          }
+        }
+      } else {
       // x = y + W4 silu(W3 y + b3) + b4 (locs.py:241): hidden layer of 2H in two column halves, one weight tile each
       {
         const float4 b3a = ld4(P.p[sl.u0b]), b3b = ld4(P.p[sl.u0b] + SH), b4 = ld4(P.p[sl.u2b]);
@@ -636,9 +735,33 @@ __global__ void __launch_bounds__(ST, 1) small_rollout_kernel(const __grid_const
         ring_fill(b + 7);
         chunk_gemm(X, SH, SH, tile(b + 7), 0, n, [&](int r, int c, float4 v) { *reinterpret_cast<float4*>(PR + r * SH + c) = add4(v, bn); });
       }
+      }
     }
 
     // ---- out MLP (locs.py:160-168,193), rotation back and Euler update (local_to_global.py:12-13, aether.py:185) -------
+    if constexpr (BF16) {
+      float acc[2][4];
+      acquire(g0 + 30);                 // orders the x writes
+      ring_fill(g0 + 30);
+      if (nact) {
+        node_mma(acc, smem_u32(X16), smem_u32(tile(g0 + 30)), true);
+        node_each(acc, [&](int r, int c, float v0, float v1) {
+          const float2 bb = __ldg(reinterpret_cast<const float2*>(P.p[P_OUT0_B] + c));
+          *reinterpret_cast<uint32_t*>(HA16 + sw16(r, c >> 3) + 2 * (c & 7)) = tc::pack_bf16(silu_s(v0 + bb.x), silu_s(v1 + bb.y));
+        });
+      }
+      acquire(g0 + 31);
+      ring_fill(g0 + 31);
+      if (nact) {
+        node_mma(acc, smem_u32(HA16), smem_u32(tile(g0 + 31)), true);
+        node_each(acc, [&](int r, int c, float v0, float v1) {
+          const float2 bb = __ldg(reinterpret_cast<const float2*>(P.p[P_OUT3_B] + c));
+          *reinterpret_cast<float2*>(Y + r * SH + swz(r, c)) = make_float2(silu_s(v0 + bb.x), silu_s(v1 + bb.y));
+        });
+      }
+      __syncthreads();
+      ring_fill(g0 + 32);
+    } else
     {
       const float4 c0 = ld4(P.p[P_OUT0_B]), c3 = ld4(P.p[P_OUT3_B]);
       acquire(g0 + 30);                 // orders the x writes
