@@ -4,22 +4,27 @@
 //   kNN     : experiments/ind/single_ind_data.py:186-217, rebuilt from x_t every step
 //
 // One CTA of 512 threads owns one scene (n <= 64 particles) for all T steps.  Nothing of a step leaves the SM except the
-// new positions: the edge state [E, 64] (fp32), the node state, the frames and the edge list live in shared memory, and
+// new positions: the edge state [E, 64], the node state, the frames and the edge list live in shared memory, and
 // the kNN lists are rebuilt there from the positions the step just produced.  The multi-launch path (step.cu) needs ~35
 // launches per step at these sizes and is launch-latency bound even inside a CUDA graph (170 us per step at 16 x 5
 // particles).
 //
 // Weights.  A step multiplies by 32 weight tiles of 64 x 64 (per layer: W_e, W_2, the two halves of W_3 and of W_4, W_s
 // and W_r of the next layer; then the out MLP's two).  A pack launch in front of the rollout writes them once as
-// [k][n] fp32 tiles (16 KB each, 512 KB in all, L2-resident and shared by every CTA); the rollout kernel streams them
-// through a ring of NB >= 3 shared-memory buffers with cp.async.bulk + mbarrier (one thread issues, nobody copies), as
-// many tiles ahead as the scene's size leaves room for (a whole layer and more at config 1's size).
+// ready-to-use shared-memory images (512 KB fp32 / 256 KB bf16, L2-resident and shared by every CTA); the rollout kernel
+// streams them through a ring of 3..16 shared-memory buffers with cp.async.bulk + mbarrier (one thread issues, nobody
+// copies), as many tiles ahead as the scene's size leaves room for.
 //
-// Arithmetic is fp32 on the CUDA cores (the tolerance for these configurations is the fp32 one, 1e-5).  GEMM tiling: a
-// warp owns 2 RW rows of a row chunk -- even rows on lanes 0-15, odd rows on lanes 16-31 -- and each lane four adjacent
-// output columns: per 4 steps of k that is 4 + RW 128-bit shared loads for 16 RW FMAs.  The A operands (edge state, node
-// state) are stored with their 16-byte chunks XOR-swizzled by the row parity, so the two rows a warp reads per instruction
-// sit in different banks.  Compiled with -fmad=false like the other geometry files; the GEMM loops use explicit fmaf.
+// Two arithmetic modes (template parameter BF16, chosen by the model's precision flag):
+//   fp32 (tolerance 1e-5): CUDA cores.  A warp owns 2 RW rows of a row chunk -- even rows on lanes 0-15, odd rows on
+//     lanes 16-31 -- and each lane four adjacent output columns: per 4 steps of k that is 4 + RW 128-bit shared loads
+//     for 16 RW FMAs.  The A operands (edge state, node state) are stored with their 16-byte chunks XOR-swizzled by the
+//     row parity, so the two rows a warp reads per instruction sit in different banks.
+//   tensor cores (tolerance 2e-2): every GEMM on mma.sync.m16n8k16 (bf16 operands, fp32 accumulate) with ldmatrix on
+//     128-byte rows swizzled by row & 7; the edge state is bf16 (twice the edges per scene), 256-edge chunks with 16
+//     rows per warp, node GEMMs with warp = (16-row tile, 16-column quarter) on bf16 copies written by the producing
+//     phases.  Aggregation, residuals, field network, geometry and the Euler update stay fp32.
+// Compiled with -fmad=false like the other geometry files; the GEMM loops use explicit fmaf.
 #include <type_traits>
 
 #include "geom.cuh"

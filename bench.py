@@ -631,8 +631,10 @@ def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="
                     "algorithmic_bytes_per_launch": nb, "peak_source": pk_src,
                     "note": "compulsory traffic only (inputs + weights + trajectory); the kernel is bound by per-scene latency "
                             "(barriers between its phases) and, in fp32 mode, by CUDA-core issue",
-                    "fp32_view": {"executed_tflops": fl / (ms * 1e-3) / 1e12, "cuda_core_peak_tflops": cc_peak,
-                                  "frac": fl / (ms * 1e-3) / 1e12 / cc_peak, "ctas": len(sizes), "sms": 148},
+                    "flops_view": {"executed_tflops": fl / (ms * 1e-3) / 1e12, "ctas": len(sizes), "sms": 148,
+                                   "mode": "CUDA cores, fp32" if args.precision == "fp32" else "mma.sync m16n8k16 bf16, fp32 accumulate",
+                                   "cuda_core_peak_tflops": cc_peak if args.precision == "fp32" else None,
+                                   "frac_of_cuda_core_peak": fl / (ms * 1e-3) / 1e12 / cc_peak if args.precision == "fp32" else None},
                     "multi_launch_graph_ms_per_step": multi_ms}
     step_ms = total / steps * 1e3
     share = {k: (prof["ms"][i] / steps) / step_ms for i, k in
@@ -785,7 +787,9 @@ def parity_report(dev, precision):
     p = {k: v.detach().cpu() for k, v in model.state_dict().items()}
     x, v, q = O.synth_state(B, N, D, seed=1)
     send, recv = ab.fc_edges(N, B, dev)
-    traj = ab.rollout(model, x.to(dev), v.to(dev), q.to(dev).reshape(-1), T, edges=(send, recv)).cpu()
+    # both rollout paths: the single launch (csrc/small.cu, what `--workload c1` times) and the per-step launches
+    traj = ab.rollout(model, x.to(dev), v.to(dev), q.to(dev).reshape(-1), T, edges=(send, recv), sizes=[N] * B, persistent=True).cpu()
+    traj_ml = ab.rollout(model, x.to(dev), v.to(dev), q.to(dev).reshape(-1), T, edges=(send, recv), persistent=False).cpu()
     so, ro = O.fc_edges(N, B)
     with torch.no_grad():
         ref = O.rollout(p, x, v, q, lambda xx: (so, ro), T)
@@ -793,7 +797,11 @@ def parity_report(dev, precision):
     n = min(traj.shape[0], ref.shape[0])
     mse = [float(((traj[-n:][t] - ref[-n:][t]) ** 2).mean()) for t in range(n)]
     out["config1_shape_rollout"] = {"shape": "D=2 N=5 B=16 H=64 %s, %d-step rollout vs fp32 CPU oracle" % (precision, T),
+                                    "path": "single launch (small_rollout_kernel)",
                                     "mse_step_1": mse[0], "mse_step_last": mse[-1], "mse_mean": sum(mse) / len(mse),
+                                    "rel_max": float((traj - ref).abs().max() / ref.abs().max()),
+                                    "multi_launch_mse_mean": float(((traj_ml - ref) ** 2).mean()),
+                                    "multi_launch_rel_max": float((traj_ml - ref).abs().max() / ref.abs().max()),
                                     "position_scale_rms": float((ref ** 2).mean().sqrt())}
     return out
 

@@ -14,6 +14,6 @@ for w in c1 c3; do for f in "" "--precision fp32" "--multi-launch"; do timeout 3
 import json,sys
 for l in sys.stdin:
     if l.startswith('{'):
-        d=json.loads(l); print('$w $f', d['ms_per_step'], d['value'], d['gpu_launches'], d['roofline'].get('fp32_view'), d['roofline'].get('multi_launch_graph_ms_per_step'))
+        d=json.loads(l); print('$w $f', d['ms_per_step'], d['value'], d['gpu_launches'], d['roofline'].get('flops_view'), d['roofline'].get('multi_launch_graph_ms_per_step'))
         open('gpurun_out/bench_${w}$(echo $f | tr -d " -").json','w').write(l)
 "; tail -2 gpurun_out/bench_small.err; done; done
