@@ -35,6 +35,7 @@ SIGNATURES = {
     "aether_graph_scratch_bytes": (c_size_t, [c_int64, c_int64]),
     "aether_graph_prepare": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(AetherGraphC), c_void_p, c_void_p,
                                      c_size_t, c_void_p]),
+    "aether_graph_prepare_static": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(AetherGraphC), c_void_p, c_void_p]),
     "aether_fc_edges": (c_int, [c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "aether_knn_edges": (c_int, [c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
     "aether_caller_prep": (c_int, [c_void_p, c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_int64, c_int64,

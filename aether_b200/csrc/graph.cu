@@ -357,6 +357,52 @@ extern "C" int aether_graph_prepare(const int64_t* send, const int64_t* recv, in
   return 0;
 }
 
+// ---- aether_graph_prepare without any allocation by anybody: the scratch is a file-scope device array ----------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The array is sized for the stated
+// maximum and is held by every GPU that loads the library until the process exits (2.5 MB).  In host code the array's
+// NAME is a host-side stand-in, not a device address: the address is asked for once per device with
+// cudaGetSymbolAddress (that device current) and only that pointer is handed to kernels.
+namespace aether {
+namespace {
+constexpr size_t static_scratch_bytes(int64_t Nn, int64_t E) {
+  return ((size_t)(Nn + 1) * 4 + 255) / 256 * 256 * 2 + ((size_t)E * 4 + 255) / 256 * 256;
+}
+constexpr size_t kStaticScratchBytes = static_scratch_bytes(AETHER_GRAPH_STATIC_MAX_NODES, AETHER_GRAPH_STATIC_MAX_EDGES);
+static __device__ __align__(256) unsigned char g_graph_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+std::atomic<void*> g_static_scratch_ptr[kMaxDevices];     // device address of the array on device i; null: not asked yet
+
+// Device address of the array on the CURRENT device (looked up once per device; no allocation: the array is part of the
+// loaded module).
+int static_scratch(void** out) {
+  int dev = -1;
+  AE_CHECK((int)cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return AETHER_E_UNSUPPORTED;
+  void* p = g_static_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    AE_CHECK((int)cudaGetSymbolAddress(&p, g_graph_static_scratch));
+    if (!p) return AETHER_E_WORKSPACE;
+    g_static_scratch_ptr[dev].store(p, std::memory_order_release);   // racing threads store the same value
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace
+}  // namespace aether
+
+extern "C" int aether_graph_prepare_static(const int64_t* send, const int64_t* recv, int64_t E, int64_t Nn, AetherGraph* g,
+                                           int32_t* status, void* stream) {
+  if (E < 0 || Nn < 0) return AETHER_E_BADARG;
+  if (Nn > AETHER_GRAPH_STATIC_MAX_NODES || E > AETHER_GRAPH_STATIC_MAX_EDGES) return AETHER_E_TOO_LARGE;
+  void* scratch = nullptr;
+  AE_CHECK(static_scratch(&scratch));
+  // the existing entry point, unchanged, on the static array: it clears the counters it needs at zero itself
+  // (csr_by_key) and overwrites the rest before reading it, so the previous call's contents do not matter
+  return aether_graph_prepare(send, recv, E, Nn, g, status, scratch, kStaticScratchBytes, stream);
+}
+
 extern "C" int aether_fc_edges(int64_t n, int64_t B, int64_t* send, int64_t* recv, void* stream) {
   if (n < 0 || B < 0) return AETHER_E_BADARG;
   const int64_t tot = n * (n - 1) * B;

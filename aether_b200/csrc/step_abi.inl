@@ -9,6 +9,7 @@ extern "C" const char* aether_error_string(int code) {
     case AETHER_E_BADARG: return "aether_b200: bad argument";
     case AETHER_E_WORKSPACE: return "aether_b200: workspace or scratch buffer too small";
     case AETHER_E_UNSUPPORTED: return "aether_b200: configuration not supported by this kernel";
+    case AETHER_E_TOO_LARGE: return "aether_b200: size exceeds the maximum of this no-allocation entry point (static scratch: at most 65536 nodes and 524288 edges); use the variant that takes caller-provided scratch";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "aether_b200: unknown error";
   }
 }

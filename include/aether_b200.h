@@ -59,6 +59,7 @@ extern "C" {
 #define AETHER_E_BADARG   (-1)
 #define AETHER_E_WORKSPACE (-2)
 #define AETHER_E_UNSUPPORTED (-3)
+#define AETHER_E_TOO_LARGE (-4)   /* beyond the fixed maximum of an entry point that works on static scratch memory */
 
 /* flags for aether_step_forward / aether_workspace_bytes */
 #define AETHER_F_SAVE_FOR_BACKWARD 1u   /* keep activations for aether_step_backward  */
@@ -112,6 +113,21 @@ size_t aether_graph_scratch_bytes(int64_t n_nodes, int64_t n_edges);
 int aether_graph_prepare(const int64_t* send, const int64_t* recv, int64_t n_edges, int64_t n_nodes,
                          AetherGraph* graph, int32_t* status /* device, 1 word: !=0 on out-of-range index */,
                          void* scratch, size_t scratch_bytes, void* stream);
+/* aether_graph_prepare for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.  Same
+ * inputs, outputs and results as aether_graph_prepare, but the scratch is a static __device__ array inside the library
+ * (2.5 MB, held by every GPU that loads the library until the process exits), so neither the caller nor the library
+ * allocates anything: no cudaMalloc / cudaFree / allocating library routine is called.
+ *   Limits: n_nodes <= AETHER_GRAPH_STATIC_MAX_NODES and n_edges <= AETHER_GRAPH_STATIC_MAX_EDGES, otherwise
+ *   AETHER_E_TOO_LARGE is returned and nothing is launched (use aether_graph_prepare with your own scratch).
+ *   Every call on a device shares the one array, which keeps the previous call's contents (the call clears what it
+ *   needs at zero itself): calls that overlap on the same GPU -- different streams, or two host threads -- RACE; run
+ *   them on one stream or order them with events.  The first call on a device looks up the array's address
+ *   (cudaGetSymbolAddress, that device current); make that first call outside stream capture. */
+#define AETHER_GRAPH_STATIC_MAX_NODES 65536
+#define AETHER_GRAPH_STATIC_MAX_EDGES 524288
+int aether_graph_prepare_static(const int64_t* send, const int64_t* recv, int64_t n_edges, int64_t n_nodes,
+                                AetherGraph* graph, int32_t* status /* device, 1 word */, void* stream);
 int aether_fc_edges(int64_t nodes_per_graph, int64_t n_graphs, int64_t* send, int64_t* recv, void* stream);
 /* Ragged batch of scenes; scene s owns nodes [node_off[s], node_off[s+1]).  Writes
  * edge_off[s] + i*kk + j for query agent i of scene s (kk = min(k, n_s - 1)).  edge_off is
