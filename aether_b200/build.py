@@ -30,6 +30,7 @@ COMMON += os.environ.get("AETHER_NVCC_FLAGS", "").split()
 # sums round separately, like the reference's eager ATen ops.
 SOURCES = [
     ("gemm_f32.cu", []),
+    ("thin.cu", []),
     ("segment.cu", []),
     ("graph.cu", []),
     ("step.cu", []),

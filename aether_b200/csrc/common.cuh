@@ -84,6 +84,8 @@ struct GemmArgs {
 };
 
 int gemm_f32(int layout, const GemmArgs& a, cudaStream_t st);
+// thin.cu: the same contract for shapes with one thin side; AETHER_E_UNSUPPORTED for every other shape
+int gemm_f32_thin(int layout, const GemmArgs& a, cudaStream_t st);
 size_t gemm_tn_partial_floats(int64_t M, int N, int64_t K);
 
 // column sums: out[n] = sum_m tf? A[m,n]  (deterministic two-stage)

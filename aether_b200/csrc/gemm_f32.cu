@@ -231,6 +231,11 @@ size_t gemm_tn_partial_floats(int64_t M, int N, int64_t K) { return (size_t)tn_s
 
 int gemm_f32(int layout, const GemmArgs& a, cudaStream_t st) {
   if (a.M <= 0 || a.N <= 0) return 0;
+  {
+    // Linears with one thin side (2..12 wide next to the hidden size) have kernels of their own (thin.cu)
+    const int rc = gemm_f32_thin(layout, a, st);
+    if (rc != AETHER_E_UNSUPPORTED) return rc;
+  }
   const bool wide = a.N > 64 && a.M >= 4096;
   dim3 grid((unsigned)ceil_div64(a.M, BM), (unsigned)ceil_div64(a.N, wide ? 128 : 64), 1);
   if (layout == GEMM_NT) {
