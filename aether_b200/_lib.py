@@ -28,6 +28,27 @@ class AetherGraphC(ctypes.Structure):
                 ("sperm", c_void_p), ("colptr", c_void_p)]
 
 
+SEQ_MAX_TYPES = 4
+
+
+class AetherSeqDims(ctypes.Structure):
+    _fields_ = [("num_dims", c_int32), ("num_vars", c_int32), ("hidden", c_int32), ("n_types", c_int32),
+                ("skip_first", c_int32), ("field_hidden", c_int32), ("batch", c_int64)]
+
+
+class AetherSeqParams(ctypes.Structure):
+    _T = c_void_p * SEQ_MAX_TYPES
+    _fields_ = [("msg_fc1_w", _T), ("msg_fc1_b", _T), ("msg_fc2_w", _T), ("msg_fc2_b", _T),
+                ("hidden_r_w", c_void_p), ("hidden_i_w", c_void_p), ("hidden_h_w", c_void_p),
+                ("present_r_w", c_void_p), ("present_r_b", c_void_p), ("present_i_w", c_void_p), ("present_i_b", c_void_p),
+                ("present_n_w", c_void_p), ("present_n_b", c_void_p),
+                ("out_w", c_void_p * 3), ("out_b", c_void_p * 3),
+                ("present_msg_fc1_w", _T), ("present_msg_fc1_b", _T), ("present_msg_fc2_w", _T), ("present_msg_fc2_b", _T),
+                ("input_r_w", c_void_p), ("input_r_b", c_void_p), ("input_i_w", c_void_p), ("input_i_b", c_void_p),
+                ("input_n_w", c_void_p), ("input_n_b", c_void_p),
+                ("rff_B", c_void_p), ("field_w", c_void_p * 3), ("field_b", c_void_p * 3)]
+
+
 # name -> (restype, argtypes); mirrors include/aether_b200.h one to one
 SIGNATURES = {
     "aether_abi_version": (c_int, []),
@@ -72,6 +93,14 @@ SIGNATURES = {
                                         c_void_p, c_size_t, c_void_p]),
     "aether_dynfield_backward": (c_int, [c_int32, c_int64, c_int32, POINTER(c_void_p), c_void_p, c_void_p, POINTER(c_void_p),
                                          c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p]),
+    "aether_seq_workspace_bytes": (c_size_t, [POINTER(AetherSeqDims)]),
+    "aether_seq_predict_field": (c_int, [POINTER(AetherSeqDims), POINTER(AetherSeqParams), c_void_p, c_void_p, c_void_p,
+                                         c_size_t, c_void_p]),
+    "aether_seq_decoder_step": (c_int, [POINTER(AetherSeqDims), POINTER(AetherSeqParams), c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "aether_seq_rollout_step": (c_int, [POINTER(AetherSeqDims), POINTER(AetherSeqParams), c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "aether_seq_localizer": (c_int, [POINTER(AetherSeqDims), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_adamw_step": (c_int, [c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
                                   POINTER(c_int64), c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,
                                   ctypes.c_double, c_void_p]),

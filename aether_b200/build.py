@@ -47,6 +47,7 @@ SOURCES = [
     ("geom.cu", ["-fmad=false"]),
     ("geom_bwd.cu", ["-fmad=false"]),
     ("small.cu", ["-fmad=false"]),
+    ("seqdec.cu", ["-fmad=false"]),
 ]
 
 

@@ -1,0 +1,684 @@
+// seq2seq decoder path: RecurrentDecoder.forward (nn/seq2seq/aether.py:589-654), AugmentedLocalizer
+// (nn/utils/augmented_global_to_local.py:51-68, nn/utils/canonicalization.py:33-56,111-172) and the field predictor
+// (nn/seq2seq/aether.py:83-87).  fp32, inference.  Built with -fmad=false so the geometry rounds like the reference's
+// eager ops; the GEMM inner loops ask for FMAs explicitly.
+//
+// One decoder step is 10 launches (14 with the field predictor), all on the caller's stream, capturable:
+//   geometry -> batch A {node terms of msg_fc1 per type, present_msg_fc1 per type} -> tanh of the pair sums
+//   -> batch B {msg_fc2 summed over types, present_msg_fc2 summed over types} -> receiver means -> batch C {gate
+//   pre-activations} -> gates + state update -> out_mlp.0 -> out_mlp.3 -> out_mlp.6 + Globalizer + inputs.
+// msg_fc1 is node-factorised: W1 [recv | send] halves applied to the N node states of a trajectory instead of its
+// N(N-1) pairs.  Every "batch" is ONE launch of a multi-problem, multi-term GEMM:
+//   C[m,n] = sum over flushed groups of  scale[m] * act( sum_terms A_t[m,:] . W_t[n,:] + bias_t[n] )
+// which covers the per-type sums (":608-613, :625-632") and the three-input gate pre-activations (":638-645").
+#include "common.cuh"
+
+namespace aether {
+namespace {
+
+constexpr float PI_F = 3.14159274f;       // float(np.pi)
+constexpr float TWO_PI_F = 6.28318548f;   // float(2 * np.pi)
+
+// ------------------------------------------------------------------------------------------------
+// geometry
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void rot3(float th, float ph, float* R) {   // nn/utils/geometry.py:24-34
+  const float ct = cosf(th), st = sinf(th), cp = cosf(ph), sp = sinf(ph);
+  R[0] = cp * ct; R[1] = -st; R[2] = sp * ct;
+  R[3] = cp * st; R[4] = ct;  R[5] = sp * st;
+  R[6] = -sp;     R[7] = 0.f; R[8] = cp;
+}
+__device__ __forceinline__ void spherical3(const float* x, float& rho, float& th, float& ph) {   // geometry.py:37-67
+  rho = sqrtf(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+  th = atan2f(x[1], x[0]);
+  if (th < 0.f) th = th + TWO_PI_F;
+  float c = x[2] / (rho + 1e-7f);
+  c = fminf(fmaxf(c, -1.0f), 1.0f);
+  ph = acosf(c);
+}
+// out = R^T v for a row-major 3x3 R
+__device__ __forceinline__ void mv3t(const float* R, const float* v, float* o) {
+  for (int a = 0; a < 3; ++a) o[a] = R[a] * v[0] + R[3 + a] * v[1] + R[6 + a] * v[2];
+}
+
+template <int D> struct SeqGeo {
+  static constexpr int O = D * (D - 1) / 2, F = 4 * D + O, NS = 3 * D;
+};
+
+// canonicalize_augmented_inputs (canonicalization.py:33-56): x = [pos | vel | field]
+template <int D>
+__device__ __forceinline__ void canonical(const float* x, float* canon, float* Rinv) {
+  if (D == 2) {
+    const float a = atan2f(x[3], x[2]);
+    const float c = cosf(a), s = sinf(a);
+    Rinv[0] = c; Rinv[1] = -s; Rinv[2] = s; Rinv[3] = c;
+    canon[0] = 0.f; canon[1] = 0.f;
+    canon[2] = sqrtf(x[2] * x[2] + x[3] * x[3]);
+    canon[3] = 0.f;
+    canon[4] = c * x[4] + s * x[5];
+    canon[5] = (-s) * x[4] + c * x[5];
+  } else {
+    float rho, th, ph;
+    spherical3(x + 3, rho, th, ph);
+    rot3(th, ph, Rinv);
+    canon[0] = canon[1] = canon[2] = 0.f;
+    mv3t(Rinv, x + 3, canon + 3);
+    mv3t(Rinv, x + 6, canon + 6);
+  }
+}
+
+// create_augmented_edge_attr_pos_vel / create_augmented_3d_edge_attr_pos_vel (canonicalization.py:111-172):
+// sender xj seen from receiver xi
+template <int D>
+__device__ __forceinline__ void pair_feat(const float* xj, const float* xi, float* o) {
+  if (D == 2) {
+    const float yaw = atan2f(xi[3], xi[2]);
+    const float c = cosf(yaw), s = sinf(yaw);
+    const float dx = xj[0] - xi[0], dy = xj[1] - xi[1];
+    o[0] = c * dx + s * dy;
+    o[1] = (-s) * dx + c * dy;
+    float d = atan2f(xj[3], xj[2]) - yaw;                 // angle_diff, geometry.py:117-128
+    if (d >= PI_F) d -= TWO_PI_F;
+    if (d < -PI_F) d += TWO_PI_F;
+    o[2] = d / PI_F;
+    o[3] = sqrtf(dx * dx + dy * dy);
+    float t = atan2f(dy, dx) - yaw;                       // wrap_angles, geometry.py:108-113
+    t = t + (t <= -PI_F ? TWO_PI_F : 0.f);
+    t = t - (t > PI_F ? TWO_PI_F : 0.f);
+    o[4] = t / PI_F;
+    o[5] = c * xj[2] + s * xj[3];
+    o[6] = (-s) * xj[2] + c * xj[3];
+    o[7] = c * xj[4] + s * xj[5];
+    o[8] = (-s) * xj[4] + c * xj[5];
+  } else {
+    float rho, sy, sp, ry, rp;
+    spherical3(xj + 3, rho, sy, sp);
+    spherical3(xi + 3, rho, ry, rp);
+    float Ri[9], Rj[9];
+    rot3(ry, rp, Ri);
+    rot3(sy, sp, Rj);
+    float dp[3] = {xj[0] - xi[0], xj[1] - xi[1], xj[2] - xi[2]};
+    // M = Ri^T Rj^T (":153-154": both factors are the transposed matrices)
+    auto M = [&](int a, int b) { return Ri[a] * Rj[3 * b] + Ri[3 + a] * Rj[3 * b + 1] + Ri[6 + a] * Rj[3 * b + 2]; };
+    mv3t(Ri, dp, o);
+    o[3] = atan2f(M(1, 0), M(0, 0));
+    o[4] = asinf(-M(2, 0));
+    o[5] = atan2f(M(2, 1), M(2, 2));
+    o[6] = sqrtf(dp[0] * dp[0] + dp[1] * dp[1] + dp[2] * dp[2]);
+    float r2, th, ph;
+    spherical3(o, r2, th, ph);
+    o[7] = th;
+    o[8] = ph;
+    mv3t(Ri, xj + 3, o + 9);
+    mv3t(Ri, xj + 6, o + 12);
+  }
+}
+
+template <int D>
+__device__ __forceinline__ void load_state(const float* states, const float* field, int64_t node, float* x) {
+  for (int i = 0; i < 2 * D; ++i) x[i] = states[node * 2 * D + i];
+  for (int i = 0; i < D; ++i) x[2 * D + i] = field[node * D + i];
+}
+
+// Thread per (trajectory, pair) and per (trajectory, particle): edge_attr[B*E, 2F+3D] = [pair | canon(recv) | origin
+// pair of recv], rel_feat[B*N, 3D+F] = [canon | origin pair], Rinv[B*N, D*D].
+template <int D>
+__global__ void seq_geom_kernel(const float* __restrict__ states, const float* __restrict__ field, int N, int64_t B,
+                                float* __restrict__ relx, float* __restrict__ Rinv, float* __restrict__ eattr) {
+  constexpr int F = SeqGeo<D>::F, NS = SeqGeo<D>::NS;
+  const int E = N * (N - 1);
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * (E + N)) return;
+  const int64_t b = idx / (E + N);
+  const int e = (int)(idx - b * (E + N));
+  float origin[NS];
+  for (int i = 0; i < NS; ++i) origin[i] = 0.f;
+  origin[D] = 1.0f;                                       // augmented_global_to_local.py:41
+  float xi[NS], canon[NS], R[D * D], of[F];
+  if (e < E) {
+    const int send = e / (N - 1), q = e - send * (N - 1), recv = q + (q >= send ? 1 : 0);
+    float xj[NS], pf[F];
+    load_state<D>(states, field, b * N + recv, xi);
+    load_state<D>(states, field, b * N + send, xj);
+    pair_feat<D>(xj, xi, pf);
+    canonical<D>(xi, canon, R);
+    pair_feat<D>(origin, xi, of);
+    float* row = eattr + (b * E + e) * (2 * F + NS);
+    for (int i = 0; i < F; ++i) row[i] = pf[i];
+    for (int i = 0; i < NS; ++i) row[F + i] = canon[i];
+    for (int i = 0; i < F; ++i) row[F + NS + i] = of[i];
+  } else {
+    const int64_t node = b * N + (e - E);
+    load_state<D>(states, field, node, xi);
+    canonical<D>(xi, canon, R);
+    pair_feat<D>(origin, xi, of);
+    float* row = relx + node * (NS + F);
+    for (int i = 0; i < NS; ++i) row[i] = canon[i];
+    for (int i = 0; i < F; ++i) row[NS + i] = of[i];
+    for (int i = 0; i < D * D; ++i) Rinv[node * D * D + i] = R[i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// multi-problem, multi-term fp32 GEMM
+// ------------------------------------------------------------------------------------------------
+constexpr int GM = 64, GN = 64, GK = 16, GT = 256, GPAD = 4;
+constexpr int MAX_TERMS = 4, MAX_PROB = 12;
+enum SeqAct { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2, ACT_SIGMOID = 3, ACT_SILU = 4 };
+
+struct Term {
+  const float* A;       // [M, K], leading dimension lda
+  const float* W;       // [N, K], leading dimension ldw (nn.Linear weight)
+  const float* bias;    // [N] or null
+  const float* scale;   // per-row factor scale[m * scale_ld] applied after the activation, or null
+  int lda, ldw, K, act, flush, scale_ld;
+};
+struct Problem {
+  Term t[MAX_TERMS];
+  float* C;
+  int ldc, M, N, nterms;
+};
+struct Batch { Problem p[MAX_PROB]; };
+
+__device__ __forceinline__ float act_f(float v, int act) {
+  switch (act) {
+    case ACT_TANH: return tanhf(v);
+    case ACT_RELU: return fmaxf(v, 0.f);
+    case ACT_SIGMOID: return 1.0f / (1.0f + expf(-v));
+    case ACT_SILU: return v / (1.0f + expf(-v));
+    default: return v;
+  }
+}
+
+__global__ void __launch_bounds__(GT) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+  const Problem& P = bt.p[blockIdx.z];
+  const int m0 = blockIdx.x * GM, n0 = blockIdx.y * GN;
+  if (m0 >= P.M || n0 >= P.N) return;
+  __shared__ __align__(16) float As[2][GK][GM + GPAD];
+  __shared__ __align__(16) float Ws[2][GK][GN + GPAD];
+  const int tid = threadIdx.x;
+  const int lr = tid >> 2, lk = (tid & 3) * 4;       // loader: row lr of the tile, k offset lk..lk+3
+  const int tx = tid & 15, ty = tid >> 4;            // compute: rows ty*4.., columns tx*4..
+  float sum[4][4], acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { sum[i][j] = 0.f; acc[i][j] = 0.f; }
+
+  for (int t = 0; t < P.nterms; ++t) {
+    const Term& T = P.t[t];
+    const int K = T.K;
+    const bool arow = m0 + lr < P.M, wrow = n0 + lr < P.N;
+    const float* ap = T.A + (size_t)(m0 + lr) * T.lda;
+    const float* wp = T.W + (size_t)(n0 + lr) * T.ldw;
+    const bool vec = (K % 4 == 0) && (T.lda % 4 == 0) && (T.ldw % 4 == 0) &&
+                     ((((uintptr_t)T.A) | ((uintptr_t)T.W)) & 15) == 0;
+    float4 ra, rw;
+    auto fetch = [&](int k0) {
+      const int k = k0 + lk;
+      ra = make_float4(0.f, 0.f, 0.f, 0.f);
+      rw = ra;
+      if (vec) {
+        if (arow && k < K) ra = *reinterpret_cast<const float4*>(ap + k);
+        if (wrow && k < K) rw = *reinterpret_cast<const float4*>(wp + k);
+      } else {
+        if (arow) {
+          if (k < K) ra.x = ap[k];
+          if (k + 1 < K) ra.y = ap[k + 1];
+          if (k + 2 < K) ra.z = ap[k + 2];
+          if (k + 3 < K) ra.w = ap[k + 3];
+        }
+        if (wrow) {
+          if (k < K) rw.x = wp[k];
+          if (k + 1 < K) rw.y = wp[k + 1];
+          if (k + 2 < K) rw.z = wp[k + 2];
+          if (k + 3 < K) rw.w = wp[k + 3];
+        }
+      }
+    };
+    auto stash = [&](int buf) {
+      As[buf][lk][lr] = ra.x; As[buf][lk + 1][lr] = ra.y; As[buf][lk + 2][lr] = ra.z; As[buf][lk + 3][lr] = ra.w;
+      Ws[buf][lk][lr] = rw.x; Ws[buf][lk + 1][lr] = rw.y; Ws[buf][lk + 2][lr] = rw.z; Ws[buf][lk + 3][lr] = rw.w;
+    };
+    const int nk = (K + GK - 1) / GK;
+    __syncthreads();            // the previous term's last slab is no longer read
+    fetch(0);
+    stash(0);
+    __syncthreads();
+    for (int kt = 0; kt < nk; ++kt) {
+      const int cur = kt & 1;
+      if (kt + 1 < nk) fetch((kt + 1) * GK);
+#pragma unroll
+      for (int kk = 0; kk < GK; ++kk) {
+        const float4 a = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 4]);
+        const float4 w = *reinterpret_cast<const float4*>(&Ws[cur][kk][tx * 4]);
+        const float av[4] = {a.x, a.y, a.z, a.w}, wv[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+      }
+      if (kt + 1 < nk) {
+        stash(cur ^ 1);         // the other buffer was last read before the barrier that ended iteration kt-1
+        __syncthreads();
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = m0 + ty * 4 + i;
+      float sc = 1.0f;
+      if (T.flush && T.scale != nullptr && m < P.M) sc = T.scale[(size_t)m * T.scale_ld];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n = n0 + tx * 4 + j;
+        float v = acc[i][j];
+        if (T.bias != nullptr && n < P.N) v = v + T.bias[n];
+        if (T.flush) {
+          v = act_f(v, T.act);
+          if (T.scale != nullptr) v = v * sc;
+          sum[i][j] = sum[i][j] + v;
+          v = 0.f;
+        }
+        acc[i][j] = v;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= P.M) continue;
+    float* c = P.C + (size_t)m * P.ldc + n0 + tx * 4;
+    const int n = n0 + tx * 4;
+    if (n + 3 < P.N && (P.ldc % 4 == 0) && (((uintptr_t)P.C) & 15) == 0) {
+      *reinterpret_cast<float4*>(c) = make_float4(sum[i][0], sum[i][1], sum[i][2], sum[i][3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (n + j < P.N) c[j] = sum[i][j];
+    }
+  }
+}
+
+Term make_term(const float* A, int lda, const float* W, int ldw, const float* bias, int K, int act, int flush,
+               const float* scale = nullptr, int scale_ld = 0) {
+  Term t;
+  t.A = A; t.W = W; t.bias = bias; t.scale = scale;
+  t.lda = lda; t.ldw = ldw; t.K = K; t.act = act; t.flush = flush; t.scale_ld = scale_ld;
+  return t;
+}
+
+int launch_batch(const Batch& bt, int nprob, cudaStream_t st) {
+  int maxM = 0, maxN = 0;
+  for (int i = 0; i < nprob; ++i) {
+    maxM = bt.p[i].M > maxM ? bt.p[i].M : maxM;
+    maxN = bt.p[i].N > maxN ? bt.p[i].N : maxN;
+  }
+  if (maxM == 0 || maxN == 0 || nprob == 0) return 0;
+  dim3 grid((maxM + GM - 1) / GM, (maxN + GN - 1) / GN, nprob);
+  seq_gemm_kernel<<<grid, GT, 0, st>>>(bt);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// elementwise pieces
+// ------------------------------------------------------------------------------------------------
+// m1[t][b*E+e, :] = tanh(P[b*N+recv, (2t)H + :] + P[b*N+send, (2t+1)H + :])   (":600, :609": msg_fc1 on cat[recv, send])
+__global__ void seq_pair_tanh_kernel(const float* __restrict__ P, int ldp, int N, int64_t BE, int H, int t0, int nt,
+                                     float* __restrict__ m1) {
+  const int H4 = H / 4;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)nt * BE * H4) return;
+  const int k4 = (int)(idx % H4);
+  const int64_t rest = idx / H4;
+  const int64_t m = rest % BE;
+  const int t = t0 + (int)(rest / BE);
+  const int E = N * (N - 1);
+  const int64_t b = m / E;
+  const int e = (int)(m - b * E);
+  const int send = e / (N - 1), q = e - send * (N - 1), recv = q + (q >= send ? 1 : 0);
+  const float4 r = *reinterpret_cast<const float4*>(P + (size_t)(b * N + recv) * ldp + (size_t)(2 * t) * H + k4 * 4);
+  const float4 s = *reinterpret_cast<const float4*>(P + (size_t)(b * N + send) * ldp + (size_t)(2 * t + 1) * H + k4 * 4);
+  float4 o;
+  o.x = tanhf(r.x + s.x); o.y = tanhf(r.y + s.y); o.z = tanhf(r.z + s.z); o.w = tanhf(r.w + s.w);
+  *reinterpret_cast<float4*>(m1 + ((size_t)t * BE + m) * H + k4 * 4) = o;
+}
+
+// agg[which][b*N+j, :] = sum over senders i != j (ascending edge id) of msgs[which][b*E + e(i,j), :] / (N-1)
+// (torch_scatter.scatter(reduce='mean') by receiver, ":616, :634")
+__global__ void seq_mean_kernel(const float* __restrict__ msgs0, const float* __restrict__ msgs1, int N, int64_t B, int H,
+                                float* __restrict__ agg0, float* __restrict__ agg1) {
+  const int H4 = H / 4;
+  const int64_t per = B * N * H4;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= 2 * per) return;
+  const int which = idx >= per;
+  const int64_t r = idx - (which ? per : 0);
+  const int h4 = (int)(r % H4);
+  const int64_t node = r / H4;
+  const int64_t b = node / N;
+  const int j = (int)(node - b * N);
+  const float* src = which ? msgs1 : msgs0;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int E = N * (N - 1);
+  for (int i = 0; i < N; ++i) {
+    if (i == j) continue;
+    const int e = i * (N - 1) + (j < i ? j : j - 1);
+    const float4 v = *reinterpret_cast<const float4*>(src + ((size_t)b * E + e) * H + h4 * 4);
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  }
+  const float cnt = (float)(N - 1);
+  s.x /= cnt; s.y /= cnt; s.z /= cnt; s.w /= cnt;
+  *reinterpret_cast<float4*>((which ? agg1 : agg0) + (size_t)node * H + h4 * 4) = s;
+}
+
+// n = tanh(inp_n + r * hidden_h(agg)); hidden' = (1 - i) n + i hidden   (":644-645")
+__global__ void seq_gate_kernel(const float* __restrict__ R, const float* __restrict__ I, const float* __restrict__ NI,
+                                const float* __restrict__ HH, const float* hidden_in, float* hidden_out, int64_t n) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const float r = R[idx], i = I[idx];
+  const float nn = tanhf(NI[idx] + r * HH[idx]);
+  hidden_out[idx] = (1.0f - i) * nn + i * hidden_in[idx];
+}
+
+// Warp per row: v[c] = A[row,:] . W[c,:] + b[c] for c < nc <= 6; with Rinv: every D-chunk rotated by Rinv[row]
+// (Globalizer, nn/utils/local_to_global.py:12-13) and added to `add` (":651-652").
+__global__ void seq_thin_kernel(const float* __restrict__ A, int K, const float* __restrict__ W, const float* __restrict__ b,
+                                int nc, const float* __restrict__ Rinv, int D, const float* __restrict__ add,
+                                float* __restrict__ out, int64_t rows) {
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int k = lane; k < K; k += 32) {
+    const float a = A[(size_t)row * K + k];
+#pragma unroll
+    for (int c = 0; c < 6; ++c)
+      if (c < nc) acc[c] = fmaf(a, W[(size_t)c * K + k], acc[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < 6; ++c)
+    for (int o = 16; o > 0; o >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+  if (lane != 0) return;
+  float v[6];
+  for (int c = 0; c < nc; ++c) v[c] = acc[c] + b[c];
+  if (Rinv != nullptr) {
+    const float* R = Rinv + (size_t)row * D * D;
+    for (int c0 = 0; c0 < nc; c0 += D)
+      for (int a = 0; a < D; ++a) {
+        float s = R[a * D] * v[c0];
+        for (int k = 1; k < D; ++k) s = s + R[a * D + k] * v[c0 + k];
+        out[(size_t)row * nc + c0 + a] = add[(size_t)row * nc + c0 + a] + s;
+      }
+  } else {
+    for (int c = 0; c < nc; ++c) out[(size_t)row * nc + c] = v[c];
+  }
+}
+
+// Fourier features of the positions: [sin(p), cos(p)], p = (2 pi x) @ B   (nn/nn/fourier_feature_mapper.py:21-23)
+__global__ void seq_rff_kernel(const float* __restrict__ states, int sd, int D, const float* __restrict__ Bm, int half,
+                               float* __restrict__ out, int64_t rows) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * half) return;
+  const int c = (int)(idx % half);
+  const int64_t row = idx / half;
+  float p = (TWO_PI_F * states[row * sd]) * Bm[c];
+  for (int d = 1; d < D; ++d) p = fmaf(TWO_PI_F * states[row * sd + d], Bm[(size_t)d * half + c], p);
+  out[(size_t)row * 2 * half + c] = sinf(p);
+  out[(size_t)row * 2 * half + half + c] = cosf(p);
+}
+
+// ------------------------------------------------------------------------------------------------
+// workspace
+// ------------------------------------------------------------------------------------------------
+struct SeqWs {
+  float *relx, *Rinv, *eattr, *P, *m1, *p1, *msgs, *pmsgs, *agg, *pagg, *gR, *gI, *gN, *gH, *o1, *o2, *f0, *f1, *f2, *field;
+  size_t bytes;
+};
+
+int seq_check(const AetherSeqDims* d) {
+  if (d == nullptr) return AETHER_E_BADARG;
+  if (d->num_dims != 2 && d->num_dims != 3) return AETHER_E_BADARG;
+  if (d->num_vars < 2 || d->num_vars > 64) return AETHER_E_BADARG;
+  if (d->hidden < 4 || d->hidden % 4 != 0) return AETHER_E_UNSUPPORTED;
+  if (d->n_types < 1 || d->n_types > AETHER_SEQ_MAX_TYPES) return AETHER_E_UNSUPPORTED;
+  if (d->skip_first != 0 && d->skip_first != 1) return AETHER_E_BADARG;
+  if (d->field_hidden < 0 || d->field_hidden % 4 != 0) return AETHER_E_UNSUPPORTED;
+  if (d->batch < 0) return AETHER_E_BADARG;
+  const int64_t BE = d->batch * d->num_vars * (d->num_vars - 1);
+  if (BE > (int64_t)1 << 30 || BE * d->hidden > ((int64_t)1 << 40)) return AETHER_E_TOO_LARGE;
+  return 0;
+}
+
+SeqWs seq_layout(const AetherSeqDims* d, void* base) {
+  const int D = d->num_dims, N = d->num_vars, H = d->hidden, Kt = d->n_types, Hf = d->field_hidden;
+  const int O = D * (D - 1) / 2, F = 4 * D + O;
+  const size_t BN = (size_t)d->batch * N, BE = BN * (N - 1);
+  size_t off = 0;
+  auto take = [&](size_t nfloats) {
+    float* p = base ? reinterpret_cast<float*>(reinterpret_cast<char*>(base) + off) : nullptr;
+    off += align_up(nfloats * sizeof(float), 256);
+    return p;
+  };
+  SeqWs w;
+  w.relx = take(BN * (3 * D + F));
+  w.Rinv = take(BN * D * D);
+  w.eattr = take(BE * (2 * F + 3 * D));
+  w.P = take(BN * 2 * Kt * H);
+  w.m1 = take((size_t)Kt * BE * H);
+  w.p1 = take((size_t)Kt * BE * H);
+  w.msgs = take(BE * H);
+  w.pmsgs = take(BE * H);
+  w.agg = take(BN * H);
+  w.pagg = take(BN * H);
+  w.gR = take(BN * H);
+  w.gI = take(BN * H);
+  w.gN = take(BN * H);
+  w.gH = take(BN * H);
+  w.o1 = take(BN * H);
+  w.o2 = take(BN * H);
+  w.f0 = take(BN * Hf);
+  w.f1 = take(BN * Hf);
+  w.f2 = take(BN * Hf);
+  w.field = take(BN * D);
+  w.bytes = off;
+  return w;
+}
+
+int seq_geometry(const AetherSeqDims* d, const float* states, const float* field, float* relx, float* Rinv, float* eattr,
+                 cudaStream_t st) {
+  const int N = d->num_vars;
+  const int64_t total = d->batch * (int64_t)(N * (N - 1) + N);
+  if (total == 0) return 0;
+  const int nb = (int)ceil_div64(total, 128);
+  if (d->num_dims == 2) seq_geom_kernel<2><<<nb, 128, 0, st>>>(states, field, N, d->batch, relx, Rinv, eattr);
+  else seq_geom_kernel<3><<<nb, 128, 0, st>>>(states, field, N, d->batch, relx, Rinv, eattr);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* states, float* field, const SeqWs& w,
+              cudaStream_t st) {
+  const int D = d->num_dims, Hf = d->field_hidden;
+  if (Hf < 4 || p->rff_B == nullptr) return AETHER_E_BADARG;
+  for (int i = 0; i < 3; ++i)
+    if (p->field_w[i] == nullptr || p->field_b[i] == nullptr) return AETHER_E_BADARG;
+  const int64_t BN = d->batch * d->num_vars;
+  if (BN == 0) return 0;
+  const int half = Hf / 2;
+  seq_rff_kernel<<<(int)ceil_div64(BN * half, 256), 256, 0, st>>>(states, 2 * D, D, p->rff_B, half, w.f0, BN);
+  AE_LAUNCH_CHECK();
+  Batch bt;
+  bt.p[0].t[0] = make_term(w.f0, Hf, p->field_w[0], Hf, p->field_b[0], Hf, ACT_SILU, 1);
+  bt.p[0].C = w.f1; bt.p[0].ldc = Hf; bt.p[0].M = (int)BN; bt.p[0].N = Hf; bt.p[0].nterms = 1;
+  AE_CHECK(launch_batch(bt, 1, st));
+  bt.p[0].t[0] = make_term(w.f1, Hf, p->field_w[1], Hf, p->field_b[1], Hf, ACT_SILU, 1);
+  bt.p[0].C = w.f2;
+  AE_CHECK(launch_batch(bt, 1, st));
+  seq_thin_kernel<<<(int)ceil_div64(BN * 32, 256), 256, 0, st>>>(w.f2, Hf, p->field_w[2], p->field_b[2], D, nullptr, D,
+                                                                nullptr, field, BN);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* states, const float* hidden_in,
+             const float* edge_types, const float* field, float* states_out, float* hidden_out, const SeqWs& w,
+             cudaStream_t st) {
+  const int D = d->num_dims, N = d->num_vars, H = d->hidden, Kt = d->n_types, t0 = d->skip_first ? 1 : 0;
+  const int O = D * (D - 1) / 2, F = 4 * D + O, KE = 2 * F + 3 * D, KR = 3 * D + F;
+  const int64_t BN = d->batch * N, BE = BN * (N - 1);
+  if (BN == 0) return 0;
+  for (int t = t0; t < Kt; ++t)
+    if (!p->msg_fc1_w[t] || !p->msg_fc1_b[t] || !p->msg_fc2_w[t] || !p->msg_fc2_b[t] || !p->present_msg_fc1_w[t] ||
+        !p->present_msg_fc1_b[t] || !p->present_msg_fc2_w[t] || !p->present_msg_fc2_b[t])
+      return AETHER_E_BADARG;
+  const int nt = Kt - t0;
+  const int ldp = 2 * Kt * H;
+
+  AE_CHECK(seq_geometry(d, states, field, w.relx, w.Rinv, w.eattr, st));
+
+  Batch bt;
+  int np = 0;
+  auto single = [&](const Term& t, float* C, int ldc, int M, int Nc) {
+    Problem& q = bt.p[np++];
+    q.t[0] = t; q.C = C; q.ldc = ldc; q.M = M; q.N = Nc; q.nterms = 1;
+  };
+  // batch A: node terms of msg_fc1 (bias with the receiver half) and present_msg_fc1 per type
+  for (int t = t0; t < Kt; ++t) {
+    single(make_term(hidden_in, H, p->msg_fc1_w[t], 2 * H, p->msg_fc1_b[t], H, ACT_NONE, 1), w.P + (size_t)(2 * t) * H,
+           ldp, (int)BN, H);
+    single(make_term(hidden_in, H, p->msg_fc1_w[t] + H, 2 * H, nullptr, H, ACT_NONE, 1), w.P + (size_t)(2 * t + 1) * H,
+           ldp, (int)BN, H);
+    single(make_term(w.eattr, KE, p->present_msg_fc1_w[t], KE, p->present_msg_fc1_b[t], KE, ACT_RELU, 1),
+           w.p1 + (size_t)t * BE * H, H, (int)BE, H);
+  }
+  AE_CHECK(launch_batch(bt, np, st));
+  if (nt > 0 && BE > 0) {
+    const int64_t total = (int64_t)nt * BE * (H / 4);
+    seq_pair_tanh_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.P, ldp, N, BE, H, t0, nt, w.m1);
+    AE_LAUNCH_CHECK();
+  }
+  // batch B: second message Linears, activation, edge-type weight, sum over types
+  np = 0;
+  if (nt > 0) {
+    Problem& a = bt.p[np++];
+    Problem& b = bt.p[np++];
+    for (int t = t0; t < Kt; ++t) {
+      a.t[t - t0] = make_term(w.m1 + (size_t)t * BE * H, H, p->msg_fc2_w[t], H, p->msg_fc2_b[t], H, ACT_TANH, 1,
+                              edge_types + t, Kt);
+      b.t[t - t0] = make_term(w.p1 + (size_t)t * BE * H, H, p->present_msg_fc2_w[t], H, p->present_msg_fc2_b[t], H,
+                              ACT_RELU, 1, edge_types + t, Kt);
+    }
+    a.C = w.msgs; a.ldc = H; a.M = (int)BE; a.N = H; a.nterms = nt;
+    b.C = w.pmsgs; b.ldc = H; b.M = (int)BE; b.N = H; b.nterms = nt;
+    AE_CHECK(launch_batch(bt, np, st));
+  } else {
+    AE_CHECK((int)cudaMemsetAsync(w.msgs, 0, (size_t)BE * H * sizeof(float), st));
+    AE_CHECK((int)cudaMemsetAsync(w.pmsgs, 0, (size_t)BE * H * sizeof(float), st));
+  }
+  {
+    const int64_t total = 2 * BN * (H / 4);
+    seq_mean_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.msgs, w.pmsgs, N, d->batch, H, w.agg, w.pagg);
+    AE_LAUNCH_CHECK();
+  }
+  // batch C: gate pre-activations
+  np = 0;
+  auto gate = [&](const float* wi, const float* bi, const float* wp, const float* bp, const float* wh, int act,
+                  float* C) {
+    Problem& q = bt.p[np++];
+    int n = 0;
+    if (wi) q.t[n++] = make_term(w.relx, KR, wi, KR, bi, KR, act, 0);
+    if (wp) q.t[n++] = make_term(w.pagg, H, wp, H, bp, H, act, 0);
+    if (wh) q.t[n++] = make_term(w.agg, H, wh, H, nullptr, H, act, 0);
+    q.t[n - 1].flush = 1;
+    q.C = C; q.ldc = H; q.M = (int)BN; q.N = H; q.nterms = n;
+  };
+  gate(p->input_r_w, p->input_r_b, p->present_r_w, p->present_r_b, p->hidden_r_w, ACT_SIGMOID, w.gR);
+  gate(p->input_i_w, p->input_i_b, p->present_i_w, p->present_i_b, p->hidden_i_w, ACT_SIGMOID, w.gI);
+  gate(p->input_n_w, p->input_n_b, p->present_n_w, p->present_n_b, nullptr, ACT_NONE, w.gN);
+  gate(nullptr, nullptr, nullptr, nullptr, p->hidden_h_w, ACT_NONE, w.gH);
+  AE_CHECK(launch_batch(bt, np, st));
+  seq_gate_kernel<<<(int)ceil_div64(BN * H, 256), 256, 0, st>>>(w.gR, w.gI, w.gN, w.gH, hidden_in, hidden_out, BN * H);
+  AE_LAUNCH_CHECK();
+  // out MLP
+  np = 0;
+  single(make_term(hidden_out, H, p->out_w[0], H, p->out_b[0], H, ACT_RELU, 1), w.o1, H, (int)BN, H);
+  AE_CHECK(launch_batch(bt, np, st));
+  np = 0;
+  single(make_term(w.o1, H, p->out_w[1], H, p->out_b[1], H, ACT_RELU, 1), w.o2, H, (int)BN, H);
+  AE_CHECK(launch_batch(bt, np, st));
+  seq_thin_kernel<<<(int)ceil_div64(BN * 32, 256), 256, 0, st>>>(w.o2, H, p->out_w[2], p->out_b[2], 2 * D, w.Rinv, D,
+                                                                states, states_out, BN);
+  AE_LAUNCH_CHECK();
+  return 0;
+}
+
+int seq_params_ok(const AetherSeqParams* p) {
+  if (p == nullptr) return AETHER_E_BADARG;
+  if (!p->hidden_r_w || !p->hidden_i_w || !p->hidden_h_w || !p->present_r_w || !p->present_r_b || !p->present_i_w ||
+      !p->present_i_b || !p->present_n_w || !p->present_n_b || !p->input_r_w || !p->input_r_b || !p->input_i_w ||
+      !p->input_i_b || !p->input_n_w || !p->input_n_b)
+    return AETHER_E_BADARG;
+  for (int i = 0; i < 3; ++i)
+    if (!p->out_w[i] || !p->out_b[i]) return AETHER_E_BADARG;
+  return 0;
+}
+
+}  // namespace
+}  // namespace aether
+
+using namespace aether;
+
+extern "C" size_t aether_seq_workspace_bytes(const AetherSeqDims* dims) {
+  if (seq_check(dims) != 0) return 0;
+  return seq_layout(dims, nullptr).bytes + 256;
+}
+
+extern "C" int aether_seq_localizer(const AetherSeqDims* dims, const float* states, const float* field, float* rel_feat,
+                                    float* Rinv, float* edge_attr, void* stream) {
+  AE_CHECK(seq_check(dims));
+  if (!states || !field || !rel_feat || !Rinv || !edge_attr) return AETHER_E_BADARG;
+  return seq_geometry(dims, states, field, rel_feat, Rinv, edge_attr, (cudaStream_t)stream);
+}
+
+static int seq_ws(const AetherSeqDims* dims, void* workspace, size_t workspace_bytes, SeqWs* w) {
+  AE_CHECK(seq_check(dims));
+  if (workspace == nullptr) return AETHER_E_WORKSPACE;
+  void* base = reinterpret_cast<void*>(align_up((size_t)(uintptr_t)workspace, 256));
+  *w = seq_layout(dims, base);
+  if ((size_t)((char*)base - (char*)workspace) + w->bytes > workspace_bytes) return AETHER_E_WORKSPACE;
+  return 0;
+}
+
+extern "C" int aether_seq_predict_field(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states,
+                                        float* field, void* workspace, size_t workspace_bytes, void* stream) {
+  SeqWs w;
+  AE_CHECK(seq_ws(dims, workspace, workspace_bytes, &w));
+  if (!params || !states || !field) return AETHER_E_BADARG;
+  return seq_field(dims, params, states, field, w, (cudaStream_t)stream);
+}
+
+extern "C" int aether_seq_decoder_step(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states,
+                                       const float* hidden_in, const float* edge_types, const float* field,
+                                       float* states_out, float* hidden_out, void* workspace, size_t workspace_bytes,
+                                       void* stream) {
+  SeqWs w;
+  AE_CHECK(seq_ws(dims, workspace, workspace_bytes, &w));
+  AE_CHECK(seq_params_ok(params));
+  if (!states || !hidden_in || !edge_types || !field || !states_out || !hidden_out) return AETHER_E_BADARG;
+  return seq_step(dims, params, states, hidden_in, edge_types, field, states_out, hidden_out, w, (cudaStream_t)stream);
+}
+
+extern "C" int aether_seq_rollout_step(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states,
+                                       const float* hidden_in, const float* edge_types, float* states_out,
+                                       float* hidden_out, float* field_out, void* workspace, size_t workspace_bytes,
+                                       void* stream) {
+  SeqWs w;
+  AE_CHECK(seq_ws(dims, workspace, workspace_bytes, &w));
+  AE_CHECK(seq_params_ok(params));
+  if (!states || !hidden_in || !edge_types || !states_out || !hidden_out) return AETHER_E_BADARG;
+  float* field = field_out ? field_out : w.field;
+  AE_CHECK(seq_field(dims, params, states, field, w, (cudaStream_t)stream));
+  return seq_step(dims, params, states, hidden_in, edge_types, field, states_out, hidden_out, w, (cudaStream_t)stream);
+}

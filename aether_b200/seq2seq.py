@@ -1,0 +1,357 @@
+"""Decoder side of the reference's seq2seq Aether (nn/seq2seq/aether.py) on libaether_b200.so.
+
+    RecurrentDecoder   nn/seq2seq/aether.py:505-654: same constructor (a ``params`` dict), parameter names, creation
+                       order (seeded inits reproduce the reference's) and ``forward(inputs, hidden, edges,
+                       predicted_field) -> (outputs, hidden)``; the step runs in csrc/seqdec.cu
+    Seq2SeqAether      the decoder-side surface of the enclosing model (:14-191): ``decoder``, ``field_net``,
+                       ``coordinate_embedding`` under the reference's names, ``predict_field``,
+                       ``single_step_forward`` and ``predict_future``.  The edge-type ENCODER (:249-...) is not built:
+                       pass the reference's own ``Encoder`` module as ``encoder=`` or give ``predict_future`` the sampled
+                       edge types directly (``edges=``)
+    DecoderRollout     T prediction steps (field predictor + decoder step each) captured in one CUDA graph
+
+Inference only (no autograd through the kernels, dropout inactive); CUDA tensors only, no CPU / ATen fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import _lib
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class FourierFeatureMapper(nn.Module):
+    """nn/nn/fourier_feature_mapper.py:7-23 (only the buffer lives here; the mapping runs in the field kernel)."""
+
+    def __init__(self, in_size, out_size, std=1.0):
+        super().__init__()
+        rng = np.random.default_rng(42)
+        self.register_buffer("B", torch.from_numpy(rng.normal(0, std, size=(in_size, out_size))).float())
+
+
+class RecurrentDecoder(nn.Module):
+    def __init__(self, params):
+        super().__init__()
+        self.num_vars = num_vars = params["num_vars"]
+        input_size = params["input_size"]
+        n_hid = params["decoder_hidden"]
+        edge_types = params["num_edge_types"]
+        self.dropout_prob = params["decoder_dropout"]
+        self.edge_types = edge_types
+        self.msg_fc1 = nn.ModuleList([nn.Linear(2 * n_hid, n_hid) for _ in range(edge_types)])
+        self.msg_fc2 = nn.ModuleList([nn.Linear(n_hid, n_hid) for _ in range(edge_types)])
+        self.msg_out_shape = n_hid
+        self.skip_first_edge_type = params["skip_first"]
+        self.hidden_r = nn.Linear(n_hid, n_hid, bias=False)
+        self.hidden_i = nn.Linear(n_hid, n_hid, bias=False)
+        self.hidden_h = nn.Linear(n_hid, n_hid, bias=False)
+        self.present_r = nn.Linear(n_hid, n_hid, bias=True)
+        self.present_i = nn.Linear(n_hid, n_hid, bias=True)
+        self.present_n = nn.Linear(n_hid, n_hid, bias=True)
+        self.out_mlp = nn.Sequential(
+            nn.Linear(n_hid, n_hid), nn.ReLU(), nn.Dropout(p=self.dropout_prob),
+            nn.Linear(n_hid, n_hid), nn.ReLU(), nn.Dropout(p=self.dropout_prob),
+            nn.Linear(n_hid, input_size))
+        self.send_edges, self.recv_edges = torch.where(~torch.eye(num_vars, dtype=torch.bool))
+        self.use_3d = params.get("use_3d", False)
+        self.num_dims = 3 if self.use_3d else 2
+        if input_size != 2 * self.num_dims:
+            raise ValueError("RecurrentDecoder: input_size must be 2 * num_dims (positions and velocities)")
+        if edge_types > _lib.SEQ_MAX_TYPES:
+            raise ValueError("RecurrentDecoder: at most %d edge types" % _lib.SEQ_MAX_TYPES)
+        if n_hid % 4 != 0:
+            raise ValueError("RecurrentDecoder: decoder_hidden must be a multiple of 4")
+        self.num_orientations = self.num_dims * (self.num_dims - 1) // 2
+        self.num_relative_features = 4 * self.num_dims + self.num_orientations
+        self.num_pos_features = self.num_dims + self.num_orientations
+        fe = 2 * self.num_relative_features + input_size + self.num_dims
+        self.present_msg_fc1 = nn.ModuleList([nn.Linear(fe, n_hid) for _ in range(edge_types)])
+        self.present_msg_fc2 = nn.ModuleList([nn.Linear(n_hid, n_hid) for _ in range(edge_types)])
+        fr = input_size + self.num_relative_features + self.num_dims
+        self.input_r = nn.Linear(fr, n_hid, bias=True)
+        self.input_i = nn.Linear(fr, n_hid, bias=True)
+        self.input_n = nn.Linear(fr, n_hid, bias=True)
+        self._ws = None
+
+    def get_initial_hidden(self, inputs):
+        return torch.zeros(inputs.size(0), inputs.size(2), self.msg_out_shape, device=inputs.device)
+
+    def init_weights(self):
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                nn.init.xavier_normal_(m.weight.data)
+                m.bias.data.fill_(0.1)
+
+    # ---- C-ABI plumbing ----------------------------------------------------------------------------------------------
+    def dims(self, batch: int, field_hidden: int = 0) -> "_lib.AetherSeqDims":
+        return _lib.AetherSeqDims(self.num_dims, self.num_vars, self.msg_out_shape, self.edge_types,
+                                  1 if self.skip_first_edge_type else 0, field_hidden, batch)
+
+    def c_params(self, field_net: Optional[nn.Module] = None, rff: Optional[torch.Tensor] = None):
+        """(struct, tensors kept alive) for the library; every parameter must be a contiguous fp32 CUDA tensor."""
+        p = _lib.AetherSeqParams()
+        keep = []
+
+        def dp(t):
+            t = t.detach()
+            if not t.is_cuda or t.dtype != torch.float32:
+                raise RuntimeError("aether_b200.seq2seq: parameters must be fp32 CUDA tensors (there is no CPU path)")
+            t = t.contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        for i in range(self.edge_types):
+            p.msg_fc1_w[i], p.msg_fc1_b[i] = dp(self.msg_fc1[i].weight), dp(self.msg_fc1[i].bias)
+            p.msg_fc2_w[i], p.msg_fc2_b[i] = dp(self.msg_fc2[i].weight), dp(self.msg_fc2[i].bias)
+            p.present_msg_fc1_w[i], p.present_msg_fc1_b[i] = dp(self.present_msg_fc1[i].weight), dp(self.present_msg_fc1[i].bias)
+            p.present_msg_fc2_w[i], p.present_msg_fc2_b[i] = dp(self.present_msg_fc2[i].weight), dp(self.present_msg_fc2[i].bias)
+        p.hidden_r_w, p.hidden_i_w, p.hidden_h_w = dp(self.hidden_r.weight), dp(self.hidden_i.weight), dp(self.hidden_h.weight)
+        for n in ("r", "i", "n"):
+            setattr(p, "present_%s_w" % n, dp(getattr(self, "present_" + n).weight))
+            setattr(p, "present_%s_b" % n, dp(getattr(self, "present_" + n).bias))
+            setattr(p, "input_%s_w" % n, dp(getattr(self, "input_" + n).weight))
+            setattr(p, "input_%s_b" % n, dp(getattr(self, "input_" + n).bias))
+        for j, k in enumerate((0, 3, 6)):
+            p.out_w[j], p.out_b[j] = dp(self.out_mlp[k].weight), dp(self.out_mlp[k].bias)
+        if field_net is not None:
+            p.rff_B = dp(rff)
+            for j, k in enumerate((0, 2, 4)):
+                p.field_w[j], p.field_b[j] = dp(field_net[k].weight), dp(field_net[k].bias)
+        return p, keep
+
+    def workspace(self, dims, device) -> torch.Tensor:
+        nbytes = _lib.load().aether_seq_workspace_bytes(ctypes.byref(dims))
+        if nbytes == 0:
+            raise RuntimeError("aether_b200.seq2seq: unsupported decoder shape")
+        if self._ws is None or self._ws.numel() < nbytes or self._ws.device != device:
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        return self._ws
+
+    def _check(self, inputs, hidden, edges, field):
+        B, N = inputs.shape[0], inputs.shape[1]
+        E = N * (N - 1)
+        if not inputs.is_cuda:
+            raise RuntimeError("aether_b200.seq2seq: CUDA tensors only (there is no CPU path)")
+        if N != self.num_vars or inputs.shape[2] != 2 * self.num_dims:
+            raise RuntimeError("RecurrentDecoder: inputs must be [batch, %d, %d]" % (self.num_vars, 2 * self.num_dims))
+        if tuple(hidden.shape) != (B, N, self.msg_out_shape):
+            raise RuntimeError("RecurrentDecoder: hidden must be [batch, num_vars, decoder_hidden]")
+        if tuple(edges.shape) != (B, E, self.edge_types):
+            raise RuntimeError("RecurrentDecoder: edges must be [batch, num_vars*(num_vars-1), num_edge_types]")
+        if tuple(field.shape) != (B, N, self.num_dims):
+            raise RuntimeError("RecurrentDecoder: predicted_field must be [batch, num_vars, num_dims]")
+
+    @torch.no_grad()
+    def forward(self, inputs, hidden, edges, predicted_field):
+        """inputs[B,N,2D], hidden[B,N,H], edges[B,N(N-1),types], predicted_field[B,N,D] -> (outputs, hidden)."""
+        if self.training and self.dropout_prob > 0:
+            raise RuntimeError("aether_b200.seq2seq.RecurrentDecoder is inference-only: call .eval() (dropout is not built)")
+        self._check(inputs, hidden, edges, predicted_field)
+        f32 = lambda t: t.detach().to(torch.float32).contiguous()
+        inputs, hidden, edges, field = f32(inputs), f32(hidden), f32(edges), f32(predicted_field)
+        lib = _lib.load()
+        with torch.cuda.device(inputs.device):
+            d = self.dims(inputs.shape[0])
+            ws = self.workspace(d, inputs.device)
+            p, keep = self.c_params()
+            out, hid = torch.empty_like(inputs), torch.empty_like(hidden)
+            _lib.check(lib.aether_seq_decoder_step(ctypes.byref(d), ctypes.byref(p), _lib.ptr(inputs), _lib.ptr(hidden),
+                                                   _lib.ptr(edges), _lib.ptr(field), _lib.ptr(out), _lib.ptr(hid),
+                                                   _lib.ptr(ws), ws.numel(), _stream()), "aether_seq_decoder_step")
+        return out, hid
+
+    @torch.no_grad()
+    def localizer(self, extended_inputs):
+        """AugmentedLocalizer.forward (nn/utils/augmented_global_to_local.py:51-68) on [B,N,3D] = [pos|vel|field]:
+        (rel_feat, Rinv, edge_attr, edge_pos)."""
+        D, N, F = self.num_dims, self.num_vars, self.num_relative_features
+        x = extended_inputs.detach().to(torch.float32)
+        states, field = x[..., :2 * D].contiguous(), x[..., 2 * D:].contiguous()
+        B = x.shape[0]
+        dev = x.device
+        rel = torch.empty(B, N, 3 * D + F, device=dev)
+        Rinv = torch.empty(B, N, D, D, device=dev)
+        ea = torch.empty(B, N * (N - 1), 2 * F + 3 * D, device=dev)
+        with torch.cuda.device(dev):
+            d = self.dims(B)
+            _lib.check(_lib.load().aether_seq_localizer(ctypes.byref(d), _lib.ptr(states), _lib.ptr(field), _lib.ptr(rel),
+                                                        _lib.ptr(Rinv), _lib.ptr(ea), _stream()), "aether_seq_localizer")
+        pos_idx = [2, 3, 4] if D == 2 else [3, 4, 5, 6, 7, 8]     # pos_representation='polar' (:18-24, :578-580)
+        return rel, Rinv, ea, ea[..., pos_idx]
+
+
+def gumbel_softmax(logits, tau=1.0, hard=False, eps=1e-10, generator=None):
+    """nn/utils/model_utils.py:57-121 (noise drawn on the logits' device)."""
+    U = torch.rand(logits.shape, device=logits.device, generator=generator)
+    y_soft = torch.softmax((logits - torch.log(eps - torch.log(U + eps))) / tau, dim=-1)
+    if not hard:
+        return y_soft
+    k = y_soft.argmax(-1, keepdim=True)
+    return torch.zeros_like(y_soft).scatter_(-1, k, 1.0)
+
+
+class Seq2SeqAether(nn.Module):
+    def __init__(self, params, encoder: Optional[nn.Module] = None):
+        super().__init__()
+        self.num_vars = params["num_vars"]
+        self.encoder = encoder
+        self.decoder = RecurrentDecoder(params)
+        self.num_edge_types = params.get("num_edge_types")
+        self.gumbel_temp = params.get("gumbel_temp")
+        self.use_3d = params.get("use_3d", False)
+        self.num_dims = 3 if self.use_3d else 2
+        hidden_size = params["encoder_hidden"]
+        if hidden_size % 2 != 0:
+            raise ValueError("Hidden size must be even")
+        if hidden_size % 4 != 0:
+            raise ValueError("Seq2SeqAether: encoder_hidden must be a multiple of 4")
+        self.field_net = nn.Sequential(nn.Linear(hidden_size, hidden_size), nn.SiLU(), nn.Linear(hidden_size, hidden_size),
+                                       nn.SiLU(), nn.Linear(hidden_size, self.num_dims))
+        self.coordinate_embedding = FourierFeatureMapper(self.num_dims, hidden_size // 2, std=params.get("rff_std", 1.0))
+        self.field_hidden = hidden_size
+
+    def _dims(self, batch):
+        return self.decoder.dims(batch, self.field_hidden)
+
+    def _params(self):
+        return self.decoder.c_params(self.field_net, self.coordinate_embedding.B)
+
+    @torch.no_grad()
+    def predict_field(self, x):
+        """nn/seq2seq/aether.py:83-87: (field at the positions in x[..., :D], the positions).  x: [..., N, >=D]."""
+        coords = x[..., :self.num_dims]
+        if x.shape[-1] < 2 * self.num_dims:
+            raise RuntimeError("predict_field: states must carry positions and velocities")
+        if not x.is_cuda:
+            raise RuntimeError("aether_b200.seq2seq: CUDA tensors only (there is no CPU path)")
+        xs = x.detach().to(torch.float32)[..., :2 * self.num_dims].reshape(-1, 2 * self.num_dims).contiguous()
+        dec = self.decoder
+        rows, N = xs.shape[0], dec.num_vars
+        if rows % N != 0:
+            raise RuntimeError("predict_field: the leading axes must hold whole trajectories of num_vars particles")
+        field = torch.empty(rows, self.num_dims, device=xs.device)
+        with torch.cuda.device(xs.device):
+            d = self._dims(rows // N)
+            ws = dec.workspace(d, xs.device)
+            p, keep = self._params()
+            _lib.check(_lib.load().aether_seq_predict_field(ctypes.byref(d), ctypes.byref(p), _lib.ptr(xs), _lib.ptr(field),
+                                                            _lib.ptr(ws), ws.numel(), _stream()), "aether_seq_predict_field")
+        return field.reshape(*x.shape[:-1], self.num_dims), coords
+
+    def single_step_forward(self, inputs, decoder_hidden, edge_logits, hard_sample, predicted_field):
+        """nn/seq2seq/aether.py:89-100."""
+        old_shape = edge_logits.shape
+        edges = gumbel_softmax(edge_logits.reshape(-1, self.num_edge_types), tau=self.gumbel_temp,
+                               hard=hard_sample).view(old_shape)
+        predictions, decoder_hidden = self.decoder(inputs, decoder_hidden, edges, predicted_field)
+        return predictions, decoder_hidden, edges
+
+    @torch.no_grad()
+    def predict_future(self, inputs, prediction_steps, return_edges=False, return_everything=False, edges=None):
+        """nn/seq2seq/aether.py:155-191.  With ``edges[B, T-1+steps, N(N-1), types]`` the sampled edge types of every
+        step are taken from the caller; otherwise ``self.encoder`` (the reference's Encoder) produces the logits."""
+        T = inputs.size(1)
+        hidden = self.decoder.get_initial_hidden(inputs)
+        all_predictions, all_edges = [], []
+        if edges is None:
+            if self.encoder is None:
+                raise RuntimeError("predict_future: no encoder was given to Seq2SeqAether; pass edges=")
+            x = inputs[:, :-1].transpose(2, 1).contiguous()
+            predicted_field, _ = self.predict_field(x)
+            prior_logits, _, prior_hidden = self.encoder(inputs[:, :-1], predicted_field)
+        for step in range(T - 1):
+            cur = inputs[:, step]
+            if edges is None:
+                pred, hidden, e = self.single_step_forward(cur, hidden, prior_logits[:, step], True,
+                                                           predicted_field[:, :, step])
+            else:
+                e = edges[:, step]
+                pred, hidden = self.decoder(cur, hidden, e, self.predict_field(cur)[0])
+            if return_everything:
+                all_edges.append(e)
+                all_predictions.append(pred)
+        pred = inputs[:, T - 1]
+        for step in range(prediction_steps):
+            field, _ = self.predict_field(pred)
+            if edges is None:
+                logits, prior_hidden = self.encoder.single_step_forward(pred, prior_hidden, field)
+                pred, hidden, e = self.single_step_forward(pred, hidden, logits, True, field)
+            else:
+                e = edges[:, T - 1 + step]
+                pred, hidden = self.decoder(pred, hidden, e, field)
+            all_predictions.append(pred)
+            all_edges.append(e)
+        predictions = torch.stack(all_predictions, dim=1)
+        if return_edges:
+            return predictions, torch.stack(all_edges, dim=1)
+        return predictions
+
+
+class DecoderRollout:
+    """``steps`` prediction steps of predict_future's second loop (:176-184) with given edge types, as one CUDA graph:
+    per step the field predictor and the decoder step (``aether_seq_rollout_step``, 14 launches)."""
+
+    def __init__(self, model: Seq2SeqAether, batch: int, steps: int, cuda_graph: bool = True, device=None):
+        self.model, self.steps, self.B = model, int(steps), int(batch)
+        dec = model.decoder
+        self.dev = torch.device(device) if device is not None else next(model.parameters()).device
+        if self.dev.type != "cuda":
+            raise RuntimeError("aether_b200.seq2seq: CUDA only (there is no CPU path)")
+        N, D, H, K = dec.num_vars, dec.num_dims, dec.msg_out_shape, dec.edge_types
+        f32 = dict(dtype=torch.float32, device=self.dev)
+        self.x0 = torch.empty(batch, N, 2 * D, **f32)
+        self.h0 = torch.zeros(batch, N, H, **f32)
+        self.hidden = torch.empty(batch, N, H, **f32)
+        self.edges = torch.empty(self.steps, batch, N * (N - 1), K, **f32)
+        self.traj = torch.empty(self.steps, batch, N, 2 * D, **f32)
+        self.dims = model._dims(batch)
+        self.lib = _lib.load()
+        self.ws = torch.empty(self.lib.aether_seq_workspace_bytes(ctypes.byref(self.dims)), dtype=torch.uint8, device=self.dev)
+        self._use_graph = cuda_graph
+        self._graph = None
+        self.launches_per_replay = 0
+
+    def _steps(self):
+        p, self._keep = self.model._params()
+        self.hidden.copy_(self.h0)
+        x = self.x0
+        for t in range(self.steps):
+            _lib.check(self.lib.aether_seq_rollout_step(ctypes.byref(self.dims), ctypes.byref(p), _lib.ptr(x),
+                                                        _lib.ptr(self.hidden), _lib.ptr(self.edges[t]), _lib.ptr(self.traj[t]),
+                                                        _lib.ptr(self.hidden), None, _lib.ptr(self.ws), self.ws.numel(),
+                                                        _stream()), "aether_seq_rollout_step")
+            x = self.traj[t]
+
+    @torch.no_grad()
+    def run(self, x0, edges, hidden0=None) -> torch.Tensor:
+        """x0[B,N,2D] (the last burn-in state), edges[steps,B,N(N-1),types] (or [B,E,types] for every step),
+        hidden0[B,N,H] (zeros when None) -> predictions[steps,B,N,2D]; the final hidden state is in ``self.hidden``."""
+        with torch.cuda.device(self.dev):
+            self.x0.copy_(x0, non_blocking=True)
+            self.edges.copy_(edges if edges.dim() == 4 else edges.unsqueeze(0).expand_as(self.edges), non_blocking=True)
+            if hidden0 is None:
+                self.h0.zero_()
+            else:
+                self.h0.copy_(hidden0, non_blocking=True)
+            if not self._use_graph:
+                self._steps()
+                return self.traj
+            if self._graph is None:
+                self._steps()
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                n0 = self.lib.aether_launch_count()
+                with torch.cuda.graph(g):
+                    self._steps()
+                self.launches_per_replay = int(self.lib.aether_launch_count() - n0)
+                self._graph = g
+            self._graph.replay()
+            return self.traj

@@ -264,6 +264,69 @@ int aether_dynfield_backward(int32_t num_dims, int64_t n_nodes, int32_t num_node
                              float* grad_vel, const void* workspace, size_t workspace_bytes, void* scratch,
                              size_t scratch_bytes, void* stream);
 
+/* ---- seq2seq decoder path (aether_b200/csrc/seqdec.cu) ---------------------------------------------------------------
+ * The paper's rollout model for the electrostatic / gravitational experiments: one step of
+ * RecurrentDecoder.forward (nn/seq2seq/aether.py:589-654; per-edge-type message MLPs weighted by the edge-type
+ * weights, receiver mean, AugmentedLocalizer nn/utils/augmented_global_to_local.py:51-68 with its virtual origin node,
+ * GRU-style gates, out MLP, Globalizer, inputs + prediction) and the field predictor of the enclosing model
+ * (Aether.predict_field, nn/seq2seq/aether.py:83-87: Fourier features nn/nn/fourier_feature_mapper.py:21-23 + field_net
+ * :72-78).  Inference only (dropout inactive).  The graph is the reference's fixed one: num_vars particles per
+ * trajectory, every ordered pair (sender-major, torch.where(~eye), :548-549).  The encoder that produces the edge-type
+ * logits (nn/seq2seq/aether.py:249-...) is not part of this path: edge-type weights are an input.
+ *
+ * Layouts: states[B, N, 2D] = [pos | vel]; hidden[B, N, H]; edge_types[B, N(N-1), n_types] (leading dimension
+ * n_types; soft weights or one-hot); field[B, N, D].  hidden_out may alias hidden_in.
+ * Every pointer of AetherSeqParams is nn.Linear layout ([out, in] row-major weight, [out] bias), named after the
+ * reference's state_dict keys; per-type arrays are indexed by edge type (entries below `skip_first` are not read).
+ * The field_* / rff_B members are only read by aether_seq_predict_field / aether_seq_rollout_step. */
+#define AETHER_SEQ_MAX_TYPES 4
+typedef struct AetherSeqDims {
+  int32_t num_dims;      /* D: 2 or 3 (use_3d)                              */
+  int32_t num_vars;      /* N particles per trajectory, 2..64               */
+  int32_t hidden;        /* decoder_hidden, multiple of 4                   */
+  int32_t n_types;       /* num_edge_types, 1..AETHER_SEQ_MAX_TYPES         */
+  int32_t skip_first;    /* 1: edge type 0 sends no message                 */
+  int32_t field_hidden;  /* encoder_hidden (width of field_net), multiple of 4; 0 when the field net is unused */
+  int64_t batch;         /* B trajectories                                  */
+} AetherSeqDims;
+typedef struct AetherSeqParams {
+  const float* msg_fc1_w[AETHER_SEQ_MAX_TYPES];          /* [H, 2H]   (columns: receiver state | sender state) */
+  const float* msg_fc1_b[AETHER_SEQ_MAX_TYPES];
+  const float* msg_fc2_w[AETHER_SEQ_MAX_TYPES];          /* [H, H] */
+  const float* msg_fc2_b[AETHER_SEQ_MAX_TYPES];
+  const float* hidden_r_w; const float* hidden_i_w; const float* hidden_h_w;             /* [H, H], no bias */
+  const float* present_r_w; const float* present_r_b;    /* [H, H] */
+  const float* present_i_w; const float* present_i_b;
+  const float* present_n_w; const float* present_n_b;
+  const float* out_w[3]; const float* out_b[3];          /* out_mlp.{0,3,6}: [H,H], [H,H], [2D,H] */
+  const float* present_msg_fc1_w[AETHER_SEQ_MAX_TYPES];  /* [H, 2F+3D], F = 4D + D(D-1)/2 */
+  const float* present_msg_fc1_b[AETHER_SEQ_MAX_TYPES];
+  const float* present_msg_fc2_w[AETHER_SEQ_MAX_TYPES];  /* [H, H] */
+  const float* present_msg_fc2_b[AETHER_SEQ_MAX_TYPES];
+  const float* input_r_w; const float* input_r_b;        /* [H, 3D+F] */
+  const float* input_i_w; const float* input_i_b;
+  const float* input_n_w; const float* input_n_b;
+  const float* rff_B;                                    /* coordinate_embedding.B: [D, field_hidden/2] */
+  const float* field_w[3]; const float* field_b[3];      /* field_net.{0,2,4}: [Hf,Hf], [Hf,Hf], [D,Hf] */
+} AetherSeqParams;
+size_t aether_seq_workspace_bytes(const AetherSeqDims* dims);
+/* field[B,N,D] = field_net(rff(states[..., :D])) */
+int aether_seq_predict_field(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states, float* field,
+                             void* workspace, size_t workspace_bytes, void* stream);
+/* (states_out, hidden_out) = RecurrentDecoder.forward(states, hidden_in, edge_types, field) */
+int aether_seq_decoder_step(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states,
+                            const float* hidden_in, const float* edge_types, const float* field, float* states_out,
+                            float* hidden_out, void* workspace, size_t workspace_bytes, void* stream);
+/* One step of the loops of Aether.predict_future (nn/seq2seq/aether.py:166-184): field = predict_field(states), then the
+ * decoder step with it.  field_out (may be NULL) receives the predicted field. */
+int aether_seq_rollout_step(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states,
+                            const float* hidden_in, const float* edge_types, float* states_out, float* hidden_out,
+                            float* field_out, void* workspace, size_t workspace_bytes, void* stream);
+/* Test hook: the three AugmentedLocalizer outputs the step consumes, rel_feat[B,N,3D+F], Rinv[B,N,D,D],
+ * edge_attr[B,N(N-1),2F+3D]. */
+int aether_seq_localizer(const AetherSeqDims* dims, const float* states, const float* field, float* rel_feat, float* Rinv,
+                         float* edge_attr, void* stream);
+
 /* ---- optimizer step of the reference's caller (torch.optim.AdamW, experiments/lorentz/main.py:164,292) ----------
  * One fused update of n_tensors parameter tensors (host arrays of device pointers; numel[i] elements each, n_tensors <= 64):
  *   p <- p (1 - lr wd);  m <- b1 m + (1-b1) g;  v <- b2 v + (1-b2) g^2;  p <- p - lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)

@@ -1,0 +1,41 @@
+"""Host-side checks of the seq2seq decoder mirror that need no GPU: parameter names / shapes / creation order against
+the reference's recorded state_dict, constructor errors."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+
+
+@pytest.mark.parametrize("name", ["seq2seq2d_h32", "seq2seq3d_h64", "seq2seq2d_h48_n3"])
+def test_state_dict_matches_reference(name):
+    from aether_b200.seq2seq import Seq2SeqAether
+    g = load_golden(name)
+    D = int(g["D"])
+    m = Seq2SeqAether({"num_vars": int(g["N"]), "input_size": 2 * D, "use_3d": D == 3, "decoder_hidden": int(g["n_hid"]),
+                       "num_edge_types": int(g["n_types"]), "skip_first": bool(g["skip_first"]), "decoder_dropout": 0.0,
+                       "encoder_hidden": 16, "gumbel_temp": 0.5, "rff_std": 1.0})
+    ref_dec = [k[4:] for k in g if k.startswith("dec.")]
+    mine = [k for k in m.decoder.state_dict()]
+    assert mine == ref_dec                                       # same names in the same (creation) order
+    for k in ref_dec:
+        assert tuple(m.decoder.state_dict()[k].shape) == g["dec." + k].shape, k
+    assert [k for k in m.field_net.state_dict()] == [k[len("field_net."):] for k in g if k.startswith("field_net.")]
+    assert np.array_equal(m.coordinate_embedding.B.numpy(), g["rff_B"])   # default_rng(42) like the reference
+    assert np.array_equal(m.decoder.send_edges.numpy(), g["send_edges"])
+    assert np.array_equal(m.decoder.recv_edges.numpy(), g["recv_edges"])
+
+
+def test_constructor_errors_and_cpu_refusal():
+    from aether_b200.seq2seq import RecurrentDecoder
+    base = {"num_vars": 5, "input_size": 4, "decoder_hidden": 32, "num_edge_types": 2, "skip_first": False,
+            "decoder_dropout": 0.0}
+    with pytest.raises(ValueError):
+        RecurrentDecoder(dict(base, num_edge_types=5))
+    with pytest.raises(ValueError):
+        RecurrentDecoder(dict(base, decoder_hidden=30))
+    with pytest.raises(ValueError):
+        RecurrentDecoder(dict(base, input_size=6))
+    dec = RecurrentDecoder(base).eval()
+    with pytest.raises(RuntimeError):                            # no CPU fallback
+        dec(torch.zeros(1, 5, 4), torch.zeros(1, 5, 32), torch.zeros(1, 20, 2), torch.zeros(1, 5, 2))

@@ -1,0 +1,146 @@
+"""seq2seq decoder path on the GPU (aether_b200/seq2seq.py -> csrc/seqdec.cu through the C ABI) against fixtures recorded
+from the unmodified reference model (tests/golden/make_golden_seq2seq.py) and against the oracle at the reference's own
+experiment shape (5 particles, 2 edge types, decoder_hidden up to 512).  fp32: 1e-5 relative to each tensor's scale for
+single steps; the multi-step rollouts compound step errors through the recurrent state, bar 1e-4."""
+import os
+
+import pytest
+import torch
+
+from conftest import load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+CASES = ["seq2seq2d_h32", "seq2seq3d_h64", "seq2seq2d_h48_n3"]
+
+
+def params_of(g, enc_hidden=16):
+    D = int(g["D"])
+    return {"num_vars": int(g["N"]), "input_size": 2 * D, "use_3d": D == 3, "decoder_hidden": int(g["n_hid"]),
+            "num_edge_types": int(g["n_types"]), "skip_first": bool(g["skip_first"]), "decoder_dropout": 0.0,
+            "encoder_hidden": enc_hidden, "gumbel_temp": 0.5, "rff_std": 1.0}
+
+
+def build(g):
+    from aether_b200.seq2seq import Seq2SeqAether
+    m = Seq2SeqAether(params_of(g))
+    sd = {"decoder." + k[4:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("dec.")}
+    sd.update({k: torch.from_numpy(v) for k, v in g.items() if k.startswith("field_net.")})
+    sd["coordinate_embedding.B"] = torch.from_numpy(g["rff_B"])
+    m.load_state_dict(sd)          # strict: every reference key of the decoder side exists here and vice versa
+    return m.cuda().eval()
+
+
+def dev(g, k):
+    return torch.from_numpy(g[k]).cuda()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_localizer_matches_reference(name):
+    g = load_golden(name)
+    m = build(g)
+    rel, Rinv, ea, pos = m.decoder.localizer(torch.cat([dev(g, "step_inputs"), dev(g, "step_field")], -1))
+    assert (rel.cpu() - torch.from_numpy(g["loc_rel_feat"])).abs().max() <= 1e-5
+    assert (Rinv.cpu() - torch.from_numpy(g["loc_Rinv"])).abs().max() <= 1e-6
+    assert (ea.cpu() - torch.from_numpy(g["loc_edge_attr"])).abs().max() <= 1e-5
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_decoder_step_matches_reference(name):
+    g = load_golden(name)
+    m = build(g)
+    out, hid = m.decoder(dev(g, "step_inputs"), dev(g, "step_hidden"), dev(g, "step_edges"), dev(g, "step_field"))
+    assert rel_err(out.cpu(), g["step_outputs"]) <= 1e-5
+    assert rel_err(hid.cpu(), g["step_hidden_new"]) <= 1e-5
+    f, coords = m.predict_field(dev(g, "step_inputs"))
+    assert rel_err(f.cpu(), g["field_pred"]) <= 2e-5
+    assert torch.equal(coords.cpu(), torch.from_numpy(g["step_inputs"])[..., :int(g["D"])])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_predict_future_matches_reference(name):
+    """The whole predict_future of the reference model (burn-in + prediction steps); the encoder's sampled edge types
+    are the recorded ones."""
+    g = load_golden(name)
+    m = build(g)
+    preds, edges = m.predict_future(dev(g, "pf_inputs"), int(g["pf_steps"]), return_edges=True, return_everything=True,
+                                    edges=dev(g, "pf_edges"))
+    assert preds.shape == g["pf_predictions"].shape and torch.equal(edges.cpu(), torch.from_numpy(g["pf_edges"]))
+    assert rel_err(preds.cpu(), g["pf_predictions"]) <= 1e-4
+    only_future = m.predict_future(dev(g, "pf_inputs"), int(g["pf_steps"]), edges=dev(g, "pf_edges"))
+    assert torch.equal(only_future, preds[:, -int(g["pf_steps"]):])
+
+
+def _oracle_weights(m):
+    w = {k[len("decoder."):]: v.detach().cpu() for k, v in m.state_dict().items() if k.startswith("decoder.")}
+    w.update({k: v.detach().cpu() for k, v in m.state_dict().items() if k.startswith("field_net.")})
+    w["rff_B"] = m.coordinate_embedding.B.detach().cpu()
+    return w
+
+
+@pytest.mark.parametrize("D,N,B,H,K,skip,Hf", [(2, 5, 64, 512, 2, False, 512), (3, 5, 32, 256, 2, True, 128),
+                                               (2, 2, 3, 36, 1, False, 20), (3, 7, 5, 64, 4, True, 64),
+                                               (2, 4, 6, 32, 1, True, 16)])
+def test_step_and_rollout_against_oracle(D, N, B, H, K, skip, Hf):
+    """Reference experiment shapes (scripts/electrostatic_field_aether.sh: 5 particles, batch 64, decoder_hidden 512,
+    2 edge types; gravitational 3D: batch 32) and edge cases: 2 particles, one edge type, no active type at all
+    (skip_first with one type: only the GRU inputs drive the state), widths that are not multiples of the tile."""
+    from aether_b200.seq2seq import DecoderRollout, Seq2SeqAether
+    from oracle import seq2seq_oracle as so
+    torch.manual_seed(11)
+    p = {"num_vars": N, "input_size": 2 * D, "use_3d": D == 3, "decoder_hidden": H, "num_edge_types": K,
+         "skip_first": skip, "decoder_dropout": 0.0, "encoder_hidden": Hf, "gumbel_temp": 0.5}
+    m = Seq2SeqAether(p).cuda().eval()
+    w = _oracle_weights(m)
+    E, T = N * (N - 1), 4
+    x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1)
+    hid = 0.5 * torch.randn(B, N, H)
+    soft = torch.softmax(torch.randn(B, E, K), -1)
+    field = 0.3 * torch.randn(B, N, D)
+    out, h2 = m.decoder(x.cuda(), hid.cuda(), soft.cuda(), field.cuda())
+    o_ref, h_ref = so.decoder_step(w, x, hid, soft, field, D, K, skip)
+    assert rel_err(out.cpu(), o_ref) <= 1e-5 and rel_err(h2.cpu(), h_ref) <= 1e-5
+    # prediction steps with one-hot edge types, captured as one CUDA graph
+    onehot = torch.nn.functional.one_hot(torch.randint(0, K, (T, B, E)), K).float()
+    r = DecoderRollout(m, B, T, cuda_graph=True)
+    traj = r.run(x.cuda(), onehot.cuda()).clone()
+    traj2 = r.run(x.cuda(), onehot.cuda()).clone()                 # replay
+    eager = DecoderRollout(m, B, T, cuda_graph=False).run(x.cuda(), onehot.cuda())
+    assert torch.equal(traj, traj2) and torch.equal(traj, eager)
+    assert r.launches_per_replay == (14 if K - int(skip) > 0 else 11) * T
+    burn = x.unsqueeze(1)
+    ref = so.predict_future(w, burn, onehot.transpose(0, 1), T, D, K, skip, return_everything=False)
+    assert rel_err(traj.transpose(0, 1).cpu(), ref) <= 1e-4
+
+
+def test_module_surface_and_errors():
+    from aether_b200.seq2seq import RecurrentDecoder, Seq2SeqAether
+    g = load_golden("seq2seq2d_h32")
+    m = build(g)
+    dec = m.decoder
+    x = dev(g, "step_inputs")
+    assert dec.get_initial_hidden(dev(g, "pf_inputs")).shape == (4, 5, 32)
+    with pytest.raises(RuntimeError):
+        dec(x.cpu(), dev(g, "step_hidden").cpu(), dev(g, "step_edges").cpu(), dev(g, "step_field").cpu())
+    with pytest.raises(RuntimeError):
+        dec(x, dev(g, "step_hidden")[:, :, :16], dev(g, "step_edges"), dev(g, "step_field"))
+    with pytest.raises(RuntimeError):
+        m.predict_future(dev(g, "pf_inputs"), 2)          # no encoder, no edges
+
+    class Enc(torch.nn.Module):                            # the reference Encoder's call surface, logits from positions
+        def forward(self, inputs, predicted_field):
+            B, T, N, _ = inputs.shape
+            lg = inputs[:, :, :, :1].repeat_interleave(N - 1, 2).repeat(1, 1, 1, 2) * torch.tensor([1.0, -1.0], device=inputs.device)
+            return lg, lg, (torch.zeros(1), torch.zeros(1))
+
+        def single_step_forward(self, inputs, prior_state, predicted_field):
+            N = inputs.shape[1]
+            lg = inputs[:, :, :1].repeat_interleave(N - 1, 1).repeat(1, 1, 2) * torch.tensor([1.0, -1.0], device=inputs.device)
+            return lg, prior_state
+
+    m.encoder = Enc()
+    torch.manual_seed(3)
+    preds, edges = m.predict_future(dev(g, "pf_inputs"), 3, return_edges=True)
+    assert preds.shape == (4, 3, 5, 4) and edges.shape == (4, 3, 20, 2)
+    assert bool(((edges == 0) | (edges == 1)).all()) and torch.equal(edges.sum(-1), torch.ones(4, 3, 20, device="cuda"))
+    again = m.predict_future(dev(g, "pf_inputs"), 3, edges=torch.cat([torch.zeros(4, 3, 20, 2, device="cuda"), edges], 1))
+    assert torch.isfinite(preds).all() and again.shape == preds.shape
