@@ -162,7 +162,7 @@ __global__ void seq_geom_kernel(const float* __restrict__ states, const float* _
 // ------------------------------------------------------------------------------------------------
 // multi-problem, multi-term fp32 GEMM
 // ------------------------------------------------------------------------------------------------
-constexpr int GM = 64, GN = 64, GK = 16, GT = 256, GPAD = 4;
+constexpr int GK = 16, GT = 256, GPAD = 4, GS = 4;
 constexpr int MAX_TERMS = 4, MAX_PROB = 12;
 enum SeqAct { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2, ACT_SIGMOID = 3, ACT_SILU = 4 };
 
@@ -190,87 +190,123 @@ __device__ __forceinline__ float act_f(float v, int act) {
   }
 }
 
-__global__ void __launch_bounds__(GT) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  const int n = valid ? 4 : 0;          // src-size 0: the 4 bytes are zero-filled, nothing is read
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(d), "l"(src), "r"(n));
+}
+// 16-byte copy of which only the first `bytes` (0..16) are read; the rest is zero-filled
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src, int bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// BM x BN tile, 256 threads, (BM/16) x (BN/16) outputs per thread: rows ty + 16 i, columns tx + 16 j.  K slabs of 16
+// go through a GS-stage cp.async ring in the operands' own layout ([row][k], rows padded to 20 floats): one 16-byte
+// copy per thread and operand tile (zero-filled past K through the copy's source size; 4-byte copies when a row is not
+// 16-byte aligned, e.g. the 39-wide 3D features).  The inner loop reads 4 k's of a row as one vector; with rows
+// strided by 16 between a thread's outputs, the 8 lanes of a shared-memory phase hit 8 different 16-byte bank groups
+// (row step = 5 groups).  The small tile exists for the node-level problems (B*N rows): at 64 x 64 they are 40 CTAs.
+template <int BM, int BN>
+__global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+  constexpr int TM = BM / 16, TN = BN / 16, LD = GK + 4;
   const Problem& P = bt.p[blockIdx.z];
-  const int m0 = blockIdx.x * GM, n0 = blockIdx.y * GN;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (m0 >= P.M || n0 >= P.N) return;
-  __shared__ __align__(16) float As[2][GK][GM + GPAD];
-  __shared__ __align__(16) float Ws[2][GK][GN + GPAD];
+  __shared__ __align__(16) float As[GS][BM][LD];
+  __shared__ __align__(16) float Ws[GS][BN][LD];
   const int tid = threadIdx.x;
-  const int lr = tid >> 2, lk = (tid & 3) * 4;       // loader: row lr of the tile, k offset lk..lk+3
-  const int tx = tid & 15, ty = tid >> 4;            // compute: rows ty*4.., columns tx*4..
-  float sum[4][4], acc[4][4];
+  const int tx = tid & 15, ty = tid >> 4;
+  float sum[TM][TN], acc[TM][TN];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < TM; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { sum[i][j] = 0.f; acc[i][j] = 0.f; }
+    for (int j = 0; j < TN; ++j) { sum[i][j] = 0.f; acc[i][j] = 0.f; }
 
   for (int t = 0; t < P.nterms; ++t) {
     const Term& T = P.t[t];
     const int K = T.K;
-    const bool arow = m0 + lr < P.M, wrow = n0 + lr < P.N;
-    const float* ap = T.A + (size_t)(m0 + lr) * T.lda;
-    const float* wp = T.W + (size_t)(n0 + lr) * T.ldw;
-    const bool vec = (K % 4 == 0) && (T.lda % 4 == 0) && (T.ldw % 4 == 0) &&
-                     ((((uintptr_t)T.A) | ((uintptr_t)T.W)) & 15) == 0;
-    float4 ra, rw;
-    auto fetch = [&](int k0) {
-      const int k = k0 + lk;
-      ra = make_float4(0.f, 0.f, 0.f, 0.f);
-      rw = ra;
-      if (vec) {
-        if (arow && k < K) ra = *reinterpret_cast<const float4*>(ap + k);
-        if (wrow && k < K) rw = *reinterpret_cast<const float4*>(wp + k);
-      } else {
-        if (arow) {
-          if (k < K) ra.x = ap[k];
-          if (k + 1 < K) ra.y = ap[k + 1];
-          if (k + 2 < K) ra.z = ap[k + 2];
-          if (k + 3 < K) ra.w = ap[k + 3];
-        }
-        if (wrow) {
-          if (k < K) rw.x = wp[k];
-          if (k + 1 < K) rw.y = wp[k + 1];
-          if (k + 2 < K) rw.z = wp[k + 2];
-          if (k + 3 < K) rw.w = wp[k + 3];
+    const float* Ab = T.A;
+    const float* Wb = T.W;
+    const int lda = T.lda, ldw = T.ldw;
+    const bool avec = (lda % 4 == 0) && ((((uintptr_t)Ab) & 15) == 0);
+    const bool wvec = (ldw % 4 == 0) && ((((uintptr_t)Wb) & 15) == 0);
+    auto issue = [&](int kt, int stage) {
+#pragma unroll
+      for (int c0 = 0; c0 < (BM + BN) * 4; c0 += GT) {
+        int c = c0 + tid;
+        const bool isA = c < BM * 4;
+        if (!isA) c -= BM * 4;
+        const int row = c >> 2, kc = (c & 3) * 4, k = kt * GK + kc;
+        const int grow = (isA ? m0 : n0) + row;
+        const bool rok = grow < (isA ? P.M : P.N);
+        const float* base = isA ? Ab : Wb;
+        const float* src = base + (size_t)grow * (isA ? lda : ldw) + k;
+        float* dst = isA ? &As[stage][row][kc] : &Ws[stage][row][kc];
+        if (isA ? avec : wvec) {
+          int nb = rok ? (K - k) * 4 : 0;
+          nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+          cp_async16(dst, nb > 0 ? src : base, nb);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const bool ok = rok && (k + e < K);
+            cp_async4(dst + e, ok ? src + e : base, ok);
+          }
         }
       }
-    };
-    auto stash = [&](int buf) {
-      As[buf][lk][lr] = ra.x; As[buf][lk + 1][lr] = ra.y; As[buf][lk + 2][lr] = ra.z; As[buf][lk + 3][lr] = ra.w;
-      Ws[buf][lk][lr] = rw.x; Ws[buf][lk + 1][lr] = rw.y; Ws[buf][lk + 2][lr] = rw.z; Ws[buf][lk + 3][lr] = rw.w;
     };
     const int nk = (K + GK - 1) / GK;
-    __syncthreads();            // the previous term's last slab is no longer read
-    fetch(0);
-    stash(0);
-    __syncthreads();
+    __syncthreads();            // the previous term's last slabs are no longer read
+#pragma unroll
+    for (int s = 0; s < GS - 1; ++s) {
+      if (s < nk) issue(s, s);
+      cp_async_commit();
+    }
     for (int kt = 0; kt < nk; ++kt) {
-      const int cur = kt & 1;
-      if (kt + 1 < nk) fetch((kt + 1) * GK);
+      cp_async_wait<GS - 2>();  // slab kt has landed (for this thread's copies; the barrier covers the others)
+      __syncthreads();          // ... and everybody is done with slab kt-1, whose stage is refilled next
+      if (kt + GS - 1 < nk) issue(kt + GS - 1, (kt + GS - 1) % GS);
+      cp_async_commit();
+      const int cur = kt % GS;
+      float4 af[2][TM], wf[2][TN];
 #pragma unroll
-      for (int kk = 0; kk < GK; ++kk) {
-        const float4 a = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 4]);
-        const float4 w = *reinterpret_cast<const float4*>(&Ws[cur][kk][tx * 4]);
-        const float av[4] = {a.x, a.y, a.z, a.w}, wv[4] = {w.x, w.y, w.z, w.w};
+      for (int i = 0; i < TM; ++i) af[0][i] = *reinterpret_cast<const float4*>(&As[cur][ty + 16 * i][0]);
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+      for (int j = 0; j < TN; ++j) wf[0][j] = *reinterpret_cast<const float4*>(&Ws[cur][tx + 16 * j][0]);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
-      }
-      if (kt + 1 < nk) {
-        stash(cur ^ 1);         // the other buffer was last read before the barrier that ended iteration kt-1
-        __syncthreads();
+      for (int k4 = 0; k4 < GK / 4; ++k4) {
+        const int b = k4 & 1;
+        if (k4 + 1 < GK / 4) {
+#pragma unroll
+          for (int i = 0; i < TM; ++i) af[b ^ 1][i] = *reinterpret_cast<const float4*>(&As[cur][ty + 16 * i][4 * k4 + 4]);
+#pragma unroll
+          for (int j = 0; j < TN; ++j) wf[b ^ 1][j] = *reinterpret_cast<const float4*>(&Ws[cur][tx + 16 * j][4 * k4 + 4]);
+        }
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+          for (int j = 0; j < TN; ++j) {
+            float v = acc[i][j];
+            v = fmaf(af[b][i].x, wf[b][j].x, v);
+            v = fmaf(af[b][i].y, wf[b][j].y, v);
+            v = fmaf(af[b][i].z, wf[b][j].z, v);
+            v = fmaf(af[b][i].w, wf[b][j].w, v);
+            acc[i][j] = v;
+          }
       }
     }
+    cp_async_wait<0>();
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int m = m0 + ty * 4 + i;
+    for (int i = 0; i < TM; ++i) {
+      const int m = m0 + ty + 16 * i;
       float sc = 1.0f;
       if (T.flush && T.scale != nullptr && m < P.M) sc = T.scale[(size_t)m * T.scale_ld];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int n = n0 + tx * 4 + j;
+      for (int j = 0; j < TN; ++j) {
+        const int n = n0 + tx + 16 * j;
         float v = acc[i][j];
         if (T.bias != nullptr && n < P.N) v = v + T.bias[n];
         if (T.flush) {
@@ -284,17 +320,13 @@ __global__ void __launch_bounds__(GT) seq_gemm_kernel(const __grid_constant__ Ba
     }
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int m = m0 + ty * 4 + i;
+  for (int i = 0; i < TM; ++i) {
+    const int m = m0 + ty + 16 * i;
     if (m >= P.M) continue;
-    float* c = P.C + (size_t)m * P.ldc + n0 + tx * 4;
-    const int n = n0 + tx * 4;
-    if (n + 3 < P.N && (P.ldc % 4 == 0) && (((uintptr_t)P.C) & 15) == 0) {
-      *reinterpret_cast<float4*>(c) = make_float4(sum[i][0], sum[i][1], sum[i][2], sum[i][3]);
-    } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (n + j < P.N) c[j] = sum[i][j];
+    for (int j = 0; j < TN; ++j) {
+      const int n = n0 + tx + 16 * j;
+      if (n < P.N) P.C[(size_t)m * P.ldc + n] = sum[i][j];
     }
   }
 }
@@ -314,8 +346,14 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st) {
     maxN = bt.p[i].N > maxN ? bt.p[i].N : maxN;
   }
   if (maxM == 0 || maxN == 0 || nprob == 0) return 0;
-  dim3 grid((maxM + GM - 1) / GM, (maxN + GN - 1) / GN, nprob);
-  seq_gemm_kernel<<<grid, GT, 0, st>>>(bt);
+  const int64_t big = (int64_t)((maxM + 63) / 64) * ((maxN + 63) / 64) * nprob;
+  if (big >= 120) {
+    dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
+    seq_gemm_kernel<64, 64><<<grid, GT, 0, st>>>(bt);
+  } else {
+    dim3 grid((maxM + 31) / 32, (maxN + 31) / 32, nprob);
+    seq_gemm_kernel<32, 32><<<grid, GT, 0, st>>>(bt);
+  }
   AE_LAUNCH_CHECK();
   return 0;
 }
@@ -391,11 +429,16 @@ __global__ void seq_thin_kernel(const float* __restrict__ A, int K, const float*
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
   float acc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int k = lane; k < K; k += 32) {
-    const float a = A[(size_t)row * K + k];
+  const float4* a4 = reinterpret_cast<const float4*>(A + (size_t)row * K);     // K % 4 == 0, rows 16-byte aligned
+#pragma unroll 4
+  for (int k = lane; k < K / 4; k += 32) {
+    const float4 a = a4[k];
 #pragma unroll
     for (int c = 0; c < 6; ++c)
-      if (c < nc) acc[c] = fmaf(a, W[(size_t)c * K + k], acc[c]);
+      if (c < nc) {
+        const float4 w = reinterpret_cast<const float4*>(W + (size_t)c * K)[k];
+        acc[c] = fmaf(a.x, w.x, fmaf(a.y, w.y, fmaf(a.z, w.z, fmaf(a.w, w.w, acc[c]))));
+      }
   }
 #pragma unroll
   for (int c = 0; c < 6; ++c)

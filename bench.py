@@ -806,6 +806,49 @@ def parity_report(dev, precision):
     return out
 
 
+def seq2seq_report(dev, steps=20, reps=10):
+    """seq2seq decoder path at the shape of scripts/electrostatic_field_aether.sh: 5 particles, batch 64,
+    decoder_hidden 512, 2 edge types, 20 prediction steps as ONE CUDA graph of field predictor + decoder steps; error of
+    the first 3 steps against the CPU oracle.  A reported secondary figure, not the headline metric."""
+    from aether_b200.seq2seq import DecoderRollout, Seq2SeqAether
+    from oracle import seq2seq_oracle as so
+    D, N, B, Hd, K = 2, 5, 64, 512, 2
+    torch.manual_seed(1)
+    m = Seq2SeqAether({"num_vars": N, "input_size": 2 * D, "use_3d": False, "decoder_hidden": Hd, "num_edge_types": K,
+                       "skip_first": False, "decoder_dropout": 0.0, "encoder_hidden": Hd, "gumbel_temp": 0.5}).to(dev).eval()
+    E = N * (N - 1)
+    x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1)
+    edges = torch.nn.functional.one_hot(torch.randint(0, K, (steps, B, E)), K).float()
+    r = DecoderRollout(m, B, steps, cuda_graph=True)
+    xd, ed = x.to(dev), edges.to(dev)
+    for _ in range(3):
+        traj = r.run(xd, ed)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ts = []
+    for _ in range(reps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        r.run(xd, ed)
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    ms = ts[len(ts) // 2]
+    w = {k[len("decoder."):]: v.detach().cpu() for k, v in m.state_dict().items() if k.startswith("decoder.")}
+    w.update({k: v.detach().cpu() for k, v in m.state_dict().items() if k.startswith("field_net.")})
+    w["rff_B"] = m.coordinate_embedding.B.detach().cpu()
+    t0 = time.perf_counter()
+    ref = so.predict_future(w, x.unsqueeze(1), edges[:3].transpose(0, 1), 3, D, K, False, return_everything=False)
+    cpu_ms_per_step = (time.perf_counter() - t0) * 1e3 / 3
+    err = float((traj[:3].transpose(0, 1).cpu() - ref).abs().max() / ref.abs().max())
+    return {"workload": "seq2seq RecurrentDecoder rollout: 2D, 5 particles, batch 64, decoder_hidden 512, 2 edge types, "
+                        "%d prediction steps, one CUDA graph" % steps, "dtype": "f32", "ms_per_rollout": ms,
+            "us_per_step": 1e3 * ms / steps, "particle_steps_per_s": B * N * steps / (ms * 1e-3),
+            "launches_per_rollout": r.launches_per_replay, "rel_err_vs_oracle_3_steps": err,
+            "cpu_oracle_ms_per_step": cpu_ms_per_step, "cpu_threads": torch.get_num_threads()}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -863,6 +906,10 @@ def main():
                         line["gpu_eager_baseline"] = {"unavailable": repr(e)[:200]}
                     release_memory()
                     line["parity"] = parity_report(ctx.dev, args.precision)
+                    try:
+                        sec["seq2seq_rollout"] = seq2seq_report(ctx.dev)
+                    except Exception as e:
+                        sec["seq2seq_rollout"] = {"unavailable": repr(e)[:200]}
         if ctx.rank == 0:
             print(json.dumps(line), flush=True)
     finally:
