@@ -233,27 +233,41 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
     const int lda = T.lda, ldw = T.ldw;
     const bool avec = (lda % 4 == 0) && ((((uintptr_t)Ab) & 15) == 0);
     const bool wvec = (ldw % 4 == 0) && ((((uintptr_t)Wb) & 15) == 0);
+    // per-thread copy slots of a slab: chunk c = tid + 256 q covers (row c/4, k offset 4 (c%4)) of A, then of W
+    constexpr int NQ = (BM + BN) * 4 / GT;
+    const float* qsrc[NQ];
+    unsigned qdst[NQ];
+    int qlim[NQ];               // number of k's (from the slot's first one at slab 0) that may be read: 0 for rows outside
+    bool qvec[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      int c = q * GT + tid;
+      const bool isA = c < BM * 4;
+      if (!isA) c -= BM * 4;
+      const int row = c >> 2, kc = (c & 3) * 4;
+      const int grow = (isA ? m0 : n0) + row;
+      const bool rok = grow < (isA ? P.M : P.N);
+      const float* base = isA ? Ab : Wb;
+      qsrc[q] = rok ? base + (size_t)grow * (isA ? lda : ldw) + kc : base;
+      qdst[q] = (unsigned)__cvta_generic_to_shared(isA ? &As[0][row][kc] : &Ws[0][row][kc]);
+      qlim[q] = rok ? K - kc : 0;
+      qvec[q] = isA ? avec : wvec;
+    }
     auto issue = [&](int kt, int stage) {
 #pragma unroll
-      for (int c0 = 0; c0 < (BM + BN) * 4; c0 += GT) {
-        int c = c0 + tid;
-        const bool isA = c < BM * 4;
-        if (!isA) c -= BM * 4;
-        const int row = c >> 2, kc = (c & 3) * 4, k = kt * GK + kc;
-        const int grow = (isA ? m0 : n0) + row;
-        const bool rok = grow < (isA ? P.M : P.N);
-        const float* base = isA ? Ab : Wb;
-        const float* src = base + (size_t)grow * (isA ? lda : ldw) + k;
-        float* dst = isA ? &As[stage][row][kc] : &Ws[stage][row][kc];
-        if (isA ? avec : wvec) {
-          int nb = rok ? (K - k) * 4 : 0;
-          nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
-          cp_async16(dst, nb > 0 ? src : base, nb);
+      for (int q = 0; q < NQ; ++q) {
+        const int left = qlim[q] - kt * GK;                       // k's left from this chunk's first element
+        const unsigned dst = qdst[q] + (unsigned)stage * (unsigned)(((q * GT + tid) < BM * 4 ? BM : BN) * LD * 4);
+        if (qvec[q]) {
+          const int nb = left <= 0 ? 0 : (left >= 4 ? 16 : left * 4);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(nb > 0 ? qsrc[q] + kt * GK : qsrc[q]),
+                       "r"(nb));
         } else {
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const bool ok = rok && (k + e < K);
-            cp_async4(dst + e, ok ? src + e : base, ok);
+            const int nb = left > e ? 4 : 0;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(dst + 4 * e),
+                         "l"(nb > 0 ? qsrc[q] + kt * GK + e : qsrc[q]), "r"(nb));
           }
         }
       }
@@ -347,7 +361,7 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st) {
   }
   if (maxM == 0 || maxN == 0 || nprob == 0) return 0;
   const int64_t big = (int64_t)((maxM + 63) / 64) * ((maxN + 63) / 64) * nprob;
-  if (big >= 120) {
+  if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
     seq_gemm_kernel<64, 64><<<grid, GT, 0, st>>>(bt);
   } else {
