@@ -79,6 +79,7 @@ SIGNATURES = {
     "aether_part_forward_phase": (c_int, [POINTER(AetherDims), POINTER(c_void_p), POINTER(AetherGraphC), c_void_p, c_void_p,
                                           c_void_p, c_void_p, c_int64, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_void_p,
                                           c_size_t, c_uint32, c_void_p]),
+    "aether_peer_allgather": (c_int, [POINTER(c_void_p), c_int32, c_int32, c_size_t, c_size_t, c_size_t, c_void_p, c_void_p]),
     "aether_radius_graph_scratch_bytes": (c_size_t, [c_int64, c_int32, POINTER(c_int32)]),
     "aether_radius_graph_neighbors": (c_int, [c_void_p, c_int32, c_int32, c_int64, c_float, c_float, c_int32,
                                               POINTER(c_float), POINTER(c_int32), c_void_p, c_void_p, c_void_p, c_size_t,

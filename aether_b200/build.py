@@ -42,6 +42,7 @@ SOURCES = [
     ("edge_bf16.cu", []),
     ("prof.cu", []),
     ("optim.cu", []),
+    ("peer.cu", []),
     ("field.cu", []),
     ("dynfield.cu", []),
     ("geom.cu", ["-fmad=false"]),

@@ -3,8 +3,12 @@
 Rank r owns a contiguous block of nodes and every edge whose receiver it owns, so the segmented mean, the node
 MLPs and the output are local.  What crosses ranks is the sender term ``P_s = x W_s^T`` of the node-factorised
 first Linear of layers 2-4 (one all-gather of ``[Nn, H]`` per layer, bf16 on the bf16 path) and the new
-positions (one all-gather of ``[Nn, D]`` per step).  The collective is torch.distributed's (NCCL over NVLink);
-the compute between two exchanges is one C-ABI call (``aether_part_forward_phase``).
+positions (one all-gather of ``[Nn, D]`` per step).  The compute between two exchanges is one C-ABI call
+(``aether_part_forward_phase``).  The exchange is either torch.distributed's in-place all-gather (NCCL over NVLink,
+``exchange="nccl"``) or the library's own (``exchange="peer"``, csrc/peer.cu): the exchange buffers live in symmetric
+memory (``torch.distributed._symmetric_memory``: every rank maps every peer's copy), and one kernel per rank stores its
+block into all peers' copies over NVLink, raises a flag there and waits for the peers' flags -- no NCCL call on the
+data path.
 
 ``parts > 1`` with ``world == 1`` runs the partitions one after another on one GPU over a shared exchange
 buffer -- the same kernels and the same slicing, used by the single-GPU parity test.
@@ -54,7 +58,8 @@ class PartitionedRollout:
     ``run(x0, v0, charges)`` returns positions ``[steps, Nn, D]`` (identical on every rank)."""
 
     def __init__(self, model, send: torch.Tensor, recv: torch.Tensor, n_nodes: int, steps: int, world: int = 1,
-                 rank: int = 0, parts: Optional[int] = None, group=None, cuda_graph: bool = False):
+                 rank: int = 0, parts: Optional[int] = None, group=None, cuda_graph: bool = False,
+                 exchange: str = "nccl"):
         self.lib = _lib.load()
         self.model, self.steps, self.world, self.rank, self.group = model, int(steps), int(world), int(rank), group
         self.D, self.H, self.Nn = model.num_dims, model.hidden_size, int(n_nodes)
@@ -70,11 +75,17 @@ class PartitionedRollout:
         self.padded = self.local[0].part.padded_nodes
         xdtype = torch.bfloat16 if (self.flags & _lib.F_BF16 and self.H in (64, 128, 256)) else torch.float32
         f32 = dict(dtype=torch.float32, device=dev)
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        self.exchange = exchange if world > 1 else "nccl"
         # two exchange buffers: a phase gathers sender terms from one and writes the next layer's into the other
-        self.xchg = [torch.zeros(self.padded, self.H, dtype=xdtype, device=dev) for _ in range(2)]
+        if self.exchange == "peer":
+            self._alloc_symmetric(xdtype)
+        else:
+            self.xchg = [torch.zeros(self.padded, self.H, dtype=xdtype, device=dev) for _ in range(2)]
+            self.xbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]   # positions ping-pong (gathered)
         self.xin = torch.zeros(self.padded, self.D, **f32)                          # static inputs of a run
         self.vin = torch.zeros(self.padded, self.D, **f32)
-        self.xbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]   # positions ping-pong (gathered)
         self.vbuf = [torch.zeros(self.padded, self.D, **f32) for _ in range(2)]
         self.q = torch.zeros(self.padded, **f32)
         self.traj = torch.empty(self.steps, self.Nn, self.D, **f32)
@@ -86,10 +97,59 @@ class PartitionedRollout:
         # in our 8-GPU run.
         self._use_graph, self._g, self.launches_per_replay = bool(cuda_graph), None, 0
 
+    def _alloc_symmetric(self, xdtype):
+        """Exchange buffers + flag row in ONE symmetric allocation; peer base pointers for aether_peer_allgather."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        dev = self.dev
+        group = self.group if self.group is not None else dist.group.WORLD
+        al = lambda n: (n + 255) // 256 * 256
+        xb = al(self.padded * self.H * (2 if xdtype == torch.bfloat16 else 4))
+        pb = al(self.padded * self.D * 4)
+        self._off = {"xchg0": 0, "xchg1": xb, "xbuf0": 2 * xb, "xbuf1": 2 * xb + pb, "flags": 2 * xb + 2 * pb}
+        total = self._off["flags"] + 256
+        self._symm = symm_mem.empty(total, dtype=torch.uint8, device=dev)
+        self._symm.zero_()
+        try:
+            hdl = symm_mem.rendezvous(self._symm, group)
+        except TypeError:
+            hdl = symm_mem.rendezvous(self._symm, group.group_name)
+        self._symm_hdl = hdl
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        if len(ptrs) != self.world or ptrs[self.rank] != self._symm.data_ptr():
+            raise RuntimeError("aether_b200: symmetric memory rendezvous returned unexpected peer pointers")
+        self._peer_base = (ctypes.c_void_p * self.world)(*ptrs)
+
+        def view(name, dtype, cols):
+            o = self._off[name]
+            n = self.padded * cols * (2 if dtype == torch.bfloat16 else 4)
+            return self._symm[o:o + n].view(dtype).view(self.padded, cols)
+
+        self.xchg = [view("xchg0", xdtype, self.H), view("xchg1", xdtype, self.H)]
+        self.xbuf = [view("xbuf0", torch.float32, self.D), view("xbuf1", torch.float32, self.D)]
+        self._peer_state = torch.zeros(4, dtype=torch.int32, device=dev)
+        self._name_of = {self.xchg[0].data_ptr(): "xchg0", self.xchg[1].data_ptr(): "xchg1",
+                         self.xbuf[0].data_ptr(): "xbuf0", self.xbuf[1].data_ptr(): "xbuf1"}
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=self.group)          # every copy and flag row is zero before anybody pushes
+
+    def peer_error(self) -> bool:
+        """True when a wait of the peer exchange gave up (a rank never arrived); synchronises."""
+        return self.exchange == "peer" and bool(int(self._peer_state[2].item()))
+
     def _gather(self, buf: torch.Tensor):
-        if self.world > 1:
+        if self.world <= 1:
+            return
+        if self.exchange == "peer":
+            block = self.local[0].part.block
+            row_bytes = buf.shape[1] * buf.element_size()
+            _lib.check(self.lib.aether_peer_allgather(self._peer_base, self.world, self.rank,
+                                                      self._off[self._name_of[buf.data_ptr()]], block * row_bytes,
+                                                      self._off["flags"], _lib.ptr(self._peer_state), _stream()),
+                       "aether_peer_allgather")
+        else:
             self.local[0].part.all_gather_rows(buf, self.group)
-            self.launch_exchanges += 1
+        self.launch_exchanges += 1
 
     def _step(self, x, v, xn, vn):
         lib = self.lib

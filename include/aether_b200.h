@@ -194,6 +194,19 @@ int aether_part_forward_phase(const AetherDims* dims, const float* const* params
                               float* out,
                               void* workspace, size_t workspace_bytes, uint32_t flags, void* stream);
 
+/* The exchange between two phases without NCCL (csrc/peer.cu; SURVEY.md 8e "producer writes its shard directly into
+ * peers' buffers over NVLink"; the reference is single-device and has no collective to replace).  Every rank holds the
+ * same symmetric allocation; peer_base[r] (HOST array of `world` device pointers) is rank r's copy as mapped into this
+ * process.  The buffer at buf_offset is `world` blocks of block_bytes; this rank has written block `rank` of its own
+ * copy.  One launch stores that block into every peer's copy, raises flags[rank] = epoch in every peer's flag row
+ * (world uint32 at flags_offset of the allocation, zero before the first call) and waits until its own row shows the
+ * epoch from every peer -- the usual in-place all-gather, done by the producers.  state: 4 uint32 of LOCAL device
+ * memory, zero before the first call ([0] epoch, [1] internal, [2] != 0 after a wait that gave up because a peer never
+ * arrived).  All ranks must issue the same sequence of calls.  Offsets and sizes are multiples of 4 (16 for vector
+ * stores); world <= 16. */
+int aether_peer_allgather(void* const* peer_base, int32_t world, int32_t rank, size_t buf_offset, size_t block_bytes,
+                          size_t flags_offset, uint32_t* state, void* stream);
+
 /* One harness-level rollout step: edge_attr = [q_i q_j, |x_i - x_j|] over the ORIGINAL
  * edge list (send64/recv64, experiments/lorentz/main.py:243-246), x_next = step(x, vel),
  * vel_next = x_next - x.  x_next/vel_next must not alias x/vel. */
