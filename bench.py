@@ -264,8 +264,18 @@ def run_c5(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True):
     # 9.5 vs 10.4 ms per 5-step rollout eager; H = 64: 3.95 vs 4.85 ms; profiles/r02_c5_8gpu.md).  The captured graphs are
     # released before the communicator is torn down (roll.release() below); --no-graph launches eagerly.
     use_graph = not args.no_graph
-    roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, cuda_graph=use_graph)
-    eager = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank) if use_graph else roll
+    # The exchange between phases is the library's own (csrc/peer.cu: stores into the peers' symmetric-memory copies,
+    # flags, no NCCL call on the data path); AETHER_B200_EXCHANGE=nccl selects torch.distributed's all-gather.
+    exchange = os.environ.get("AETHER_B200_EXCHANGE", "peer") if world > 1 else "nccl"
+    try:
+        roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, cuda_graph=use_graph, exchange=exchange)
+    except Exception as e:                       # no symmetric memory on this box: say so and use NCCL
+        if exchange != "peer":
+            raise
+        print("bench: peer-memory exchange unavailable (%r), using NCCL all-gathers" % (e,), file=sys.stderr, flush=True)
+        exchange = "nccl"
+        roll = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, cuda_graph=use_graph)
+    eager = ab.PartitionedRollout(model, send, recv, n, T, world=world, rank=rank, exchange=exchange) if use_graph else roll
 
     def step_resident():
         roll.run(xd, vd, qd)
@@ -326,6 +336,8 @@ def run_c5(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True):
         e2e = 4.0 * E * T * steps / e2e_total
     # captured graphs (and the communicator work they hold) are dropped before anything else uses the communicator
     roll.release()
+    if roll.peer_error() or eager.peer_error():
+        raise RuntimeError("bench: a wait of the peer-memory exchange gave up (a rank did not arrive)")
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -349,6 +361,8 @@ def run_c5(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True):
                        "l2": "working set exceeds L2" if E * H * 2 * 2 > 126e6 * world else "flushed: no (L2-resident edge state)"},
             "particle_steps_per_sec": n * T * steps / total, "gpu_launches": int(launches), "clocks": clocks,
             "collectives_per_step": 4 * T if world > 1 else 0,
+            "exchange": ("peer-memory stores + flags (csrc/peer.cu), no NCCL on the data path" if exchange == "peer"
+                         else "NCCL all-gather") if world > 1 else None,
             "roofline": {"bound": "tensor", "kernel": "edge-MLP forward (message_fn, per layer, rank 0's edges)",
                          "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                          "traffic": None, "peak_source": pk_src + " bf16 sustained",
@@ -694,7 +708,7 @@ def brief(line):
     if line is None:
         return None
     keep = ("value", "unit", "ms_per_step", "n_gpus", "steps", "scaling", "gpu_launches", "collectives_per_step",
-            "particle_steps_per_sec")
+            "particle_steps_per_sec", "exchange")
     out = {k: line[k] for k in keep if k in line}
     c = line["config"]
     out["config"] = {k: c[k] for k in ("workload", "hidden", "graphs_per_gpu", "edges_per_gpu", "particles", "edges",
