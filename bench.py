@@ -418,7 +418,7 @@ def run_reference(args, cfg, H):
             "cpu_baseline": {"value": val, "unit": "edge-messages/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "edge-messages/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_dp(args, cfg, H, ctx, steps, warmup, do_e2e=True, do_cpu=True, scaling="weak"):
@@ -863,7 +863,18 @@ def seq2seq_report(dev, steps=20, reps=10):
             "cpu_oracle_ms_per_step": cpu_ms_per_step, "cpu_threads": torch.get_num_threads()}
 
 
+_REAL_STDOUT = sys.stdout
+
+
+def emit(line):
+    """The ONE JSON line of the contract goes to the real stdout; everything else a run prints (the modules mirror the
+    reference's constructor, which prints "Network Size N", nn/state2state/aether.py:163-167) goes to stderr."""
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def main():
+    sys.stdout = sys.stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -925,7 +936,7 @@ def main():
                     except Exception as e:
                         sec["seq2seq_rollout"] = {"unavailable": repr(e)[:200]}
         if ctx.rank == 0:
-            print(json.dumps(line), flush=True)
+            emit(line)
     finally:
         ctx.close()
 
