@@ -194,3 +194,84 @@ def predict_future(w: Dict[str, Tensor], inputs: Tensor, edges: Tensor, predicti
         p, hidden = decoder_step(w, p, hidden, edges[:, T - 1 + t], f, D, n_types, skip_first)
         out.append(p)
     return torch.stack(out, 1)
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# Edge-type encoder, prior branch (nn/seq2seq/aether.py:249-438): what predict_future needs of it
+# --------------------------------------------------------------------------------------------------------------------
+def _bn_eval(w: Dict[str, Tensor], name: str, x: Tensor) -> Tensor:
+    """nn.BatchNorm1d in eval mode on the flattened rows (nn/utils/model_utils.py:41-45)."""
+    return torch.nn.functional.batch_norm(x.reshape(-1, x.shape[-1]), w[name + ".running_mean"], w[name + ".running_var"],
+                                          w[name + ".weight"], w[name + ".bias"], False, 0.0, 1e-5).view(x.shape)
+
+
+def _nri_mlp(w: Dict[str, Tensor], name: str, x: Tensor) -> Tensor:
+    """RefNRIMLP.forward, dropout inactive (nn/utils/model_utils.py:15-54)."""
+    x = torch.nn.functional.elu(_lin(w, name + ".model.0", x))
+    x = torch.nn.functional.elu(_lin(w, name + ".model.3", x))
+    return _bn_eval(w, name + ".bn", x) if (name + ".bn.weight") in w else x
+
+
+def _fc_out(w: Dict[str, Tensor], name: str, x: Tensor) -> Tensor:
+    """prior_fc_out: one Linear, or Linear/ELU pairs and a last Linear (nn/seq2seq/aether.py:289-299)."""
+    if (name + ".weight") in w:
+        return _lin(w, name, x)
+    idx = sorted(int(k.split(".")[-2]) for k in w if k.startswith(name + ".") and k.endswith(".weight"))
+    for i in idx[:-1]:
+        x = torch.nn.functional.elu(_lin(w, "%s.%d" % (name, i), x))
+    return _lin(w, "%s.%d" % (name, idx[-1]), x)
+
+
+def encoder_embed(w: Dict[str, Tensor], states: Tensor, field: Tensor, D: int, pos_representation: str) -> Tensor:
+    """The per-timestep part of Encoder.forward / single_step_forward (nn/seq2seq/aether.py:364-381, 400-413):
+    states[B,N,2D], field[B,N,D] -> edge embeddings [B, N(N-1), hidden]."""
+    B, N, _ = states.shape
+    send, recv = fc_edges_sender_major(N)
+    F = 4 * D + D * (D - 1) // 2
+    rel_feat, _, edge_attr = augmented_localizer(torch.cat([states, field], -1), D)
+    pos_idx = {(2, "cart"): [0, 1, 2], (2, "polar"): [2, 3, 4], (3, "cart"): [0, 1, 2, 3, 4, 5],
+               (3, "polar"): [3, 4, 5, 6, 7, 8]}[(D, pos_representation)]      # augmented_global_to_local.py:18-24
+    edge_pos = edge_attr[..., pos_idx]
+    # AnisotropicEdgeFilter (nn/nn/anisotropic_filter.py:35-41): a per-edge [Fin, H] matrix from the positions
+    a = torch.nn.functional.elu(_lin(w, "edge_filter.edge_filter.0", edge_pos))
+    ew = _lin(w, "edge_filter.edge_filter.2", a)
+    Fin = edge_attr.shape[-1]
+    ew = ew.reshape(ew.shape[:-1] + (Fin, ew.shape[-1] // Fin))
+    filt = (edge_attr.unsqueeze(-2) @ ew).squeeze(-2)
+    res_x = _lin(w, "res1", rel_feat)
+    incoming = torch.zeros(B, N, filt.shape[-1], dtype=filt.dtype).index_add_(1, recv, filt) / (N - 1)   # edge2node :351-360
+    x = _nri_mlp(w, "mlp3", incoming + res_x)
+    x = torch.cat([x[:, send], x[:, recv], filt], -1)                                                    # node2edge :344-349
+    return _nri_mlp(w, "mlp4", x)
+
+
+def lstm_cell(w: Dict[str, Tensor], name: str, x: Tensor, h: Tensor, c: Tensor):
+    """One step of nn.LSTM (gate order i, f, g, o)."""
+    g = x @ w[name + ".weight_ih_l0"].t() + w[name + ".bias_ih_l0"] + h @ w[name + ".weight_hh_l0"].t() + w[name + ".bias_hh_l0"]
+    i, f, gg, o = g.chunk(4, -1)
+    c = torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(gg)
+    return torch.sigmoid(o) * torch.tanh(c), c
+
+
+def encoder_step(w: Dict[str, Tensor], states: Tensor, field: Tensor, h: Tensor, c: Tensor, D: int,
+                 pos_representation: str):
+    """Encoder.single_step_forward (nn/seq2seq/aether.py:397-425): prior logits [B, N(N-1), types] and the new LSTM state
+    (h, c: [B*N(N-1), rnn_hidden])."""
+    x = encoder_embed(w, states, field, D, pos_representation)
+    B, E, H = x.shape
+    h, c = lstm_cell(w, "forward_rnn", x.reshape(B * E, H), h, c)
+    return _fc_out(w, "prior_fc_out", h).view(B, E, -1), h, c
+
+
+def encoder_prior(w: Dict[str, Tensor], inputs: Tensor, D: int, pos_representation: str):
+    """The prior branch of Encoder.forward over a burn-in sequence (nn/seq2seq/aether.py:362-395): inputs[B,T,N,2D] ->
+    prior logits [B,T,N(N-1),types] and the final LSTM state.  The field at every step is the field predictor's."""
+    B, T, N, _ = inputs.shape
+    R = w["forward_rnn.weight_hh_l0"].shape[1]
+    h = torch.zeros(B * N * (N - 1), R, dtype=inputs.dtype)
+    c = torch.zeros_like(h)
+    out = []
+    for t in range(T):
+        lg, h, c = encoder_step(w, inputs[:, t], predict_field(w, inputs[:, t], D), h, c, D, pos_representation)
+        out.append(lg)
+    return torch.stack(out, 1), h, c

@@ -27,7 +27,7 @@ sys.path.insert(0, HERE)
 import make_golden as mg  # noqa: E402
 
 
-def params_dict(D, N, n_hid, enc_hid, n_types, skip_first):
+def params_dict(D, N, n_hid, enc_hid, n_types, skip_first, pos_rep="polar"):
     return {
         "num_vars": N, "input_size": 2 * D, "gpu": False, "use_3d": D == 3,
         "decoder_hidden": n_hid, "num_edge_types": n_types, "skip_first": skip_first, "decoder_dropout": 0.0,
@@ -36,7 +36,7 @@ def params_dict(D, N, n_hid, enc_hid, n_types, skip_first):
         "encoder_mlp_num_layers": 3, "encoder_mlp_hidden": 16, "prior_num_layers": 3, "prior_hidden_size": 16,
         "gumbel_temp": 0.5, "train_hard_sample": False, "teacher_forcing_steps": -1, "normalize_kl": True,
         "normalize_nll": True, "kl_coef": 1.0, "nll_loss_type": "gaussian", "prior_variance": 5e-5,
-        "add_uniform_prior": True, "no_edge_prior": 0.5, "rff_std": 1.0, "pos_representation": "polar",
+        "add_uniform_prior": True, "no_edge_prior": 0.5, "rff_std": 1.0, "pos_representation": pos_rep,
     }
 
 
@@ -49,20 +49,32 @@ def synth_states(B, N, D, gen, zero_vel_first=False):
     return torch.cat([pos, vel], -1)
 
 
-def run_case(name, D, N, B, n_hid, n_types, skip_first, seed, zero_vel_first=False, burn_in=4, pred_steps=3):
+def run_case(name, D, N, B, n_hid, n_types, skip_first, seed, zero_vel_first=False, burn_in=4, pred_steps=3,
+             pos_rep="polar"):
     from nn.seq2seq.aether import Aether
     torch.manual_seed(seed)
     np.random.seed(seed)
-    p = params_dict(D, N, n_hid, 16, n_types, skip_first)
+    p = params_dict(D, N, n_hid, 16, n_types, skip_first, pos_rep)
     model = Aether(p)
     model.eval()
     dec = model.decoder
+    bn_gen = torch.Generator().manual_seed(seed + 50)
+    for m in model.encoder.modules():        # fresh BatchNorm statistics are (0, 1): give them values so that the
+        if isinstance(m, torch.nn.BatchNorm1d):   # recorded eval-mode outputs depend on them (state only, no code changed)
+            m.running_mean.copy_(0.2 * torch.randn(m.num_features, generator=bn_gen))
+            m.running_var.copy_(0.5 + torch.rand(m.num_features, generator=bn_gen))
+            m.weight.data.copy_(1.0 + 0.1 * torch.randn(m.num_features, generator=bn_gen))
+            m.bias.data.copy_(0.1 * torch.randn(m.num_features, generator=bn_gen))
     gen = torch.Generator().manual_seed(seed + 100)
     out = {"D": D, "N": N, "B": B, "n_hid": n_hid, "n_types": n_types, "skip_first": int(skip_first), "seed": seed}
     for k, v in dec.state_dict().items():
         out["dec." + k] = v.clone()
     for k, v in model.field_net.state_dict().items():
         out["field_net." + k] = v.clone()
+    for k, v in model.encoder.state_dict().items():
+        out["enc." + k] = v.clone()
+    out["enc_pos_representation"] = p["pos_representation"]
+    out["enc_rnn_hidden"], out["enc_mlp_hidden"], out["enc_prior_hidden"] = 16, 16, 16
     out["rff_B"] = model.coordinate_embedding.B.clone()
 
     # --- one decoder step with soft edge weights -----------------------------------------------
@@ -87,6 +99,14 @@ def run_case(name, D, N, B, n_hid, n_types, skip_first, seed, zero_vel_first=Fal
         nxt[..., :D] = prev[..., :D] + 0.1 * prev[..., D:]
         traj.append(nxt)
     burn = torch.stack(traj, 1)    # [B, T, N, 2D]
+    with torch.no_grad():          # the encoder alone: burn-in pass (prior logits + LSTM state) and one more step
+        x_t = burn[:, :-1].transpose(2, 1).contiguous()
+        pfield, _ = model.predict_field(x_t)
+        prior_logits, _, prior_state = model.encoder(burn[:, :-1], pfield)
+        f_last, _ = model.predict_field(burn[:, -1])
+        step_logits, step_state = model.encoder.single_step_forward(burn[:, -1], prior_state, f_last)
+    out.update(enc_prior_logits=prior_logits, enc_state_h=prior_state[0], enc_state_c=prior_state[1],
+               enc_step_logits=step_logits, enc_step_state_h=step_state[0], enc_step_state_c=step_state[1])
     torch.manual_seed(seed + 7)    # the gumbel noise
     with torch.no_grad():
         preds, all_edges = model.predict_future(burn, pred_steps, return_edges=True, return_everything=True)
@@ -99,7 +119,7 @@ def main():
     mg._install_shims()
     torch.Tensor.cuda = lambda self, *a, **k: self   # see the module docstring
     run_case("seq2seq2d_h32", D=2, N=5, B=4, n_hid=32, n_types=2, skip_first=False, seed=1, zero_vel_first=True)
-    run_case("seq2seq3d_h64", D=3, N=5, B=3, n_hid=64, n_types=3, skip_first=True, seed=2)
+    run_case("seq2seq3d_h64", D=3, N=5, B=3, n_hid=64, n_types=3, skip_first=True, seed=2, pos_rep="cart")
     run_case("seq2seq2d_h48_n3", D=2, N=3, B=2, n_hid=48, n_types=2, skip_first=True, seed=3, burn_in=3, pred_steps=5)
 
 

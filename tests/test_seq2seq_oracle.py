@@ -41,3 +41,20 @@ def test_oracle_matches_reference(path):
     pf = so.predict_future(w, t("pf_inputs"), t("pf_edges"), int(g["pf_steps"]), D, K, skip)
     assert pf.shape == t("pf_predictions").shape
     assert (pf - t("pf_predictions")).abs().max() <= 1e-5
+
+
+@pytest.mark.parametrize("path", CASES, ids=[os.path.basename(p)[:-4] for p in CASES])
+def test_encoder_oracle_matches_reference(path):
+    """Prior branch of the reference Encoder (BatchNorm with non-trivial running statistics, LSTM over the burn-in,
+    then one single_step_forward)."""
+    g, w = load(path)
+    w.update({k[4:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("enc.")})
+    D, rep = int(g["D"]), str(g["enc_pos_representation"])
+    t = lambda k: torch.from_numpy(g[k])
+    burn = t("pf_inputs")
+    logits, h, c = so.encoder_prior(w, burn[:, :-1], D, rep)
+    assert (logits - t("enc_prior_logits")).abs().max() <= 2e-6
+    assert (h - t("enc_state_h")[0]).abs().max() <= 2e-6 and (c - t("enc_state_c")[0]).abs().max() <= 2e-6
+    lg, h2, c2 = so.encoder_step(w, burn[:, -1], so.predict_field(w, burn[:, -1], D), h, c, D, rep)
+    assert (lg - t("enc_step_logits")).abs().max() <= 2e-6
+    assert (h2 - t("enc_step_state_h")[0]).abs().max() <= 2e-6 and (c2 - t("enc_step_state_c")[0]).abs().max() <= 2e-6
