@@ -33,7 +33,17 @@ SEQ_MAX_TYPES = 4
 
 class AetherSeqDims(ctypes.Structure):
     _fields_ = [("num_dims", c_int32), ("num_vars", c_int32), ("hidden", c_int32), ("n_types", c_int32),
-                ("skip_first", c_int32), ("field_hidden", c_int32), ("batch", c_int64)]
+                ("skip_first", c_int32), ("field_hidden", c_int32), ("rnn_hidden", c_int32), ("prior_hidden", c_int32),
+                ("batch", c_int64)]
+
+
+class AetherSeqEncParams(ctypes.Structure):
+    _fields_ = [("filter_w0", c_void_p), ("filter_b0", c_void_p), ("filter_w2", c_void_p), ("filter_b2", c_void_p),
+                ("res1_w", c_void_p), ("res1_b", c_void_p), ("mlp3_w", c_void_p * 2), ("mlp3_b", c_void_p * 2),
+                ("mlp3_bn_scale", c_void_p), ("mlp3_bn_shift", c_void_p), ("mlp4_w", c_void_p * 2), ("mlp4_b", c_void_p * 2),
+                ("mlp4_bn_scale", c_void_p), ("mlp4_bn_shift", c_void_p), ("lstm_w_ih", c_void_p), ("lstm_w_hh", c_void_p),
+                ("lstm_b_ih", c_void_p), ("lstm_b_hh", c_void_p), ("prior_w", c_void_p * 4), ("prior_b", c_void_p * 4),
+                ("n_prior_layers", c_int32), ("pos_offset", c_int32)]
 
 
 class AetherSeqParams(ctypes.Structure):
@@ -101,6 +111,8 @@ SIGNATURES = {
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "aether_seq_rollout_step": (c_int, [POINTER(AetherSeqDims), POINTER(AetherSeqParams), c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "aether_seq_encoder_step": (c_int, [POINTER(AetherSeqDims), POINTER(AetherSeqEncParams), c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "aether_seq_localizer": (c_int, [POINTER(AetherSeqDims), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_adamw_step": (c_int, [c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
                                   POINTER(c_int64), c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,

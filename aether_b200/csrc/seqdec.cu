@@ -163,15 +163,19 @@ __global__ void seq_geom_kernel(const float* __restrict__ states, const float* _
 // multi-problem, multi-term fp32 GEMM
 // ------------------------------------------------------------------------------------------------
 constexpr int GK = 16, GT = 256, GPAD = 4, GS = 4;
-constexpr int MAX_TERMS = 4, MAX_PROB = 12;
-enum SeqAct { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2, ACT_SIGMOID = 3, ACT_SILU = 4 };
+constexpr int MAX_TERMS = 4, MAX_PROB = 9;     // sizeof(Batch) stays under the 4 KB of kernel parameters
+enum SeqAct { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2, ACT_SIGMOID = 3, ACT_SILU = 4, ACT_ELU = 5 };
 
 struct Term {
   const float* A;       // [M, K], leading dimension lda
   const float* W;       // [N, K], leading dimension ldw (nn.Linear weight)
   const float* bias;    // [N] or null
   const float* scale;   // per-row factor scale[m * scale_ld] applied after the activation, or null
+  const float* colscale;  // per-column affine after the activation (BatchNorm in eval mode): v * colscale[n] + colshift[n]
+  const float* colshift;
   int lda, ldw, K, act, flush, scale_ld;
+  int repeat;           // > 1: the term stands for `repeat` terms r = 0..repeat-1 with W + r * w_rep, bias + r * b_rep,
+  int w_rep, b_rep;     //      scale + r (the anisotropic edge filter: one [out, K] weight block per input feature)
 };
 struct Problem {
   Term t[MAX_TERMS];
@@ -186,6 +190,7 @@ __device__ __forceinline__ float act_f(float v, int act) {
     case ACT_RELU: return fmaxf(v, 0.f);
     case ACT_SIGMOID: return 1.0f / (1.0f + expf(-v));
     case ACT_SILU: return v / (1.0f + expf(-v));
+    case ACT_ELU: return v > 0.f ? v : expm1f(v);
     default: return v;
   }
 }
@@ -225,11 +230,14 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
 #pragma unroll
     for (int j = 0; j < TN; ++j) { sum[i][j] = 0.f; acc[i][j] = 0.f; }
 
-  for (int t = 0; t < P.nterms; ++t) {
+  for (int t = 0; t < P.nterms; ++t)
+  for (int rep = 0; rep < (P.t[t].repeat > 1 ? P.t[t].repeat : 1); ++rep) {
     const Term& T = P.t[t];
     const int K = T.K;
     const float* Ab = T.A;
-    const float* Wb = T.W;
+    const float* Wb = T.W + (size_t)rep * T.w_rep;
+    const float* biasp = T.bias ? T.bias + (size_t)rep * T.b_rep : nullptr;
+    const float* scalep = T.scale ? T.scale + rep : nullptr;
     const int lda = T.lda, ldw = T.ldw;
     const bool avec = (lda % 4 == 0) && ((((uintptr_t)Ab) & 15) == 0);
     const bool wvec = (ldw % 4 == 0) && ((((uintptr_t)Wb) & 15) == 0);
@@ -317,15 +325,16 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
     for (int i = 0; i < TM; ++i) {
       const int m = m0 + ty + 16 * i;
       float sc = 1.0f;
-      if (T.flush && T.scale != nullptr && m < P.M) sc = T.scale[(size_t)m * T.scale_ld];
+      if (T.flush && scalep != nullptr && m < P.M) sc = scalep[(size_t)m * T.scale_ld];
 #pragma unroll
       for (int j = 0; j < TN; ++j) {
         const int n = n0 + tx + 16 * j;
         float v = acc[i][j];
-        if (T.bias != nullptr && n < P.N) v = v + T.bias[n];
+        if (biasp != nullptr && n < P.N) v = v + biasp[n];
         if (T.flush) {
           v = act_f(v, T.act);
-          if (T.scale != nullptr) v = v * sc;
+          if (T.colscale != nullptr && n < P.N) v = v * T.colscale[n] + T.colshift[n];
+          if (scalep != nullptr) v = v * sc;
           sum[i][j] = sum[i][j] + v;
           v = 0.f;
         }
@@ -350,6 +359,7 @@ Term make_term(const float* A, int lda, const float* W, int ldw, const float* bi
   Term t;
   t.A = A; t.W = W; t.bias = bias; t.scale = scale;
   t.lda = lda; t.ldw = ldw; t.K = K; t.act = act; t.flush = flush; t.scale_ld = scale_ld;
+  t.colscale = nullptr; t.colshift = nullptr; t.repeat = 1; t.w_rep = 0; t.b_rep = 0;
   return t;
 }
 
@@ -398,12 +408,14 @@ __global__ void seq_pair_tanh_kernel(const float* __restrict__ P, int ldp, int N
 
 // agg[which][b*N+j, :] = sum over senders i != j (ascending edge id) of msgs[which][b*E + e(i,j), :] / (N-1)
 // (torch_scatter.scatter(reduce='mean') by receiver, ":616, :634")
+// msgs1 == nullptr: one source only; add0 (optional, [B*N, H]) is added to agg0 after the division (the encoder's
+// edge2node(...) + res_x, nn/seq2seq/aether.py:378).
 __global__ void seq_mean_kernel(const float* __restrict__ msgs0, const float* __restrict__ msgs1, int N, int64_t B, int H,
-                                float* __restrict__ agg0, float* __restrict__ agg1) {
+                                float* __restrict__ agg0, float* __restrict__ agg1, const float* __restrict__ add0) {
   const int H4 = H / 4;
   const int64_t per = B * N * H4;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= 2 * per) return;
+  if (idx >= (msgs1 != nullptr ? 2 : 1) * per) return;
   const int which = idx >= per;
   const int64_t r = idx - (which ? per : 0);
   const int h4 = (int)(r % H4);
@@ -421,6 +433,10 @@ __global__ void seq_mean_kernel(const float* __restrict__ msgs0, const float* __
   }
   const float cnt = (float)(N - 1);
   s.x /= cnt; s.y /= cnt; s.z /= cnt; s.w /= cnt;
+  if (!which && add0 != nullptr) {
+    const float4 a = *reinterpret_cast<const float4*>(add0 + (size_t)node * H + h4 * 4);
+    s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
+  }
   *reinterpret_cast<float4*>((which ? agg1 : agg0) + (size_t)node * H + h4 * 4) = s;
 }
 
@@ -486,11 +502,49 @@ __global__ void seq_rff_kernel(const float* __restrict__ states, int sd, int D, 
   out[(size_t)row * 2 * half + half + c] = cosf(p);
 }
 
+// encoder, first Linear of mlp4 on cat[x_send, x_recv, filt] (nn/seq2seq/aether.py:379-381), node-factorised:
+// out[b*E+e, :] = elu(Pn[b*N+send, 0:H] + Pn[b*N+recv, H:2H] + Pe[b*E+e, :])   (Pe carries the bias)
+__global__ void seq_enc_pair_kernel(const float* __restrict__ Pn, const float* __restrict__ Pe, int N, int64_t BE, int H,
+                                    float* __restrict__ out) {
+  const int H4 = H / 4;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= BE * H4) return;
+  const int k4 = (int)(idx % H4);
+  const int64_t m = idx / H4;
+  const int E = N * (N - 1);
+  const int64_t b = m / E;
+  const int e = (int)(m - b * E);
+  const int send = e / (N - 1), q = e - send * (N - 1), recv = q + (q >= send ? 1 : 0);
+  const float4 s = *reinterpret_cast<const float4*>(Pn + (size_t)(b * N + send) * 2 * H + k4 * 4);
+  const float4 r = *reinterpret_cast<const float4*>(Pn + (size_t)(b * N + recv) * 2 * H + H + k4 * 4);
+  const float4 pe = *reinterpret_cast<const float4*>(Pe + (size_t)m * H + k4 * 4);
+  float4 o;
+  o.x = act_f(s.x + r.x + pe.x, ACT_ELU); o.y = act_f(s.y + r.y + pe.y, ACT_ELU);
+  o.z = act_f(s.z + r.z + pe.z, ACT_ELU); o.w = act_f(s.w + r.w + pe.w, ACT_ELU);
+  *reinterpret_cast<float4*>(out + (size_t)m * H + k4 * 4) = o;
+}
+
+// LSTM cell (nn.LSTM, gate order i, f, g, o): G[rows, 4R] holds W_ih x + b_ih + W_hh h + b_hh
+__global__ void seq_lstm_cell_kernel(const float* __restrict__ G, const float* c_in, float* h_out, float* c_out, int R,
+                                     int64_t rows) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * R) return;
+  const int64_t row = idx / R;
+  const int j = (int)(idx - row * R);
+  const float* g = G + (size_t)row * 4 * R;
+  const float gi = 1.0f / (1.0f + expf(-g[j])), gf = 1.0f / (1.0f + expf(-g[R + j]));
+  const float gg = tanhf(g[2 * R + j]), go = 1.0f / (1.0f + expf(-g[3 * R + j]));
+  const float c = gf * c_in[idx] + gi * gg;
+  c_out[idx] = c;
+  h_out[idx] = go * tanhf(c);
+}
+
 // ------------------------------------------------------------------------------------------------
 // workspace
 // ------------------------------------------------------------------------------------------------
 struct SeqWs {
   float *relx, *Rinv, *eattr, *P, *m1, *p1, *msgs, *pmsgs, *agg, *pagg, *gR, *gI, *gN, *gH, *o1, *o2, *f0, *f1, *f2, *field;
+  float *ea, *eres, *efilt, *exin, *et1, *ex3, *ePn, *ePe, *eh1, *eemb, *eG, *ep0, *ep1;   // encoder
   size_t bytes;
 };
 
@@ -502,6 +556,7 @@ int seq_check(const AetherSeqDims* d) {
   if (d->n_types < 1 || d->n_types > AETHER_SEQ_MAX_TYPES) return AETHER_E_UNSUPPORTED;
   if (d->skip_first != 0 && d->skip_first != 1) return AETHER_E_BADARG;
   if (d->field_hidden < 0 || d->field_hidden % 4 != 0) return AETHER_E_UNSUPPORTED;
+  if (d->rnn_hidden < 0 || d->prior_hidden < 0) return AETHER_E_BADARG;
   if (d->batch < 0) return AETHER_E_BADARG;
   const int64_t BE = d->batch * d->num_vars * (d->num_vars - 1);
   if (BE > (int64_t)1 << 30 || BE * d->hidden > ((int64_t)1 << 40)) return AETHER_E_TOO_LARGE;
@@ -539,6 +594,21 @@ SeqWs seq_layout(const AetherSeqDims* d, void* base) {
   w.f1 = take(BN * Hf);
   w.f2 = take(BN * Hf);
   w.field = take(BN * D);
+  const size_t R = (size_t)d->rnn_hidden, PH = (size_t)d->prior_hidden;
+  const size_t He = R > 0 ? (size_t)Hf : 0;       // the encoder's buffers exist when an LSTM width is given
+  w.ea = take(BE * He);
+  w.eres = take(BN * He);
+  w.efilt = take(BE * He);
+  w.exin = take(BN * He);
+  w.et1 = take(BN * He);
+  w.ex3 = take(BN * He);
+  w.ePn = take(BN * 2 * He);
+  w.ePe = take(BE * He);
+  w.eh1 = take(BE * He);
+  w.eemb = take(BE * He);
+  w.eG = take(BE * 4 * R);
+  w.ep0 = take(BE * PH);
+  w.ep1 = take(BE * PH);
   w.bytes = off;
   return w;
 }
@@ -603,6 +673,10 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   };
   // batch A: node terms of msg_fc1 (bias with the receiver half) and present_msg_fc1 per type
   for (int t = t0; t < Kt; ++t) {
+    if (np + 3 > MAX_PROB) {          // four active edge types: the batch goes out in two launches
+      AE_CHECK(launch_batch(bt, np, st));
+      np = 0;
+    }
     single(make_term(hidden_in, H, p->msg_fc1_w[t], 2 * H, p->msg_fc1_b[t], H, ACT_NONE, 1), w.P + (size_t)(2 * t) * H,
            ldp, (int)BN, H);
     single(make_term(hidden_in, H, p->msg_fc1_w[t] + H, 2 * H, nullptr, H, ACT_NONE, 1), w.P + (size_t)(2 * t + 1) * H,
@@ -636,7 +710,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   }
   {
     const int64_t total = 2 * BN * (H / 4);
-    seq_mean_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.msgs, w.pmsgs, N, d->batch, H, w.agg, w.pagg);
+    seq_mean_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.msgs, w.pmsgs, N, d->batch, H, w.agg, w.pagg, nullptr);
     AE_LAUNCH_CHECK();
   }
   // batch C: gate pre-activations
@@ -679,6 +753,99 @@ int seq_params_ok(const AetherSeqParams* p) {
     return AETHER_E_BADARG;
   for (int i = 0; i < 3; ++i)
     if (!p->out_w[i] || !p->out_b[i]) return AETHER_E_BADARG;
+  return 0;
+}
+
+int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float* states, const float* field,
+                const float* h_in, const float* c_in, float* logits, float* h_out, float* c_out, const SeqWs& w,
+                cudaStream_t st) {
+  const int D = d->num_dims, N = d->num_vars, H = d->field_hidden, R = d->rnn_hidden, PH = d->prior_hidden, Kt = d->n_types;
+  const int O = D * (D - 1) / 2, F = 4 * D + O, KE = 2 * F + 3 * D, KR = 3 * D + F, KP = D + O;
+  const int64_t BN = d->batch * N, BE = BN * (N - 1);
+  if (H < 4 || R < 1 || p->n_prior_layers < 1 || p->n_prior_layers > 4 || (p->n_prior_layers > 1 && PH < 1))
+    return AETHER_E_BADARG;
+  if (p->pos_offset < 0 || p->pos_offset + KP > F) return AETHER_E_BADARG;
+  if (!p->filter_w0 || !p->filter_b0 || !p->filter_w2 || !p->filter_b2 || !p->res1_w || !p->res1_b || !p->lstm_w_ih ||
+      !p->lstm_w_hh || !p->lstm_b_ih || !p->lstm_b_hh)
+    return AETHER_E_BADARG;
+  for (int i = 0; i < 2; ++i)
+    if (!p->mlp3_w[i] || !p->mlp3_b[i] || !p->mlp4_w[i] || !p->mlp4_b[i]) return AETHER_E_BADARG;
+  for (int i = 0; i < p->n_prior_layers; ++i)
+    if (!p->prior_w[i] || !p->prior_b[i]) return AETHER_E_BADARG;
+  if (BN == 0) return 0;
+
+  AE_CHECK(seq_geometry(d, states, field, w.relx, w.Rinv, w.eattr, st));
+  Batch bt;
+  int np = 0;
+  auto add = [&](const Term& t, float* C, int ldc, int64_t M, int Nc) -> Problem& {
+    Problem& q = bt.p[np++];
+    q.t[0] = t; q.C = C; q.ldc = ldc; q.M = (int)M; q.N = Nc; q.nterms = 1;
+    return q;
+  };
+  // filter generator's first Linear on the edge positions (a column range of edge_attr) and the residual Linear
+  add(make_term(w.eattr + p->pos_offset, KE, p->filter_w0, KP, p->filter_b0, KP, ACT_ELU, 1), w.ea, H, BE, H);
+  add(make_term(w.relx, KR, p->res1_w, KR, p->res1_b, KR, ACT_NONE, 1), w.eres, H, BN, H);
+  AE_CHECK(launch_batch(bt, np, st));
+  // anisotropic filter (nn/nn/anisotropic_filter.py:35-41): filt[e,:] = sum_f attr[e,f] (a[e,:] W2_f^T + b2_f), W2_f the
+  // f-th block of H rows of edge_filter.2 -- one repeated term, the [E, Fin*H] weight tensor is never formed
+  np = 0;
+  {
+    Term t = make_term(w.ea, H, p->filter_w2, H, p->filter_b2, H, ACT_NONE, 1, w.eattr, KE);
+    t.repeat = KE; t.w_rep = H * H; t.b_rep = H;
+    add(t, w.efilt, H, BE, H);
+  }
+  AE_CHECK(launch_batch(bt, np, st));
+  seq_mean_kernel<<<(int)ceil_div64(BN * (H / 4), 256), 256, 0, st>>>(w.efilt, nullptr, N, d->batch, H, w.exin, nullptr,
+                                                                     w.eres);
+  AE_LAUNCH_CHECK();
+  np = 0;
+  add(make_term(w.exin, H, p->mlp3_w[0], H, p->mlp3_b[0], H, ACT_ELU, 1), w.et1, H, BN, H);
+  AE_CHECK(launch_batch(bt, np, st));
+  np = 0;
+  {
+    Problem& q = add(make_term(w.et1, H, p->mlp3_w[1], H, p->mlp3_b[1], H, ACT_ELU, 1), w.ex3, H, BN, H);
+    q.t[0].colscale = p->mlp3_bn_scale; q.t[0].colshift = p->mlp3_bn_shift;
+  }
+  AE_CHECK(launch_batch(bt, np, st));
+  np = 0;   // mlp4's first Linear [H, 3H] on cat[x_send, x_recv, filt]: the two node parts per particle, the edge part per pair
+  add(make_term(w.ex3, H, p->mlp4_w[0], 3 * H, nullptr, H, ACT_NONE, 1), w.ePn, 2 * H, BN, H);
+  add(make_term(w.ex3, H, p->mlp4_w[0] + H, 3 * H, nullptr, H, ACT_NONE, 1), w.ePn + H, 2 * H, BN, H);
+  add(make_term(w.efilt, H, p->mlp4_w[0] + 2 * H, 3 * H, p->mlp4_b[0], H, ACT_NONE, 1), w.ePe, H, BE, H);
+  AE_CHECK(launch_batch(bt, np, st));
+  if (BE > 0) {
+    seq_enc_pair_kernel<<<(int)ceil_div64(BE * (H / 4), 256), 256, 0, st>>>(w.ePn, w.ePe, N, BE, H, w.eh1);
+    AE_LAUNCH_CHECK();
+  }
+  np = 0;
+  {
+    Problem& q = add(make_term(w.eh1, H, p->mlp4_w[1], H, p->mlp4_b[1], H, ACT_ELU, 1), w.eemb, H, BE, H);
+    q.t[0].colscale = p->mlp4_bn_scale; q.t[0].colshift = p->mlp4_bn_shift;
+  }
+  AE_CHECK(launch_batch(bt, np, st));
+  np = 0;   // LSTM gates
+  {
+    Problem& q = bt.p[np++];
+    q.t[0] = make_term(w.eemb, H, p->lstm_w_ih, H, p->lstm_b_ih, H, ACT_NONE, 0);
+    q.t[1] = make_term(h_in, R, p->lstm_w_hh, R, p->lstm_b_hh, R, ACT_NONE, 1);
+    q.C = w.eG; q.ldc = 4 * R; q.M = (int)BE; q.N = 4 * R; q.nterms = 2;
+  }
+  AE_CHECK(launch_batch(bt, np, st));
+  if (BE > 0) {
+    seq_lstm_cell_kernel<<<(int)ceil_div64(BE * R, 256), 256, 0, st>>>(w.eG, c_in, h_out, c_out, R, BE);
+    AE_LAUNCH_CHECK();
+  }
+  const float* cur = h_out;
+  int kin = R;
+  for (int i = 0; i < p->n_prior_layers; ++i) {
+    const bool last = i == p->n_prior_layers - 1;
+    float* dst = last ? logits : (i & 1 ? w.ep1 : w.ep0);
+    const int nout = last ? Kt : PH;
+    np = 0;
+    add(make_term(cur, kin, p->prior_w[i], kin, p->prior_b[i], kin, last ? ACT_NONE : ACT_ELU, 1), dst, nout, BE, nout);
+    AE_CHECK(launch_batch(bt, np, st));
+    cur = dst;
+    kin = nout;
+  }
   return 0;
 }
 
@@ -738,4 +905,14 @@ extern "C" int aether_seq_rollout_step(const AetherSeqDims* dims, const AetherSe
   float* field = field_out ? field_out : w.field;
   AE_CHECK(seq_field(dims, params, states, field, w, (cudaStream_t)stream));
   return seq_step(dims, params, states, hidden_in, edge_types, field, states_out, hidden_out, w, (cudaStream_t)stream);
+}
+
+extern "C" int aether_seq_encoder_step(const AetherSeqDims* dims, const AetherSeqEncParams* params, const float* states,
+                                       const float* field, const float* h_in, const float* c_in, float* logits,
+                                       float* h_out, float* c_out, void* workspace, size_t workspace_bytes, void* stream) {
+  SeqWs w;
+  AE_CHECK(seq_ws(dims, workspace, workspace_bytes, &w));
+  if (!params || !states || !field || !h_in || !c_in || !logits || !h_out || !c_out) return AETHER_E_BADARG;
+  if (dims->rnn_hidden < 1) return AETHER_E_BADARG;
+  return seq_encoder(dims, params, states, field, h_in, c_in, logits, h_out, c_out, w, (cudaStream_t)stream);
 }

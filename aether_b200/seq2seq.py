@@ -91,9 +91,9 @@ class RecurrentDecoder(nn.Module):
                 m.bias.data.fill_(0.1)
 
     # ---- C-ABI plumbing ----------------------------------------------------------------------------------------------
-    def dims(self, batch: int, field_hidden: int = 0) -> "_lib.AetherSeqDims":
+    def dims(self, batch: int, field_hidden: int = 0, rnn_hidden: int = 0, prior_hidden: int = 0) -> "_lib.AetherSeqDims":
         return _lib.AetherSeqDims(self.num_dims, self.num_vars, self.msg_out_shape, self.edge_types,
-                                  1 if self.skip_first_edge_type else 0, field_hidden, batch)
+                                  1 if self.skip_first_edge_type else 0, field_hidden, rnn_hidden, prior_hidden, batch)
 
     def c_params(self, field_net: Optional[nn.Module] = None, rff: Optional[torch.Tensor] = None):
         """(struct, tensors kept alive) for the library; every parameter must be a contiguous fp32 CUDA tensor."""
@@ -188,6 +188,188 @@ class RecurrentDecoder(nn.Module):
         return rel, Rinv, ea, ea[..., pos_idx]
 
 
+class RefNRIMLP(nn.Module):
+    """Parameter holder with the reference's names (nn/utils/model_utils.py:15-54)."""
+
+    def __init__(self, n_in, n_hid, n_out, do_prob=0.0, no_bn=False):
+        super().__init__()
+        self.model = nn.Sequential(nn.Linear(n_in, n_hid), nn.ELU(inplace=True), nn.Dropout(do_prob),
+                                   nn.Linear(n_hid, n_out), nn.ELU(inplace=True))
+        self.bn = None if no_bn else nn.BatchNorm1d(n_out)
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                nn.init.xavier_normal_(m.weight.data)
+                m.bias.data.fill_(0.1)
+
+    def bn_affine(self):
+        """BatchNorm1d in eval mode as (scale, shift)."""
+        if self.bn is None:
+            return None, None
+        scale = self.bn.weight.detach() / torch.sqrt(self.bn.running_var + self.bn.eps)
+        return scale.contiguous(), (self.bn.bias.detach() - self.bn.running_mean * scale).contiguous()
+
+
+class AnisotropicEdgeFilter(nn.Module):
+    """Parameter holder with the reference's names (nn/nn/anisotropic_filter.py:12-33)."""
+
+    def __init__(self, in_size, pos_size, hidden_size, out_size):
+        super().__init__()
+        self.num_relative_features, self.out_size = in_size, out_size
+        self.edge_filter = nn.Sequential(nn.Linear(pos_size, hidden_size), nn.ELU(),
+                                         nn.Linear(hidden_size, in_size * out_size))
+        nn.init.orthogonal_(self.edge_filter[0].weight, gain=nn.init.calculate_gain("relu"))
+        nn.init.orthogonal_(self.edge_filter[2].weight)
+
+
+class Encoder(nn.Module):
+    """Prior branch of the reference's edge-type encoder (nn/seq2seq/aether.py:249-425) on csrc/seqdec.cu: same
+    constructor (``params`` dict), submodule / parameter names and creation order (a reference ``encoder.*`` state_dict
+    loads strictly), ``forward(inputs, predicted_field)`` and ``single_step_forward(inputs, prior_state,
+    predicted_field)`` as ``predict_future`` calls them.  Eval mode only (BatchNorm uses its running statistics, dropout
+    is inactive).  The posterior branch (reverse LSTM + ``encoder_fc_out``, used by the training loss only) holds its
+    parameters but is not computed: ``forward`` returns ``None`` in its place."""
+
+    def __init__(self, params):
+        super().__init__()
+        num_vars = params["num_vars"]
+        self.num_vars = num_vars
+        self.num_edges = params["num_edge_types"]
+        dropout = params["encoder_dropout"]
+        hidden_size = params["encoder_hidden"]
+        rnn_hidden_size = params["encoder_rnn_hidden"]
+        if params.get("encoder_rnn_type", "lstm") != "lstm":
+            raise ValueError("aether_b200.seq2seq.Encoder: only encoder_rnn_type='lstm' is built")
+        inp_size = params["input_size"]
+        self.mlp3 = RefNRIMLP(hidden_size, hidden_size, hidden_size, dropout)
+        self.mlp4 = RefNRIMLP(hidden_size * 3, hidden_size, hidden_size, dropout)
+        if rnn_hidden_size is None:
+            rnn_hidden_size = hidden_size
+        self.forward_rnn = nn.LSTM(hidden_size, rnn_hidden_size, batch_first=True)
+        self.reverse_rnn = nn.LSTM(hidden_size, rnn_hidden_size, batch_first=True)
+
+        def head(n_in, num_layers, hid):
+            if num_layers == 1:
+                return nn.Linear(n_in, self.num_edges)
+            layers = [nn.Linear(n_in, hid), nn.ELU(inplace=True)]
+            for _ in range(num_layers - 2):
+                layers += [nn.Linear(hid, hid), nn.ELU(inplace=True)]
+            layers.append(nn.Linear(hid, self.num_edges))
+            return nn.Sequential(*layers)
+
+        self.encoder_fc_out = head(2 * rnn_hidden_size, params["encoder_mlp_num_layers"], params.get("encoder_mlp_hidden"))
+        self.prior_layers = params["prior_num_layers"]
+        if not 1 <= self.prior_layers <= 4:
+            raise ValueError("aether_b200.seq2seq.Encoder: prior_num_layers must be 1..4")
+        self.prior_hidden = params.get("prior_hidden_size") if self.prior_layers > 1 else 0
+        self.prior_fc_out = head(rnn_hidden_size, self.prior_layers, self.prior_hidden)
+        self.use_3d = params.get("use_3d", False)
+        self.num_dims = D = 3 if self.use_3d else 2
+        if inp_size != 2 * D:
+            raise ValueError("Encoder: input_size must be 2 * num_dims")
+        if hidden_size % 4 != 0:
+            raise ValueError("Encoder: encoder_hidden must be a multiple of 4")
+        self.num_orientations = D * (D - 1) // 2
+        self.num_relative_features = 4 * D + self.num_orientations
+        self.num_pos_features = D + self.num_orientations
+        self.res1 = nn.Linear(inp_size + self.num_relative_features + D, hidden_size)
+        self.edge_filter = AnisotropicEdgeFilter(2 * self.num_relative_features + inp_size + D, self.num_pos_features,
+                                                 hidden_size, hidden_size)
+        self.pos_representation = params.get("pos_representation", "cart")
+        if self.pos_representation not in ("cart", "polar"):
+            raise ValueError
+        self.hidden_size, self.rnn_hidden = hidden_size, rnn_hidden_size
+        self.init_weights()
+        self._ws = None
+
+    def init_weights(self):
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                nn.init.xavier_normal_(m.weight.data)
+                m.bias.data.fill_(0.1)
+
+    def _c_params(self):
+        keep = []
+
+        def dp(t):
+            if t is None:
+                return None
+            t = t.detach()
+            if not t.is_cuda or t.dtype != torch.float32:
+                raise RuntimeError("aether_b200.seq2seq: parameters must be fp32 CUDA tensors (there is no CPU path)")
+            t = t.contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        p = _lib.AetherSeqEncParams()
+        f = self.edge_filter.edge_filter
+        p.filter_w0, p.filter_b0, p.filter_w2, p.filter_b2 = dp(f[0].weight), dp(f[0].bias), dp(f[2].weight), dp(f[2].bias)
+        p.res1_w, p.res1_b = dp(self.res1.weight), dp(self.res1.bias)
+        for name in ("mlp3", "mlp4"):
+            m = getattr(self, name)
+            w, b = getattr(p, name + "_w"), getattr(p, name + "_b")
+            w[0], b[0], w[1], b[1] = dp(m.model[0].weight), dp(m.model[0].bias), dp(m.model[3].weight), dp(m.model[3].bias)
+            sc, sh = m.bn_affine()
+            setattr(p, name + "_bn_scale", dp(sc))
+            setattr(p, name + "_bn_shift", dp(sh))
+        r = self.forward_rnn
+        p.lstm_w_ih, p.lstm_w_hh, p.lstm_b_ih, p.lstm_b_hh = dp(r.weight_ih_l0), dp(r.weight_hh_l0), dp(r.bias_ih_l0), dp(r.bias_hh_l0)
+        lins = [self.prior_fc_out] if self.prior_layers == 1 else [m for m in self.prior_fc_out if isinstance(m, nn.Linear)]
+        for i, lin in enumerate(lins):
+            p.prior_w[i], p.prior_b[i] = dp(lin.weight), dp(lin.bias)
+        p.n_prior_layers = len(lins)
+        p.pos_offset = 0 if self.pos_representation == "cart" else self.num_dims
+        return p, keep
+
+    def _dims(self, batch):
+        return _lib.AetherSeqDims(self.num_dims, self.num_vars, 4, self.num_edges, 0, self.hidden_size, self.rnn_hidden,
+                                  int(self.prior_hidden or 0), batch)
+
+    def initial_state(self, batch, device):
+        n = batch * self.num_vars * (self.num_vars - 1)
+        return (torch.zeros(1, n, self.rnn_hidden, device=device), torch.zeros(1, n, self.rnn_hidden, device=device))
+
+    @torch.no_grad()
+    def single_step_forward(self, inputs, prior_state, predicted_field):
+        """inputs[B,N,2D], prior_state (h, c) each [1, B*N(N-1), R], predicted_field[B,N,D] -> (logits[B,E,types], state)."""
+        if self.training:
+            raise RuntimeError("aether_b200.seq2seq.Encoder is inference-only: call .eval()")
+        if not inputs.is_cuda:
+            raise RuntimeError("aether_b200.seq2seq: CUDA tensors only (there is no CPU path)")
+        B, N = inputs.shape[0], inputs.shape[1]
+        E = N * (N - 1)
+        if N != self.num_vars or inputs.shape[2] != 2 * self.num_dims or tuple(predicted_field.shape) != (B, N, self.num_dims):
+            raise RuntimeError("Encoder: inputs must be [batch, num_vars, 2*num_dims], the field [batch, num_vars, num_dims]")
+        h, c = prior_state
+        if h.numel() != B * E * self.rnn_hidden or c.numel() != h.numel():
+            raise RuntimeError("Encoder: prior_state must hold [batch * num_edges, encoder_rnn_hidden] per tensor")
+        f32 = lambda t: t.detach().to(torch.float32).contiguous()
+        x, fld, h, c = f32(inputs), f32(predicted_field), f32(h), f32(c)
+        lib = _lib.load()
+        with torch.cuda.device(x.device):
+            d = self._dims(B)
+            nbytes = lib.aether_seq_workspace_bytes(ctypes.byref(d))
+            if self._ws is None or self._ws.numel() < nbytes or self._ws.device != x.device:
+                self._ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+            p, keep = self._c_params()
+            logits = torch.empty(B, E, self.num_edges, device=x.device)
+            h2, c2 = torch.empty_like(h), torch.empty_like(c)
+            _lib.check(lib.aether_seq_encoder_step(ctypes.byref(d), ctypes.byref(p), _lib.ptr(x), _lib.ptr(fld), _lib.ptr(h),
+                                                   _lib.ptr(c), _lib.ptr(logits), _lib.ptr(h2), _lib.ptr(c2),
+                                                   _lib.ptr(self._ws), self._ws.numel(), _stream()), "aether_seq_encoder_step")
+        return logits, (h2, c2)
+
+    @torch.no_grad()
+    def forward(self, inputs, predicted_field):
+        """inputs[B,T,N,2D], predicted_field[B,N,T,D] -> (prior logits [B,T,E,types], None, final LSTM state)."""
+        B, T = inputs.shape[0], inputs.shape[1]
+        state = self.initial_state(B, inputs.device)
+        out = []
+        for t in range(T):
+            lg, state = self.single_step_forward(inputs[:, t], state, predicted_field[:, :, t])
+            out.append(lg)
+        return torch.stack(out, 1), None, state
+
+
 def gumbel_softmax(logits, tau=1.0, hard=False, eps=1e-10, generator=None):
     """nn/utils/model_utils.py:57-121 (noise drawn on the logits' device)."""
     U = torch.rand(logits.shape, device=logits.device, generator=generator)
@@ -220,6 +402,11 @@ class Seq2SeqAether(nn.Module):
 
     def _dims(self, batch):
         return self.decoder.dims(batch, self.field_hidden)
+
+    @classmethod
+    def with_encoder(cls, params):
+        """The whole inference model: decoder side + this package's Encoder (prior branch)."""
+        return cls(params, encoder=Encoder(params))
 
     def _params(self):
         return self.decoder.c_params(self.field_net, self.coordinate_embedding.B)

@@ -299,7 +299,9 @@ typedef struct AetherSeqDims {
   int32_t hidden;        /* decoder_hidden, multiple of 4                   */
   int32_t n_types;       /* num_edge_types, 1..AETHER_SEQ_MAX_TYPES         */
   int32_t skip_first;    /* 1: edge type 0 sends no message                 */
-  int32_t field_hidden;  /* encoder_hidden (width of field_net), multiple of 4; 0 when the field net is unused */
+  int32_t field_hidden;  /* encoder_hidden (width of field_net and of the encoder), multiple of 4; 0 when unused */
+  int32_t rnn_hidden;    /* encoder_rnn_hidden (LSTM width); 0 when aether_seq_encoder_step is not used */
+  int32_t prior_hidden;  /* prior_hidden_size (0 with a one-layer prior head)                            */
   int64_t batch;         /* B trajectories                                  */
 } AetherSeqDims;
 typedef struct AetherSeqParams {
@@ -335,6 +337,32 @@ int aether_seq_decoder_step(const AetherSeqDims* dims, const AetherSeqParams* pa
 int aether_seq_rollout_step(const AetherSeqDims* dims, const AetherSeqParams* params, const float* states,
                             const float* hidden_in, const float* edge_types, float* states_out, float* hidden_out,
                             float* field_out, void* workspace, size_t workspace_bytes, void* stream);
+/* Prior branch of the edge-type encoder, one time step (Encoder.single_step_forward, nn/seq2seq/aether.py:397-425; the
+ * burn-in pass Encoder.forward :362-395 is the same step applied to every burn-in time step, eval mode): localizer ->
+ * anisotropic edge filter (nn/nn/anisotropic_filter.py:12-41) -> edge2node + res1 -> mlp3 -> node2edge + skip -> mlp4
+ * (RefNRIMLP, nn/utils/model_utils.py:15-54, BatchNorm in eval mode) -> one LSTM step -> prior_fc_out.
+ *   h_in / c_in / h_out / c_out: [B*N(N-1), rnn_hidden] (out may alias in); logits: [B, N(N-1), n_types].
+ * BatchNorm enters as its eval-mode affine map: *_bn_scale = weight / sqrt(running_var + eps), *_bn_shift = bias -
+ * running_mean * scale ([encoder_hidden] each; NULL without batch norm).  pos_offset: first column of the edge features
+ * that the filter generator reads (pos_representation 'cart': 0; 'polar': 2 in 2D, 3 in 3D;
+ * nn/utils/augmented_global_to_local.py:18-24), D + D(D-1)/2 columns. */
+typedef struct AetherSeqEncParams {
+  const float* filter_w0; const float* filter_b0;      /* edge_filter.edge_filter.0: [He, D+O]                      */
+  const float* filter_w2; const float* filter_b2;      /* edge_filter.edge_filter.2: [(2F+3D)*He, He]               */
+  const float* res1_w; const float* res1_b;            /* [He, 3D+F]                                                */
+  const float* mlp3_w[2]; const float* mlp3_b[2];      /* mlp3.model.{0,3}: [He, He]                                */
+  const float* mlp3_bn_scale; const float* mlp3_bn_shift;
+  const float* mlp4_w[2]; const float* mlp4_b[2];      /* mlp4.model.{0,3}: [He, 3He], [He, He]                     */
+  const float* mlp4_bn_scale; const float* mlp4_bn_shift;
+  const float* lstm_w_ih; const float* lstm_w_hh;      /* forward_rnn.weight_{ih,hh}_l0: [4R, He], [4R, R]          */
+  const float* lstm_b_ih; const float* lstm_b_hh;
+  const float* prior_w[4]; const float* prior_b[4];    /* prior_fc_out Linears in order                             */
+  int32_t n_prior_layers;                              /* prior_num_layers, 1..4                                    */
+  int32_t pos_offset;
+} AetherSeqEncParams;
+int aether_seq_encoder_step(const AetherSeqDims* dims, const AetherSeqEncParams* params, const float* states,
+                            const float* field, const float* h_in, const float* c_in, float* logits, float* h_out,
+                            float* c_out, void* workspace, size_t workspace_bytes, void* stream);
 /* Test hook: the three AugmentedLocalizer outputs the step consumes, rel_feat[B,N,3D+F], Rinv[B,N,D,D],
  * edge_attr[B,N(N-1),2F+3D]. */
 int aether_seq_localizer(const AetherSeqDims* dims, const float* states, const float* field, float* rel_feat, float* Rinv,

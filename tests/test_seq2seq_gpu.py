@@ -144,3 +144,98 @@ def test_module_surface_and_errors():
     assert bool(((edges == 0) | (edges == 1)).all()) and torch.equal(edges.sum(-1), torch.ones(4, 3, 20, device="cuda"))
     again = m.predict_future(dev(g, "pf_inputs"), 3, edges=torch.cat([torch.zeros(4, 3, 20, 2, device="cuda"), edges], 1))
     assert torch.isfinite(preds).all() and again.shape == preds.shape
+
+
+# ---- edge-type encoder, prior branch ------------------------------------------------------------------------------------
+def enc_params_of(g):
+    p = params_of(g)
+    p.update({"encoder_rnn_hidden": int(g["enc_rnn_hidden"]), "encoder_rnn_type": "lstm", "encoder_dropout": 0.0,
+              "encoder_mlp_num_layers": 3, "encoder_mlp_hidden": int(g["enc_mlp_hidden"]), "prior_num_layers": 3,
+              "prior_hidden_size": int(g["enc_prior_hidden"]), "pos_representation": str(g["enc_pos_representation"])})
+    return p
+
+
+def build_full(g):
+    from aether_b200.seq2seq import Seq2SeqAether
+    m = Seq2SeqAether.with_encoder(enc_params_of(g))
+    sd = {"decoder." + k[4:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("dec.")}
+    sd.update({"encoder." + k[4:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("enc.")})
+    sd.update({k: torch.from_numpy(v) for k, v in g.items() if k.startswith("field_net.")})
+    sd["coordinate_embedding.B"] = torch.from_numpy(g["rff_B"])
+    m.load_state_dict(sd)          # strict: the reference model's whole state_dict
+    return m.cuda().eval()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_encoder_matches_reference(name):
+    """Burn-in pass of the reference Encoder (prior logits of every step, final LSTM state) and one single_step_forward,
+    with non-trivial BatchNorm running statistics."""
+    g = load_golden(name)
+    m = build_full(g)
+    burn = dev(g, "pf_inputs")
+    field, _ = m.predict_field(burn[:, :-1].transpose(2, 1).contiguous())
+    logits, post, (h, c) = m.encoder(burn[:, :-1], field)
+    assert post is None and logits.shape == g["enc_prior_logits"].shape and h.shape == g["enc_state_h"].shape
+    assert rel_err(logits.cpu(), g["enc_prior_logits"]) <= 1e-5
+    assert rel_err(h.cpu(), g["enc_state_h"]) <= 1e-5 and rel_err(c.cpu(), g["enc_state_c"]) <= 1e-5
+    f_last, _ = m.predict_field(burn[:, -1])
+    lg, (h2, c2) = m.encoder.single_step_forward(burn[:, -1], (h, c), f_last)
+    assert rel_err(lg.cpu(), g["enc_step_logits"]) <= 1e-5
+    assert rel_err(h2.cpu(), g["enc_step_state_h"]) <= 1e-5 and rel_err(c2.cpu(), g["enc_step_state_c"]) <= 1e-5
+
+
+def test_predict_future_whole_model_on_device():
+    """predict_future as the reference calls it (no edges given): encoder, gumbel hard samples, field, decoder all on the
+    GPU.  The random stream differs from the reference's CPU torch.rand, so the check is structural + the decoder side
+    re-run on the sampled edges."""
+    g = load_golden("seq2seq2d_h32")
+    m = build_full(g)
+    burn = dev(g, "pf_inputs")
+    torch.manual_seed(5)
+    preds, edges = m.predict_future(burn, 4, return_edges=True, return_everything=True)
+    assert preds.shape == (4, 3 + 4, 5, 4) and edges.shape == (4, 3 + 4, 20, 2)
+    assert bool(((edges == 0) | (edges == 1)).all()) and bool((edges.sum(-1) == 1).all())
+    torch.manual_seed(5)
+    again = m.predict_future(burn, 4, return_everything=True)
+    assert torch.equal(again, preds)
+    replay = m.predict_future(burn, 4, return_everything=True, edges=edges)
+    assert torch.equal(replay, preds)
+    # with the noise switched off (eps so large that every sample is the arg-max of the logits), the edges follow the
+    # encoder's logits: compare with the oracle's arg-max on the burn-in steps
+    from oracle import seq2seq_oracle as so
+    w = {k[4:]: torch.from_numpy(v) for k, v in g.items() if k.startswith("enc.")}
+    w.update({k: torch.from_numpy(v) for k, v in g.items() if k.startswith("field_net.")})
+    w["rff_B"] = torch.from_numpy(g["rff_B"])
+    lg, _, _ = so.encoder_prior(w, torch.from_numpy(g["pf_inputs"])[:, :-1], 2, str(g["enc_pos_representation"]))
+    field, _ = m.predict_field(burn[:, :-1].transpose(2, 1).contiguous())
+    mine, _, _ = m.encoder(burn[:, :-1], field)
+    margin = (lg[..., 0] - lg[..., 1]).abs() > 1e-4
+    assert torch.equal(mine.argmax(-1).cpu()[margin], lg.argmax(-1)[margin])
+
+
+@pytest.mark.parametrize("D,N,B,He,R,PH,layers,rep", [(2, 5, 16, 128, 64, 32, 3, "polar"), (3, 4, 5, 64, 32, 0, 1, "polar"),
+                                                      (3, 5, 3, 32, 16, 24, 4, "cart"), (2, 2, 3, 36, 20, 12, 2, "cart")])
+def test_encoder_against_oracle(D, N, B, He, R, PH, layers, rep):
+    from aether_b200.seq2seq import Encoder
+    from oracle import seq2seq_oracle as so
+    torch.manual_seed(21)
+    p = {"num_vars": N, "input_size": 2 * D, "use_3d": D == 3, "num_edge_types": 3, "encoder_hidden": He,
+         "encoder_rnn_hidden": R, "encoder_rnn_type": "lstm", "encoder_dropout": 0.0, "encoder_mlp_num_layers": 2,
+         "encoder_mlp_hidden": 16, "prior_num_layers": layers, "prior_hidden_size": PH, "pos_representation": rep}
+    enc = Encoder(p)
+    for mod in enc.modules():
+        if isinstance(mod, torch.nn.BatchNorm1d):
+            mod.running_mean.normal_(0, 0.2)
+            mod.running_var.uniform_(0.5, 1.5)
+            mod.weight.data.normal_(1.0, 0.1)
+            mod.bias.data.normal_(0, 0.1)
+    enc = enc.cuda().eval()
+    w = {k: v.detach().cpu() for k, v in enc.state_dict().items()}
+    E = N * (N - 1)
+    x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1)
+    field = 0.3 * torch.randn(B, N, D)
+    h, c = 0.3 * torch.randn(B * E, R), 0.3 * torch.randn(B * E, R)
+    lg, (h2, c2) = enc.single_step_forward(x.cuda(), (h.cuda().unsqueeze(0), c.cuda().unsqueeze(0)), field.cuda())
+    lo, ho, co = so.encoder_step(w, x, field, h, c, D, rep)
+    assert rel_err(lg.cpu(), lo) <= 2e-5
+    assert rel_err(h2.cpu()[0], ho) <= 1e-5 and rel_err(c2.cpu()[0], co) <= 1e-5
