@@ -506,6 +506,72 @@ class DecoderRollout:
         self._graph = None
         self.launches_per_replay = 0
 
+    def _steps_sampled(self):
+        """predict_future's second loop as the reference runs it (:176-184): field -> encoder step -> hard gumbel sample
+        -> decoder step, every call on the current stream (capturable, torch's graph-safe generator draws the noise)."""
+        m, dec, enc = self.model, self.model.decoder, self.model.encoder
+        p, self._keep = m._params()
+        pe, keep_e = enc._c_params()
+        self._keep += keep_e
+        de = enc._dims(self.B)
+        self.hidden.copy_(self.h0)
+        self.enc_h.copy_(self.enc_h0)
+        self.enc_c.copy_(self.enc_c0)
+        x = self.x0
+        lib = self.lib
+        for t in range(self.steps):
+            _lib.check(lib.aether_seq_predict_field(ctypes.byref(self.dims), ctypes.byref(p), _lib.ptr(x), _lib.ptr(self.field),
+                                                    _lib.ptr(self.ws), self.ws.numel(), _stream()), "aether_seq_predict_field")
+            _lib.check(lib.aether_seq_encoder_step(ctypes.byref(de), ctypes.byref(pe), _lib.ptr(x), _lib.ptr(self.field),
+                                                   _lib.ptr(self.enc_h), _lib.ptr(self.enc_c), _lib.ptr(self.logits),
+                                                   _lib.ptr(self.enc_h), _lib.ptr(self.enc_c), _lib.ptr(self.ws_enc),
+                                                   self.ws_enc.numel(), _stream()), "aether_seq_encoder_step")
+            U = torch.rand(self.logits.shape, device=self.dev)
+            k = (self.logits - torch.log(1e-10 - torch.log(U + 1e-10))).argmax(-1, keepdim=True)
+            self.edges[t].zero_().scatter_(-1, k, 1.0)
+            _lib.check(lib.aether_seq_decoder_step(ctypes.byref(self.dims), ctypes.byref(p), _lib.ptr(x), _lib.ptr(self.hidden),
+                                                   _lib.ptr(self.edges[t]), _lib.ptr(self.field), _lib.ptr(self.traj[t]),
+                                                   _lib.ptr(self.hidden), _lib.ptr(self.ws), self.ws.numel(), _stream()),
+                       "aether_seq_decoder_step")
+            x = self.traj[t]
+
+    @torch.no_grad()
+    def run_sampled(self, x0, hidden0, prior_state) -> torch.Tensor:
+        """The prediction loop with the model's own Encoder: x0[B,N,2D], the decoder's hidden state and the encoder's LSTM
+        state after the burn-in -> predictions[steps,B,N,2D]; the sampled edge types are left in ``self.edges``."""
+        enc = self.model.encoder
+        if not isinstance(enc, Encoder):
+            raise RuntimeError("DecoderRollout.run_sampled needs a model built with aether_b200.seq2seq.Encoder")
+        with torch.cuda.device(self.dev):
+            if not hasattr(self, "enc_h"):
+                n = self.B * self.edges.shape[2]
+                f32 = dict(dtype=torch.float32, device=self.dev)
+                self.enc_h0, self.enc_c0 = torch.zeros(n, enc.rnn_hidden, **f32), torch.zeros(n, enc.rnn_hidden, **f32)
+                self.enc_h, self.enc_c = torch.empty_like(self.enc_h0), torch.empty_like(self.enc_c0)
+                self.logits = torch.empty(self.B, self.edges.shape[2], enc.num_edges, **f32)
+                self.field = torch.empty(self.B, self.x0.shape[1], self.model.num_dims, **f32)
+                de = enc._dims(self.B)
+                self.ws_enc = torch.empty(self.lib.aether_seq_workspace_bytes(ctypes.byref(de)), dtype=torch.uint8, device=self.dev)
+                self._graph_s = None
+            self.x0.copy_(x0, non_blocking=True)
+            self.h0.copy_(hidden0, non_blocking=True)
+            self.enc_h0.copy_(prior_state[0].reshape(self.enc_h0.shape), non_blocking=True)
+            self.enc_c0.copy_(prior_state[1].reshape(self.enc_c0.shape), non_blocking=True)
+            if not self._use_graph:
+                self._steps_sampled()
+                return self.traj
+            if self._graph_s is None:
+                self._steps_sampled()
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                n0 = self.lib.aether_launch_count()
+                with torch.cuda.graph(g):
+                    self._steps_sampled()
+                self.launches_per_replay_sampled = int(self.lib.aether_launch_count() - n0)
+                self._graph_s = g
+            self._graph_s.replay()
+            return self.traj
+
     def _steps(self):
         p, self._keep = self.model._params()
         self.hidden.copy_(self.h0)

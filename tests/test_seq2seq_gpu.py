@@ -239,3 +239,24 @@ def test_encoder_against_oracle(D, N, B, He, R, PH, layers, rep):
     lo, ho, co = so.encoder_step(w, x, field, h, c, D, rep)
     assert rel_err(lg.cpu(), lo) <= 2e-5
     assert rel_err(h2.cpu()[0], ho) <= 1e-5 and rel_err(c2.cpu()[0], co) <= 1e-5
+
+
+def test_sampled_rollout_graph_matches_stepwise():
+    """DecoderRollout.run_sampled: field -> encoder -> sample -> decoder for T steps as ONE CUDA graph; replaying the
+    decoder side on the edges it sampled reproduces its trajectory bit for bit, eager and captured."""
+    from aether_b200.seq2seq import DecoderRollout
+    g = load_golden("seq2seq3d_h64")
+    m = build_full(g)
+    burn = dev(g, "pf_inputs")
+    B, T = burn.shape[0], 4
+    field, _ = m.predict_field(burn[:, :-1].transpose(2, 1).contiguous())
+    _, _, state = m.encoder(burn[:, :-1], field)
+    hid = 0.1 * torch.randn(B, 5, 64, device="cuda")
+    for graph in (False, True):
+        r = DecoderRollout(m, B, T, cuda_graph=graph)
+        for _ in range(2):                                  # second call = replay of the captured graph
+            traj = r.run_sampled(burn[:, -1], hid, state).clone()
+            edges = r.edges.clone()
+            assert bool((edges.sum(-1) == 1).all()) and torch.isfinite(traj).all()
+            again = DecoderRollout(m, B, T, cuda_graph=False).run(burn[:, -1], edges, hidden0=hid)
+            assert torch.equal(again, traj)

@@ -48,3 +48,35 @@ if __name__ == "__main__":
     run(2, 5, 64, 512, 2, 512, 20)     # scripts/electrostatic_field_aether.sh, --test_pred_steps 20
     run(3, 5, 32, 512, 2, 512, 5)      # scripts/gravitational_field_3d_aether.sh, --test_pred_steps 5
     run(2, 5, 1024, 256, 2, 256, 20)   # a large evaluation batch
+
+
+def run_full(D, N, B, H, K, He, R, T, reps=10):
+    """The whole prediction loop (field -> encoder -> gumbel sample -> decoder) as one CUDA graph."""
+    torch.manual_seed(0)
+    p = {"num_vars": N, "input_size": 2 * D, "use_3d": D == 3, "decoder_hidden": H, "num_edge_types": K, "skip_first": False,
+         "decoder_dropout": 0.0, "encoder_hidden": He, "gumbel_temp": 0.5, "encoder_rnn_hidden": R, "encoder_rnn_type": "lstm",
+         "encoder_dropout": 0.0, "encoder_mlp_num_layers": 3, "encoder_mlp_hidden": 256, "prior_num_layers": 3,
+         "prior_hidden_size": 256, "pos_representation": "polar"}
+    m = Seq2SeqAether.with_encoder(p).cuda().eval()
+    x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1).cuda()
+    r = DecoderRollout(m, B, T, cuda_graph=True)
+    state = m.encoder.initial_state(B, x.device)
+    hid = torch.zeros(B, N, H, device="cuda")
+    for _ in range(3):
+        r.run_sampled(x, hid, state)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    ts = []
+    for _ in range(reps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); r.run_sampled(x, hid, state); b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    ms = ts[len(ts) // 2]
+    print(json.dumps({"whole_model_rollout": dict(D=D, N=N, B=B, H=H, K=K, He=He, R=R, T=T), "ms_graph": ms,
+                      "us_per_step": 1e3 * ms / T, "library_launches_per_rollout": r.launches_per_replay_sampled}))
+
+
+if __name__ == "__main__":
+    run_full(2, 5, 64, 512, 2, 512, 128, 20)    # electrostatic script: encoder_hidden 512, encoder_rnn_hidden 128
