@@ -284,8 +284,8 @@ int aether_dynfield_backward(int32_t num_dims, int64_t n_nodes, int32_t num_node
  * GRU-style gates, out MLP, Globalizer, inputs + prediction) and the field predictor of the enclosing model
  * (Aether.predict_field, nn/seq2seq/aether.py:83-87: Fourier features nn/nn/fourier_feature_mapper.py:21-23 + field_net
  * :72-78).  Inference only (dropout inactive).  The graph is the reference's fixed one: num_vars particles per
- * trajectory, every ordered pair (sender-major, torch.where(~eye), :548-549).  The encoder that produces the edge-type
- * logits (nn/seq2seq/aether.py:249-...) is not part of this path: edge-type weights are an input.
+ * trajectory, every ordered pair (sender-major, torch.where(~eye), :548-549).  The decoder takes the
+ * edge-type weights as an input; aether_seq_encoder_step below is the prior branch of the encoder that produces their logits.
  *
  * Layouts: states[B, N, 2D] = [pos | vel]; hidden[B, N, H]; edge_types[B, N(N-1), n_types] (leading dimension
  * n_types; soft weights or one-hot); field[B, N, D].  hidden_out may alias hidden_in.
