@@ -223,7 +223,10 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
   __shared__ __align__(16) float As[GS][BM][LD];
   __shared__ __align__(16) float Ws[GS][BN][LD];
   const int tid = threadIdx.x;
-  const int tx = tid & 15, ty = tid >> 4;
+  // a warp covers 8 columns x 4 rows of the 16 x 16 thread grid: a 128-bit operand read touches 8 distinct W rows
+  // (one 128-byte wavefront) and 4 distinct A rows (broadcast within each quarter warp) -- 8 wavefronts per 64 FFMAs
+  // where a 16 x 2 warp shape needs 12
+  const int tx = ((tid >> 5) & 1) * 8 + (tid & 7), ty = (tid >> 6) * 4 + ((tid >> 3) & 3);
   float sum[TM][TN], acc[TM][TN];
 #pragma unroll
   for (int i = 0; i < TM; ++i)
