@@ -16,5 +16,5 @@ edges = torch.nn.functional.one_hot(torch.randint(0, K, (T, B, E)), K).float().c
 r = DecoderRollout(m, B, T, cuda_graph=False)
 r.run(x, edges); torch.cuda.synchronize()
 PY
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/seq_launches.csv python /tmp/seq_one.py > gpurun_out/seq_ncu.log 2>&1
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none -c 200 --csv --log-file gpurun_out/seq_launches.csv python /tmp/seq_one.py > gpurun_out/seq_ncu.log 2>&1
 tail -3 gpurun_out/seq_ncu.log
