@@ -34,7 +34,7 @@ SEQ_MAX_TYPES = 4
 class AetherSeqDims(ctypes.Structure):
     _fields_ = [("num_dims", c_int32), ("num_vars", c_int32), ("hidden", c_int32), ("n_types", c_int32),
                 ("skip_first", c_int32), ("field_hidden", c_int32), ("rnn_hidden", c_int32), ("prior_hidden", c_int32),
-                ("batch", c_int64)]
+                ("flags", c_uint32), ("batch", c_int64)]
 
 
 class AetherSeqEncParams(ctypes.Structure):

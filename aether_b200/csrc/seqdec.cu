@@ -205,6 +205,12 @@ __device__ __forceinline__ void cp_async16(float* dst_smem, const float* src, in
   const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(src), "r"(bytes));
 }
+// (lo, hi) -> one register of two bf16, round to nearest even
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
@@ -214,8 +220,14 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // 16-byte aligned, e.g. the 39-wide 3D features).  The inner loop reads 4 k's of a row as one vector; with rows
 // strided by 16 between a thread's outputs, the 8 lanes of a shared-memory phase hit 8 different 16-byte bank groups
 // (row step = 5 groups).  The small tile exists for the node-level problems (B*N rows): at 64 x 64 they are 40 CTAs.
-template <int BM, int BN>
+//
+// TC (64 x 64 only; models with precision = "bf16", tolerance 2e-2): the same ring, but the products run on the tensor
+// cores -- mma.sync.m16n8k16, bf16 operands rounded from the fp32 tiles in registers, fp32 accumulate; 8 warps as 2 x 4,
+// a warp owns 32 rows x 16 columns (2 x 2 MMAs per 16-k slab: 12 64-bit shared-memory reads, 12 packs, 4 MMAs where the
+// CUDA-core loop has 32 reads and 256 FFMAs).  Biases, activations, sums over terms and outputs stay fp32.
+template <int BM, int BN, bool TC>
 __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+  static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variant: 64 x 64 tiles");
   constexpr int TM = BM / 16, TN = BN / 16, LD = GK + 4;
   const Problem& P = bt.p[blockIdx.z];
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
@@ -227,6 +239,11 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
   // (one 128-byte wavefront) and 4 distinct A rows (broadcast within each quarter warp) -- 8 wavefronts per 64 FFMAs
   // where a 16 x 2 warp shape needs 12
   const int tx = ((tid >> 5) & 1) * 8 + (tid & 7), ty = (tid >> 6) * 4 + ((tid >> 3) & 3);
+  // TC: warp (wm, wn) of the 2 x 4 warp grid, lane = (g, tq); acc[2 mt + half][2 nt + low] is element `2 half + low` of
+  // the accumulator fragment of MMA (mt, nt): row wm*32 + mt*16 + g + 8 half, column wn*16 + nt*8 + 2 tq + low
+  const int lane = tid & 31, g = lane >> 2, tq = lane & 3, wm = (tid >> 5) & 1, wn = tid >> 6;
+  auto row_of = [&](int i) { return TC ? wm * 32 + (i >> 1) * 16 + g + 8 * (i & 1) : ty + 16 * i; };
+  auto col_of = [&](int j) { return TC ? wn * 16 + (j >> 1) * 8 + 2 * tq + (j & 1) : tx + 16 * j; };
   float sum[TM][TN], acc[TM][TN];
 #pragma unroll
   for (int i = 0; i < TM; ++i)
@@ -296,6 +313,35 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
       if (kt + GS - 1 < nk) issue(kt + GS - 1, (kt + GS - 1) % GS);
       cp_async_commit();
       const int cur = kt % GS;
+      if (TC) {
+        if constexpr (TC) {
+          uint32_t afr[2][4], bfr[2][2];
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt) {
+            const float* r0 = &As[cur][wm * 32 + mt * 16 + g][2 * tq];
+            const float2 v0 = *reinterpret_cast<const float2*>(r0), v1 = *reinterpret_cast<const float2*>(r0 + 8 * LD);
+            const float2 v2 = *reinterpret_cast<const float2*>(r0 + 8), v3 = *reinterpret_cast<const float2*>(r0 + 8 * LD + 8);
+            afr[mt][0] = pack_bf16x2(v0.x, v0.y); afr[mt][1] = pack_bf16x2(v1.x, v1.y);
+            afr[mt][2] = pack_bf16x2(v2.x, v2.y); afr[mt][3] = pack_bf16x2(v3.x, v3.y);
+          }
+#pragma unroll
+          for (int nt = 0; nt < 2; ++nt) {
+            const float* r0 = &Ws[cur][wn * 16 + nt * 8 + g][2 * tq];
+            const float2 v0 = *reinterpret_cast<const float2*>(r0), v1 = *reinterpret_cast<const float2*>(r0 + 8);
+            bfr[nt][0] = pack_bf16x2(v0.x, v0.y); bfr[nt][1] = pack_bf16x2(v1.x, v1.y);
+          }
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+              asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+                           "{%0, %1, %2, %3};"
+                           : "+f"(acc[2 * mt][2 * nt]), "+f"(acc[2 * mt][2 * nt + 1]), "+f"(acc[2 * mt + 1][2 * nt]),
+                             "+f"(acc[2 * mt + 1][2 * nt + 1])
+                           : "r"(afr[mt][0]), "r"(afr[mt][1]), "r"(afr[mt][2]), "r"(afr[mt][3]), "r"(bfr[nt][0]), "r"(bfr[nt][1]));
+        }
+        continue;
+      }
       float4 af[2][TM], wf[2][TN];
 #pragma unroll
       for (int i = 0; i < TM; ++i) af[0][i] = *reinterpret_cast<const float4*>(&As[cur][ty + 16 * i][0]);
@@ -326,12 +372,12 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
     cp_async_wait<0>();
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
-      const int m = m0 + ty + 16 * i;
+      const int m = m0 + row_of(i);
       float sc = 1.0f;
       if (T.flush && scalep != nullptr && m < P.M) sc = scalep[(size_t)m * T.scale_ld];
 #pragma unroll
       for (int j = 0; j < TN; ++j) {
-        const int n = n0 + tx + 16 * j;
+        const int n = n0 + col_of(j);
         float v = acc[i][j];
         if (biasp != nullptr && n < P.N) v = v + biasp[n];
         if (T.flush) {
@@ -347,11 +393,11 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
   }
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
-    const int m = m0 + ty + 16 * i;
+    const int m = m0 + row_of(i);
     if (m >= P.M) continue;
 #pragma unroll
     for (int j = 0; j < TN; ++j) {
-      const int n = n0 + tx + 16 * j;
+      const int n = n0 + col_of(j);
       if (n < P.N) P.C[(size_t)m * P.ldc + n] = sum[i][j];
     }
   }
@@ -366,7 +412,7 @@ Term make_term(const float* A, int lda, const float* W, int ldw, const float* bi
   return t;
 }
 
-int launch_batch(const Batch& bt, int nprob, cudaStream_t st) {
+int launch_batch(const Batch& bt, int nprob, cudaStream_t st, bool tc = false) {
   int maxM = 0, maxN = 0;
   for (int i = 0; i < nprob; ++i) {
     maxM = bt.p[i].M > maxM ? bt.p[i].M : maxM;
@@ -374,12 +420,15 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st) {
   }
   if (maxM == 0 || maxN == 0 || nprob == 0) return 0;
   const int64_t big = (int64_t)((maxM + 63) / 64) * ((maxN + 63) / 64) * nprob;
-  if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
+  if (tc) {           // tensor-core mode: every problem on the 64 x 64 MMA variant
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64><<<grid, GT, 0, st>>>(bt);
+    seq_gemm_kernel<64, 64, true><<<grid, GT, 0, st>>>(bt);
+  } else if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
+    dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
+    seq_gemm_kernel<64, 64, false><<<grid, GT, 0, st>>>(bt);
   } else {
     dim3 grid((maxM + 31) / 32, (maxN + 31) / 32, nprob);
-    seq_gemm_kernel<32, 32><<<grid, GT, 0, st>>>(bt);
+    seq_gemm_kernel<32, 32, false><<<grid, GT, 0, st>>>(bt);
   }
   AE_LAUNCH_CHECK();
   return 0;
@@ -630,6 +679,7 @@ int seq_geometry(const AetherSeqDims* d, const float* states, const float* field
 
 int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* states, float* field, const SeqWs& w,
               cudaStream_t st) {
+  const bool tcm = (d->flags & AETHER_SEQ_F_BF16) != 0;
   const int D = d->num_dims, Hf = d->field_hidden;
   if (Hf < 4 || p->rff_B == nullptr) return AETHER_E_BADARG;
   for (int i = 0; i < 3; ++i)
@@ -642,10 +692,10 @@ int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* sta
   Batch bt;
   bt.p[0].t[0] = make_term(w.f0, Hf, p->field_w[0], Hf, p->field_b[0], Hf, ACT_SILU, 1);
   bt.p[0].C = w.f1; bt.p[0].ldc = Hf; bt.p[0].M = (int)BN; bt.p[0].N = Hf; bt.p[0].nterms = 1;
-  AE_CHECK(launch_batch(bt, 1, st));
+  AE_CHECK(launch_batch(bt, 1, st, tcm));
   bt.p[0].t[0] = make_term(w.f1, Hf, p->field_w[1], Hf, p->field_b[1], Hf, ACT_SILU, 1);
   bt.p[0].C = w.f2;
-  AE_CHECK(launch_batch(bt, 1, st));
+  AE_CHECK(launch_batch(bt, 1, st, tcm));
   seq_thin_kernel<<<(int)ceil_div64(BN * 32, 256), 256, 0, st>>>(w.f2, Hf, p->field_w[2], p->field_b[2], D, nullptr, D,
                                                                 nullptr, field, BN);
   AE_LAUNCH_CHECK();
@@ -655,6 +705,7 @@ int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* sta
 int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* states, const float* hidden_in,
              const float* edge_types, const float* field, float* states_out, float* hidden_out, const SeqWs& w,
              cudaStream_t st) {
+  const bool tcm = (d->flags & AETHER_SEQ_F_BF16) != 0;
   const int D = d->num_dims, N = d->num_vars, H = d->hidden, Kt = d->n_types, t0 = d->skip_first ? 1 : 0;
   const int O = D * (D - 1) / 2, F = 4 * D + O, KE = 2 * F + 3 * D, KR = 3 * D + F;
   const int64_t BN = d->batch * N, BE = BN * (N - 1);
@@ -677,7 +728,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   // batch A: node terms of msg_fc1 (bias with the receiver half) and present_msg_fc1 per type
   for (int t = t0; t < Kt; ++t) {
     if (np + 3 > MAX_PROB) {          // four active edge types: the batch goes out in two launches
-      AE_CHECK(launch_batch(bt, np, st));
+      AE_CHECK(launch_batch(bt, np, st, tcm));
       np = 0;
     }
     single(make_term(hidden_in, H, p->msg_fc1_w[t], 2 * H, p->msg_fc1_b[t], H, ACT_NONE, 1), w.P + (size_t)(2 * t) * H,
@@ -687,7 +738,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
     single(make_term(w.eattr, KE, p->present_msg_fc1_w[t], KE, p->present_msg_fc1_b[t], KE, ACT_RELU, 1),
            w.p1 + (size_t)t * BE * H, H, (int)BE, H);
   }
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   if (nt > 0 && BE > 0) {
     const int64_t total = (int64_t)nt * BE * (H / 4);
     seq_pair_tanh_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.P, ldp, N, BE, H, t0, nt, w.m1);
@@ -706,7 +757,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
     }
     a.C = w.msgs; a.ldc = H; a.M = (int)BE; a.N = H; a.nterms = nt;
     b.C = w.pmsgs; b.ldc = H; b.M = (int)BE; b.N = H; b.nterms = nt;
-    AE_CHECK(launch_batch(bt, np, st));
+    AE_CHECK(launch_batch(bt, np, st, tcm));
   } else {
     AE_CHECK((int)cudaMemsetAsync(w.msgs, 0, (size_t)BE * H * sizeof(float), st));
     AE_CHECK((int)cudaMemsetAsync(w.pmsgs, 0, (size_t)BE * H * sizeof(float), st));
@@ -732,16 +783,16 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   gate(p->input_i_w, p->input_i_b, p->present_i_w, p->present_i_b, p->hidden_i_w, ACT_SIGMOID, w.gI);
   gate(p->input_n_w, p->input_n_b, p->present_n_w, p->present_n_b, nullptr, ACT_NONE, w.gN);
   gate(nullptr, nullptr, nullptr, nullptr, p->hidden_h_w, ACT_NONE, w.gH);
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   seq_gate_kernel<<<(int)ceil_div64(BN * H, 256), 256, 0, st>>>(w.gR, w.gI, w.gN, w.gH, hidden_in, hidden_out, BN * H);
   AE_LAUNCH_CHECK();
   // out MLP
   np = 0;
   single(make_term(hidden_out, H, p->out_w[0], H, p->out_b[0], H, ACT_RELU, 1), w.o1, H, (int)BN, H);
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   np = 0;
   single(make_term(w.o1, H, p->out_w[1], H, p->out_b[1], H, ACT_RELU, 1), w.o2, H, (int)BN, H);
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   seq_thin_kernel<<<(int)ceil_div64(BN * 32, 256), 256, 0, st>>>(w.o2, H, p->out_w[2], p->out_b[2], 2 * D, w.Rinv, D,
                                                                 states, states_out, BN);
   AE_LAUNCH_CHECK();
@@ -762,6 +813,7 @@ int seq_params_ok(const AetherSeqParams* p) {
 int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float* states, const float* field,
                 const float* h_in, const float* c_in, float* logits, float* h_out, float* c_out, const SeqWs& w,
                 cudaStream_t st) {
+  const bool tcm = (d->flags & AETHER_SEQ_F_BF16) != 0;
   const int D = d->num_dims, N = d->num_vars, H = d->field_hidden, R = d->rnn_hidden, PH = d->prior_hidden, Kt = d->n_types;
   const int O = D * (D - 1) / 2, F = 4 * D + O, KE = 2 * F + 3 * D, KR = 3 * D + F, KP = D + O;
   const int64_t BN = d->batch * N, BE = BN * (N - 1);
@@ -788,7 +840,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
   // filter generator's first Linear on the edge positions (a column range of edge_attr) and the residual Linear
   add(make_term(w.eattr + p->pos_offset, KE, p->filter_w0, KP, p->filter_b0, KP, ACT_ELU, 1), w.ea, H, BE, H);
   add(make_term(w.relx, KR, p->res1_w, KR, p->res1_b, KR, ACT_NONE, 1), w.eres, H, BN, H);
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   // anisotropic filter (nn/nn/anisotropic_filter.py:35-41): filt[e,:] = sum_f attr[e,f] (a[e,:] W2_f^T + b2_f), W2_f the
   // f-th block of H rows of edge_filter.2 -- one repeated term, the [E, Fin*H] weight tensor is never formed
   np = 0;
@@ -797,24 +849,24 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
     t.repeat = KE; t.w_rep = H * H; t.b_rep = H;
     add(t, w.efilt, H, BE, H);
   }
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   seq_mean_kernel<<<(int)ceil_div64(BN * (H / 4), 256), 256, 0, st>>>(w.efilt, nullptr, N, d->batch, H, w.exin, nullptr,
                                                                      w.eres);
   AE_LAUNCH_CHECK();
   np = 0;
   add(make_term(w.exin, H, p->mlp3_w[0], H, p->mlp3_b[0], H, ACT_ELU, 1), w.et1, H, BN, H);
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   np = 0;
   {
     Problem& q = add(make_term(w.et1, H, p->mlp3_w[1], H, p->mlp3_b[1], H, ACT_ELU, 1), w.ex3, H, BN, H);
     q.t[0].colscale = p->mlp3_bn_scale; q.t[0].colshift = p->mlp3_bn_shift;
   }
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   np = 0;   // mlp4's first Linear [H, 3H] on cat[x_send, x_recv, filt]: the two node parts per particle, the edge part per pair
   add(make_term(w.ex3, H, p->mlp4_w[0], 3 * H, nullptr, H, ACT_NONE, 1), w.ePn, 2 * H, BN, H);
   add(make_term(w.ex3, H, p->mlp4_w[0] + H, 3 * H, nullptr, H, ACT_NONE, 1), w.ePn + H, 2 * H, BN, H);
   add(make_term(w.efilt, H, p->mlp4_w[0] + 2 * H, 3 * H, p->mlp4_b[0], H, ACT_NONE, 1), w.ePe, H, BE, H);
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   if (BE > 0) {
     seq_enc_pair_kernel<<<(int)ceil_div64(BE * (H / 4), 256), 256, 0, st>>>(w.ePn, w.ePe, N, BE, H, w.eh1);
     AE_LAUNCH_CHECK();
@@ -824,7 +876,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
     Problem& q = add(make_term(w.eh1, H, p->mlp4_w[1], H, p->mlp4_b[1], H, ACT_ELU, 1), w.eemb, H, BE, H);
     q.t[0].colscale = p->mlp4_bn_scale; q.t[0].colshift = p->mlp4_bn_shift;
   }
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   np = 0;   // LSTM gates
   {
     Problem& q = bt.p[np++];
@@ -832,7 +884,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
     q.t[1] = make_term(h_in, R, p->lstm_w_hh, R, p->lstm_b_hh, R, ACT_NONE, 1);
     q.C = w.eG; q.ldc = 4 * R; q.M = (int)BE; q.N = 4 * R; q.nterms = 2;
   }
-  AE_CHECK(launch_batch(bt, np, st));
+  AE_CHECK(launch_batch(bt, np, st, tcm));
   if (BE > 0) {
     seq_lstm_cell_kernel<<<(int)ceil_div64(BE * R, 256), 256, 0, st>>>(w.eG, c_in, h_out, c_out, R, BE);
     AE_LAUNCH_CHECK();
@@ -845,7 +897,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
     const int nout = last ? Kt : PH;
     np = 0;
     add(make_term(cur, kin, p->prior_w[i], kin, p->prior_b[i], kin, last ? ACT_NONE : ACT_ELU, 1), dst, nout, BE, nout);
-    AE_CHECK(launch_batch(bt, np, st));
+    AE_CHECK(launch_batch(bt, np, st, tcm));
     cur = dst;
     kin = nout;
   }

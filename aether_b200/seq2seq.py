@@ -93,7 +93,8 @@ class RecurrentDecoder(nn.Module):
     # ---- C-ABI plumbing ----------------------------------------------------------------------------------------------
     def dims(self, batch: int, field_hidden: int = 0, rnn_hidden: int = 0, prior_hidden: int = 0) -> "_lib.AetherSeqDims":
         return _lib.AetherSeqDims(self.num_dims, self.num_vars, self.msg_out_shape, self.edge_types,
-                                  1 if self.skip_first_edge_type else 0, field_hidden, rnn_hidden, prior_hidden, batch)
+                                  1 if self.skip_first_edge_type else 0, field_hidden, rnn_hidden, prior_hidden,
+                                  1 if getattr(self, "precision", "fp32") == "bf16" else 0, batch)
 
     def c_params(self, field_net: Optional[nn.Module] = None, rff: Optional[torch.Tensor] = None):
         """(struct, tensors kept alive) for the library; every parameter must be a contiguous fp32 CUDA tensor."""
@@ -322,7 +323,7 @@ class Encoder(nn.Module):
 
     def _dims(self, batch):
         return _lib.AetherSeqDims(self.num_dims, self.num_vars, 4, self.num_edges, 0, self.hidden_size, self.rnn_hidden,
-                                  int(self.prior_hidden or 0), batch)
+                                  int(self.prior_hidden or 0), 1 if getattr(self, "precision", "fp32") == "bf16" else 0, batch)
 
     def initial_state(self, batch, device):
         n = batch * self.num_vars * (self.num_vars - 1)
@@ -381,11 +382,18 @@ def gumbel_softmax(logits, tau=1.0, hard=False, eps=1e-10, generator=None):
 
 
 class Seq2SeqAether(nn.Module):
-    def __init__(self, params, encoder: Optional[nn.Module] = None):
+    def __init__(self, params, encoder: Optional[nn.Module] = None, precision: str = "fp32"):
+        """precision: "fp32" (CUDA cores, 1e-5 against the reference) or "bf16" (every Linear on the tensor cores with
+        bf16 operands and fp32 accumulation, 2e-2)."""
         super().__init__()
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
         self.num_vars = params["num_vars"]
         self.encoder = encoder
         self.decoder = RecurrentDecoder(params)
+        self.decoder.precision = precision
+        if isinstance(encoder, Encoder):
+            encoder.precision = precision
         self.num_edge_types = params.get("num_edge_types")
         self.gumbel_temp = params.get("gumbel_temp")
         self.use_3d = params.get("use_3d", False)
@@ -404,9 +412,9 @@ class Seq2SeqAether(nn.Module):
         return self.decoder.dims(batch, self.field_hidden)
 
     @classmethod
-    def with_encoder(cls, params):
+    def with_encoder(cls, params, precision: str = "fp32"):
         """The whole inference model: decoder side + this package's Encoder (prior branch)."""
-        return cls(params, encoder=Encoder(params))
+        return cls(params, encoder=Encoder(params), precision=precision)
 
     def _params(self):
         return self.decoder.c_params(self.field_net, self.coordinate_embedding.B)

@@ -293,6 +293,9 @@ int aether_dynfield_backward(int32_t num_dims, int64_t n_nodes, int32_t num_node
  * reference's state_dict keys; per-type arrays are indexed by edge type (entries below `skip_first` are not read).
  * The field_* / rff_B members are only read by aether_seq_predict_field / aether_seq_rollout_step. */
 #define AETHER_SEQ_MAX_TYPES 4
+/* every Linear on the tensor cores (mma.sync, bf16 operands rounded from the fp32 tensors on the fly, fp32 accumulate;
+ * biases, activations, sums and all inputs / outputs stay fp32): the bf16 tolerance (2e-2) instead of 1e-5 */
+#define AETHER_SEQ_F_BF16 1u
 typedef struct AetherSeqDims {
   int32_t num_dims;      /* D: 2 or 3 (use_3d)                              */
   int32_t num_vars;      /* N particles per trajectory, 2..64               */
@@ -302,6 +305,7 @@ typedef struct AetherSeqDims {
   int32_t field_hidden;  /* encoder_hidden (width of field_net and of the encoder), multiple of 4; 0 when unused */
   int32_t rnn_hidden;    /* encoder_rnn_hidden (LSTM width); 0 when aether_seq_encoder_step is not used */
   int32_t prior_hidden;  /* prior_hidden_size (0 with a one-layer prior head)                            */
+  uint32_t flags;        /* AETHER_SEQ_F_*                                                               */
   int64_t batch;         /* B trajectories                                  */
 } AetherSeqDims;
 typedef struct AetherSeqParams {

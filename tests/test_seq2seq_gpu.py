@@ -260,3 +260,48 @@ def test_sampled_rollout_graph_matches_stepwise():
             assert bool((edges.sum(-1) == 1).all()) and torch.isfinite(traj).all()
             again = DecoderRollout(m, B, T, cuda_graph=False).run(burn[:, -1], edges, hidden0=hid)
             assert torch.equal(again, traj)
+
+
+# ---- tensor-core mode (precision="bf16"): the bf16 tolerance of the other paths, 2e-2 relative to each tensor's scale -----
+@pytest.mark.parametrize("name", CASES)
+def test_bf16_mode_matches_reference(name):
+    from aether_b200.seq2seq import Seq2SeqAether
+    g = load_golden(name)
+    m = Seq2SeqAether.with_encoder(enc_params_of(g), precision="bf16")
+    m.load_state_dict(build_full(g).state_dict())
+    m = m.cuda().eval()
+    out, hid = m.decoder(dev(g, "step_inputs"), dev(g, "step_hidden"), dev(g, "step_edges"), dev(g, "step_field"))
+    disp = out.cpu() - torch.from_numpy(g["step_inputs"])          # what the step adds to its input
+    ref_disp = torch.from_numpy(g["step_outputs"] - g["step_inputs"])
+    assert rel_err(disp, ref_disp) <= 2e-2 and rel_err(hid.cpu(), g["step_hidden_new"]) <= 2e-2
+    f, _ = m.predict_field(dev(g, "step_inputs"))
+    assert rel_err(f.cpu(), g["field_pred"]) <= 2e-2
+    burn = dev(g, "pf_inputs")
+    field, _ = m.predict_field(burn[:, :-1].transpose(2, 1).contiguous())
+    logits, _, (h, c) = m.encoder(burn[:, :-1], field)
+    assert rel_err(logits.cpu(), g["enc_prior_logits"]) <= 2e-2
+    assert rel_err(h.cpu(), g["enc_state_h"]) <= 2e-2 and rel_err(c.cpu(), g["enc_state_c"]) <= 2e-2
+    preds = m.predict_future(burn, int(g["pf_steps"]), return_everything=True, edges=dev(g, "pf_edges"))
+    assert rel_err(preds.cpu(), g["pf_predictions"]) <= 2e-2
+
+
+def test_bf16_mode_at_experiment_shape_against_oracle():
+    from aether_b200.seq2seq import DecoderRollout, Seq2SeqAether
+    from oracle import seq2seq_oracle as so
+    torch.manual_seed(11)
+    D, N, B, H, K, T = 2, 5, 64, 512, 2, 4
+    p = {"num_vars": N, "input_size": 2 * D, "use_3d": False, "decoder_hidden": H, "num_edge_types": K,
+         "skip_first": False, "decoder_dropout": 0.0, "encoder_hidden": H, "gumbel_temp": 0.5}
+    m = Seq2SeqAether(p, precision="bf16").cuda().eval()
+    w = _oracle_weights(m)
+    E = N * (N - 1)
+    x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1)
+    onehot = torch.nn.functional.one_hot(torch.randint(0, K, (T, B, E)), K).float()
+    r = DecoderRollout(m, B, T, cuda_graph=True)
+    traj = r.run(x.cuda(), onehot.cuda()).clone()
+    assert torch.equal(traj, r.run(x.cuda(), onehot.cuda()))
+    ref = so.predict_future(w, x.unsqueeze(1), onehot.transpose(0, 1), T, D, K, False, return_everything=False)
+    step = traj.transpose(0, 1).cpu() - torch.cat([x.unsqueeze(1), ref[:, :-1]], 1)      # per-step displacement vs oracle's
+    ref_step = ref - torch.cat([x.unsqueeze(1), ref[:, :-1]], 1)
+    assert rel_err(traj.transpose(0, 1).cpu(), ref) <= 2e-2
+    assert rel_err(step[:, 0], ref_step[:, 0]) <= 2e-2
