@@ -162,7 +162,7 @@ __global__ void seq_geom_kernel(const float* __restrict__ states, const float* _
 // ------------------------------------------------------------------------------------------------
 // multi-problem, multi-term fp32 GEMM
 // ------------------------------------------------------------------------------------------------
-constexpr int GK = 16, GT = 256, GPAD = 4, GS = 4;
+constexpr int GT = 256;
 constexpr int MAX_TERMS = 4, MAX_PROB = 9;     // sizeof(Batch) stays under the 4 KB of kernel parameters
 enum SeqAct { ACT_NONE = 0, ACT_TANH = 1, ACT_RELU = 2, ACT_SIGMOID = 3, ACT_SILU = 4, ACT_ELU = 5 };
 
@@ -228,12 +228,16 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 template <int BM, int BN, bool TC>
 __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
   static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variant: 64 x 64 tiles");
+  // K slab: 16 on the CUDA cores; 32 in tensor-core mode (3 stages), where a slab's arithmetic is a handful of MMAs and
+  // the copy ring / barrier per slab is what the loop costs -- dynamic shared memory there (54 KB per CTA)
+  constexpr int GK = TC ? 32 : 16, GS = TC ? 3 : 4, CPR = GK / 4;
   constexpr int TM = BM / 16, TN = BN / 16, LD = GK + 4;
   const Problem& P = bt.p[blockIdx.z];
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (m0 >= P.M || n0 >= P.N) return;
-  __shared__ __align__(16) float As[GS][BM][LD];
-  __shared__ __align__(16) float Ws[GS][BN][LD];
+  extern __shared__ __align__(16) float seq_smem[];
+  float (*As)[BM][LD] = reinterpret_cast<float (*)[BM][LD]>(seq_smem);
+  float (*Ws)[BN][LD] = reinterpret_cast<float (*)[BN][LD]>(seq_smem + GS * BM * LD);
   const int tid = threadIdx.x;
   // a warp covers 8 columns x 4 rows of the 16 x 16 thread grid: a 128-bit operand read touches 8 distinct W rows
   // (one 128-byte wavefront) and 4 distinct A rows (broadcast within each quarter warp) -- 8 wavefronts per 64 FFMAs
@@ -261,8 +265,8 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
     const int lda = T.lda, ldw = T.ldw;
     const bool avec = (lda % 4 == 0) && ((((uintptr_t)Ab) & 15) == 0);
     const bool wvec = (ldw % 4 == 0) && ((((uintptr_t)Wb) & 15) == 0);
-    // per-thread copy slots of a slab: chunk c = tid + 256 q covers (row c/4, k offset 4 (c%4)) of A, then of W
-    constexpr int NQ = (BM + BN) * 4 / GT;
+    // per-thread copy slots of a slab: chunk c = tid + 256 q covers (row c/CPR, k offset 4 (c%CPR)) of A, then of W
+    constexpr int NQ = (BM + BN) * CPR / GT;
     const float* qsrc[NQ];
     unsigned qdst[NQ];
     int qlim[NQ];               // number of k's (from the slot's first one at slab 0) that may be read: 0 for rows outside
@@ -270,9 +274,9 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
       int c = q * GT + tid;
-      const bool isA = c < BM * 4;
-      if (!isA) c -= BM * 4;
-      const int row = c >> 2, kc = (c & 3) * 4;
+      const bool isA = c < BM * CPR;
+      if (!isA) c -= BM * CPR;
+      const int row = c / CPR, kc = (c % CPR) * 4;
       const int grow = (isA ? m0 : n0) + row;
       const bool rok = grow < (isA ? P.M : P.N);
       const float* base = isA ? Ab : Wb;
@@ -285,7 +289,7 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
 #pragma unroll
       for (int q = 0; q < NQ; ++q) {
         const int left = qlim[q] - kt * GK;                       // k's left from this chunk's first element
-        const unsigned dst = qdst[q] + (unsigned)stage * (unsigned)(((q * GT + tid) < BM * 4 ? BM : BN) * LD * 4);
+        const unsigned dst = qdst[q] + (unsigned)stage * (unsigned)(((q * GT + tid) < BM * CPR ? BM : BN) * LD * 4);
         if (qvec[q]) {
           const int nb = left <= 0 ? 0 : (left >= 4 ? 16 : left * 4);
           asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(nb > 0 ? qsrc[q] + kt * GK : qsrc[q]),
@@ -315,10 +319,12 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
       const int cur = kt % GS;
       if (TC) {
         if constexpr (TC) {
+#pragma unroll
+          for (int ks = 0; ks < GK / 16; ++ks) {
           uint32_t afr[2][4], bfr[2][2];
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt) {
-            const float* r0 = &As[cur][wm * 32 + mt * 16 + g][2 * tq];
+            const float* r0 = &As[cur][wm * 32 + mt * 16 + g][16 * ks + 2 * tq];
             const float2 v0 = *reinterpret_cast<const float2*>(r0), v1 = *reinterpret_cast<const float2*>(r0 + 8 * LD);
             const float2 v2 = *reinterpret_cast<const float2*>(r0 + 8), v3 = *reinterpret_cast<const float2*>(r0 + 8 * LD + 8);
             afr[mt][0] = pack_bf16x2(v0.x, v0.y); afr[mt][1] = pack_bf16x2(v1.x, v1.y);
@@ -326,7 +332,7 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
           }
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) {
-            const float* r0 = &Ws[cur][wn * 16 + nt * 8 + g][2 * tq];
+            const float* r0 = &Ws[cur][wn * 16 + nt * 8 + g][16 * ks + 2 * tq];
             const float2 v0 = *reinterpret_cast<const float2*>(r0), v1 = *reinterpret_cast<const float2*>(r0 + 8);
             bfr[nt][0] = pack_bf16x2(v0.x, v0.y); bfr[nt][1] = pack_bf16x2(v1.x, v1.y);
           }
@@ -339,6 +345,7 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
                            : "+f"(acc[2 * mt][2 * nt]), "+f"(acc[2 * mt][2 * nt + 1]), "+f"(acc[2 * mt + 1][2 * nt]),
                              "+f"(acc[2 * mt + 1][2 * nt + 1])
                            : "r"(afr[mt][0]), "r"(afr[mt][1]), "r"(afr[mt][2]), "r"(afr[mt][3]), "r"(bfr[nt][0]), "r"(bfr[nt][1]));
+          }
         }
         continue;
       }
@@ -422,13 +429,22 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, bool tc = false) {
   const int64_t big = (int64_t)((maxM + 63) / 64) * ((maxN + 63) / 64) * nprob;
   if (tc) {           // tensor-core mode: every problem on the 64 x 64 MMA variant
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64, true><<<grid, GT, 0, st>>>(bt);
+    constexpr int smem_tc = 3 * 128 * 36 * 4;
+    static std::atomic<int> opted{-1};      // the opt-in above 48 KB is per device; redo it when the device changes
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (opted.load(std::memory_order_relaxed) != dev) {
+      cudaError_t e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_tc);
+      if (e != cudaSuccess) return (int)e;
+      opted.store(dev, std::memory_order_relaxed);
+    }
+    seq_gemm_kernel<64, 64, true><<<grid, GT, smem_tc, st>>>(bt);
   } else if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64, false><<<grid, GT, 0, st>>>(bt);
+    seq_gemm_kernel<64, 64, false><<<grid, GT, 4 * 128 * 20 * 4, st>>>(bt);
   } else {
     dim3 grid((maxM + 31) / 32, (maxN + 31) / 32, nprob);
-    seq_gemm_kernel<32, 32, false><<<grid, GT, 0, st>>>(bt);
+    seq_gemm_kernel<32, 32, false><<<grid, GT, 4 * 64 * 20 * 4, st>>>(bt);
   }
   AE_LAUNCH_CHECK();
   return 0;
