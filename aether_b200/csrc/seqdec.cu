@@ -314,9 +314,14 @@ __global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __
     for (int kt = 0; kt < nk; ++kt) {
       cp_async_wait<GS - 2>();  // slab kt has landed (for this thread's copies; the barrier covers the others)
       __syncthreads();          // ... and everybody is done with slab kt-1, whose stage is refilled next
+#if !defined(SEQ_EXP_NOCOPY)      // diagnostic builds (tools/seq_exp.py): the loop without its copies / without its arithmetic
       if (kt + GS - 1 < nk) issue(kt + GS - 1, (kt + GS - 1) % GS);
+#endif
       cp_async_commit();
       const int cur = kt % GS;
+#if defined(SEQ_EXP_NOMATH)
+      continue;
+#endif
       if (TC) {
         if constexpr (TC) {
 #pragma unroll
