@@ -9,7 +9,7 @@ torch.manual_seed(0)
 D, N, B, H, K, Hf, T = 2, 5, 64, 512, 2, 512, 3
 p = {"num_vars": N, "input_size": 2 * D, "use_3d": False, "decoder_hidden": H, "num_edge_types": K, "skip_first": False,
      "decoder_dropout": 0.0, "encoder_hidden": Hf, "gumbel_temp": 0.5}
-m = Seq2SeqAether(p).cuda().eval()
+m = Seq2SeqAether(p, precision=os.environ.get("SEQ_PREC", "fp32")).cuda().eval()
 E = N * (N - 1)
 x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1).cuda()
 edges = torch.nn.functional.one_hot(torch.randint(0, K, (T, B, E)), K).float().cuda()
