@@ -226,12 +226,14 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // a warp owns 32 rows x 16 columns (2 x 2 MMAs per 16-k slab: 12 64-bit shared-memory reads, 12 packs, 4 MMAs where the
 // CUDA-core loop has 32 reads and 256 FFMAs).  Biases, activations, sums over terms and outputs stay fp32.
 template <int BM, int BN, bool TC>
-__global__ void __launch_bounds__(GT, BM == 64 ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+__global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
   static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variant: 64 x 64 tiles");
   // K slab: 16 on the CUDA cores; 32 in tensor-core mode (3 stages), where a slab's arithmetic is a handful of MMAs and
   // the copy ring / barrier per slab is what the loop costs -- dynamic shared memory there (54 KB per CTA)
   constexpr int GK = TC ? 32 : 16, GS = TC ? 3 : 4, CPR = GK / 4;
-  constexpr int TM = BM / 16, TN = BN / 16, LD = GK + 4;
+  // row pitch: +4 floats keeps the CUDA-core loop's 128-bit reads on distinct bank groups; +8 does the same for the 64-bit
+  // fragment reads of the tensor-core loop (bank = 8 g + 2 tq over a half warp)
+  constexpr int TM = BM / 16, TN = BN / 16, LD = GK + (TC ? 8 : 4);
   const Problem& P = bt.p[blockIdx.z];
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (m0 >= P.M || n0 >= P.N) return;
@@ -434,7 +436,7 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, bool tc = false) {
   const int64_t big = (int64_t)((maxM + 63) / 64) * ((maxN + 63) / 64) * nprob;
   if (tc) {           // tensor-core mode: every problem on the 64 x 64 MMA variant
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    constexpr int smem_tc = 3 * 128 * 36 * 4;
+    constexpr int smem_tc = 3 * 128 * 40 * 4;
     static std::atomic<int> opted{-1};      // the opt-in above 48 KB is per device; redo it when the device changes
     int dev = 0;
     cudaGetDevice(&dev);
