@@ -215,7 +215,7 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
 // BM x BN tile, 256 threads, (BM/16) x (BN/16) outputs per thread: rows ty + 16 i, columns tx + 16 j.  K slabs of 16
-// go through a GS-stage cp.async ring in the operands' own layout ([row][k], rows padded to 20 floats): one 16-byte
+// go through a GS-stage cp.async ring in the operands' own layout ([row][k], rows padded by 4 floats): 16-byte
 // copy per thread and operand tile (zero-filled past K through the copy's source size; 4-byte copies when a row is not
 // 16-byte aligned, e.g. the 39-wide 3D features).  The inner loop reads 4 k's of a row as one vector; with rows
 // strided by 16 between a thread's outputs, the 8 lanes of a shared-memory phase hit 8 different 16-byte bank groups
@@ -228,9 +228,9 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 template <int BM, int BN, bool TC>
 __global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
   static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variant: 64 x 64 tiles");
-  // K slab: 16 on the CUDA cores; 32 in tensor-core mode (3 stages), where a slab's arithmetic is a handful of MMAs and
-  // the copy ring / barrier per slab is what the loop costs -- dynamic shared memory there (54 KB per CTA)
-  constexpr int GK = TC ? 32 : 16, GS = TC ? 3 : 4, CPR = GK / 4;
+  // K slabs of 32 (16-wide slabs measured 2-5 % slower on the CUDA cores, 6 % in tensor-core mode: a barrier and a copy
+  // group per slab either way), 3 stages for the 64 x 64 tiles, 4 for 32 x 32; dynamic shared memory (54-60 KB at 64 x 64)
+  constexpr int GK = 32, GS = (BM == 64) ? 3 : 4, CPR = GK / 4;
   // row pitch: +4 floats keeps the CUDA-core loop's 128-bit reads on distinct bank groups; +8 does the same for the 64-bit
   // fragment reads of the tensor-core loop (bank = 8 g + 2 tq over a half warp)
   constexpr int TM = BM / 16, TN = BN / 16, LD = GK + (TC ? 8 : 4);
@@ -434,24 +434,27 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, bool tc = false) {
   }
   if (maxM == 0 || maxN == 0 || nprob == 0) return 0;
   const int64_t big = (int64_t)((maxM + 63) / 64) * ((maxN + 63) / 64) * nprob;
+  // dynamic shared memory of the three instantiations (above 48 KB needs a per-device opt-in)
+  constexpr int smem_tc = 3 * 128 * 40 * 4, smem_64 = 3 * 128 * 36 * 4, smem_32 = 4 * 64 * 36 * 4;
+  static std::atomic<int> opted{-1};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (opted.load(std::memory_order_relaxed) != dev) {
+    cudaError_t e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_tc);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_64);
+    if (e != cudaSuccess) return (int)e;
+    opted.store(dev, std::memory_order_relaxed);
+  }
   if (tc) {           // tensor-core mode: every problem on the 64 x 64 MMA variant
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    constexpr int smem_tc = 3 * 128 * 40 * 4;
-    static std::atomic<int> opted{-1};      // the opt-in above 48 KB is per device; redo it when the device changes
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (opted.load(std::memory_order_relaxed) != dev) {
-      cudaError_t e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_tc);
-      if (e != cudaSuccess) return (int)e;
-      opted.store(dev, std::memory_order_relaxed);
-    }
     seq_gemm_kernel<64, 64, true><<<grid, GT, smem_tc, st>>>(bt);
   } else if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64, false><<<grid, GT, 4 * 128 * 20 * 4, st>>>(bt);
+    seq_gemm_kernel<64, 64, false><<<grid, GT, smem_64, st>>>(bt);
   } else {
     dim3 grid((maxM + 31) / 32, (maxN + 31) / 32, nprob);
-    seq_gemm_kernel<32, 32, false><<<grid, GT, 4 * 64 * 20 * 4, st>>>(bt);
+    seq_gemm_kernel<32, 32, false><<<grid, GT, smem_32, st>>>(bt);
   }
   AE_LAUNCH_CHECK();
   return 0;
