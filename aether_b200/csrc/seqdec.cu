@@ -214,12 +214,12 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
-// BM x BN tile, 256 threads, (BM/16) x (BN/16) outputs per thread: rows ty + 16 i, columns tx + 16 j.  K slabs of 16
+// BM x BN tile, 256 threads, (BM/16) x (BN/16) outputs per thread: rows ty + 16 i, columns tx + 16 j.  K slabs of 32
 // go through a GS-stage cp.async ring in the operands' own layout ([row][k], rows padded by 4 floats): 16-byte
 // copy per thread and operand tile (zero-filled past K through the copy's source size; 4-byte copies when a row is not
 // 16-byte aligned, e.g. the 39-wide 3D features).  The inner loop reads 4 k's of a row as one vector; with rows
 // strided by 16 between a thread's outputs, the 8 lanes of a shared-memory phase hit 8 different 16-byte bank groups
-// (row step = 5 groups).  The small tile exists for the node-level problems (B*N rows): at 64 x 64 they are 40 CTAs.
+// (row pitch 36 floats = 9 groups).  The small tile exists for the node-level problems (B*N rows): at 64 x 64 they are 40 CTAs.
 //
 // TC (64 x 64 only; models with precision = "bf16", tolerance 2e-2): the same ring, but the products run on the tensor
 // cores -- mma.sync.m16n8k16, bf16 operands rounded from the fp32 tiles in registers, fp32 accumulate; 8 warps as 2 x 4,
