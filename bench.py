@@ -856,7 +856,28 @@ def seq2seq_report(dev, steps=20, reps=10):
     ref = so.predict_future(w, x.unsqueeze(1), edges[:3].transpose(0, 1), 3, D, K, False, return_everything=False)
     cpu_ms_per_step = (time.perf_counter() - t0) * 1e3 / 3
     err = float((traj[:3].transpose(0, 1).cpu() - ref).abs().max() / ref.abs().max())
-    return {"workload": "seq2seq RecurrentDecoder rollout: 2D, 5 particles, batch 64, decoder_hidden 512, 2 edge types, "
+    # the same rollout in tensor-core mode (precision="bf16": mma.sync, 2e-2 tolerance), error against the same oracle steps
+    mb = Seq2SeqAether({"num_vars": N, "input_size": 2 * D, "use_3d": False, "decoder_hidden": Hd, "num_edge_types": K,
+                        "skip_first": False, "decoder_dropout": 0.0, "encoder_hidden": Hd, "gumbel_temp": 0.5},
+                       precision="bf16").to(dev).eval()
+    mb.load_state_dict(m.state_dict())
+    rb = DecoderRollout(mb, B, steps, cuda_graph=True)
+    for _ in range(3):
+        trajb = rb.run(xd, ed)
+    tb = []
+    for _ in range(reps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rb.run(xd, ed)
+        b.record()
+        torch.cuda.synchronize()
+        tb.append(a.elapsed_time(b))
+    tb.sort()
+    errb = float((trajb[:3].transpose(0, 1).cpu() - ref).abs().max() / ref.abs().max())
+    bf16 = {"us_per_step": 1e3 * tb[len(tb) // 2] / steps, "rel_err_vs_oracle_3_steps": errb, "tolerance": 2e-2}
+    return {"tensor_core_mode": bf16,
+            "workload": "seq2seq RecurrentDecoder rollout: 2D, 5 particles, batch 64, decoder_hidden 512, 2 edge types, "
                         "%d prediction steps, one CUDA graph" % steps, "dtype": "f32", "ms_per_rollout": ms,
             "us_per_step": 1e3 * ms / steps, "particle_steps_per_s": B * N * steps / (ms * 1e-3),
             "launches_per_rollout": r.launches_per_replay, "rel_err_vs_oracle_3_steps": err,
