@@ -37,7 +37,16 @@ class FourierFeatureMapper(nn.Module):
         self.register_buffer("B", torch.from_numpy(rng.normal(0, std, size=(in_size, out_size))).float())
 
 
-class RecurrentDecoder(nn.Module):
+class _NoWorkspacePickle:
+    """torch.save(model) must not carry the scratch workspace (it is re-created on the next call)."""
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        d["_ws"] = None
+        return d
+
+
+class RecurrentDecoder(_NoWorkspacePickle, nn.Module):
     def __init__(self, params):
         super().__init__()
         self.num_vars = num_vars = params["num_vars"]
@@ -222,7 +231,7 @@ class AnisotropicEdgeFilter(nn.Module):
         nn.init.orthogonal_(self.edge_filter[2].weight)
 
 
-class Encoder(nn.Module):
+class Encoder(_NoWorkspacePickle, nn.Module):
     """Prior branch of the reference's edge-type encoder (nn/seq2seq/aether.py:249-425) on csrc/seqdec.cu: same
     constructor (``params`` dict), submodule / parameter names and creation order (a reference ``encoder.*`` state_dict
     loads strictly), ``forward(inputs, predicted_field)`` and ``single_step_forward(inputs, prior_state,

@@ -61,3 +61,21 @@ def test_seeded_init_reproduces_the_reference():
             assert np.array_equal(sd[k].numpy(), g[k]), k
         elif k.startswith("enc.") and ".bn." not in k:
             assert np.array_equal(sd["encoder." + k[4:]].numpy(), g[k]), k
+
+
+def test_pickle_drops_workspace():
+    import io
+    from aether_b200.seq2seq import Seq2SeqAether
+    m = Seq2SeqAether.with_encoder({
+        "num_vars": 3, "input_size": 4, "use_3d": False, "decoder_hidden": 8, "num_edge_types": 2, "skip_first": False,
+        "decoder_dropout": 0.0, "encoder_hidden": 8, "encoder_rnn_hidden": 4, "encoder_rnn_type": "lstm",
+        "encoder_dropout": 0.0, "encoder_mlp_num_layers": 1, "prior_num_layers": 1, "gumbel_temp": 0.5})
+    m.decoder._ws = torch.zeros(1 << 20, dtype=torch.uint8)
+    m.encoder._ws = torch.zeros(1 << 20, dtype=torch.uint8)
+    buf = io.BytesIO()
+    torch.save(m, buf)                                      # the reference saves whole modules (experiments/*/main.py)
+    assert buf.tell() < (1 << 19)
+    buf.seek(0)
+    m2 = torch.load(buf, weights_only=False)
+    assert m2.decoder._ws is None and m2.encoder._ws is None
+    assert all(torch.equal(a, b) for a, b in zip(m.state_dict().values(), m2.state_dict().values()))
