@@ -225,9 +225,9 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // cores -- mma.sync.m16n8k16, bf16 operands rounded from the fp32 tiles in registers, fp32 accumulate; 8 warps as 2 x 4,
 // a warp owns 32 rows x 16 columns (2 x 2 MMAs per 16-k slab: 12 64-bit shared-memory reads, 12 packs, 4 MMAs where the
 // CUDA-core loop has 32 reads and 256 FFMAs).  Biases, activations, sums over terms and outputs stay fp32.
-template <int BM, int BN, bool TC>
-__global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : 3) seq_gemm_kernel(const __grid_constant__ Batch bt) {
-  static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variant: 64 x 64 tiles");
+template <int BM, int BN, int TC>
+__global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : (TC == 2 ? 2 : 3)) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+  static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variants: 64 x 64 tiles");
   // K slabs of 32 (16-wide slabs measured 2-5 % slower on the CUDA cores, 6 % in tensor-core mode: a barrier and a copy
   // group per slab either way), 3 stages for the 64 x 64 tiles, 4 for 32 x 32; dynamic shared memory (54-60 KB at 64 x 64)
   constexpr int GK = 32, GS = (BM == 64) ? 3 : 4, CPR = GK / 4;
@@ -328,30 +328,65 @@ __global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : 3) seq_gemm_kernel
         if constexpr (TC) {
 #pragma unroll
           for (int ks = 0; ks < GK / 16; ++ks) {
-          uint32_t afr[2][4], bfr[2][2];
+          // NS = 1: operands rounded to bf16.  NS = 3 (TC == 2): every fp32 operand as hi + mid + lo, three bf16 of 8
+          // mantissa bits each (24 in all), and the six products whose weight is >= 2^-16 of the full one -- lo.hi,
+          // hi.lo, mid.mid, mid.hi, hi.mid, hi.hi, smallest first -- accumulate in fp32: the fp32 tolerance on tensor cores
+          constexpr int NS = TC == 2 ? 3 : 1;
+          uint32_t afr[NS][2][4], bfr[NS][2][2];
+          auto split = [&](float x, float y, uint32_t (&out)[NS]) {
+            out[0] = pack_bf16x2(x, y);
+            if constexpr (NS == 3) {
+              const float rx = x - __uint_as_float(out[0] << 16), ry = y - __uint_as_float(out[0] & 0xffff0000u);
+              out[1] = pack_bf16x2(rx, ry);
+              const float sx = rx - __uint_as_float(out[1] << 16), sy = ry - __uint_as_float(out[1] & 0xffff0000u);
+              out[2] = pack_bf16x2(sx, sy);
+            }
+          };
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt) {
             const float* r0 = &As[cur][wm * 32 + mt * 16 + g][16 * ks + 2 * tq];
-            const float2 v0 = *reinterpret_cast<const float2*>(r0), v1 = *reinterpret_cast<const float2*>(r0 + 8 * LD);
-            const float2 v2 = *reinterpret_cast<const float2*>(r0 + 8), v3 = *reinterpret_cast<const float2*>(r0 + 8 * LD + 8);
-            afr[mt][0] = pack_bf16x2(v0.x, v0.y); afr[mt][1] = pack_bf16x2(v1.x, v1.y);
-            afr[mt][2] = pack_bf16x2(v2.x, v2.y); afr[mt][3] = pack_bf16x2(v3.x, v3.y);
+            const float2 v[4] = {*reinterpret_cast<const float2*>(r0), *reinterpret_cast<const float2*>(r0 + 8 * LD),
+                                 *reinterpret_cast<const float2*>(r0 + 8), *reinterpret_cast<const float2*>(r0 + 8 * LD + 8)};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              uint32_t o[NS];
+              split(v[e].x, v[e].y, o);
+#pragma unroll
+              for (int q = 0; q < NS; ++q) afr[q][mt][e] = o[q];
+            }
           }
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) {
             const float* r0 = &Ws[cur][wn * 16 + nt * 8 + g][16 * ks + 2 * tq];
-            const float2 v0 = *reinterpret_cast<const float2*>(r0), v1 = *reinterpret_cast<const float2*>(r0 + 8);
-            bfr[nt][0] = pack_bf16x2(v0.x, v0.y); bfr[nt][1] = pack_bf16x2(v1.x, v1.y);
+            const float2 v[2] = {*reinterpret_cast<const float2*>(r0), *reinterpret_cast<const float2*>(r0 + 8)};
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              uint32_t o[NS];
+              split(v[e].x, v[e].y, o);
+#pragma unroll
+              for (int q = 0; q < NS; ++q) bfr[q][nt][e] = o[q];
+            }
           }
+          auto mma = [&](int mt, int nt, const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+            asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+                         "{%0, %1, %2, %3};"
+                         : "+f"(acc[2 * mt][2 * nt]), "+f"(acc[2 * mt][2 * nt + 1]), "+f"(acc[2 * mt + 1][2 * nt]),
+                           "+f"(acc[2 * mt + 1][2 * nt + 1])
+                         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+          };
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-            for (int nt = 0; nt < 2; ++nt)
-              asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
-                           "{%0, %1, %2, %3};"
-                           : "+f"(acc[2 * mt][2 * nt]), "+f"(acc[2 * mt][2 * nt + 1]), "+f"(acc[2 * mt + 1][2 * nt]),
-                             "+f"(acc[2 * mt + 1][2 * nt + 1])
-                           : "r"(afr[mt][0]), "r"(afr[mt][1]), "r"(afr[mt][2]), "r"(afr[mt][3]), "r"(bfr[nt][0]), "r"(bfr[nt][1]));
+            for (int nt = 0; nt < 2; ++nt) {
+              if constexpr (NS == 3) {
+                mma(mt, nt, afr[2][mt], bfr[0][nt]);
+                mma(mt, nt, afr[0][mt], bfr[2][nt]);
+                mma(mt, nt, afr[1][mt], bfr[1][nt]);
+                mma(mt, nt, afr[1][mt], bfr[0][nt]);
+                mma(mt, nt, afr[0][mt], bfr[1][nt]);
+              }
+              mma(mt, nt, afr[0][mt], bfr[0][nt]);
+            }
           }
         }
         continue;
@@ -426,7 +461,7 @@ Term make_term(const float* A, int lda, const float* W, int ldw, const float* bi
   return t;
 }
 
-int launch_batch(const Batch& bt, int nprob, cudaStream_t st, bool tc = false) {
+int launch_batch(const Batch& bt, int nprob, cudaStream_t st, int tc = 0) {
   int maxM = 0, maxN = 0;
   for (int i = 0; i < nprob; ++i) {
     maxM = bt.p[i].M > maxM ? bt.p[i].M : maxM;
@@ -440,21 +475,24 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, bool tc = false) {
   int dev = 0;
   cudaGetDevice(&dev);
   if (opted.load(std::memory_order_relaxed) != dev) {
-    cudaError_t e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_tc);
+    cudaError_t e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_tc);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_64);
+      e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_64);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(seq_gemm_kernel<64, 64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_tc);
     if (e != cudaSuccess) return (int)e;
     opted.store(dev, std::memory_order_relaxed);
   }
-  if (tc) {           // tensor-core mode: every problem on the 64 x 64 MMA variant
+  if (tc) {           // tensor-core modes: every problem on the 64 x 64 MMA variants
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64, true><<<grid, GT, smem_tc, st>>>(bt);
+    if (tc == 2) seq_gemm_kernel<64, 64, 2><<<grid, GT, smem_tc, st>>>(bt);
+    else seq_gemm_kernel<64, 64, 1><<<grid, GT, smem_tc, st>>>(bt);
   } else if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64, false><<<grid, GT, smem_64, st>>>(bt);
+    seq_gemm_kernel<64, 64, 0><<<grid, GT, smem_64, st>>>(bt);
   } else {
     dim3 grid((maxM + 31) / 32, (maxN + 31) / 32, nprob);
-    seq_gemm_kernel<32, 32, false><<<grid, GT, smem_32, st>>>(bt);
+    seq_gemm_kernel<32, 32, 0><<<grid, GT, smem_32, st>>>(bt);
   }
   AE_LAUNCH_CHECK();
   return 0;
@@ -705,7 +743,7 @@ int seq_geometry(const AetherSeqDims* d, const float* states, const float* field
 
 int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* states, float* field, const SeqWs& w,
               cudaStream_t st) {
-  const bool tcm = (d->flags & AETHER_SEQ_F_BF16) != 0;
+  const int tcm = (d->flags & AETHER_SEQ_F_BF16) ? 1 : ((d->flags & AETHER_SEQ_F_SPLIT) ? 2 : 0);
   const int D = d->num_dims, Hf = d->field_hidden;
   if (Hf < 4 || p->rff_B == nullptr) return AETHER_E_BADARG;
   for (int i = 0; i < 3; ++i)
@@ -731,7 +769,7 @@ int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* sta
 int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* states, const float* hidden_in,
              const float* edge_types, const float* field, float* states_out, float* hidden_out, const SeqWs& w,
              cudaStream_t st) {
-  const bool tcm = (d->flags & AETHER_SEQ_F_BF16) != 0;
+  const int tcm = (d->flags & AETHER_SEQ_F_BF16) ? 1 : ((d->flags & AETHER_SEQ_F_SPLIT) ? 2 : 0);
   const int D = d->num_dims, N = d->num_vars, H = d->hidden, Kt = d->n_types, t0 = d->skip_first ? 1 : 0;
   const int O = D * (D - 1) / 2, F = 4 * D + O, KE = 2 * F + 3 * D, KR = 3 * D + F;
   const int64_t BN = d->batch * N, BE = BN * (N - 1);
@@ -839,7 +877,7 @@ int seq_params_ok(const AetherSeqParams* p) {
 int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float* states, const float* field,
                 const float* h_in, const float* c_in, float* logits, float* h_out, float* c_out, const SeqWs& w,
                 cudaStream_t st) {
-  const bool tcm = (d->flags & AETHER_SEQ_F_BF16) != 0;
+  const int tcm = (d->flags & AETHER_SEQ_F_BF16) ? 1 : ((d->flags & AETHER_SEQ_F_SPLIT) ? 2 : 0);
   const int D = d->num_dims, N = d->num_vars, H = d->field_hidden, R = d->rnn_hidden, PH = d->prior_hidden, Kt = d->n_types;
   const int O = D * (D - 1) / 2, F = 4 * D + O, KE = 2 * F + 3 * D, KR = 3 * D + F, KP = D + O;
   const int64_t BN = d->batch * N, BE = BN * (N - 1);

@@ -103,7 +103,7 @@ class RecurrentDecoder(_NoWorkspacePickle, nn.Module):
     def dims(self, batch: int, field_hidden: int = 0, rnn_hidden: int = 0, prior_hidden: int = 0) -> "_lib.AetherSeqDims":
         return _lib.AetherSeqDims(self.num_dims, self.num_vars, self.msg_out_shape, self.edge_types,
                                   1 if self.skip_first_edge_type else 0, field_hidden, rnn_hidden, prior_hidden,
-                                  1 if getattr(self, "precision", "fp32") == "bf16" else 0, batch)
+                                  {"bf16": 1, "fp32x3": 2}.get(getattr(self, "precision", "fp32"), 0), batch)
 
     def c_params(self, field_net: Optional[nn.Module] = None, rff: Optional[torch.Tensor] = None):
         """(struct, tensors kept alive) for the library; every parameter must be a contiguous fp32 CUDA tensor."""
@@ -332,7 +332,7 @@ class Encoder(_NoWorkspacePickle, nn.Module):
 
     def _dims(self, batch):
         return _lib.AetherSeqDims(self.num_dims, self.num_vars, 4, self.num_edges, 0, self.hidden_size, self.rnn_hidden,
-                                  int(self.prior_hidden or 0), 1 if getattr(self, "precision", "fp32") == "bf16" else 0, batch)
+                                  int(self.prior_hidden or 0), {"bf16": 1, "fp32x3": 2}.get(getattr(self, "precision", "fp32"), 0), batch)
 
     def initial_state(self, batch, device):
         n = batch * self.num_vars * (self.num_vars - 1)
@@ -395,8 +395,8 @@ class Seq2SeqAether(nn.Module):
         """precision: "fp32" (CUDA cores, 1e-5 against the reference) or "bf16" (every Linear on the tensor cores with
         bf16 operands and fp32 accumulation, 2e-2)."""
         super().__init__()
-        if precision not in ("fp32", "bf16"):
-            raise ValueError("precision must be 'fp32' or 'bf16'")
+        if precision not in ("fp32", "bf16", "fp32x3"):
+            raise ValueError("precision must be 'fp32', 'fp32x3' or 'bf16'")
         self.num_vars = params["num_vars"]
         self.encoder = encoder
         self.decoder = RecurrentDecoder(params)

@@ -296,6 +296,10 @@ int aether_dynfield_backward(int32_t num_dims, int64_t n_nodes, int32_t num_node
 /* every Linear on the tensor cores (mma.sync, bf16 operands rounded from the fp32 tensors on the fly, fp32 accumulate;
  * biases, activations, sums and all inputs / outputs stay fp32): the bf16 tolerance (2e-2) instead of 1e-5 */
 #define AETHER_SEQ_F_BF16 1u
+/* every Linear on the tensor cores with fp32 accuracy: each fp32 operand split into three bf16 (hi + mid + lo, 24 mantissa
+ * bits), six mma.sync products per operand pair, fp32 accumulate -- the fp32 tolerance (1e-5), not bit-identical to the
+ * CUDA-core summation order */
+#define AETHER_SEQ_F_SPLIT 2u
 typedef struct AetherSeqDims {
   int32_t num_dims;      /* D: 2 or 3 (use_3d)                              */
   int32_t num_vars;      /* N particles per trajectory, 2..64               */

@@ -305,3 +305,47 @@ def test_bf16_mode_at_experiment_shape_against_oracle():
     ref_step = ref - torch.cat([x.unsqueeze(1), ref[:, :-1]], 1)
     assert rel_err(traj.transpose(0, 1).cpu(), ref) <= 2e-2
     assert rel_err(step[:, 0], ref_step[:, 0]) <= 2e-2
+
+
+# ---- fp32x3 mode: tensor cores at the fp32 tolerance (each operand split into three bf16, six products) -----------------
+@pytest.mark.parametrize("name", CASES)
+def test_fp32x3_mode_meets_the_fp32_bars(name):
+    from aether_b200.seq2seq import Seq2SeqAether
+    g = load_golden(name)
+    m = Seq2SeqAether.with_encoder(enc_params_of(g), precision="fp32x3")
+    m.load_state_dict(build_full(g).state_dict())
+    m = m.cuda().eval()
+    out, hid = m.decoder(dev(g, "step_inputs"), dev(g, "step_hidden"), dev(g, "step_edges"), dev(g, "step_field"))
+    assert rel_err(out.cpu(), g["step_outputs"]) <= 1e-5 and rel_err(hid.cpu(), g["step_hidden_new"]) <= 1e-5
+    f, _ = m.predict_field(dev(g, "step_inputs"))
+    assert rel_err(f.cpu(), g["field_pred"]) <= 2e-5
+    burn = dev(g, "pf_inputs")
+    field, _ = m.predict_field(burn[:, :-1].transpose(2, 1).contiguous())
+    logits, _, (h, c) = m.encoder(burn[:, :-1], field)
+    assert rel_err(logits.cpu(), g["enc_prior_logits"]) <= 1e-5
+    assert rel_err(h.cpu(), g["enc_state_h"]) <= 1e-5 and rel_err(c.cpu(), g["enc_state_c"]) <= 1e-5
+    preds = m.predict_future(burn, int(g["pf_steps"]), return_everything=True, edges=dev(g, "pf_edges"))
+    assert rel_err(preds.cpu(), g["pf_predictions"]) <= 1e-4
+
+
+def test_fp32x3_mode_at_experiment_shape_against_oracle():
+    from aether_b200.seq2seq import DecoderRollout, Seq2SeqAether
+    from oracle import seq2seq_oracle as so
+    torch.manual_seed(11)
+    D, N, B, H, K, T = 2, 5, 64, 512, 2, 4
+    p = {"num_vars": N, "input_size": 2 * D, "use_3d": False, "decoder_hidden": H, "num_edge_types": K,
+         "skip_first": False, "decoder_dropout": 0.0, "encoder_hidden": H, "gumbel_temp": 0.5}
+    m = Seq2SeqAether(p, precision="fp32x3").cuda().eval()
+    w = _oracle_weights(m)
+    E = N * (N - 1)
+    x = torch.cat([torch.randn(B, N, D), 0.5 * torch.nn.functional.normalize(torch.randn(B, N, D), dim=-1)], -1)
+    hid = 0.5 * torch.randn(B, N, H)
+    soft = torch.softmax(torch.randn(B, E, K), -1)
+    field = 0.3 * torch.randn(B, N, D)
+    out, h2 = m.decoder(x.cuda(), hid.cuda(), soft.cuda(), field.cuda())
+    o_ref, h_ref = so.decoder_step(w, x, hid, soft, field, D, K, False)
+    assert rel_err(out.cpu(), o_ref) <= 1e-5 and rel_err(h2.cpu(), h_ref) <= 1e-5
+    onehot = torch.nn.functional.one_hot(torch.randint(0, K, (T, B, E)), K).float()
+    traj = DecoderRollout(m, B, T, cuda_graph=True).run(x.cuda(), onehot.cuda())
+    ref = so.predict_future(w, x.unsqueeze(1), onehot.transpose(0, 1), T, D, K, False, return_everything=False)
+    assert rel_err(traj.transpose(0, 1).cpu(), ref) <= 1e-4

@@ -49,6 +49,8 @@ if __name__ == "__main__":
     run(3, 5, 32, 512, 2, 512, 5)      # scripts/gravitational_field_3d_aether.sh, --test_pred_steps 5
     run(2, 5, 1024, 256, 2, 256, 20)   # a large evaluation batch
     run(2, 5, 64, 512, 2, 512, 20, precision="bf16")
+    run(2, 5, 64, 512, 2, 512, 20, precision="fp32x3")
+    run(2, 5, 1024, 256, 2, 256, 20, precision="fp32x3")
     run(2, 5, 1024, 256, 2, 256, 20, precision="bf16")
 
 
@@ -83,3 +85,4 @@ def run_full(D, N, B, H, K, He, R, T, reps=10, precision="fp32"):
 if __name__ == "__main__":
     run_full(2, 5, 64, 512, 2, 512, 128, 20)    # electrostatic script: encoder_hidden 512, encoder_rnn_hidden 128
     run_full(2, 5, 64, 512, 2, 512, 128, 20, precision="bf16")
+    run_full(2, 5, 64, 512, 2, 512, 128, 20, precision="fp32x3")
