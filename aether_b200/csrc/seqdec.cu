@@ -483,7 +483,8 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, int tc = 0) {
     if (e != cudaSuccess) return (int)e;
     opted.store(dev, std::memory_order_relaxed);
   }
-  if (tc) {           // tensor-core modes: every problem on the 64 x 64 MMA variants
+  if (tc == 2 && big < 296 && maxM < 1024) tc = 0;   // split mode: node-level launches stay on the small CUDA-core tile
+  if (tc) {           // tensor-core modes: the 64 x 64 MMA variants
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
     if (tc == 2) seq_gemm_kernel<64, 64, 2><<<grid, GT, smem_tc, st>>>(bt);
     else seq_gemm_kernel<64, 64, 1><<<grid, GT, smem_tc, st>>>(bt);
