@@ -79,7 +79,7 @@ def _oracle_weights(m):
 
 @pytest.mark.parametrize("D,N,B,H,K,skip,Hf", [(2, 5, 64, 512, 2, False, 512), (3, 5, 32, 256, 2, True, 128),
                                                (2, 2, 3, 36, 1, False, 20), (3, 7, 5, 64, 4, True, 64),
-                                               (2, 4, 6, 32, 1, True, 16)])
+                                               (2, 4, 6, 32, 1, True, 16), (2, 3, 4, 32, 4, False, 16)])
 def test_step_and_rollout_against_oracle(D, N, B, H, K, skip, Hf):
     """Reference experiment shapes (scripts/electrostatic_field_aether.sh: 5 particles, batch 64, decoder_hidden 512,
     2 edge types; gravitational 3D: batch 32) and edge cases: 2 particles, one edge type, no active type at all
@@ -106,7 +106,8 @@ def test_step_and_rollout_against_oracle(D, N, B, H, K, skip, Hf):
     traj2 = r.run(x.cuda(), onehot.cuda()).clone()                 # replay
     eager = DecoderRollout(m, B, T, cuda_graph=False).run(x.cuda(), onehot.cuda())
     assert torch.equal(traj, traj2) and torch.equal(traj, eager)
-    assert r.launches_per_replay == (14 if K - int(skip) > 0 else 11) * T
+    # (four active edge types: batch A goes out in two launches)
+    assert r.launches_per_replay == (11 if K - int(skip) == 0 else (15 if K - int(skip) == 4 else 14)) * T
     burn = x.unsqueeze(1)
     ref = so.predict_future(w, burn, onehot.transpose(0, 1), T, D, K, skip, return_everything=False)
     assert rel_err(traj.transpose(0, 1).cpu(), ref) <= 1e-4
