@@ -16,6 +16,30 @@
 namespace aether {
 namespace {
 
+// Programmatic dependent launch: every kernel of this file is launched with the programmatic-stream-serialization
+// attribute, lets its dependents be scheduled when its CTAs are done with their main loops (pdl_trigger; triggering at
+// CTA start measured slower: the waiting dependents take SM slots from the primary's later waves) and reads nothing a
+// predecessor wrote before pdl_wait returns (= the predecessor grid has completed and its writes are visible).  The
+// next kernel's CTAs are then resident and past their set-up when the previous one drains, which takes the launch
+// latency out of the 14-link chain of a decoder step (also inside a captured CUDA graph: programmatic edges).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+cudaError_t seq_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 constexpr float PI_F = 3.14159274f;       // float(np.pi)
 constexpr float TWO_PI_F = 6.28318548f;   // float(2 * np.pi)
 
@@ -125,6 +149,7 @@ __device__ __forceinline__ void load_state(const float* states, const float* fie
 template <int D>
 __global__ void seq_geom_kernel(const float* __restrict__ states, const float* __restrict__ field, int N, int64_t B,
                                 float* __restrict__ relx, float* __restrict__ Rinv, float* __restrict__ eattr) {
+  pdl_wait();
   constexpr int F = SeqGeo<D>::F, NS = SeqGeo<D>::NS;
   const int E = N * (N - 1);
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -227,6 +252,7 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // CUDA-core loop has 32 reads and 256 FFMAs).  Biases, activations, sums over terms and outputs stay fp32.
 template <int BM, int BN, int TC>
 __global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : (TC == 2 ? 2 : 3)) seq_gemm_kernel(const __grid_constant__ Batch bt) {
+  pdl_wait();
   static_assert(!TC || (BM == 64 && BN == 64), "tensor-core variants: 64 x 64 tiles");
   // K slabs of 32 (16-wide slabs measured 2-5 % slower on the CUDA cores, 6 % in tensor-core mode: a barrier and a copy
   // group per slab either way), 3 stages for the 64 x 64 tiles, 4 for 32 x 32; dynamic shared memory (54-60 KB at 64 x 64)
@@ -440,6 +466,7 @@ __global__ void __launch_bounds__(GT, (BM == 64 && !TC) ? 2 : (TC == 2 ? 2 : 3))
       }
     }
   }
+  pdl_trigger();              // the dependents may be scheduled while the last tiles store
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
     const int m = m0 + row_of(i);
@@ -486,14 +513,14 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, int tc = 0) {
   if (tc == 2 && big < 296 && maxM < 1024) tc = 0;   // split mode: node-level launches stay on the small CUDA-core tile
   if (tc) {           // tensor-core modes: the 64 x 64 MMA variants
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    if (tc == 2) seq_gemm_kernel<64, 64, 2><<<grid, GT, smem_tc, st>>>(bt);
-    else seq_gemm_kernel<64, 64, 1><<<grid, GT, smem_tc, st>>>(bt);
+    if (tc == 2) (void)seq_launch(seq_gemm_kernel<64, 64, 2>, dim3(grid), dim3(GT), smem_tc, st, bt);
+    else (void)seq_launch(seq_gemm_kernel<64, 64, 1>, dim3(grid), dim3(GT), smem_tc, st, bt);
   } else if (big >= 296) {   // two resident 64x64 CTAs on every SM; below that the small tile keeps more warps in flight
     dim3 grid((maxM + 63) / 64, (maxN + 63) / 64, nprob);
-    seq_gemm_kernel<64, 64, 0><<<grid, GT, smem_64, st>>>(bt);
+    (void)seq_launch(seq_gemm_kernel<64, 64, 0>, dim3(grid), dim3(GT), smem_64, st, bt);
   } else {
     dim3 grid((maxM + 31) / 32, (maxN + 31) / 32, nprob);
-    seq_gemm_kernel<32, 32, 0><<<grid, GT, smem_32, st>>>(bt);
+    (void)seq_launch(seq_gemm_kernel<32, 32, 0>, dim3(grid), dim3(GT), smem_32, st, bt);
   }
   AE_LAUNCH_CHECK();
   return 0;
@@ -505,6 +532,7 @@ int launch_batch(const Batch& bt, int nprob, cudaStream_t st, int tc = 0) {
 // m1[t][b*E+e, :] = tanh(P[b*N+recv, (2t)H + :] + P[b*N+send, (2t+1)H + :])   (":600, :609": msg_fc1 on cat[recv, send])
 __global__ void seq_pair_tanh_kernel(const float* __restrict__ P, int ldp, int N, int64_t BE, int H, int t0, int nt,
                                      float* __restrict__ m1) {
+  pdl_wait();
   const int H4 = H / 4;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)nt * BE * H4) return;
@@ -529,6 +557,7 @@ __global__ void seq_pair_tanh_kernel(const float* __restrict__ P, int ldp, int N
 // edge2node(...) + res_x, nn/seq2seq/aether.py:378).
 __global__ void seq_mean_kernel(const float* __restrict__ msgs0, const float* __restrict__ msgs1, int N, int64_t B, int H,
                                 float* __restrict__ agg0, float* __restrict__ agg1, const float* __restrict__ add0) {
+  pdl_wait();
   const int H4 = H / 4;
   const int64_t per = B * N * H4;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -560,6 +589,7 @@ __global__ void seq_mean_kernel(const float* __restrict__ msgs0, const float* __
 // n = tanh(inp_n + r * hidden_h(agg)); hidden' = (1 - i) n + i hidden   (":644-645")
 __global__ void seq_gate_kernel(const float* __restrict__ R, const float* __restrict__ I, const float* __restrict__ NI,
                                 const float* __restrict__ HH, const float* hidden_in, float* hidden_out, int64_t n) {
+  pdl_wait();
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   const float r = R[idx], i = I[idx];
@@ -572,6 +602,7 @@ __global__ void seq_gate_kernel(const float* __restrict__ R, const float* __rest
 __global__ void seq_thin_kernel(const float* __restrict__ A, int K, const float* __restrict__ W, const float* __restrict__ b,
                                 int nc, const float* __restrict__ Rinv, int D, const float* __restrict__ add,
                                 float* __restrict__ out, int64_t rows) {
+  pdl_wait();
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -609,6 +640,7 @@ __global__ void seq_thin_kernel(const float* __restrict__ A, int K, const float*
 // Fourier features of the positions: [sin(p), cos(p)], p = (2 pi x) @ B   (nn/nn/fourier_feature_mapper.py:21-23)
 __global__ void seq_rff_kernel(const float* __restrict__ states, int sd, int D, const float* __restrict__ Bm, int half,
                                float* __restrict__ out, int64_t rows) {
+  pdl_wait();
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= rows * half) return;
   const int c = (int)(idx % half);
@@ -623,6 +655,7 @@ __global__ void seq_rff_kernel(const float* __restrict__ states, int sd, int D, 
 // out[b*E+e, :] = elu(Pn[b*N+send, 0:H] + Pn[b*N+recv, H:2H] + Pe[b*E+e, :])   (Pe carries the bias)
 __global__ void seq_enc_pair_kernel(const float* __restrict__ Pn, const float* __restrict__ Pe, int N, int64_t BE, int H,
                                     float* __restrict__ out) {
+  pdl_wait();
   const int H4 = H / 4;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= BE * H4) return;
@@ -644,6 +677,7 @@ __global__ void seq_enc_pair_kernel(const float* __restrict__ Pn, const float* _
 // LSTM cell (nn.LSTM, gate order i, f, g, o): G[rows, 4R] holds W_ih x + b_ih + W_hh h + b_hh
 __global__ void seq_lstm_cell_kernel(const float* __restrict__ G, const float* c_in, float* h_out, float* c_out, int R,
                                      int64_t rows) {
+  pdl_wait();
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= rows * R) return;
   const int64_t row = idx / R;
@@ -736,8 +770,8 @@ int seq_geometry(const AetherSeqDims* d, const float* states, const float* field
   const int64_t total = d->batch * (int64_t)(N * (N - 1) + N);
   if (total == 0) return 0;
   const int nb = (int)ceil_div64(total, 128);
-  if (d->num_dims == 2) seq_geom_kernel<2><<<nb, 128, 0, st>>>(states, field, N, d->batch, relx, Rinv, eattr);
-  else seq_geom_kernel<3><<<nb, 128, 0, st>>>(states, field, N, d->batch, relx, Rinv, eattr);
+  if (d->num_dims == 2) (void)seq_launch(seq_geom_kernel<2>, dim3(nb), dim3(128), 0, st, states, field, N, d->batch, relx, Rinv, eattr);
+  else (void)seq_launch(seq_geom_kernel<3>, dim3(nb), dim3(128), 0, st, states, field, N, d->batch, relx, Rinv, eattr);
   AE_LAUNCH_CHECK();
   return 0;
 }
@@ -752,7 +786,7 @@ int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* sta
   const int64_t BN = d->batch * d->num_vars;
   if (BN == 0) return 0;
   const int half = Hf / 2;
-  seq_rff_kernel<<<(int)ceil_div64(BN * half, 256), 256, 0, st>>>(states, 2 * D, D, p->rff_B, half, w.f0, BN);
+  (void)seq_launch(seq_rff_kernel, dim3((int)ceil_div64(BN * half, 256)), dim3(256), 0, st, states, 2 * D, D, p->rff_B, half, w.f0, BN);
   AE_LAUNCH_CHECK();
   Batch bt;
   bt.p[0].t[0] = make_term(w.f0, Hf, p->field_w[0], Hf, p->field_b[0], Hf, ACT_SILU, 1);
@@ -761,7 +795,7 @@ int seq_field(const AetherSeqDims* d, const AetherSeqParams* p, const float* sta
   bt.p[0].t[0] = make_term(w.f1, Hf, p->field_w[1], Hf, p->field_b[1], Hf, ACT_SILU, 1);
   bt.p[0].C = w.f2;
   AE_CHECK(launch_batch(bt, 1, st, tcm));
-  seq_thin_kernel<<<(int)ceil_div64(BN * 32, 256), 256, 0, st>>>(w.f2, Hf, p->field_w[2], p->field_b[2], D, nullptr, D,
+  (void)seq_launch(seq_thin_kernel, dim3((int)ceil_div64(BN * 32, 256)), dim3(256), 0, st, w.f2, Hf, p->field_w[2], p->field_b[2], D, nullptr, D,
                                                                 nullptr, field, BN);
   AE_LAUNCH_CHECK();
   return 0;
@@ -806,7 +840,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   AE_CHECK(launch_batch(bt, np, st, tcm));
   if (nt > 0 && BE > 0) {
     const int64_t total = (int64_t)nt * BE * (H / 4);
-    seq_pair_tanh_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.P, ldp, N, BE, H, t0, nt, w.m1);
+    (void)seq_launch(seq_pair_tanh_kernel, dim3((int)ceil_div64(total, 256)), dim3(256), 0, st, w.P, ldp, N, BE, H, t0, nt, w.m1);
     AE_LAUNCH_CHECK();
   }
   // batch B: second message Linears, activation, edge-type weight, sum over types
@@ -829,7 +863,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   }
   {
     const int64_t total = 2 * BN * (H / 4);
-    seq_mean_kernel<<<(int)ceil_div64(total, 256), 256, 0, st>>>(w.msgs, w.pmsgs, N, d->batch, H, w.agg, w.pagg, nullptr);
+    (void)seq_launch(seq_mean_kernel, dim3((int)ceil_div64(total, 256)), dim3(256), 0, st, w.msgs, w.pmsgs, N, d->batch, H, w.agg, w.pagg, nullptr);
     AE_LAUNCH_CHECK();
   }
   // batch C: gate pre-activations
@@ -849,7 +883,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   gate(p->input_n_w, p->input_n_b, p->present_n_w, p->present_n_b, nullptr, ACT_NONE, w.gN);
   gate(nullptr, nullptr, nullptr, nullptr, p->hidden_h_w, ACT_NONE, w.gH);
   AE_CHECK(launch_batch(bt, np, st, tcm));
-  seq_gate_kernel<<<(int)ceil_div64(BN * H, 256), 256, 0, st>>>(w.gR, w.gI, w.gN, w.gH, hidden_in, hidden_out, BN * H);
+  (void)seq_launch(seq_gate_kernel, dim3((int)ceil_div64(BN * H, 256)), dim3(256), 0, st, w.gR, w.gI, w.gN, w.gH, hidden_in, hidden_out, BN * H);
   AE_LAUNCH_CHECK();
   // out MLP
   np = 0;
@@ -858,7 +892,7 @@ int seq_step(const AetherSeqDims* d, const AetherSeqParams* p, const float* stat
   np = 0;
   single(make_term(w.o1, H, p->out_w[1], H, p->out_b[1], H, ACT_RELU, 1), w.o2, H, (int)BN, H);
   AE_CHECK(launch_batch(bt, np, st, tcm));
-  seq_thin_kernel<<<(int)ceil_div64(BN * 32, 256), 256, 0, st>>>(w.o2, H, p->out_w[2], p->out_b[2], 2 * D, w.Rinv, D,
+  (void)seq_launch(seq_thin_kernel, dim3((int)ceil_div64(BN * 32, 256)), dim3(256), 0, st, w.o2, H, p->out_w[2], p->out_b[2], 2 * D, w.Rinv, D,
                                                                 states, states_out, BN);
   AE_LAUNCH_CHECK();
   return 0;
@@ -915,7 +949,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
     add(t, w.efilt, H, BE, H);
   }
   AE_CHECK(launch_batch(bt, np, st, tcm));
-  seq_mean_kernel<<<(int)ceil_div64(BN * (H / 4), 256), 256, 0, st>>>(w.efilt, nullptr, N, d->batch, H, w.exin, nullptr,
+  (void)seq_launch(seq_mean_kernel, dim3((int)ceil_div64(BN * (H / 4), 256)), dim3(256), 0, st, w.efilt, nullptr, N, d->batch, H, w.exin, nullptr,
                                                                      w.eres);
   AE_LAUNCH_CHECK();
   np = 0;
@@ -933,7 +967,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
   add(make_term(w.efilt, H, p->mlp4_w[0] + 2 * H, 3 * H, p->mlp4_b[0], H, ACT_NONE, 1), w.ePe, H, BE, H);
   AE_CHECK(launch_batch(bt, np, st, tcm));
   if (BE > 0) {
-    seq_enc_pair_kernel<<<(int)ceil_div64(BE * (H / 4), 256), 256, 0, st>>>(w.ePn, w.ePe, N, BE, H, w.eh1);
+    (void)seq_launch(seq_enc_pair_kernel, dim3((int)ceil_div64(BE * (H / 4), 256)), dim3(256), 0, st, w.ePn, w.ePe, N, BE, H, w.eh1);
     AE_LAUNCH_CHECK();
   }
   np = 0;
@@ -951,7 +985,7 @@ int seq_encoder(const AetherSeqDims* d, const AetherSeqEncParams* p, const float
   }
   AE_CHECK(launch_batch(bt, np, st, tcm));
   if (BE > 0) {
-    seq_lstm_cell_kernel<<<(int)ceil_div64(BE * R, 256), 256, 0, st>>>(w.eG, c_in, h_out, c_out, R, BE);
+    (void)seq_launch(seq_lstm_cell_kernel, dim3((int)ceil_div64(BE * R, 256)), dim3(256), 0, st, w.eG, c_in, h_out, c_out, R, BE);
     AE_LAUNCH_CHECK();
   }
   const float* cur = h_out;
