@@ -34,5 +34,21 @@ int main(int argc, char** argv) {
          (long long)d.n_edges);
   printf("workspace inference %zu  training fp32 %zu  training bf16 %zu  backward scratch %zu  graph scratch %zu\n", infer,
          train, train16, scratch, graph);
+  /* the seq2seq decoder path at the shape of scripts/electrostatic_field_aether.sh: 5 particles, batch 64, decoder and
+   * encoder hidden 512, LSTM 128, prior head 256, 2 edge types */
+  {
+    AetherSeqDims s;
+    s.num_dims = d.num_dims == 3 ? 3 : 2;
+    s.num_vars = 5;
+    s.hidden = 512;
+    s.n_types = 2;
+    s.skip_first = 0;
+    s.field_hidden = 512;
+    s.rnn_hidden = 128;
+    s.prior_hidden = 256;
+    s.flags = 0;
+    s.batch = 64;
+    printf("seq2seq decoder + encoder workspace %zu\n", aether_seq_workspace_bytes(&s));
+  }
   return 0;
 }

@@ -152,4 +152,6 @@ def test_header_is_plain_c_and_c_caller_links(lib, tmp_path):
     from aether_b200 import _lib
     d = _lib.AetherDims(2, 256, 102400, 10137600)
     assert ("training fp32 %d " % lib.aether_workspace_bytes(ctypes.byref(d), _lib.F_SAVE)) in r.stdout
+    sd = _lib.AetherSeqDims(2, 5, 512, 2, 0, 512, 128, 256, 0, 64)
+    assert ("seq2seq decoder + encoder workspace %d" % lib.aether_seq_workspace_bytes(ctypes.byref(sd))) in r.stdout
     assert subprocess.run([exe, "4", "64", "1", "1"], capture_output=True).returncode == 1      # D = 4 is rejected
