@@ -450,6 +450,11 @@ class Seq2SeqAether(nn.Module):
                                                             _lib.ptr(ws), ws.numel(), _stream()), "aether_seq_predict_field")
         return field.reshape(*x.shape[:-1], self.num_dims), coords
 
+    def calculate_loss(self, *args, **kwargs):
+        """nn/seq2seq/aether.py:102-153 (training: teacher forcing, NLL + KL) is not built: the kernels are inference-only."""
+        raise RuntimeError("aether_b200.seq2seq.Seq2SeqAether.calculate_loss: seq2seq training is not built (inference only: "
+                           "predict_future / single_step_forward); train with the reference and load its state_dict here")
+
     def single_step_forward(self, inputs, decoder_hidden, edge_logits, hard_sample, predicted_field):
         """nn/seq2seq/aether.py:89-100."""
         old_shape = edge_logits.shape

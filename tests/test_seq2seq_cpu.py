@@ -79,3 +79,11 @@ def test_pickle_drops_workspace():
     m2 = torch.load(buf, weights_only=False)
     assert m2.decoder._ws is None and m2.encoder._ws is None
     assert all(torch.equal(a, b) for a, b in zip(m.state_dict().values(), m2.state_dict().values()))
+
+
+def test_training_entry_point_says_what_is_missing():
+    from aether_b200.seq2seq import Seq2SeqAether
+    m = Seq2SeqAether({"num_vars": 3, "input_size": 4, "use_3d": False, "decoder_hidden": 8, "num_edge_types": 2,
+                       "skip_first": False, "decoder_dropout": 0.0, "encoder_hidden": 8, "gumbel_temp": 0.5})
+    with pytest.raises(RuntimeError, match="training is not built"):
+        m.calculate_loss(torch.zeros(1, 3, 3, 4))
