@@ -113,6 +113,7 @@ SIGNATURES = {
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "aether_seq_encoder_step": (c_int, [POINTER(AetherSeqDims), POINTER(AetherSeqEncParams), c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "aether_seq_sample_hard": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p]),
     "aether_seq_localizer": (c_int, [POINTER(AetherSeqDims), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "aether_adamw_step": (c_int, [c_int32, POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p), POINTER(c_void_p),
                                   POINTER(c_int64), c_void_p, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double,

@@ -690,6 +690,23 @@ __global__ void seq_lstm_cell_kernel(const float* __restrict__ G, const float* c
   h_out[idx] = go * tanhf(c);
 }
 
+// Hard gumbel-softmax sample (nn/utils/model_utils.py:57-121 with hard=True): one-hot of argmax_k(logit_k + g_k),
+// g = -log(eps - log(U + eps)), first maximum on ties like torch's max; the temperature does not change an arg-max.
+__global__ void seq_sample_hard_kernel(const float* __restrict__ logits, const float* __restrict__ U, float* __restrict__ out,
+                                       int K, int64_t rows) {
+  pdl_wait();
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  int best = 0;
+  float bv = 0.f;
+  for (int k = 0; k < K; ++k) {
+    const float g = -logf(1e-10f - logf(U[r * K + k] + 1e-10f));
+    const float v = logits[r * K + k] + g;
+    if (k == 0 || v > bv) { bv = v; best = k; }
+  }
+  for (int k = 0; k < K; ++k) out[r * K + k] = k == best ? 1.0f : 0.0f;
+}
+
 // ------------------------------------------------------------------------------------------------
 // workspace
 // ------------------------------------------------------------------------------------------------
@@ -1069,4 +1086,14 @@ extern "C" int aether_seq_encoder_step(const AetherSeqDims* dims, const AetherSe
   if (!params || !states || !field || !h_in || !c_in || !logits || !h_out || !c_out) return AETHER_E_BADARG;
   if (dims->rnn_hidden < 1) return AETHER_E_BADARG;
   return seq_encoder(dims, params, states, field, h_in, c_in, logits, h_out, c_out, w, (cudaStream_t)stream);
+}
+
+extern "C" int aether_seq_sample_hard(const float* logits, const float* uniform, float* onehot, int64_t rows, int32_t n_types,
+                                      void* stream) {
+  if (!logits || !uniform || !onehot || rows < 0 || n_types < 1) return AETHER_E_BADARG;
+  if (rows == 0) return 0;
+  (void)seq_launch(seq_sample_hard_kernel, dim3((unsigned)ceil_div64(rows, 256)), dim3(256), 0, (cudaStream_t)stream, logits,
+                   uniform, onehot, (int)n_types, rows);
+  AE_LAUNCH_CHECK();
+  return 0;
 }

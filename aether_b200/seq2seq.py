@@ -383,11 +383,24 @@ class Encoder(_NoWorkspacePickle, nn.Module):
 def gumbel_softmax(logits, tau=1.0, hard=False, eps=1e-10, generator=None):
     """nn/utils/model_utils.py:57-121 (noise drawn on the logits' device)."""
     U = torch.rand(logits.shape, device=logits.device, generator=generator)
+    if hard and logits.is_cuda and logits.dtype == torch.float32 and eps == 1e-10:
+        return sample_hard(logits, U)
     y_soft = torch.softmax((logits - torch.log(eps - torch.log(U + eps))) / tau, dim=-1)
     if not hard:
         return y_soft
     k = y_soft.argmax(-1, keepdim=True)
     return torch.zeros_like(y_soft).scatter_(-1, k, 1.0)
+
+
+def sample_hard(logits, U, out=None):
+    """One-hot arg-max of logits + gumbel(U) in one launch (aether_seq_sample_hard)."""
+    lg, U = logits.detach().contiguous(), U.contiguous()
+    out = torch.empty_like(lg) if out is None else out
+    K = lg.shape[-1]
+    with torch.cuda.device(lg.device):
+        _lib.check(_lib.load().aether_seq_sample_hard(_lib.ptr(lg), _lib.ptr(U), _lib.ptr(out), lg.numel() // K, K, _stream()),
+                   "aether_seq_sample_hard")
+    return out
 
 
 class Seq2SeqAether(nn.Module):
@@ -548,9 +561,7 @@ class DecoderRollout:
                                                    _lib.ptr(self.enc_h), _lib.ptr(self.enc_c), _lib.ptr(self.logits),
                                                    _lib.ptr(self.enc_h), _lib.ptr(self.enc_c), _lib.ptr(self.ws_enc),
                                                    self.ws_enc.numel(), _stream()), "aether_seq_encoder_step")
-            U = torch.rand(self.logits.shape, device=self.dev)
-            k = (self.logits - torch.log(1e-10 - torch.log(U + 1e-10))).argmax(-1, keepdim=True)
-            self.edges[t].zero_().scatter_(-1, k, 1.0)
+            sample_hard(self.logits, torch.rand(self.logits.shape, device=self.dev), out=self.edges[t])
             _lib.check(lib.aether_seq_decoder_step(ctypes.byref(self.dims), ctypes.byref(p), _lib.ptr(x), _lib.ptr(self.hidden),
                                                    _lib.ptr(self.edges[t]), _lib.ptr(self.field), _lib.ptr(self.traj[t]),
                                                    _lib.ptr(self.hidden), _lib.ptr(self.ws), self.ws.numel(), _stream()),

@@ -371,6 +371,11 @@ typedef struct AetherSeqEncParams {
 int aether_seq_encoder_step(const AetherSeqDims* dims, const AetherSeqEncParams* params, const float* states,
                             const float* field, const float* h_in, const float* c_in, float* logits, float* h_out,
                             float* c_out, void* workspace, size_t workspace_bytes, void* stream);
+/* Hard gumbel-softmax sample of the edge types (nn/utils/model_utils.py:57-121 with hard=True, as predict_future samples,
+ * nn/seq2seq/aether.py:91-95): onehot[r, :] = one-hot of argmax_k(logits[r, k] - log(1e-10 - log(uniform[r, k] + 1e-10))),
+ * first maximum on ties.  uniform: U(0,1) noise from the caller's generator, [rows, n_types] like logits. */
+int aether_seq_sample_hard(const float* logits, const float* uniform, float* onehot, int64_t rows, int32_t n_types,
+                           void* stream);
 /* Test hook: the three AugmentedLocalizer outputs the step consumes, rel_feat[B,N,3D+F], Rinv[B,N,D,D],
  * edge_attr[B,N(N-1),2F+3D]. */
 int aether_seq_localizer(const AetherSeqDims* dims, const float* states, const float* field, float* rel_feat, float* Rinv,

@@ -350,3 +350,19 @@ def test_fp32x3_mode_at_experiment_shape_against_oracle():
     traj = DecoderRollout(m, B, T, cuda_graph=True).run(x.cuda(), onehot.cuda())
     ref = so.predict_future(w, x.unsqueeze(1), onehot.transpose(0, 1), T, D, K, False, return_everything=False)
     assert rel_err(traj.transpose(0, 1).cpu(), ref) <= 1e-4
+
+
+def test_hard_sample_kernel_matches_torch():
+    from aether_b200.seq2seq import sample_hard
+    torch.manual_seed(9)
+    for K in (1, 2, 3, 4):
+        lg = torch.randn(1000, K, device="cuda")
+        U = torch.rand(1000, K, device="cuda")
+        got = sample_hard(lg, U)
+        y = lg - torch.log(1e-10 - torch.log(U + 1e-10))
+        want = torch.zeros_like(lg).scatter_(-1, y.argmax(-1, keepdim=True), 1.0)
+        top2 = y.topk(min(2, K), dim=-1).values
+        clear = torch.ones(1000, dtype=torch.bool, device="cuda") if K == 1 else (top2[:, 0] - top2[:, 1]) > 1e-5
+        assert bool((got.sum(-1) == 1).all()) and torch.equal(got[clear], want[clear])
+    tie = torch.zeros(4, 3, device="cuda")
+    assert torch.equal(sample_hard(tie, torch.full((4, 3), 0.5, device="cuda")).argmax(-1).cpu(), torch.zeros(4, dtype=torch.long))
